@@ -1,0 +1,156 @@
+"""Deterministic parity cases shared by the golden generator (run once, in the build container, against the
+real reference) and by the tests (run anywhere, without the reference).
+
+Nothing here imports the reference or the product; it only defines shapes, seeds and how synthetic parameters and
+inputs are drawn, so that `make_golden.py` and the tests see bit-identical tensors.
+"""
+import hashlib
+import math
+from dataclasses import dataclass, field
+from typing import Dict, Tuple
+
+import torch
+
+TXT_LEN = 58  # pos_emb.pt is [58, 5120]
+
+
+@dataclass
+class BlockCase:
+    name: str
+    model: str                      # "3b" | "7b"
+    dim: int
+    heads: int
+    grid: Tuple[int, int, int]      # token grid T, H, W (after 2x2 patching)
+    shifted: bool
+    shared: bool = False            # 3B only
+    is_last: bool = False           # 3B only
+    txt_len: int = TXT_LEN
+    seed: int = 0
+    head_dim: int = 128
+    window: Tuple[int, int, int] = (4, 3, 3)
+    # |out| stays below 2 at these scales, so one bf16 ulp (<= 0.0078) is well under the 2e-2 north-star tolerance and
+    # the tolerance is meaningful; at unit scale the reference's OWN bf16-vs-fp32 gap is 0.06-0.2 (make_golden.py log).
+    in_scale: float = 0.25
+    emb_scale: float = 0.25
+
+    @property
+    def mlp_hidden(self) -> int:
+        if self.model == "3b":      # SwiGLU hidden, reference mlp.py:53-54
+            h = int(2 * self.dim * 4 / 3)
+            return 256 * ((h + 255) // 256)
+        return self.dim * 4
+
+
+BLOCK_CASES = [
+    BlockCase("3b_sep_win", "3b", 128, 2, (2, 20, 36), shifted=False, shared=False, seed=11),
+    BlockCase("3b_shared_swin", "3b", 128, 2, (2, 20, 36), shifted=True, shared=True, seed=12),
+    BlockCase("3b_last_swin", "3b", 128, 2, (1, 32, 32), shifted=True, shared=True, is_last=True, seed=13),
+    BlockCase("7b_win", "7b", 128, 3, (3, 20, 36), shifted=False, seed=14),
+    BlockCase("7b_swin", "7b", 128, 3, (5, 17, 30), shifted=True, seed=15),
+]
+
+
+def rope_freqs(model: str, head_dim: int = 128) -> torch.Tensor:
+    """The persistent buffer ``attn.rope.rope.freqs`` as the reference constructors create it.
+    3B: RotaryEmbedding(dim=128//3, freqs_for='lang', theta=10000)  (dit_3b/rope.py:77-81, rope_dim=128 in the YAML)
+    7B: RotaryEmbedding(dim=(128//2)//3, freqs_for='pixel', max_freq=256) (dit_7b/rope.py:28-32, mmsr_block.py:64)"""
+    if model == "3b":
+        dim = head_dim // 3
+        return 1.0 / (10000 ** (torch.arange(0, dim, 2)[: dim // 2].float() / dim))
+    dim = (head_dim // 2) // 3
+    return torch.linspace(1.0, 256 / 2, dim // 2) * math.pi
+
+
+def block_param_shapes(c: BlockCase) -> Dict[str, Tuple[int, ...]]:
+    """State-dict contract of one block; `make_golden.py` asserts it against the reference block."""
+    D, I, Hd = c.dim, c.heads * c.head_dim, c.mlp_hidden
+    out: Dict[str, Tuple[int, ...]] = {}
+    if c.model == "3b":
+        br = ["all"] if c.shared else ["vid", "txt"]
+        br_tail = ["all"] if c.shared else (["vid"] if c.is_last else ["vid", "txt"])
+        for b in br:
+            out[f"attn.proj_qkv.{b}.weight"] = (3 * I, D)
+            out[f"attn.proj_out.{b}.weight"] = (D, I)
+            out[f"attn.proj_out.{b}.bias"] = (D,)
+            out[f"attn.norm_q.{b}.weight"] = (c.head_dim,)
+            out[f"attn.norm_k.{b}.weight"] = (c.head_dim,)
+        for b in br_tail:
+            out[f"mlp.{b}.proj_in_gate.weight"] = (Hd, D)
+            out[f"mlp.{b}.proj_in.weight"] = (Hd, D)
+            out[f"mlp.{b}.proj_out.weight"] = (D, Hd)
+            for l in ("attn", "mlp"):
+                for g in ("shift", "scale", "gate"):
+                    out[f"ada.{b}.{l}_{g}"] = (D,)
+        out["attn.rope.rope.freqs"] = (c.head_dim // 3 // 2,)
+    else:
+        for b in ("vid", "txt"):
+            out[f"attn.proj_qkv.{b}.weight"] = (3 * I, D)
+            out[f"attn.proj_out.{b}.weight"] = (D, I)
+            out[f"attn.proj_out.{b}.bias"] = (D,)
+            out[f"attn.norm_q.{b}.weight"] = (c.head_dim,)
+            out[f"attn.norm_k.{b}.weight"] = (c.head_dim,)
+            out[f"mlp.{b}.proj_in.weight"] = (Hd, D)
+            out[f"mlp.{b}.proj_in.bias"] = (Hd,)
+            out[f"mlp.{b}.proj_out.weight"] = (D, Hd)
+            out[f"mlp.{b}.proj_out.bias"] = (D,)
+            for l in ("attn", "mlp"):
+                for g in ("shift", "scale", "gate"):
+                    out[f"ada.{b}.{l}_{g}"] = (D,)
+        out["attn.rope.rope.freqs"] = ((c.head_dim // 2) // 3 // 2,)
+    return out
+
+
+def _gen(seed: int, key: str) -> torch.Generator:
+    h = int.from_bytes(hashlib.sha256(f"{seed}:{key}".encode()).digest()[:4], "little")
+    return torch.Generator().manual_seed(h)
+
+
+def draw_param(key: str, shape: Tuple[int, ...], seed: int, model: str) -> torch.Tensor:
+    """bf16-representable fp32 values, reference-like magnitudes (Linear ~1/sqrt(in), AdaSingle modulation.py:58-63)."""
+    if key.endswith("rope.freqs"):
+        return rope_freqs(model)          # checkpoint data, kept fp32
+    g = _gen(seed, key)
+    r = torch.randn(*shape, generator=g)
+    if ".norm_q." in key or ".norm_k." in key or key.endswith("_norm.weight"):
+        v = 1.0 + 0.1 * r
+    elif key.endswith("_scale"):
+        v = 1.0 + r / math.sqrt(shape[0])
+    elif key.endswith(("_shift", "_gate")):
+        v = r / math.sqrt(shape[0])
+    elif key.endswith(".bias"):
+        v = 0.02 * r
+    else:
+        v = r / math.sqrt(shape[-1])
+    return v.bfloat16().float()
+
+
+def block_params(c: BlockCase) -> Dict[str, torch.Tensor]:
+    return {k: draw_param(k, s, c.seed, c.model) for k, s in block_param_shapes(c).items()}
+
+
+def block_inputs(c: BlockCase):
+    """vid [L, D], txt [Lt, D], emb [1, 6D] — scaled normal, bf16-representable."""
+    T, H, W = c.grid
+    vid = (c.in_scale * torch.randn(T * H * W, c.dim, generator=_gen(c.seed, "in.vid"))).bfloat16().float()
+    txt = (c.in_scale * torch.randn(c.txt_len, c.dim, generator=_gen(c.seed, "in.txt"))).bfloat16().float()
+    emb = (c.emb_scale * torch.randn(1, 6 * c.dim, generator=_gen(c.seed, "in.emb"))).bfloat16().float()
+    return vid, txt, emb
+
+
+def tensor_digest(t: torch.Tensor) -> str:
+    return hashlib.sha256(t.detach().contiguous().cpu().numpy().tobytes()).hexdigest()[:16]
+
+
+# ---- geometry cases: (T, H, W) token grids; the five BASELINE configs + edge cases ------------------------------
+GEOMETRY_GRIDS = [
+    (1, 32, 32),      # C0 512^2 image
+    (1, 128, 128),    # C1 2048^2 image
+    (9, 90, 160),     # C2 33 f 1440p
+    (31, 68, 120),    # C3 121 f 1080p
+    (6, 68, 120),     # C3 per rank @ 8 GPUs
+    (5, 68, 120),     # C3 last rank
+    (10, 135, 240),   # C4 4K chunk
+    (1, 1, 1), (1, 2, 3), (2, 3, 5), (4, 45, 80), (3, 46, 81), (7, 17, 29), (2, 20, 36), (5, 17, 30),
+    (33, 9, 7), (1, 200, 3), (1, 3, 200), (30, 15, 27), (31, 15, 27), (8, 64, 64), (1, 67, 119),
+]
+GEOMETRY_FULL_LIMIT = 4096   # grids with <= this many tokens store full index arrays, larger ones store sha256
