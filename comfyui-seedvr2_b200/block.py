@@ -1,0 +1,302 @@
+"""B200-native drop-ins for the reference's ``NaMMSRTransformerBlock`` (3B and 7B).
+
+Boundary: the reference instantiates ``get_nablock("mmdit_sr")(**kwargs)`` per layer
+(src/models/dit_3b/nadit.py:135-165, dit_7b/nadit.py:109-136) and calls
+``block(vid=, txt=, vid_shape=, txt_shape=, emb=, cache=)`` (dit_3b/nadit.py:221-231).  The classes below keep
+* the constructor keyword arguments of src/models/dit_3b/nablocks/mmsr_block.py:31-52 and
+  src/models/dit_7b/nablocks/mmsr_block.py:161-180,
+* every parameter / buffer NAME and shape of the reference block (``attn.proj_qkv.vid.weight`` ... incl. the persistent
+  ``attn.rope.rope.freqs`` buffer), so checkpoints load with ``load_state_dict(..., assign=True)`` unchanged,
+* the forward signature and return tuple of mmsr_block.py:84-128.
+
+What differs is how the work is done: GEMMs stay torch/cuBLAS calls; everything else is the C-ABI CUDA path
+(ops.py) — 6 launches per block instead of ~60 ATen kernels plus one SDPA call per window.
+"""
+import math
+from typing import Callable, Optional, Tuple
+
+import torch
+import torch.nn.functional as F
+from torch import nn
+
+from . import ops
+from .plan import WindowPlan, get_plan
+
+_SHIFTED = {"720pwin_by_size_bysize": False, "720pswin_by_size_bysize": True}
+
+
+def _factory_kind(f) -> Optional[str]:
+    """The reference passes ``norm`` / ``qk_norm`` as closures of get_norm_layer(norm_type) (normalization.py:112-149)
+    and ``ada`` as the AdaSingle class (modulation.py:29-32); recover the kind to reject what is not implemented."""
+    if f is None or isinstance(f, str):
+        return f
+    cl = getattr(f, "__closure__", None)
+    if cl:
+        for c in cl:
+            if isinstance(c.cell_contents, (str, type(None))):
+                return c.cell_contents
+    return getattr(f, "__name__", None)
+
+
+class _Slot(nn.Module):
+    """Parameter holder standing in for the reference's MMModule (src/models/dit_3b/mm.py:35-74): children are named
+    ``vid`` / ``txt`` (separate weights) or ``all`` (shared) so state-dict keys match."""
+
+    def __init__(self, make: Callable[[], nn.Module], shared: bool, vid_only: bool = False):
+        super().__init__()
+        self.shared_weights, self.vid_only = shared, vid_only
+        if shared:
+            self.all = make()
+        else:
+            self.vid = make()
+            self.txt = None if vid_only else make()
+
+    def pick(self, branch: str) -> nn.Module:
+        return self.all if self.shared_weights else getattr(self, branch)
+
+
+class _Weight(nn.Module):
+    def __init__(self, dim: int):
+        super().__init__()
+        self.weight = nn.Parameter(torch.ones(dim))
+
+
+class _AdaParams(nn.Module):
+    """AdaSingle parameters, layers=["attn","mlp"] (modulation.py:43-63)."""
+
+    def __init__(self, dim: int):
+        super().__init__()
+        for layer in ("attn", "mlp"):
+            setattr(self, f"{layer}_shift", nn.Parameter(torch.randn(dim) / dim ** 0.5))
+            setattr(self, f"{layer}_scale", nn.Parameter(torch.randn(dim) / dim ** 0.5 + 1))
+            setattr(self, f"{layer}_gate", nn.Parameter(torch.randn(dim) / dim ** 0.5))
+
+
+class _Freqs(nn.Module):
+    def __init__(self, freqs: torch.Tensor):
+        super().__init__()
+        self.register_buffer("freqs", freqs)     # persistent: it IS in the checkpoints
+
+
+class _Rope(nn.Module):
+    """Holds ``rope.freqs`` under the reference's name.  No ``get_axial_freqs`` attribute on purpose: the product's
+    RoPE "stabilisation" / BlockSwap wrappers are hasattr-guarded (compatibility.py:388-408, blockswap.py:556-631)."""
+
+    def __init__(self, kind: int, head_dim: int):
+        super().__init__()
+        if kind == ops.ROPE_3B_MM:   # RotaryEmbedding(dim=rope_dim//3, freqs_for="lang", theta=10000)  dit_3b/rope.py:77-81
+            dim = head_dim // 3
+            freqs = 1.0 / (10000 ** (torch.arange(0, dim, 2)[: dim // 2].float() / dim))
+        else:                        # RotaryEmbedding(dim=(head_dim//2)//3, freqs_for="pixel", max_freq=256)  dit_7b/rope.py:28-32
+            dim = (head_dim // 2) // 3
+            freqs = torch.linspace(1.0, 256 / 2, dim // 2) * math.pi
+        self.kind = kind
+        self.mm = kind == ops.ROPE_3B_MM
+        self.rope = _Freqs(freqs)
+
+
+class _SwiGLU(nn.Module):      # reference mlp.py:46-62
+    def __init__(self, dim: int, expand_ratio: int, multiple_of: int = 256):
+        super().__init__()
+        hidden = int(2 * dim * expand_ratio / 3)
+        hidden = multiple_of * ((hidden + multiple_of - 1) // multiple_of)
+        self.proj_in_gate = nn.Linear(dim, hidden, bias=False)
+        self.proj_out = nn.Linear(hidden, dim, bias=False)
+        self.proj_in = nn.Linear(dim, hidden, bias=False)
+
+    def forward(self, x):
+        return self.proj_out(F.silu(self.proj_in_gate(x)) * self.proj_in(x))
+
+
+class _GeluMLP(nn.Module):     # reference mlp.py:28-43
+    def __init__(self, dim: int, expand_ratio: int):
+        super().__init__()
+        self.proj_in = nn.Linear(dim, dim * expand_ratio)
+        self.proj_out = nn.Linear(dim * expand_ratio, dim)
+
+    def forward(self, x):
+        return self.proj_out(F.gelu(self.proj_in(x), approximate="tanh"))
+
+
+def _bf16(t: torch.Tensor) -> torch.Tensor:
+    """Parameters are used as bf16.  Checkpoints loaded with assign=True may be fp16/fp32: cast on use."""
+    return t if t.dtype == torch.bfloat16 else t.to(torch.bfloat16)
+
+
+class _GridMemo:
+    """vid_shape lives on the GPU (na.py:97); reading it is a D2H sync the reference pays several times per layer.
+    The same tensor OBJECT flows through all blocks of a forward, so one sync per forward is enough — also for 7B,
+    whose forward disables the reference Cache (quirk Q2)."""
+    tensor = None
+    version = -1
+    value = None
+
+    @classmethod
+    def read(cls, vid_shape: torch.Tensor, txt_shape: torch.Tensor):
+        if cls.tensor is vid_shape and cls.version == vid_shape._version:
+            return cls.value
+        vs = vid_shape.tolist()
+        ts = txt_shape.tolist()
+        if len(vs) != 1 or len(ts) != 1:
+            # the pipeline always runs b=1 (generation_phases.py:678,701); b>1 hits reference quirk Q7
+            raise NotImplementedError("seedvr2_b200 blocks support batch size 1 only")
+        cls.tensor, cls.version = vid_shape, vid_shape._version
+        cls.value = (tuple(int(v) for v in vs[0]), int(math.prod(ts[0])))
+        return cls.value
+
+
+class NaSwinAttentionB200(nn.Module):
+    """Window attention of one block.  Reference: src/models/dit_3b/nablocks/attention/mmattn.py:145-271 and
+    src/models/dit_7b/nablocks/mmsr_block.py:34-157."""
+
+    def __init__(self, *, vid_dim: int, txt_dim: int, heads: int, head_dim: int, qk_bias: bool, qk_norm_eps: float,
+                 rope_kind: int, shared_weights: bool, shared_qknorm: bool, window, window_method: str):
+        super().__init__()
+        if head_dim != 128:
+            raise NotImplementedError("seedvr2_b200: head_dim must be 128")
+        if vid_dim != txt_dim:
+            raise NotImplementedError("seedvr2_b200: vid_dim != txt_dim is not supported")
+        if qk_bias:
+            raise NotImplementedError("seedvr2_b200: qk_bias=True is not used by the 3B/7B configs")
+        if window_method not in _SHIFTED:
+            raise NotImplementedError(f"seedvr2_b200: window_method {window_method!r} is not supported")
+        inner = heads * head_dim
+        self.heads, self.head_dim, self.eps = heads, head_dim, float(qk_norm_eps)
+        self.window = tuple(int(v) for v in (window if isinstance(window, (tuple, list)) else (window,) * 3))
+        self.window_method = window_method
+        self.shifted = _SHIFTED[window_method]
+        self.proj_qkv = _Slot(lambda: nn.Linear(vid_dim, inner * 3, bias=False), shared_weights)
+        self.proj_out = _Slot(lambda: nn.Linear(inner, vid_dim), shared_weights)
+        self.norm_q = _Slot(lambda: _Weight(head_dim), shared_qknorm)
+        self.norm_k = _Slot(lambda: _Weight(head_dim), shared_qknorm)
+        self.rope = _Rope(rope_kind, head_dim) if rope_kind != ops.ROPE_NONE else None
+
+    def core(self, vid: torch.Tensor, txt: torch.Tensor, plan: WindowPlan):
+        """proj_qkv -> pack (norm+rope+partition) -> window attention; returns attention outputs BEFORE proj_out."""
+        vqkv = F.linear(vid, _bf16(self.proj_qkv.pick("vid").weight))
+        tqkv = F.linear(txt, _bf16(self.proj_qkv.pick("txt").weight))
+        if self.rope is not None:
+            freqs = self.rope.rope.freqs
+            if freqs.dtype != torch.float32:
+                freqs = freqs.float()
+            kind = self.rope.kind
+        else:
+            freqs, kind = None, ops.ROPE_NONE
+        q, k, v = ops.qkv_pack(plan, vqkv, tqkv, _bf16(self.norm_q.pick("vid").weight), _bf16(self.norm_k.pick("vid").weight),
+                               _bf16(self.norm_q.pick("txt").weight), _bf16(self.norm_k.pick("txt").weight), freqs, kind,
+                               self.heads, self.eps)
+        return ops.window_attn(plan, q, k, v, self.heads)
+
+    def forward(self, vid, txt, vid_shape, txt_shape, cache=None):
+        grid, txt_len = _GridMemo.read(vid_shape, txt_shape)
+        plan = get_plan(grid, self.window, self.shifted, txt_len)
+        ov, ot = self.core(vid, txt, plan)
+        po_v, po_t = self.proj_out.pick("vid"), self.proj_out.pick("txt")
+        return (F.linear(ov, _bf16(po_v.weight), _bf16(po_v.bias)), F.linear(ot, _bf16(po_t.weight), _bf16(po_t.bias)))
+
+
+class _BlockBase(nn.Module):
+    """Shared forward: norm->mod->attn->gate->+res ; norm->mod->mlp->gate->+res (mmsr_block.py:98-128)."""
+
+    txt_tail_skipped = False      # 3B last layer: ada / mlp_norm / mlp are vid_only
+
+    def _ada(self, branch: str) -> Optional[_AdaParams]:
+        return self.ada.pick(branch)
+
+    def forward(self, vid, txt, vid_shape, txt_shape, emb, cache=None):
+        if vid.dtype != torch.bfloat16:
+            raise NotImplementedError(f"seedvr2_b200 blocks compute in bf16 (got {vid.dtype}); there is no other path")
+        grid, txt_len = _GridMemo.read(vid_shape, txt_shape)
+        if cache is not None:
+            # Honour the reference Cache (src/common/cache.py): same keys the reference blocks fill.  Quirk Q1:
+            # dit_3b/nadit.py:236-244 later asks for "emb_repeat_0_vid" and must find the ATTN-layer triple [L, D, 3].
+            cache("vid_len", lambda: vid_shape.prod(-1))
+            cache("txt_len", lambda: txt_shape.prod(-1))
+            cache("emb_repeat_0_vid", lambda: emb.reshape(emb.shape[0], -1, 2, 3)[:, :, 0, :].expand(vid.shape[0], -1, -1))
+        plan = get_plan(grid, self.attn.window, self.attn.shifted, txt_len)
+        if plan.n_tokens != vid.shape[0] or txt_len != txt.shape[0]:
+            raise RuntimeError(f"vid/txt rows {vid.shape[0]}/{txt.shape[0]} do not match vid_shape {grid} / txt_shape {txt_len}")
+        e = _bf16(emb).reshape(-1).contiguous()
+        vid, txt = vid.contiguous(), txt.contiguous()
+        eps = self.norm_eps
+        av, at = self._ada("vid"), (None if self.txt_tail_skipped else self._ada("txt"))
+
+        # --- attention half
+        a_v = ops.modnorm(vid, e, _bf16(av.attn_shift), _bf16(av.attn_scale), 0, eps)
+        a_t = (ops.modnorm(txt, e, _bf16(at.attn_shift), _bf16(at.attn_scale), 0, eps) if at is not None
+               else ops.modnorm(txt, None, None, None, 0, eps))
+        o_v, o_t = self.attn(a_v, a_t, vid_shape, txt_shape, cache)
+        # --- gate + residual, fused with the MLP half's norm + modulation
+        vid1, m_v = ops.gate_residual_modnorm(o_v, vid, e, _bf16(av.attn_gate), _bf16(av.mlp_shift), _bf16(av.mlp_scale), eps)
+        m_v = self.mlp.pick("vid")(m_v)
+        vid2 = ops.gate_residual(m_v, vid1, e, _bf16(av.mlp_gate), 1)
+        if at is not None:
+            txt1, m_t = ops.gate_residual_modnorm(o_t, txt, e, _bf16(at.attn_gate), _bf16(at.mlp_shift), _bf16(at.mlp_scale), eps)
+            m_t = self.mlp.pick("txt")(m_t)
+            txt2 = ops.gate_residual(m_t, txt1, e, _bf16(at.mlp_gate), 1)
+        else:
+            # vid_only MMModules pass txt through untouched (mm.py:69-73): txt1 = attn(txt) + txt ; txt2 = txt1 + txt1
+            txt1 = ops.gate_residual(o_t, txt, None, None, 0)
+            txt2 = ops.gate_residual(txt1, txt1, None, None, 1)
+        return vid2, txt2, vid_shape, txt_shape
+
+
+class NaMMSRTransformerBlockB200(_BlockBase):
+    """SeedVR2-3B block.  Constructor kwargs of src/models/dit_3b/nablocks/mmsr_block.py:31-52."""
+
+    def __init__(self, *, vid_dim: int, txt_dim: int, emb_dim: int, heads: int, head_dim: int, expand_ratio: int,
+                 norm=None, norm_eps: float = 1e-5, ada=None, qk_bias: bool = False, qk_norm=None,
+                 mlp_type: str = "swiglu", shared_weights: bool = False, rope_type: Optional[str] = "mmrope3d",
+                 rope_dim: int = 128, is_last_layer: bool = False, attention_mode: str = "sdpa", **kwargs):
+        super().__init__()
+        for what, f in (("norm", norm), ("qk_norm", qk_norm)):
+            kind = _factory_kind(f)
+            if kind not in (None, "fusedrms", "_norm_layer"):
+                raise NotImplementedError(f"seedvr2_b200: {what}={kind!r}; only 'fusedrms' is implemented")
+        if emb_dim != 6 * vid_dim:
+            raise NotImplementedError("seedvr2_b200: AdaSingle needs emb_dim == 6 * dim (modulation.py:52)")
+        if mlp_type != "swiglu":
+            raise NotImplementedError("seedvr2_b200: the 3B block uses mlp_type='swiglu'")
+        if rope_type not in ("mmrope3d", None):
+            raise NotImplementedError(f"seedvr2_b200: rope_type {rope_type!r}")
+        if rope_type is not None and rope_dim != 128:
+            raise NotImplementedError("seedvr2_b200: rope_dim must be 128 (configs_3b/main.yaml:36)")
+        self.norm_eps = float(norm_eps)
+        self.is_last_layer = is_last_layer
+        self.txt_tail_skipped = bool(is_last_layer)
+        self.attn_norm = nn.Module()     # RMSNorm without affine: no state
+        self.attn = NaSwinAttentionB200(
+            vid_dim=vid_dim, txt_dim=txt_dim, heads=heads, head_dim=head_dim, qk_bias=qk_bias, qk_norm_eps=norm_eps,
+            rope_kind=ops.ROPE_3B_MM if rope_type == "mmrope3d" else ops.ROPE_NONE, shared_weights=shared_weights,
+            shared_qknorm=shared_weights, window=kwargs.pop("window", None), window_method=kwargs.pop("window_method", None))
+        self.mlp_norm = nn.Module()
+        self.mlp = _Slot(lambda: _SwiGLU(vid_dim, expand_ratio), shared_weights, vid_only=is_last_layer)
+        self.ada = _Slot(lambda: _AdaParams(vid_dim), shared_weights, vid_only=is_last_layer)
+
+
+class NaMMSRTransformerBlockB200_7B(_BlockBase):
+    """SeedVR2-7B block.  Constructor kwargs of src/models/dit_7b/nablocks/mmsr_block.py:161-180."""
+
+    def __init__(self, *, vid_dim: int, txt_dim: int, emb_dim: int, heads: int, head_dim: int, expand_ratio: int,
+                 norm=None, norm_eps: float = 1e-5, ada=None, qk_bias: bool = False, qk_rope: bool = True, qk_norm=None,
+                 shared_qkv: bool = False, shared_mlp: bool = False, mlp_type: str = "normal", window=None,
+                 window_method: Optional[str] = None, attention_mode: str = "sdpa", **kwargs):
+        super().__init__()
+        for what, f in (("norm", norm), ("qk_norm", qk_norm)):
+            kind = _factory_kind(f)
+            if kind not in (None, "fusedrms", "_norm_layer"):
+                raise NotImplementedError(f"seedvr2_b200: {what}={kind!r}; only 'fusedrms' is implemented")
+        if emb_dim != 6 * vid_dim:
+            raise NotImplementedError("seedvr2_b200: AdaSingle needs emb_dim == 6 * dim")
+        if mlp_type != "normal":
+            raise NotImplementedError("seedvr2_b200: the 7B block uses mlp_type='normal' (GELU-tanh)")
+        self.norm_eps = float(norm_eps)
+        self.attn_norm = nn.Module()
+        self.attn = NaSwinAttentionB200(
+            vid_dim=vid_dim, txt_dim=txt_dim, heads=heads, head_dim=head_dim, qk_bias=qk_bias, qk_norm_eps=norm_eps,
+            rope_kind=ops.ROPE_7B_PIX if qk_rope else ops.ROPE_NONE, shared_weights=shared_qkv,
+            shared_qknorm=False,   # 7B never shares norm_q/norm_k (blocks/mmdit_window_block.py:63-64)
+            window=window, window_method=window_method)
+        self.mlp_norm = nn.Module()
+        self.mlp = _Slot(lambda: _GeluMLP(vid_dim, expand_ratio), shared_mlp)
+        self.ada = _Slot(lambda: _AdaParams(vid_dim), False)   # 7B ada is never shared (mmdit_window_block.py:211)

@@ -1,0 +1,220 @@
+// Fused adaLN kernels: RMSNorm + modulate ("in"), gate + residual ("out"), and the pair fused.
+// Replaces CustomRMSNorm.forward (reference src/models/dit_3b/normalization.py:88-109) and AdaSingle.forward
+// (modulation.py:65-118) plus the residual adds of mmsr_block.py:114,126.
+//
+// HBM-bound.  Algorithmic bytes (bf16): modnorm 4*L*D, gate_residual 6*L*D, fused pair 8*L*D.
+// One warp owns one row, the row lives in registers as packed bf16 (lossless: every value is bf16 already), all global
+// accesses are 16-byte vectors, consecutive lanes touch consecutive 16 B.  The (embA + paramB) sums are formed once per
+// CTA in shared memory; CTAs are persistent (grid = k * #SM) and stride over rows.
+//
+// Numerics: the reference runs op by op in bf16 — ATen computes each op in fp32 and rounds the result to bf16.  Every
+// such rounding point is reproduced with bf16r(), so results match the reference's bf16 path to the
+// last bit except for the fp32 summation order inside mean().
+#include "common.cuh"
+
+namespace svr2 {
+
+constexpr int kWarpsPerCta = 8;
+
+template <int MAXCH, bool FUSE_GATE>
+__global__ void __launch_bounds__(kWarpsPerCta * 32)
+modnorm_kernel(const __nv_bfloat16* __restrict__ x,       // FUSE_GATE: h (branch output), else the row to normalise
+               const __nv_bfloat16* __restrict__ resid,   // FUSE_GATE only
+               const __nv_bfloat16* __restrict__ emb, const __nv_bfloat16* __restrict__ gateB,
+               const __nv_bfloat16* __restrict__ shiftB, const __nv_bfloat16* __restrict__ scaleB,
+               __nv_bfloat16* __restrict__ out,           // FUSE_GATE only: gated residual sum
+               __nv_bfloat16* __restrict__ y, int64_t L, int D, int gate_layer, int mod_layer, float eps, int has_mod) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    __nv_bfloat16* s_scale = reinterpret_cast<__nv_bfloat16*>(smem_raw);
+    __nv_bfloat16* s_shift = s_scale + D;
+    __nv_bfloat16* s_gate = s_shift + D;
+    for (int d = threadIdx.x; d < D; d += blockDim.x) {
+        if (has_mod) {
+            const float shA = __bfloat162float(emb[d * 6 + mod_layer * 3 + 0]);
+            const float scA = __bfloat162float(emb[d * 6 + mod_layer * 3 + 1]);
+            s_shift[d] = __float2bfloat16_rn(shA + __bfloat162float(shiftB[d]));
+            s_scale[d] = __float2bfloat16_rn(scA + __bfloat162float(scaleB[d]));
+        }
+        if (FUSE_GATE) {
+            const float gA = __bfloat162float(emb[d * 6 + gate_layer * 3 + 2]);
+            s_gate[d] = __float2bfloat16_rn(gA + __bfloat162float(gateB[d]));
+        }
+    }
+    __syncthreads();
+
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const float inv_d = 1.0f / (float)D;
+    for (int64_t row = (int64_t)blockIdx.x * kWarpsPerCta + warp; row < L; row += (int64_t)gridDim.x * kWarpsPerCta) {
+        const __nv_bfloat16* xr = x + row * D;
+        bf16x8 v[MAXCH];
+#pragma unroll
+        for (int c = 0; c < MAXCH; ++c) {
+            const int col = c * 256 + lane * 8;
+            if (col < D) v[c] = ldg8_stream(xr + col);
+        }
+        if (FUSE_GATE) {
+            const __nv_bfloat16* rr = resid + row * D;
+            bf16x8 r[MAXCH];
+#pragma unroll
+            for (int c = 0; c < MAXCH; ++c) {
+                const int col = c * 256 + lane * 8;
+                if (col < D) r[c] = ldg8_stream(rr + col);
+            }
+#pragma unroll
+            for (int c = 0; c < MAXCH; ++c) {
+                const int col = c * 256 + lane * 8;
+                if (col < D) {
+                    float h[8], rf[8], g[8];
+                    unpack8(v[c], h);
+                    unpack8(r[c], rf);
+                    unpack8(*reinterpret_cast<const bf16x8*>(s_gate + col), g);
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) h[i] = bf16r(h[i] * g[i]) + rf[i];   // mul_ rounds, then the add rounds (pack8)
+                    v[c] = pack8(h);
+                    stg8(out + row * D + col, v[c]);
+                }
+            }
+        }
+        float ss = 0.f;
+#pragma unroll
+        for (int c = 0; c < MAXCH; ++c) {
+            const int col = c * 256 + lane * 8;
+            if (col < D) {
+                float f[8];
+                unpack8(v[c], f);
+#pragma unroll
+                for (int i = 0; i < 8; ++i) ss += bf16r(f[i] * f[i]);   // input.pow(2) is a bf16 tensor
+            }
+        }
+        ss = warp_sum(ss);
+        const float var = bf16r(ss * inv_d);          // .mean() -> bf16
+        const float rms = bf16r(sqrtf(bf16r(var + eps)));
+#pragma unroll
+        for (int c = 0; c < MAXCH; ++c) {
+            const int col = c * 256 + lane * 8;
+            if (col < D) {
+                float f[8];
+                unpack8(v[c], f);
+                if (has_mod) {
+                    float sc[8], sh[8];
+                    unpack8(*reinterpret_cast<const bf16x8*>(s_scale + col), sc);
+                    unpack8(*reinterpret_cast<const bf16x8*>(s_shift + col), sh);
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) f[i] = bf16r(bf16r(__fdiv_rn(f[i], rms)) * sc[i]) + sh[i];
+                } else {
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) f[i] = __fdiv_rn(f[i], rms);
+                }
+                stg8(y + row * D + col, pack8(f));
+            }
+        }
+    }
+}
+
+// out = h * gate + resid, pure streaming.  A thread owns 8 fixed columns (gate values live in registers) and walks rows.
+__global__ void __launch_bounds__(1024)
+gate_residual_kernel(const __nv_bfloat16* __restrict__ h, const __nv_bfloat16* __restrict__ resid,
+                     const __nv_bfloat16* __restrict__ emb, const __nv_bfloat16* __restrict__ gateB,
+                     __nv_bfloat16* __restrict__ out, int64_t L, int D, int layer, int has_gate) {
+    const int col = threadIdx.x * 8;
+    if (col >= D) return;
+    float g[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+        g[i] = has_gate ? bf16r(__bfloat162float(emb[(col + i) * 6 + layer * 3 + 2]) + __bfloat162float(gateB[col + i])) : 1.f;
+    int64_t row = blockIdx.x;
+    const int64_t step = gridDim.x;
+    for (; row + 3 * step < L; row += 4 * step) {     // 8 independent 16-B loads in flight per thread
+        bf16x8 hv[4], rv[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            hv[u] = ldg8_stream(h + (row + u * step) * D + col);
+            rv[u] = ldg8_stream(resid + (row + u * step) * D + col);
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            float a[8], b[8];
+            unpack8(hv[u], a);
+            unpack8(rv[u], b);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) a[i] = (has_gate ? bf16r(a[i] * g[i]) : a[i]) + b[i];
+            stg8_stream(out + (row + u * step) * D + col, pack8(a));
+        }
+    }
+    for (; row < L; row += step) {
+        float a[8], b[8];
+        unpack8(ldg8_stream(h + row * D + col), a);
+        unpack8(ldg8_stream(resid + row * D + col), b);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) a[i] = (has_gate ? bf16r(a[i] * g[i]) : a[i]) + b[i];
+        stg8_stream(out + row * D + col, pack8(a));
+    }
+}
+
+template <bool FUSE>
+static int launch_modnorm(const void* x, const void* resid, const void* emb, const void* gateB, const void* shiftB,
+                          const void* scaleB, void* out, void* y, int64_t L, int D, int gate_layer, int mod_layer,
+                          float eps, int has_mod, cudaStream_t st, const char* name) {
+    if (L == 0) return SVR2_OK;
+    const int64_t want = (L + kWarpsPerCta - 1) / kWarpsPerCta;
+    const int64_t cap = (int64_t)sm_count() * 6;     // 6 CTAs x 8 warps = 48 warps / SM resident
+    const int grid = (int)(want < cap ? want : cap);
+    const size_t smem = (size_t)3 * D * sizeof(__nv_bfloat16);
+#define SVR2_LAUNCH_MN(MAXCH)                                                                                       \
+    do {                                                                                                             \
+        auto k = modnorm_kernel<MAXCH, FUSE>;                                                                        \
+        if (smem > 48 * 1024) cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);       \
+        k<<<grid, kWarpsPerCta * 32, smem, st>>>((const __nv_bfloat16*)x, (const __nv_bfloat16*)resid,               \
+                                                 (const __nv_bfloat16*)emb, (const __nv_bfloat16*)gateB,             \
+                                                 (const __nv_bfloat16*)shiftB, (const __nv_bfloat16*)scaleB,         \
+                                                 (__nv_bfloat16*)out, (__nv_bfloat16*)y, L, D, gate_layer, mod_layer, \
+                                                 eps, has_mod);                                                      \
+    } while (0)
+    if (D <= 1024) SVR2_LAUNCH_MN(4);
+    else if (D <= 3072) SVR2_LAUNCH_MN(12);
+    else SVR2_LAUNCH_MN(16);
+#undef SVR2_LAUNCH_MN
+    SVR2_CHECK_LAUNCH(name);
+    return SVR2_OK;
+}
+
+}  // namespace svr2
+
+extern "C" int svr2_modnorm_fwd(const void* x, const void* emb, const void* shiftB, const void* scaleB, void* y,
+                                int64_t L, int D, int layer, float eps, void* stream) {
+    SVR2_CHECK_ARG(x && y, "svr2_modnorm_fwd: null x/y");
+    SVR2_CHECK_ARG(L >= 0 && D > 0 && D % 8 == 0 && D <= 4096, "svr2_modnorm_fwd: D=%d must be a multiple of 8, <= 8192", D);
+    SVR2_CHECK_ARG(layer == 0 || layer == 1, "svr2_modnorm_fwd: layer must be 0 (attn) or 1 (mlp)");
+    const int has_mod = (shiftB != nullptr || scaleB != nullptr || emb != nullptr) ? 1 : 0;
+    SVR2_CHECK_ARG(!has_mod || (shiftB && scaleB && emb), "svr2_modnorm_fwd: emb, shiftB and scaleB go together");
+    return svr2::launch_modnorm<false>(x, nullptr, emb, nullptr, shiftB, scaleB, nullptr, y, L, D, 0, layer, eps,
+                                       has_mod, (cudaStream_t)stream, "svr2_modnorm_fwd");
+}
+
+extern "C" int svr2_gate_residual_modnorm_fwd(const void* h, const void* resid, const void* emb, const void* gateB,
+                                              const void* shiftB2, const void* scaleB2, void* out, void* y, int64_t L,
+                                              int D, int layer, float eps, void* stream) {
+    SVR2_CHECK_ARG(h && resid && emb && gateB && shiftB2 && scaleB2 && out && y, "svr2_gate_residual_modnorm_fwd: null pointer");
+    SVR2_CHECK_ARG(L >= 0 && D > 0 && D % 8 == 0 && D <= 4096, "svr2_gate_residual_modnorm_fwd: bad D=%d", D);
+    SVR2_CHECK_ARG(layer == 0, "svr2_gate_residual_modnorm_fwd: gate layer must be 0 (attn); modulation uses layer 1");
+    return svr2::launch_modnorm<true>(h, resid, emb, gateB, shiftB2, scaleB2, out, y, L, D, layer, layer + 1, eps, 1,
+                                      (cudaStream_t)stream, "svr2_gate_residual_modnorm_fwd");
+}
+
+extern "C" int svr2_gate_residual_fwd(const void* h, const void* resid, const void* emb, const void* gateB, void* out,
+                                      int64_t L, int D, int layer, void* stream) {
+    SVR2_CHECK_ARG(h && resid && out, "svr2_gate_residual_fwd: null pointer");
+    SVR2_CHECK_ARG(L >= 0 && D > 0 && D % 8 == 0 && D <= 4096, "svr2_gate_residual_fwd: bad D=%d", D);
+    SVR2_CHECK_ARG(layer == 0 || layer == 1, "svr2_gate_residual_fwd: layer must be 0 or 1");
+    const int has_gate = (emb != nullptr || gateB != nullptr) ? 1 : 0;
+    SVR2_CHECK_ARG(!has_gate || (emb && gateB), "svr2_gate_residual_fwd: emb and gateB go together");
+    if (L == 0) return SVR2_OK;
+    const int threads = ((D / 8) + 31) / 32 * 32;
+    const int64_t cap = (int64_t)svr2::sm_count() * (2048 / threads);
+    const int grid = (int)(L < cap ? L : cap);
+    svr2::gate_residual_kernel<<<grid, threads, 0, (cudaStream_t)stream>>>(
+        (const __nv_bfloat16*)h, (const __nv_bfloat16*)resid, (const __nv_bfloat16*)emb, (const __nv_bfloat16*)gateB,
+        (__nv_bfloat16*)out, L, D, layer, has_gate);
+    SVR2_CHECK_LAUNCH("svr2_gate_residual_fwd");
+    return SVR2_OK;
+}

@@ -1,0 +1,113 @@
+// Shared helpers for the seedvr2_b200 kernels (sm_100a only).
+#pragma once
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include "../../include/seedvr2_b200.h"
+
+namespace svr2 {
+
+void set_error(const char* fmt, ...);
+
+#define SVR2_CHECK_ARG(cond, ...)                 \
+    do {                                          \
+        if (!(cond)) {                            \
+            ::svr2::set_error(__VA_ARGS__);       \
+            return SVR2_E_INVALID;                \
+        }                                         \
+    } while (0)
+
+#define SVR2_CHECK_LAUNCH(name)                                                          \
+    do {                                                                                 \
+        cudaError_t e__ = cudaGetLastError();                                            \
+        if (e__ != cudaSuccess) {                                                        \
+            ::svr2::set_error("%s: launch failed: %s", name, cudaGetErrorString(e__));   \
+            return SVR2_E_CUDA;                                                          \
+        }                                                                                \
+    } while (0)
+
+struct __align__(16) bf16x8 {
+    __nv_bfloat162 v[4];
+};
+
+// Round an fp32 value to bf16 precision and return it as fp32: the rounding point of every elementwise ATen op of the
+// reference's bf16 path (ATen computes in fp32 and stores bf16).
+__device__ __forceinline__ float bf16r(float x) { return __bfloat162float(__float2bfloat16_rn(x)); }
+
+__device__ __forceinline__ bf16x8 ldg8(const __nv_bfloat16* p) {
+    bf16x8 r;
+    *reinterpret_cast<uint4*>(&r) = __ldg(reinterpret_cast<const uint4*>(p));
+    return r;
+}
+// streaming variants: data touched once, keep it out of L1
+__device__ __forceinline__ bf16x8 ldg8_stream(const __nv_bfloat16* p) {
+    bf16x8 r;
+    uint4 u;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(u.x), "=r"(u.y), "=r"(u.z), "=r"(u.w) : "l"(p));
+    *reinterpret_cast<uint4*>(&r) = u;
+    return r;
+}
+__device__ __forceinline__ void stg8(__nv_bfloat16* p, const bf16x8& v) {
+    *reinterpret_cast<uint4*>(p) = *reinterpret_cast<const uint4*>(&v);
+}
+__device__ __forceinline__ void stg8_stream(__nv_bfloat16* p, const bf16x8& v) {
+    const uint4 u = *reinterpret_cast<const uint4*>(&v);
+    asm volatile("st.global.L1::no_allocate.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(u.x), "r"(u.y), "r"(u.z), "r"(u.w) : "memory");
+}
+__device__ __forceinline__ void unpack8(const bf16x8& v, float* f) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        float2 t = __bfloat1622float2(v.v[i]);
+        f[2 * i] = t.x;
+        f[2 * i + 1] = t.y;
+    }
+}
+__device__ __forceinline__ bf16x8 pack8(const float* f) {
+    bf16x8 r;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) r.v[i] = __floats2bfloat162_rn(f[2 * i], f[2 * i + 1]);
+    return r;
+}
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+// device window table entry (SVR2_WIN_FIELDS int32)
+struct Win {
+    int t0, h0, w0, nt, nh, nw, row_start, n_vid;
+};
+__device__ __forceinline__ Win load_win(const int32_t* tab, int i) {
+    const int4 a = __ldg(reinterpret_cast<const int4*>(tab) + 2 * i);
+    const int4 b = __ldg(reinterpret_cast<const int4*>(tab) + 2 * i + 1);
+    Win w;
+    w.t0 = a.x; w.h0 = a.y; w.w0 = a.z; w.nt = a.w;
+    w.nh = b.x; w.nw = b.y; w.row_start = b.z; w.n_vid = b.w;
+    return w;
+}
+// global token id of the j-th video row of a window (row-major t,h,w inside the window)
+__device__ __forceinline__ int64_t win_token(const Win& w, int j, int H, int W, int* lt, int* lh, int* lw) {
+    const int hw = w.nh * w.nw;
+    const int t = j / hw, r = j - t * hw;
+    const int h = r / w.nw, x = r - h * w.nw;
+    *lt = t; *lh = h; *lw = x;
+    return ((int64_t)(w.t0 + t) * H + (w.h0 + h)) * W + (w.w0 + x);
+}
+
+inline int sm_count() {
+    static int n = 0;
+    if (n == 0) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+        if (n <= 0) n = 148;
+    }
+    return n;
+}
+
+}  // namespace svr2

@@ -1,0 +1,146 @@
+"""Tensor-level wrappers over the C ABI: validate, fetch raw pointers + the current CUDA stream, call, raise on error.
+
+PyTorch is plumbing here (memory + streams).  Every function runs on the tensor's CUDA device and is stream-ordered on
+``torch.cuda.current_stream()``.  Non-CUDA or non-bf16 inputs raise — there is no CPU / eager fallback.
+Calls sit behind ``torch._dynamo.disable`` like the reference's own flash-attn call (src/models/dit_3b/attention.py:64),
+so an optional ``torch.compile(model)`` (model_configuration.py:1217-1219) treats them as opaque.
+"""
+from typing import Optional, Tuple
+
+import torch
+
+from . import _lib
+from .plan import WindowPlan
+
+ROPE_NONE, ROPE_3B_MM, ROPE_7B_PIX = 0, 1, 2
+
+
+def _ptr(t: Optional[torch.Tensor]) -> Optional[int]:
+    return None if t is None else t.data_ptr()
+
+
+def _need(t: torch.Tensor, name: str, dtype=torch.bfloat16) -> torch.Tensor:
+    if not t.is_cuda:
+        raise RuntimeError(f"seedvr2_b200: `{name}` must live on a CUDA device (got {t.device}); there is no CPU path")
+    if t.dtype != dtype:
+        raise NotImplementedError(f"seedvr2_b200: `{name}` must be {dtype} (got {t.dtype})")
+    if not t.is_contiguous():
+        raise RuntimeError(f"seedvr2_b200: `{name}` must be contiguous")
+    return t
+
+
+def _stream(t: torch.Tensor) -> int:
+    return torch.cuda.current_stream(t.device).cuda_stream
+
+
+@torch._dynamo.disable
+def modnorm(x: torch.Tensor, emb: Optional[torch.Tensor], shift_b: Optional[torch.Tensor],
+            scale_b: Optional[torch.Tensor], layer: int, eps: float, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """y = rmsnorm(x) * (scaleA + scaleB) + (shiftA + shiftB);  emb/shift_b/scale_b all None -> norm only."""
+    _need(x, "x")
+    L, D = x.shape
+    y = torch.empty_like(x) if out is None else _need(out, "out")
+    for n, t in (("emb", emb), ("shift_b", shift_b), ("scale_b", scale_b)):
+        if t is not None:
+            _need(t, n)
+    with torch.cuda.device(x.device):
+        _lib.check(_lib.lib().svr2_modnorm_fwd(x.data_ptr(), _ptr(emb), _ptr(shift_b), _ptr(scale_b), y.data_ptr(),
+                                               L, D, layer, float(eps), _stream(x)), "svr2_modnorm_fwd")
+    return y
+
+
+@torch._dynamo.disable
+def gate_residual(h: torch.Tensor, resid: torch.Tensor, emb: Optional[torch.Tensor], gate_b: Optional[torch.Tensor],
+                  layer: int) -> torch.Tensor:
+    """out = h * (gateA + gateB) + resid;  emb/gate_b None -> out = h + resid."""
+    _need(h, "h"); _need(resid, "resid")
+    if h.shape != resid.shape:
+        raise RuntimeError("gate_residual: shape mismatch")
+    L, D = h.shape
+    out = torch.empty_like(h)
+    for n, t in (("emb", emb), ("gate_b", gate_b)):
+        if t is not None:
+            _need(t, n)
+    with torch.cuda.device(h.device):
+        _lib.check(_lib.lib().svr2_gate_residual_fwd(h.data_ptr(), resid.data_ptr(), _ptr(emb), _ptr(gate_b),
+                                                     out.data_ptr(), L, D, layer, _stream(h)), "svr2_gate_residual_fwd")
+    return out
+
+
+@torch._dynamo.disable
+def gate_residual_modnorm(h: torch.Tensor, resid: torch.Tensor, emb: torch.Tensor, gate_b: torch.Tensor,
+                          shift_b2: torch.Tensor, scale_b2: torch.Tensor, eps: float) -> Tuple[torch.Tensor, torch.Tensor]:
+    """(out, y): out = h*gate(attn) + resid ; y = rmsnorm(out)*scale(mlp) + shift(mlp)."""
+    for n, t in (("h", h), ("resid", resid), ("emb", emb), ("gate_b", gate_b), ("shift_b2", shift_b2), ("scale_b2", scale_b2)):
+        _need(t, n)
+    L, D = h.shape
+    out, y = torch.empty_like(h), torch.empty_like(h)
+    with torch.cuda.device(h.device):
+        _lib.check(_lib.lib().svr2_gate_residual_modnorm_fwd(
+            h.data_ptr(), resid.data_ptr(), emb.data_ptr(), gate_b.data_ptr(), shift_b2.data_ptr(), scale_b2.data_ptr(),
+            out.data_ptr(), y.data_ptr(), L, D, 0, float(eps), _stream(h)), "svr2_gate_residual_modnorm_fwd")
+    return out, y
+
+
+@torch._dynamo.disable
+def qkv_pack(plan: WindowPlan, qkv_vid: torch.Tensor, qkv_txt: torch.Tensor, wq_vid, wk_vid, wq_txt, wk_txt,
+             freqs: Optional[torch.Tensor], rope_kind: int, heads: int, eps: float):
+    """-> (q, k, v) packed [P, heads, 128] bf16: q/k RMSNorm + RoPE + window partition + text interleave."""
+    _need(qkv_vid, "qkv_vid"); _need(qkv_txt, "qkv_txt")
+    for n, t in (("wq_vid", wq_vid), ("wk_vid", wk_vid), ("wq_txt", wq_txt), ("wk_txt", wk_txt)):
+        _need(t, n)
+    T, H, W = plan.grid
+    if qkv_vid.shape != (plan.n_tokens, 3 * heads * 128) or qkv_txt.shape != (plan.txt_len, 3 * heads * 128):
+        raise RuntimeError(f"qkv_pack: bad shapes {tuple(qkv_vid.shape)} / {tuple(qkv_txt.shape)} for plan {plan.grid}")
+    n_freqs = 0
+    if rope_kind != ROPE_NONE:
+        _need(freqs, "freqs", torch.float32)
+        n_freqs = freqs.numel()
+    dev = qkv_vid.device
+    P = plan.packed_rows
+    q = torch.empty(P, heads, 128, dtype=torch.bfloat16, device=dev)
+    k = torch.empty_like(q)
+    v = torch.empty_like(q)
+    d = plan.on(dev)
+    with torch.cuda.device(dev):
+        _lib.check(_lib.lib().svr2_qkv_pack_fwd(
+            qkv_vid.data_ptr(), qkv_txt.data_ptr(), wq_vid.data_ptr(), wk_vid.data_ptr(), wq_txt.data_ptr(),
+            wk_txt.data_ptr(), _ptr(freqs), n_freqs, rope_kind, d["table"].data_ptr(), plan.n_windows, T, H, W,
+            plan.txt_len, heads, float(eps), q.data_ptr(), k.data_ptr(), v.data_ptr(), P, _stream(qkv_vid)),
+            "svr2_qkv_pack_fwd")
+    return q, k, v
+
+
+@torch._dynamo.disable
+def window_attn(plan: WindowPlan, q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, heads: int):
+    """-> (out_vid [L, heads*128] in original token order, out_txt [Lt, heads*128] mean over windows)."""
+    for n, t in (("q", q), ("k", k), ("v", v)):
+        _need(t, n)
+        if t.shape != (plan.packed_rows, heads, 128):
+            raise RuntimeError(f"window_attn: `{n}` has shape {tuple(t.shape)}, expected {(plan.packed_rows, heads, 128)}")
+    dev = q.device
+    T, H, W = plan.grid
+    out_vid = torch.empty(plan.n_tokens, heads * 128, dtype=torch.bfloat16, device=dev)
+    txt_part = torch.empty(plan.n_windows, plan.txt_len, heads * 128, dtype=torch.bfloat16, device=dev)
+    out_txt = torch.empty(plan.txt_len, heads * 128, dtype=torch.bfloat16, device=dev)
+    d = plan.on(dev)
+    with torch.cuda.device(dev):
+        _lib.check(_lib.lib().svr2_window_attn_fwd(
+            q.data_ptr(), k.data_ptr(), v.data_ptr(), d["table"].data_ptr(), d["work"].data_ptr(), plan.work.shape[0],
+            plan.n_windows, T, H, W, plan.txt_len, heads, plan.packed_rows, out_vid.data_ptr(), txt_part.data_ptr(),
+            out_txt.data_ptr(), _stream(q)), "svr2_window_attn_fwd")
+    return out_vid, out_txt
+
+
+@torch._dynamo.disable
+def halo_blend(prev_tail: torch.Tensor, cur_head: torch.Tensor, overlap: int, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """Crossfade of `overlap` frames [overlap, ...] fp32: prev*w + cur*(1-w), Hann for overlap >= 3 else linear."""
+    _need(prev_tail, "prev_tail", torch.float32); _need(cur_head, "cur_head", torch.float32)
+    if prev_tail.shape != cur_head.shape or prev_tail.shape[0] != overlap:
+        raise RuntimeError("halo_blend: inputs must both be [overlap, ...]")
+    out = torch.empty_like(prev_tail) if out is None else _need(out, "out", torch.float32)
+    frame = prev_tail[0].numel()
+    with torch.cuda.device(prev_tail.device):
+        _lib.check(_lib.lib().svr2_halo_blend(prev_tail.data_ptr(), cur_head.data_ptr(), out.data_ptr(), int(overlap),
+                                              frame, _stream(prev_tail)), "svr2_halo_blend")
+    return out

@@ -1,0 +1,125 @@
+"""Window plan: host mirror of the reference's per-forward window metadata.
+
+Replaces what the reference memoises in its ``Cache`` per window method (src/models/dit_3b/nablocks/attention/
+mmattn.py:187-221): window slices (window.py:28-83), ``na.window_idx`` (na.py:616-641), window lengths, cu_seqlens.
+The geometry itself is computed by the C ABI (``svr2_window_plan`` — host, integer) and the index tensors by
+``svr2_window_index`` on the device; this module only owns the buffers and caches plans by (grid, window, method, Lt).
+"""
+import ctypes
+from collections import OrderedDict
+from typing import Dict, Optional, Tuple
+
+import numpy as np
+import torch
+
+from . import _lib
+
+WIN_FIELDS = 8
+_MAX_WINDOWS = 1 << 16
+
+
+class WindowPlan:
+    """Geometry of one (grid, window triple, method, Lt).  Host arrays are numpy; device copies are made lazily."""
+
+    def __init__(self, grid: Tuple[int, int, int], window: Tuple[int, int, int], shifted: bool, txt_len: int):
+        L = _lib.lib()
+        T, H, W = (int(v) for v in grid)
+        nt, nh, nw = (int(v) for v in window)
+        counts = (ctypes.c_int64 * 8)()
+        # first call sizes the table
+        _lib.check(L.svr2_window_plan(T, H, W, nt, nh, nw, int(shifted), int(txt_len), None, 0, counts), "svr2_window_plan")
+        n = int(counts[0])
+        if n <= 0 or n > _MAX_WINDOWS:
+            raise RuntimeError(f"svr2_window_plan: unexpected window count {n}")
+        table = np.zeros((n, WIN_FIELDS), dtype=np.int32)
+        _lib.check(L.svr2_window_plan(T, H, W, nt, nh, nw, int(shifted), int(txt_len),
+                                      table.ctypes.data_as(ctypes.POINTER(ctypes.c_int32)), n, counts), "svr2_window_plan")
+        self.grid, self.window, self.shifted, self.txt_len = (T, H, W), (nt, nh, nw), bool(shifted), int(txt_len)
+        self.table = table
+        self.n_windows = n
+        self.n_tokens = int(counts[1])
+        self.max_len = int(counts[2])
+        self.packed_rows = int(counts[3])
+        self.min_len = int(counts[5])
+        n_items = ctypes.c_int64(0)
+        tp = table.ctypes.data_as(ctypes.POINTER(ctypes.c_int32))
+        _lib.check(L.svr2_window_attn_worklist(tp, n, self.txt_len, None, 0, ctypes.byref(n_items)), "svr2_window_attn_worklist")
+        work = np.zeros((int(n_items.value), 2), dtype=np.int32)
+        _lib.check(L.svr2_window_attn_worklist(tp, n, self.txt_len, work.ctypes.data_as(ctypes.POINTER(ctypes.c_int32)),
+                                               work.shape[0], ctypes.byref(n_items)), "svr2_window_attn_worklist")
+        self.work = work
+        self._dev: Dict[torch.device, Dict[str, torch.Tensor]] = {}
+
+    # ---- host-side views (reference vocabulary) -----------------------------------------------------------------
+    @property
+    def bounds(self) -> np.ndarray:
+        """[nw, 6] = t0, t1, h0, h1, w0, w1 — the reference's slice triples (window.py:37-49)."""
+        t = self.table
+        return np.stack([t[:, 0], t[:, 0] + t[:, 3], t[:, 1], t[:, 1] + t[:, 4], t[:, 2], t[:, 2] + t[:, 5]], axis=1)
+
+    @property
+    def window_shape(self) -> np.ndarray:
+        return self.table[:, 3:6].astype(np.int64)
+
+    @property
+    def window_lens(self) -> np.ndarray:
+        return self.table[:, 7].astype(np.int64)
+
+    @property
+    def cu_seqlens(self) -> np.ndarray:
+        cu = np.zeros(self.n_windows + 1, dtype=np.int32)
+        cu[1:] = np.cumsum(self.window_lens + self.txt_len)
+        return cu
+
+    def attention_flops(self, heads: int, head_dim: int = 128) -> float:
+        """heads * 4 * d * sum_w (Lw + Lt)^2 — the reference's own formula (attention.py:130-136)."""
+        s = (self.window_lens + self.txt_len).astype(np.float64)
+        return float(heads) * 4.0 * head_dim * float((s * s).sum())
+
+    # ---- device-side tables -------------------------------------------------------------------------------------
+    def on(self, device: torch.device) -> Dict[str, torch.Tensor]:
+        device = torch.device(device)
+        d = self._dev.get(device)
+        if d is None:
+            d = {
+                "table": torch.from_numpy(self.table).to(device),
+                "work": torch.from_numpy(self.work).to(device),
+            }
+            self._dev[device] = d
+        return d
+
+    def index_tensors(self, device: torch.device):
+        """(tgt_idx, src_idx, window_shape, cu_seqlens) on `device`, computed by svr2_window_index (bit-exact)."""
+        d = self.on(device)
+        if "tgt_idx" not in d:
+            if torch.device(device).type != "cuda":
+                raise RuntimeError("svr2_window_index runs on a CUDA device only (no CPU fallback)")
+            tgt = torch.empty(self.n_tokens, dtype=torch.int64, device=device)
+            src = torch.empty(self.n_tokens, dtype=torch.int64, device=device)
+            wshape = torch.empty(self.n_windows, 3, dtype=torch.int64, device=device)
+            cu = torch.empty(self.n_windows + 1, dtype=torch.int32, device=device)
+            T, H, W = self.grid
+            with torch.cuda.device(device):
+                stream = torch.cuda.current_stream(device).cuda_stream
+                _lib.check(_lib.lib().svr2_window_index(d["table"].data_ptr(), self.n_windows, T, H, W, self.txt_len,
+                                                        tgt.data_ptr(), src.data_ptr(), wshape.data_ptr(), cu.data_ptr(),
+                                                        stream), "svr2_window_index")
+            d.update(tgt_idx=tgt, src_idx=src, window_shape=wshape, cu_seqlens=cu)
+        return d["tgt_idx"], d["src_idx"], d["window_shape"], d["cu_seqlens"]
+
+
+_PLANS: "OrderedDict[tuple, WindowPlan]" = OrderedDict()
+_PLAN_CAP = 64
+
+
+def get_plan(grid, window, shifted: bool, txt_len: int) -> WindowPlan:
+    key = (tuple(int(v) for v in grid), tuple(int(v) for v in window), bool(shifted), int(txt_len))
+    p = _PLANS.get(key)
+    if p is None:
+        p = WindowPlan(key[0], key[1], key[2], key[3])
+        _PLANS[key] = p
+        if len(_PLANS) > _PLAN_CAP:
+            _PLANS.popitem(last=False)
+    else:
+        _PLANS.move_to_end(key)
+    return p

@@ -1,0 +1,128 @@
+"""Minimal NaDiT driver around the B200 blocks — for bench.py / smoke() / tests on a box WITHOUT the reference.
+
+In production the reference's own ``NaDiT`` (src/models/dit_3b/nadit.py:39-248, dit_7b/nadit.py:39-191) drives the
+blocks after ``install()`` swapped the block class.  The reference is not present on the GPU box, so this file restates
+the thin glue AROUND the block loop with plain torch (SURVEY §8f row N2 — "next", not hot path): text projection,
+patchify + Linear, timestep embedding, output norm + modulation (incl. cache-key quirk Q1), un-patchify.
+Parameter names equal the reference's (``vid_in.proj.weight``, ``emb_in.proj_in.weight``, ``blocks.N. ...``,
+``vid_out_norm.weight``, ``vid_out_ada.out_shift`` ...), checked against the real NaDiT by tests/golden/make_golden.py.
+"""
+import math
+from typing import Optional, Tuple
+
+import torch
+import torch.nn.functional as F
+from torch import nn
+
+from .block import NaMMSRTransformerBlockB200, NaMMSRTransformerBlockB200_7B, _Weight
+
+WIN_METHODS = ("720pwin_by_size_bysize", "720pswin_by_size_bysize")
+
+CONFIGS = {
+    # configs_3b/main.yaml:11-36
+    "3b": dict(vid_in_channels=33, vid_out_channels=16, vid_dim=2560, txt_in_dim=5120, heads=20, head_dim=128,
+               expand_ratio=4, num_layers=32, mm_layers=10, patch_size=(1, 2, 2), window=(4, 3, 3), out_norm=True),
+    # configs_7b/main.yaml:11-33
+    "7b": dict(vid_in_channels=33, vid_out_channels=16, vid_dim=3072, txt_in_dim=5120, heads=24, head_dim=128,
+               expand_ratio=4, num_layers=36, mm_layers=None, patch_size=(1, 2, 2), window=(4, 3, 3), out_norm=False),
+}
+
+
+class _Proj(nn.Module):
+    def __init__(self, i: int, o: int):
+        super().__init__()
+        self.proj = nn.Linear(i, o)
+
+
+class _TimeEmbedding(nn.Module):
+    """src/models/dit_3b/embedding.py:25-62 (+ diffusers get_timestep_embedding, flip_sin_to_cos=False, shift 0)."""
+
+    def __init__(self, hidden: int, out: int, sinusoidal_dim: int = 256):
+        super().__init__()
+        self.sinusoidal_dim = sinusoidal_dim
+        self.proj_in = nn.Linear(sinusoidal_dim, hidden)
+        self.proj_hid = nn.Linear(hidden, hidden)
+        self.proj_out = nn.Linear(hidden, out)
+
+    def forward(self, timestep: torch.Tensor, dtype: torch.dtype) -> torch.Tensor:
+        half = self.sinusoidal_dim // 2
+        exponent = -math.log(10000) * torch.arange(half, dtype=torch.float32, device=timestep.device) / half
+        ang = timestep[:, None].float() * torch.exp(exponent)[None, :]
+        emb = torch.cat([torch.sin(ang), torch.cos(ang)], dim=-1).to(dtype)
+        return self.proj_out(F.silu(self.proj_hid(F.silu(self.proj_in(emb)))))
+
+
+class _OutAda(nn.Module):
+    def __init__(self, dim: int):
+        super().__init__()
+        self.out_shift = nn.Parameter(torch.randn(dim) / dim ** 0.5)
+        self.out_scale = nn.Parameter(torch.randn(dim) / dim ** 0.5 + 1)
+
+
+class NaDiTStack(nn.Module):
+    def __init__(self, model: str = "3b", num_layers: Optional[int] = None, vid_dim: Optional[int] = None,
+                 heads: Optional[int] = None, mm_layers: Optional[int] = None, txt_in_dim: Optional[int] = None):
+        super().__init__()
+        c = dict(CONFIGS[model])
+        for k, v in (("num_layers", num_layers), ("vid_dim", vid_dim), ("heads", heads), ("mm_layers", mm_layers),
+                     ("txt_in_dim", txt_in_dim)):
+            if v is not None:
+                c[k] = v
+        self.model, self.cfg = model, c
+        D, pt, ph, pw = c["vid_dim"], *c["patch_size"]
+        self.patch = (pt, ph, pw)
+        self.vid_in = _Proj(c["vid_in_channels"] * pt * ph * pw, D)
+        self.txt_in = nn.Linear(c["txt_in_dim"], D)
+        self.emb_in = _TimeEmbedding(D, 6 * D)
+        n = c["num_layers"]
+        blocks = []
+        for i in range(n):
+            common = dict(vid_dim=D, txt_dim=D, emb_dim=6 * D, heads=c["heads"], head_dim=c["head_dim"],
+                          expand_ratio=c["expand_ratio"], norm_eps=1e-5, qk_bias=False, window=c["window"],
+                          window_method=WIN_METHODS[i % 2])
+            if model == "3b":
+                blocks.append(NaMMSRTransformerBlockB200(
+                    **common, mlp_type="swiglu", shared_weights=not (i < c["mm_layers"]), rope_type="mmrope3d",
+                    rope_dim=128, is_last_layer=(i == n - 1)))
+            else:
+                blocks.append(NaMMSRTransformerBlockB200_7B(**common, qk_rope=True, shared_qkv=False, shared_mlp=False,
+                                                            mlp_type="normal"))
+        self.blocks = nn.ModuleList(blocks)
+        if c["out_norm"]:
+            self.vid_out_norm = _Weight(D)
+            self.vid_out_ada = _OutAda(D)
+        else:
+            self.vid_out_norm = None
+        self.vid_out = _Proj(D, c["vid_out_channels"] * pt * ph * pw)
+
+    @torch.no_grad()
+    def forward(self, vid: torch.Tensor, txt: torch.Tensor, vid_shape: torch.Tensor, txt_shape: torch.Tensor,
+                timestep: torch.Tensor, grid: Optional[Tuple[int, int, int]] = None) -> torch.Tensor:
+        """vid [T*H2*W2, 33] (pre-patch latent rows), txt [Lt, 5120], vid_shape [[T, H2, W2]] -> [T*H2*W2, 16].
+        `grid` = (T, H2, W2) as Python ints avoids a device sync when vid_shape is on the GPU."""
+        pt, ph, pw = self.patch
+        T2, H2, W2 = grid if grid is not None else (int(v) for v in vid_shape[0].tolist())
+        if pt != 1 or H2 % ph or W2 % pw:
+            raise NotImplementedError("NaDiTStack: patch (1,2,2) on even latent grids only")
+        C = vid.shape[-1]
+        T, H, W = T2, H2 // ph, W2 // pw
+        txt = self.txt_in(txt)
+        # "(T t)(H h)(W w) c -> T H W (t h w c)"  (patch/patch_v1.py:91)
+        x = vid.view(T, H, ph, W, pw, C).permute(0, 1, 3, 2, 4, 5).reshape(T * H * W, ph * pw * C)
+        x = self.vid_in.proj(x)
+        tok_shape = torch.tensor([[T, H, W]], dtype=torch.long, device=vid.device) if grid is None else \
+            torch.tensor([[T, H, W]], dtype=torch.long)       # host tensor: the blocks read it without a sync
+        emb = self.emb_in(timestep.to(vid.device), x.dtype)
+        for blk in self.blocks:
+            x, txt, tok_shape, txt_shape = blk(vid=x, txt=txt, vid_shape=tok_shape, txt_shape=txt_shape, emb=emb, cache=None)
+        if self.vid_out_norm is not None:
+            # CustomRMSNorm affine (normalization.py:88-109) then vid_out_ada; quirk Q1: the cache hands it the ATTN
+            # (shift, scale) of `emb` (dit_3b/nadit.py:236-244) — reproduced, not fixed.
+            var = x.pow(2).mean(dim=-1, keepdim=True)
+            x = x / torch.sqrt(var + 1e-5) * self.vid_out_norm.weight
+            e = emb.reshape(1, -1, 2, 3)[:, :, 0, :]
+            x = x * (e[..., 1] + self.vid_out_ada.out_scale) + (e[..., 0] + self.vid_out_ada.out_shift)
+        x = self.vid_out.proj(x)
+        # "T H W (t h w c) -> (T t)(H h)(W w) c"  (patch/patch_v1.py:121)
+        co = x.shape[-1] // (ph * pw)
+        return x.view(T, H, W, ph, pw, co).permute(0, 1, 3, 2, 4, 5).reshape(T * H2 * W2, co)

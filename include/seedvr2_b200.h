@@ -1,0 +1,133 @@
+/*
+ * seedvr2_b200.h — C ABI of libseedvr2_b200.so: the B200-native (sm_100a) hot path of SeedVR2's one-step NaDiT
+ * transformer block.  Every entry point takes raw device pointers, sizes and a cudaStream_t (passed as void*), is an
+ * asynchronous stream-ordered launch, never allocates or retains caller memory and returns 0 on success or a negative
+ * SVR2_E_* code (message via svr2_last_error()).  No torch types appear here; PyTorch only owns the memory.
+ *
+ * Each function cites the reference code (disk02/ComfyUI-SeedVR2 v2.5.18, paths relative to its root) it replaces.
+ * The reference is pure Python, so "the reference FFI for this path" is a ctypes binding: see INTEGRATION.md.
+ */
+#ifndef SEEDVR2_B200_H
+#define SEEDVR2_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SVR2_OK             0
+#define SVR2_E_INVALID     -1   /* bad argument (null pointer, unsupported size, b != 1, head_dim != 128 ...) */
+#define SVR2_E_CUDA        -2   /* CUDA runtime / driver error, text in svr2_last_error() */
+#define SVR2_E_UNSUPPORTED -3   /* valid request this build does not implement (never a silent fallback) */
+
+#define SVR2_ROPE_NONE   0      /* 7B text rows */
+#define SVR2_ROPE_3B_MM  1      /* dit_3b/rope.py:88-176  lang freqs, positions (Lt+t, h, w) / text (j,j,j) */
+#define SVR2_ROPE_7B_PIX 2      /* dit_7b/rope.py:73-111  pixel freqs, linspace(-1,1,n) per window, bf16 angles, video only */
+
+#define SVR2_HEAD_DIM 128
+#define SVR2_WIN_FIELDS 8       /* int32 per window in a window table: t0,h0,w0, nt,nh,nw, row_start, n_vid */
+
+/* Last error text of the calling thread ("" if none). */
+const char* svr2_last_error(void);
+/* ABI version (bumped when a signature changes). */
+int svr2_abi_version(void);
+
+/*
+ * Window geometry, host side, pure integer/double arithmetic.
+ * Replaces make_720Pwindows_bysize / make_shifted_720Pwindows_bysize (src/models/dit_3b/window.py:28-83, same file in
+ * dit_7b) incl. Python banker's round, ceil of double quotients and int() truncation.
+ *   T,H,W        token grid;  nt,nh,nw  the YAML `window` triple (4,3,3);  shifted  0/1;  txt_len  Lt
+ *   win_table    [max_windows][SVR2_WIN_FIELDS] int32, windows in the reference order (iw outer, ih, it inner);
+ *                row_start = first packed row of the window's sequence [vid rows ; txt rows]
+ *   out_counts   [0]=n_windows [1]=sum Lw (== T*H*W) [2]=max Lw [3]=packed rows P = sum Lw + n_windows*Lt
+ *                [4]=number of 128-row query tiles over all windows [5]=min Lw
+ * Returns SVR2_E_INVALID if max_windows is too small (out_counts[0] is still set).
+ */
+int svr2_window_plan(int T, int H, int W, int nt, int nh, int nw, int shifted, int txt_len,
+                     int32_t* win_table, int max_windows, int64_t* out_counts);
+
+/*
+ * Window partition indices on the device (bit-exact integers).
+ * Replaces na.window_idx / na.window (src/models/dit_3b/na.py:583-641): tgt_idx (gather), src_idx (its inverse, the
+ * reference's argsort), window_shape [nw,3] int64, cu_seqlens [nw+1] int32 with Lt text rows appended per window
+ * (mmattn.py:211-255).  win_table is the DEVICE copy of svr2_window_plan's table.
+ */
+int svr2_window_index(const int32_t* win_table, int n_windows, int T, int H, int W, int txt_len,
+                      int64_t* tgt_idx, int64_t* src_idx, int64_t* window_shape, int32_t* cu_seqlens, void* stream);
+
+/*
+ * Fused RMSNorm (no affine) + adaLN "in" modulation:  y = rmsnorm(x) * (scaleA + scaleB) + (shiftA + shiftB)
+ * Replaces CustomRMSNorm.forward (src/models/dit_3b/normalization.py:88-109) + AdaSingle.forward mode="in"
+ * (modulation.py:65-110) — about nine ATen kernels.  bf16 in/out, every intermediate rounded to bf16 where the
+ * reference's op-by-op bf16 path rounds.
+ *   x,y [L,D] bf16 (may alias); emb [6*D] bf16 laid out (d, layer, {shift,scale,gate}); shiftB/scaleB [D] bf16 or both
+ *   NULL (norm only: the 3B last layer's vid_only text branch); layer 0=attn 1=mlp.  D % 8 == 0, D <= 4096.
+ */
+int svr2_modnorm_fwd(const void* x, const void* emb, const void* shiftB, const void* scaleB, void* y,
+                     int64_t L, int D, int layer, float eps, void* stream);
+
+/*
+ * Gate + residual:  out = h * (gateA + gateB) + resid      (modulation.py:111-116 + mmsr_block.py:114,126)
+ * gateB NULL with emb NULL means plain residual add (vid_only text branch).  h/resid/out [L,D] bf16, out may alias h.
+ */
+int svr2_gate_residual_fwd(const void* h, const void* resid, const void* emb, const void* gateB, void* out,
+                           int64_t L, int D, int layer, void* stream);
+
+/*
+ * Gate + residual fused with the FOLLOWING RMSNorm + modulation (saves one [L,D] read):
+ *   out = h * (gateA[layer] + gateB) + resid ;  y = rmsnorm(out) * (scaleA[layer+1] + scaleB2) + (shiftA[layer+1] + shiftB2)
+ * i.e. mmsr_block.py:113-121 in one pass.  `layer` is the gate's layer (0); the modulation uses layer+1.
+ */
+int svr2_gate_residual_modnorm_fwd(const void* h, const void* resid, const void* emb, const void* gateB,
+                                   const void* shiftB2, const void* scaleB2, void* out, void* y,
+                                   int64_t L, int D, int layer, float eps, void* stream);
+
+/*
+ * q/k RMSNorm (affine, per head) + 3D RoPE + window partition + text interleave, one pass over qkv.
+ * Replaces window_partition index_select (na.py:637, mmattn.py:199), norm_q/norm_k (mmattn.py:207-208,
+ * normalization.py:88-109), the text repeat (mmattn.py:223-236), RoPE (dit_3b/rope.py:92-127, dit_7b/rope.py:73-91 +
+ * third-party apply_rotary_emb) and concat_win (na.py:320-424) — writes q,k,v directly in the packed varlen layout
+ * [P, heads, 128]: sequence k = [video rows of window k ; all Lt text rows].
+ *   qkv_vid [L, 3, heads, 128] bf16 (token order), qkv_txt [Lt, 3, heads, 128] bf16
+ *   wq_vid,wk_vid,wq_txt,wk_txt [128] bf16;  freqs fp32 [n_freqs] = the checkpoint buffer attn.rope.rope.freqs
+ */
+int svr2_qkv_pack_fwd(const void* qkv_vid, const void* qkv_txt, const void* wq_vid, const void* wk_vid,
+                      const void* wq_txt, const void* wk_txt, const float* freqs, int n_freqs, int rope_kind,
+                      const int32_t* win_table, int n_windows, int T, int H, int W, int txt_len, int heads,
+                      float eps, void* q_pack, void* k_pack, void* v_pack, int64_t P, void* stream);
+
+/*
+ * Work list for svr2_window_attn_fwd, host side, pure integer: one item = (window, pair of 128-row query tiles), items
+ * sorted longest sequence first so the ragged shifted-window remnants fill the tail of the last wave.
+ *   work [max_items][2] int32 (window, q_pair) or NULL to only count;  *n_items receives the item count.
+ */
+int svr2_window_attn_worklist(const int32_t* win_table_host, int n_windows, int txt_len, int32_t* work,
+                              int max_items, int64_t* n_items);
+
+/*
+ * Variable-length window attention over the packed layout, window reverse and text pooling fused in the epilogue.
+ * Replaces FlashAttentionVarlen / pytorch_varlen_attention's per-window SDPA loop (src/models/dit_3b/attention.py:
+ * 24-61,138-157), unconcat_win (na.py:396-417) and window_reverse (na.py:638, mmattn.py:264).
+ * softmax(QK^T / sqrt(128)) V per sequence, non-causal, fp32 softmax, bf16 P.  TMA + tcgen05 + TMEM (sm_100a).
+ *   q,k,v_pack [P, heads, 128] bf16;  win_table / work: DEVICE copies of the plan's tables;
+ *   out_vid [L, heads*128] bf16 in ORIGINAL token order;
+ *   txt_part [n_windows, Lt, heads*128] bf16 workspace (per-window text rows);  out_txt [Lt, heads*128] bf16 = mean
+ *   over windows (na.py:414).
+ */
+int svr2_window_attn_fwd(const void* q_pack, const void* k_pack, const void* v_pack, const int32_t* win_table,
+                         const int32_t* work, int n_work, int n_windows, int T, int H, int W, int txt_len, int heads,
+                         int64_t P, void* out_vid, void* txt_part, void* out_txt, void* stream);
+
+/*
+ * Overlap crossfade between neighbouring temporal segments (Hann for overlap >= 3, linear below), fp32.
+ * Replaces blend_overlapping_frames (src/core/generation_utils.py:284-312) as used by the multi-GPU parent
+ * (inference_cli.py:1163-1198):  out[f] = prev_tail[f]*w[f] + cur_head[f]*(1-w[f]).   out may alias either input.
+ */
+int svr2_halo_blend(const float* prev_tail, const float* cur_head, float* out, int overlap, int64_t frame_elems,
+                    void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SEEDVR2_B200_H */

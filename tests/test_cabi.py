@@ -1,0 +1,63 @@
+"""CPU: the C-ABI shared library loads and exports every symbol include/seedvr2_b200.h declares; host-only entry points
+(window geometry, work list) are checked against the reference golden vectors.  No device work here."""
+import ctypes
+import json
+import os
+import re
+
+import numpy as np
+import pytest
+
+import cases
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+GEO = json.load(open(os.path.join(ROOT, "tests", "golden", "geometry.json")))
+
+
+def test_exports_every_declared_symbol(svr2):
+    hdr = open(os.path.join(ROOT, "include", "seedvr2_b200.h")).read()
+    declared = set(re.findall(r"\b(svr2_[a-z0-9_]+)\s*\(", hdr))
+    assert declared, "header parse failed"
+    assert declared == set(svr2._lib.SIGNATURES), declared ^ set(svr2._lib.SIGNATURES)
+    handle = ctypes.CDLL(svr2._lib.LIB_PATH)
+    for name in declared:
+        assert hasattr(handle, name), f"{name} is declared but not exported"
+    assert svr2._lib.lib().svr2_abi_version() == 1
+
+
+def test_errors_are_reported_not_swallowed(svr2):
+    L = svr2._lib.lib()
+    counts = (ctypes.c_int64 * 8)()
+    assert L.svr2_window_plan(0, 4, 4, 4, 3, 3, 0, 58, None, 0, counts) == -1
+    assert b"grid" in L.svr2_last_error()
+    with pytest.raises(RuntimeError):
+        svr2._lib.check(-1, "svr2_window_plan")
+
+
+@pytest.mark.parametrize("key", sorted(GEO))
+def test_host_plan_matches_reference(svr2, key):
+    rec = GEO[key]
+    grid, method = key.split(":")
+    T, H, W = (int(v) for v in grid.split("x"))
+    p = svr2.WindowPlan((T, H, W), (4, 3, 3), method == "swin", cases.TXT_LEN)
+    assert p.bounds.tolist() == rec["bounds"]
+    assert p.window_shape.tolist() == rec["window_shape"]
+    assert p.cu_seqlens.tolist() == rec["cu_seqlens_txt58"]
+    assert p.n_windows == rec["window_count"] and p.n_tokens == T * H * W
+    assert p.packed_rows == rec["cu_seqlens_txt58"][-1]
+    # work list: every 256-row query pair of every window exactly once, longest sequences first
+    seqs = p.window_lens + cases.TXT_LEN
+    want = sorted((int(w), q) for w in range(p.n_windows) for q in range((int(seqs[w]) + 255) // 256))
+    assert sorted(map(tuple, p.work.tolist())) == want
+    lens = [int(seqs[w]) for w, _ in p.work.tolist()]
+    assert lens == sorted(lens, reverse=True)
+
+
+def test_product_has_no_oracle_or_fallback():
+    """The product package must not import oracle/ or fall back to torch attention."""
+    pkg = os.path.join(ROOT, "comfyui-seedvr2_b200")
+    for fn in os.listdir(pkg):
+        if fn.endswith(".py"):
+            src = open(os.path.join(pkg, fn)).read()
+            assert "import oracle" not in src and "from oracle" not in src, fn
+            assert "scaled_dot_product_attention" not in src and "flash_attn" not in src, fn

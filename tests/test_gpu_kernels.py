@@ -1,0 +1,210 @@
+"""GPU parity tests, kernel by kernel, every call through the C ABI (ctypes -> libseedvr2_b200.so).
+The checker is the oracle (oracle/), itself pinned to the reference by tests/test_oracle_golden.py."""
+import hashlib
+import json
+import os
+
+import numpy as np
+import pytest
+import torch
+import torch.nn.functional as F
+
+import cases
+from oracle import block as oblock
+from oracle import geometry, partition, rope
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+GEO = json.load(open(os.path.join(ROOT, "tests", "golden", "geometry.json")))
+BF16_ULP_AT_4 = 2.0 ** -6     # one bf16 ulp for |x| in [2, 4)
+
+
+def _sha(t: torch.Tensor) -> str:
+    return hashlib.sha256(np.ascontiguousarray(t.cpu().numpy()).tobytes()).hexdigest()
+
+
+# ----------------------------------------------------------------------------------------------- window index
+@pytest.mark.parametrize("key", sorted(GEO))
+def test_window_index_bit_exact(svr2, cuda, key):
+    """Bit-exact vs the reference's na.window_idx at every BASELINE grid (sha256 of the full int64 arrays)."""
+    rec = GEO[key]
+    grid, method = key.split(":")
+    T, H, W = (int(v) for v in grid.split("x"))
+    plan = svr2.WindowPlan((T, H, W), (4, 3, 3), method == "swin", cases.TXT_LEN)
+    tgt, src, wshape, cu = plan.index_tensors(cuda)
+    torch.cuda.synchronize()
+    assert tgt.dtype == torch.int64 and src.dtype == torch.int64 and cu.dtype == torch.int32
+    assert _sha(tgt) == rec["tgt_sha256"]
+    assert _sha(src) == rec["src_sha256"]
+    assert wshape.cpu().tolist() == rec["window_shape"]
+    assert cu.cpu().tolist() == rec["cu_seqlens_txt58"]
+    # size-independent property: src is the inverse permutation of tgt
+    assert torch.equal(src[tgt], torch.arange(T * H * W, device=cuda))
+
+
+# ----------------------------------------------------------------------------------------------- adaLN kernels
+def _ada_inputs(L, D, seed, dev):
+    g = torch.Generator().manual_seed(seed)
+    x = torch.randn(L, D, generator=g).bfloat16()
+    r = torch.randn(L, D, generator=g).bfloat16()
+    emb = (0.5 * torch.randn(1, 6 * D, generator=g)).bfloat16()
+    shift, gate = (torch.randn(D, generator=g) / D ** 0.5).bfloat16(), (torch.randn(D, generator=g) / D ** 0.5).bfloat16()
+    scale = (1 + torch.randn(D, generator=g) / D ** 0.5).bfloat16()
+    return [t.to(dev) for t in (x, r, emb, shift, scale, gate)]
+
+
+def _close_bf16(a, b, what, max_ulp_frac=2e-3):
+    """Same op order and rounding points -> equal except where fp32 summation order flips a bf16 rounding."""
+    a, b = a.float(), b.float()
+    d = (a - b).abs()
+    tol = 2.0 ** -7 * b.abs().clamp(min=1.0)        # <= 1 bf16 ulp of the value
+    assert bool((d <= tol).all()), f"{what}: max diff {float(d.max())}"
+    assert float((d > 0).float().mean()) <= max_ulp_frac, f"{what}: {float((d > 0).float().mean())} of elements differ"
+
+
+@pytest.mark.parametrize("L,D", [(58, 128), (1000, 2560), (333, 3072), (5, 1024), (64, 4096)])
+@pytest.mark.parametrize("layer", [0, 1])
+def test_modnorm(svr2, cuda, L, D, layer):
+    x, _, emb, shift, scale, _ = _ada_inputs(L, D, 100 + layer, cuda)
+    y = svr2.ops.modnorm(x, emb.reshape(-1), shift, scale, layer, 1e-5)
+    ref = oblock.ada_in(oblock.rmsnorm(x, 1e-5), emb, layer, shift, scale)      # torch bf16 ops, the reference's order
+    _close_bf16(y, ref, "modnorm")
+    y0 = svr2.ops.modnorm(x, None, None, None, layer, 1e-5)
+    _close_bf16(y0, oblock.rmsnorm(x, 1e-5), "rmsnorm only")
+
+
+@pytest.mark.parametrize("L,D", [(58, 128), (1000, 2560), (333, 3072), (4099, 256)])
+def test_gate_residual(svr2, cuda, L, D):
+    x, r, emb, shift, scale, gate = _ada_inputs(L, D, 7, cuda)
+    for layer in (0, 1):
+        out = svr2.ops.gate_residual(x, r, emb.reshape(-1), gate, layer)
+        ref = oblock.ada_out(x, emb, layer, gate) + r
+        assert torch.equal(out, ref), f"gate_residual layer {layer}: max diff {float((out.float() - ref.float()).abs().max())}"
+    assert torch.equal(svr2.ops.gate_residual(x, r, None, None, 0), x + r)
+    out, y = svr2.ops.gate_residual_modnorm(x, r, emb.reshape(-1), gate, shift, scale, 1e-5)
+    ref_out = oblock.ada_out(x, emb, 0, gate) + r
+    assert torch.equal(out, ref_out)
+    _close_bf16(y, oblock.ada_in(oblock.rmsnorm(ref_out, 1e-5), emb, 1, shift, scale), "fused modnorm")
+
+
+# ----------------------------------------------------------------------------------------------- qkv pack
+def _pack_case(model, grid, shifted, heads, seed, txt_len=cases.TXT_LEN):
+    g = torch.Generator().manual_seed(seed)
+    T, H, W = grid
+    L = T * H * W
+    qkv_v = torch.randn(L, 3 * heads * 128, generator=g).bfloat16()
+    qkv_t = torch.randn(txt_len, 3 * heads * 128, generator=g).bfloat16()
+    w = [(1 + 0.1 * torch.randn(128, generator=g)).bfloat16() for _ in range(4)]
+    return qkv_v, qkv_t, w, cases.rope_freqs(model)
+
+
+def _oracle_pack(model, grid, shifted, heads, qkv_v, qkv_t, w, freqs, txt_len):
+    """Expected packed q,k,v from the oracle's op sequence (bf16 on CPU)."""
+    T, H, W = grid
+    tgt, src, wshape, cu = geometry.window_index(T, H, W, (4, 3, 3), shifted, txt_len)
+    vq, vk, vv = qkv_v.index_select(0, torch.from_numpy(tgt)).reshape(-1, 3, heads, 128).unbind(1)
+    tq, tk, tv = qkv_t.reshape(-1, 3, heads, 128).unbind(1)
+    vq, vk = oblock.rmsnorm(vq, 1e-5, w[0]), oblock.rmsnorm(vk, 1e-5, w[1])
+    tq, tk = oblock.rmsnorm(tq, 1e-5, w[2]), oblock.rmsnorm(tk, 1e-5, w[3])
+    ws = [tuple(int(v) for v in r) for r in wshape]
+    if model == "3b":
+        va, ta = rope.angles_3b(ws, txt_len, freqs)
+        vq, vk, tq, tk = rope.rotate(vq, va), rope.rotate(vk, va), rope.rotate(tq, ta), rope.rotate(tk, ta)
+    else:
+        va = rope.angles_7b(ws, freqs).to(vq.dtype)
+        vq, vk = rope.rotate(vq, va), rope.rotate(vk, va)
+    qs, ks, vs, off = [], [], [], 0
+    for (f, h, w_) in ws:
+        n = f * h * w_
+        qs += [vq[off:off + n], tq]; ks += [vk[off:off + n], tk]; vs += [vv[off:off + n], tv]
+        off += n
+    return torch.cat(qs), torch.cat(ks), torch.cat(vs)
+
+
+@pytest.mark.parametrize("model,grid,shifted,heads", [
+    ("3b", (2, 20, 36), False, 2), ("3b", (1, 32, 32), True, 3), ("7b", (3, 20, 36), False, 2), ("7b", (5, 17, 30), True, 3),
+    ("3b", (1, 1, 1), False, 1), ("7b", (1, 2, 3), True, 1),
+])
+def test_qkv_pack(svr2, cuda, model, grid, shifted, heads):
+    qkv_v, qkv_t, w, freqs = _pack_case(model, grid, shifted, heads, 5)
+    plan = svr2.get_plan(grid, (4, 3, 3), shifted, cases.TXT_LEN)
+    kind = svr2.ops.ROPE_3B_MM if model == "3b" else svr2.ops.ROPE_7B_PIX
+    q, k, v = svr2.ops.qkv_pack(plan, qkv_v.to(cuda), qkv_t.to(cuda), *[t.to(cuda) for t in w], freqs.to(cuda), kind, heads, 1e-5)
+    eq, ek, ev = _oracle_pack(model, grid, shifted, heads, qkv_v, qkv_t, w, freqs, cases.TXT_LEN)
+    assert torch.equal(v.cpu(), ev), "v rows are a pure gather: must be bit-exact"
+    for got, exp, nm in ((q, eq, "q"), (k, ek, "k")):
+        d = (got.cpu().float() - exp.float()).abs()
+        # cosf/sinf (device) vs the host libm differ by <= 1 ulp fp32 -> a bf16 rounding flips on a few elements
+        assert float(d.max()) <= 2 * BF16_ULP_AT_4, f"{nm}: max diff {float(d.max())}"
+        assert float((d > 0).float().mean()) < 5e-3, f"{nm}: {float((d > 0).float().mean())} of elements differ"
+
+
+# ----------------------------------------------------------------------------------------------- window attention
+def _sdpa_reference(plan, q, k, v, heads):
+    """fp32 per-window attention on the packed layout (the reference's pytorch_varlen_attention semantics)."""
+    cu = plan.cu_seqlens
+    T, H, W = plan.grid
+    out_v = torch.zeros(plan.n_tokens, heads * 128)
+    tacc = torch.zeros(plan.txt_len, heads * 128)
+    tgt = geometry.window_index(T, H, W, plan.window, plan.shifted, plan.txt_len)[0]
+    voff = 0
+    for i in range(plan.n_windows):
+        a, b = int(cu[i]), int(cu[i + 1])
+        qi, ki, vi = (t[a:b].float().permute(1, 0, 2).unsqueeze(0) for t in (q, k, v))
+        o = F.scaled_dot_product_attention(qi, ki, vi).squeeze(0).permute(1, 0, 2).reshape(b - a, heads * 128)
+        n = b - a - plan.txt_len
+        out_v[torch.from_numpy(tgt[voff:voff + n])] = o[:n]
+        tacc += o[n:].bfloat16().float()       # per-window text rows are bf16 before the mean (na.py:414)
+        voff += n
+    return out_v, tacc / plan.n_windows
+
+
+ATTN_CASES = [((2, 20, 36), False, 2), ((1, 32, 32), True, 3), ((5, 17, 30), True, 2), ((1, 1, 1), False, 1),
+              ((9, 30, 54), False, 1), ((3, 46, 81), True, 1)]
+
+
+@pytest.mark.parametrize("impl", ["tcgen05", "mma"])
+@pytest.mark.parametrize("grid,shifted,heads", ATTN_CASES)
+def test_window_attn_vs_fp32(svr2, cuda, monkeypatch, impl, grid, shifted, heads):
+    monkeypatch.setenv("SVR2_ATTN_IMPL", impl)
+    plan = svr2.get_plan(grid, (4, 3, 3), shifted, cases.TXT_LEN)
+    g = torch.Generator().manual_seed(3)
+    q, k, v = (torch.randn(plan.packed_rows, heads, 128, generator=g).bfloat16() for _ in range(3))
+    q = q * 1.5      # sharper softmax
+    ov, ot = svr2.ops.window_attn(plan, q.to(cuda), k.to(cuda), v.to(cuda), heads)
+    torch.cuda.synchronize()
+    ev, et = _sdpa_reference(plan, q, k, v, heads)
+    dv, dt = (ov.cpu().float() - ev).abs().max(), (ot.cpu().float() - et).abs().max()
+    assert float(dv) <= 2e-2 and float(dt) <= 2e-2, f"{impl}: vid {float(dv)} txt {float(dt)}"   # north-star tolerance
+
+
+@pytest.mark.parametrize("grid,shifted,heads", [((1, 128, 128), False, 20), ((1, 128, 128), True, 20), ((9, 90, 160), True, 4)])
+def test_window_attn_full_size_properties(svr2, cuda, monkeypatch, grid, shifted, heads):
+    """BASELINE-size runs checked through size-independent properties:
+    (1) V = ones -> every output row is exactly softmax-normalised (1.0): masking + all tiles + scatter coverage;
+    (2) linearity in V; (3) tcgen05 and the mma.sync comparator agree."""
+    plan = svr2.get_plan(grid, (4, 3, 3), shifted, cases.TXT_LEN)
+    g = torch.Generator(device="cuda").manual_seed(11)
+    P = plan.packed_rows
+    q, k, v1, v2 = (torch.randn(P, heads, 128, generator=g, device=cuda, dtype=torch.float32).bfloat16() for _ in range(4))
+    monkeypatch.setenv("SVR2_ATTN_IMPL", "tcgen05")
+    ones = torch.ones_like(v1)
+    ov, ot = svr2.ops.window_attn(plan, q, k, ones, heads)
+    assert float((ov.float() - 1).abs().max()) <= 2 ** -7 and float((ot.float() - 1).abs().max()) <= 2 ** -7
+    o1, t1 = svr2.ops.window_attn(plan, q, k, v1, heads)
+    o2, t2 = svr2.ops.window_attn(plan, q, k, v2, heads)
+    o3, t3 = svr2.ops.window_attn(plan, q, k, (v1.float() * 0.5 + v2.float() * 0.25).bfloat16(), heads)
+    assert float((o3.float() - (0.5 * o1.float() + 0.25 * o2.float())).abs().max()) <= 2e-2
+    monkeypatch.setenv("SVR2_ATTN_IMPL", "mma")
+    m1, mt1 = svr2.ops.window_attn(plan, q, k, v1, heads)
+    assert float((m1.float() - o1.float()).abs().max()) <= 2e-2 and float((mt1.float() - t1.float()).abs().max()) <= 2e-2
+
+
+# ----------------------------------------------------------------------------------------------- halo blend
+@pytest.mark.parametrize("overlap", [1, 2, 3, 4, 7])
+def test_halo_blend(svr2, cuda, overlap):
+    g = torch.Generator().manual_seed(overlap)
+    a, b = torch.rand(overlap, 18, 20, 3, generator=g), torch.rand(overlap, 18, 20, 3, generator=g)
+    out = svr2.ops.halo_blend(a.to(cuda), b.to(cuda), overlap)
+    ref = partition.blend(a, b, overlap)
+    assert float((out.cpu() - ref).abs().max()) <= 1e-6

@@ -1,0 +1,74 @@
+"""CPU: the oracle (oracle/) against the golden vectors generated from the real reference (tests/golden/make_golden.py).
+This is what pins the oracle; everything else is checked against the oracle."""
+import hashlib
+import json
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import cases
+from oracle import block as oblock
+from oracle import geometry, partition
+
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
+GEO = json.load(open(os.path.join(GOLD, "geometry.json")))
+
+
+def _sha(a: np.ndarray) -> str:
+    return hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()
+
+
+@pytest.mark.parametrize("key", sorted(GEO))
+def test_geometry_matches_reference(key):
+    rec = GEO[key]
+    grid, method = key.split(":")
+    T, H, W = (int(v) for v in grid.split("x"))
+    shifted = method == "swin"
+    b = geometry.window_bounds(T, H, W, (4, 3, 3), shifted)
+    assert [list(x) for x in b] == rec["bounds"]
+    tgt, src, shape, cu = geometry.window_index(T, H, W, (4, 3, 3), shifted, cases.TXT_LEN)
+    assert shape.tolist() == rec["window_shape"]
+    assert len(b) == rec["window_count"]
+    assert cu.tolist() == rec["cu_seqlens_txt58"]
+    assert _sha(tgt) == rec["tgt_sha256"] and _sha(src) == rec["src_sha256"]
+    if "tgt_idx" in rec:
+        assert tgt.tolist() == rec["tgt_idx"] and src.tolist() == rec["src_idx"]
+    # domain properties: a permutation and its inverse
+    assert np.array_equal(np.sort(tgt), np.arange(T * H * W))
+    assert np.array_equal(src[tgt], np.arange(T * H * W))
+
+
+@pytest.mark.parametrize("case", cases.BLOCK_CASES, ids=lambda c: c.name)
+def test_block_matches_reference(case):
+    gold = torch.load(os.path.join(GOLD, f"block_{case.name}.pt"))
+    params = cases.block_params(case)
+    vid, txt, emb = cases.block_inputs(case)
+    assert gold["in_digest"] == {"vid": cases.tensor_digest(vid), "txt": cases.tensor_digest(txt), "emb": cases.tensor_digest(emb)}
+    cfg = oblock.BlockCfg(model=case.model, dim=case.dim, heads=case.heads, head_dim=case.head_dim, shared=case.shared,
+                          is_last=case.is_last, shifted=case.shifted, window=case.window)
+    with torch.no_grad():
+        ov, ot = oblock.block_forward(cfg, params, vid, txt, case.grid, emb)
+    # fp32: same ops in the same order -> identical up to the text-mean summation order
+    assert torch.equal(ov, gold["vid_out_fp32"])
+    assert float((ot - gold["txt_out_fp32"]).abs().max()) < 1e-5
+    p16 = {k: (v if k.endswith("rope.freqs") else v.bfloat16()) for k, v in params.items()}
+    with torch.no_grad():
+        ov16, ot16 = oblock.block_forward(cfg, p16, vid.bfloat16(), txt.bfloat16(), case.grid, emb.bfloat16())
+    assert torch.equal(ov16, gold["vid_out_bf16"])
+    assert float((ot16.float() - gold["txt_out_bf16"].float()).abs().max()) <= 2 ** -7
+
+
+def test_partition_split_and_blend():
+    # inference_cli.py:1087-1097 — 121 frames, 8 GPUs, overlap 4
+    r = partition.segment_ranges(121, 8, 4)
+    assert [b - a for a, b in r] == [20, 19, 19, 19, 19, 19, 19, 15]
+    assert r[0] == (0, 20) and r[-1] == (106, 121)
+    assert partition.segment_ranges(10, 3, 0) == [(0, 4), (4, 7), (7, 10)]
+    w = partition.blend_weights(4)
+    assert torch.allclose(w, torch.tensor([1.0, 1.0, 0.0, 0.0]), atol=1e-6)      # Hann over the middle third
+    assert torch.allclose(partition.blend_weights(2), torch.tensor([1.0, 0.0]))
+    a, b = torch.ones(4, 2, 2, 3), torch.zeros(4, 2, 2, 3)
+    out = partition.stitch([torch.cat([torch.ones(6, 2, 2, 3), a]), torch.cat([b, torch.zeros(5, 2, 2, 3)])], 4)
+    assert out.shape[0] == 15 and float(out[:8].min()) == 1.0 and float(out[8:].max()) == 0.0
