@@ -89,7 +89,7 @@ class _Rope(nn.Module):
             freqs = 1.0 / (10000 ** (torch.arange(0, dim, 2)[: dim // 2].float() / dim))
         else:                        # RotaryEmbedding(dim=(head_dim//2)//3, freqs_for="pixel", max_freq=256)  dit_7b/rope.py:28-32
             dim = (head_dim // 2) // 3
-            freqs = torch.linspace(1.0, 256 / 2, dim // 2) * math.pi
+            freqs = torch.linspace(1.0, 256 / 2, dim // 2, dtype=torch.float32) * math.pi
         self.kind = kind
         self.mm = kind == ops.ROPE_3B_MM
         self.rope = _Freqs(freqs)

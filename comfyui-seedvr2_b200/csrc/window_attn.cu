@@ -400,7 +400,7 @@ extern "C" int svr2_window_attn_fwd(const void* q_pack, const void* k_pack, cons
                                     const int32_t* work, int n_work, int n_windows, int T, int H, int W, int txt_len,
                                     int heads, int64_t P, void* out_vid, void* txt_part, void* out_txt, void* stream) {
     SVR2_CHECK_ARG(q_pack && k_pack && v_pack && win_table && work && out_vid, "svr2_window_attn_fwd: null pointer");
-    SVR2_CHECK_ARG(txt_len == 0 || (txt_part && out_txt), "svr2_window_attn_fwd: text buffers missing");
+    SVR2_CHECK_ARG(txt_len == 0 || txt_part, "svr2_window_attn_fwd: text workspace missing");
     SVR2_CHECK_ARG(n_work > 0 && n_windows > 0 && heads > 0 && heads <= 65535 && P > 0 && P < ((int64_t)1 << 31),
                    "svr2_window_attn_fwd: bad sizes");
     (void)T;
@@ -412,5 +412,11 @@ extern "C" int svr2_window_attn_fwd(const void* q_pack, const void* k_pack, cons
                  ? svr2::launch_window_attn_mma(q_pack, k_pack, v_pack, win_table, work, n_work, H, W, txt_len, heads, out_vid, txt_part, st)
                  : svr2::launch_window_attn_tc(q_pack, k_pack, v_pack, win_table, work, n_work, H, W, txt_len, heads, P, out_vid, txt_part, st);
     if (rc != SVR2_OK) return rc;
+    if (out_txt == nullptr) return SVR2_OK;      // caller pools the text rows itself with svr2_txt_pool_fwd
     return svr2::launch_txt_pool(txt_part, out_txt, n_windows, txt_len, heads, st);
+}
+
+extern "C" int svr2_txt_pool_fwd(const void* txt_part, void* out_txt, int n_windows, int txt_len, int heads, void* stream) {
+    SVR2_CHECK_ARG(txt_part && out_txt && n_windows > 0 && txt_len >= 0 && heads > 0, "svr2_txt_pool_fwd: bad arguments");
+    return svr2::launch_txt_pool(txt_part, out_txt, n_windows, txt_len, heads, (cudaStream_t)stream);
 }

@@ -15,6 +15,57 @@ from .plan import WindowPlan
 ROPE_NONE, ROPE_3B_MM, ROPE_7B_PIX = 0, 1, 2
 
 
+class KernelTimer:
+    """Optional per-kernel CUDA-event timing on the launching stream (bench.py's live roofline measurement).
+    Install with ``ops.set_timer(KernelTimer())``; every C-ABI launch is then bracketed by two events."""
+
+    def __init__(self, only=None):
+        self.only = None if only is None else set(only)
+        self.records = {}
+
+    def wants(self, name: str) -> bool:
+        return self.only is None or name in self.only
+
+    def start(self, device):
+        e = torch.cuda.Event(enable_timing=True)
+        e.record(torch.cuda.current_stream(device))
+        return e
+
+    def stop(self, name: str, e0, device):
+        e1 = torch.cuda.Event(enable_timing=True)
+        e1.record(torch.cuda.current_stream(device))
+        self.records.setdefault(name, []).append((e0, e1))
+
+    def summary(self):
+        """{name: (launches, total_ms)} — call after torch.cuda.synchronize()."""
+        return {k: (len(v), sum(a.elapsed_time(b) for a, b in v)) for k, v in self.records.items()}
+
+
+_timer: Optional[KernelTimer] = None
+_launches = 0      # kernels of libseedvr2_b200.so launched by this process (bench.py's `gpu_launches`)
+
+
+def set_timer(t: Optional[KernelTimer]) -> None:
+    global _timer
+    _timer = t
+
+
+def launch_count() -> int:
+    return _launches
+
+
+def _call(name: str, n_kernels: int, device, fn, *args) -> None:
+    global _launches
+    t = _timer
+    timed = t is not None and t.wants(name)
+    with torch.cuda.device(device):
+        e0 = t.start(device) if timed else None
+        _lib.check(fn(*args), name)
+        if timed:
+            t.stop(name, e0, device)
+    _launches += n_kernels
+
+
 def _ptr(t: Optional[torch.Tensor]) -> Optional[int]:
     return None if t is None else t.data_ptr()
 
@@ -43,9 +94,9 @@ def modnorm(x: torch.Tensor, emb: Optional[torch.Tensor], shift_b: Optional[torc
     for n, t in (("emb", emb), ("shift_b", shift_b), ("scale_b", scale_b)):
         if t is not None:
             _need(t, n)
-    with torch.cuda.device(x.device):
-        _lib.check(_lib.lib().svr2_modnorm_fwd(x.data_ptr(), _ptr(emb), _ptr(shift_b), _ptr(scale_b), y.data_ptr(),
-                                               L, D, layer, float(eps), _stream(x)), "svr2_modnorm_fwd")
+    if L:
+        _call("svr2_modnorm_fwd", 1, x.device, _lib.lib().svr2_modnorm_fwd, x.data_ptr(), _ptr(emb), _ptr(shift_b),
+              _ptr(scale_b), y.data_ptr(), L, D, layer, float(eps), _stream(x))
     return y
 
 
@@ -61,9 +112,9 @@ def gate_residual(h: torch.Tensor, resid: torch.Tensor, emb: Optional[torch.Tens
     for n, t in (("emb", emb), ("gate_b", gate_b)):
         if t is not None:
             _need(t, n)
-    with torch.cuda.device(h.device):
-        _lib.check(_lib.lib().svr2_gate_residual_fwd(h.data_ptr(), resid.data_ptr(), _ptr(emb), _ptr(gate_b),
-                                                     out.data_ptr(), L, D, layer, _stream(h)), "svr2_gate_residual_fwd")
+    if L:
+        _call("svr2_gate_residual_fwd", 1, h.device, _lib.lib().svr2_gate_residual_fwd, h.data_ptr(), resid.data_ptr(),
+              _ptr(emb), _ptr(gate_b), out.data_ptr(), L, D, layer, _stream(h))
     return out
 
 
@@ -75,10 +126,10 @@ def gate_residual_modnorm(h: torch.Tensor, resid: torch.Tensor, emb: torch.Tenso
         _need(t, n)
     L, D = h.shape
     out, y = torch.empty_like(h), torch.empty_like(h)
-    with torch.cuda.device(h.device):
-        _lib.check(_lib.lib().svr2_gate_residual_modnorm_fwd(
-            h.data_ptr(), resid.data_ptr(), emb.data_ptr(), gate_b.data_ptr(), shift_b2.data_ptr(), scale_b2.data_ptr(),
-            out.data_ptr(), y.data_ptr(), L, D, 0, float(eps), _stream(h)), "svr2_gate_residual_modnorm_fwd")
+    if L:
+        _call("svr2_gate_residual_modnorm_fwd", 1, h.device, _lib.lib().svr2_gate_residual_modnorm_fwd,
+              h.data_ptr(), resid.data_ptr(), emb.data_ptr(), gate_b.data_ptr(), shift_b2.data_ptr(), scale_b2.data_ptr(),
+              out.data_ptr(), y.data_ptr(), L, D, 0, float(eps), _stream(h))
     return out, y
 
 
@@ -102,12 +153,10 @@ def qkv_pack(plan: WindowPlan, qkv_vid: torch.Tensor, qkv_txt: torch.Tensor, wq_
     k = torch.empty_like(q)
     v = torch.empty_like(q)
     d = plan.on(dev)
-    with torch.cuda.device(dev):
-        _lib.check(_lib.lib().svr2_qkv_pack_fwd(
-            qkv_vid.data_ptr(), qkv_txt.data_ptr(), wq_vid.data_ptr(), wk_vid.data_ptr(), wq_txt.data_ptr(),
-            wk_txt.data_ptr(), _ptr(freqs), n_freqs, rope_kind, d["table"].data_ptr(), plan.n_windows, T, H, W,
-            plan.txt_len, heads, float(eps), q.data_ptr(), k.data_ptr(), v.data_ptr(), P, _stream(qkv_vid)),
-            "svr2_qkv_pack_fwd")
+    _call("svr2_qkv_pack_fwd", 1, dev, _lib.lib().svr2_qkv_pack_fwd,
+          qkv_vid.data_ptr(), qkv_txt.data_ptr(), wq_vid.data_ptr(), wk_vid.data_ptr(), wq_txt.data_ptr(),
+          wk_txt.data_ptr(), _ptr(freqs), n_freqs, rope_kind, d["table"].data_ptr(), plan.n_windows, T, H, W,
+          plan.txt_len, heads, float(eps), q.data_ptr(), k.data_ptr(), v.data_ptr(), P, _stream(qkv_vid))
     return q, k, v
 
 
@@ -124,11 +173,14 @@ def window_attn(plan: WindowPlan, q: torch.Tensor, k: torch.Tensor, v: torch.Ten
     txt_part = torch.empty(plan.n_windows, plan.txt_len, heads * 128, dtype=torch.bfloat16, device=dev)
     out_txt = torch.empty(plan.txt_len, heads * 128, dtype=torch.bfloat16, device=dev)
     d = plan.on(dev)
-    with torch.cuda.device(dev):
-        _lib.check(_lib.lib().svr2_window_attn_fwd(
-            q.data_ptr(), k.data_ptr(), v.data_ptr(), d["table"].data_ptr(), d["work"].data_ptr(), plan.work.shape[0],
-            plan.n_windows, T, H, W, plan.txt_len, heads, plan.packed_rows, out_vid.data_ptr(), txt_part.data_ptr(),
-            out_txt.data_ptr(), _stream(q)), "svr2_window_attn_fwd")
+    # attention and text pooling are two kernels; they are launched separately so the attention kernel can be timed alone
+    _call("svr2_window_attn_fwd", 1, dev, _lib.lib().svr2_window_attn_fwd,
+          q.data_ptr(), k.data_ptr(), v.data_ptr(), d["table"].data_ptr(), d["work"].data_ptr(), plan.work.shape[0],
+          plan.n_windows, T, H, W, plan.txt_len, heads, plan.packed_rows, out_vid.data_ptr(), txt_part.data_ptr(),
+          None, _stream(q))
+    if plan.txt_len:
+        _call("svr2_txt_pool_fwd", 1, dev, _lib.lib().svr2_txt_pool_fwd, txt_part.data_ptr(), out_txt.data_ptr(),
+              plan.n_windows, plan.txt_len, heads, _stream(q))
     return out_vid, out_txt
 
 
@@ -140,7 +192,6 @@ def halo_blend(prev_tail: torch.Tensor, cur_head: torch.Tensor, overlap: int, ou
         raise RuntimeError("halo_blend: inputs must both be [overlap, ...]")
     out = torch.empty_like(prev_tail) if out is None else _need(out, "out", torch.float32)
     frame = prev_tail[0].numel()
-    with torch.cuda.device(prev_tail.device):
-        _lib.check(_lib.lib().svr2_halo_blend(prev_tail.data_ptr(), cur_head.data_ptr(), out.data_ptr(), int(overlap),
-                                              frame, _stream(prev_tail)), "svr2_halo_blend")
+    _call("svr2_halo_blend", 1, prev_tail.device, _lib.lib().svr2_halo_blend, prev_tail.data_ptr(), cur_head.data_ptr(),
+          out.data_ptr(), int(overlap), frame, _stream(prev_tail))
     return out

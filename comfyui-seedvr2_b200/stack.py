@@ -126,3 +126,19 @@ class NaDiTStack(nn.Module):
         # "T H W (t h w c) -> (T t)(H h)(W w) c"  (patch/patch_v1.py:121)
         co = x.shape[-1] // (ph * pw)
         return x.view(T, H, W, ph, pw, co).permute(0, 1, 3, 2, 4, 5).reshape(T * H2 * W2, co)
+
+
+    @torch.no_grad()
+    def forward_host(self, vid_host: torch.Tensor, txt_host: torch.Tensor, grid: Tuple[int, int, int], timestep: float,
+                     out_host: torch.Tensor, device: torch.device) -> torch.Tensor:
+        """End-to-end call with HOST buffers (what a pipeline stage hands over): pinned host latents/text are copied to
+        the device, one NaDiT forward runs, the predicted latent is copied back into the pinned ``out_host``.
+        Stream-ordered on the current stream; returns ``out_host`` after the copy-back completed."""
+        vid = vid_host.to(device, non_blocking=True)
+        txt = txt_host.to(device, non_blocking=True)
+        ts = torch.tensor([[txt.shape[0]]], dtype=torch.long)
+        t = torch.full((1,), float(timestep), dtype=torch.float32, device=device)
+        out = self.forward(vid, txt, None, ts, t, grid=grid)
+        out_host.copy_(out, non_blocking=True)
+        torch.cuda.current_stream(device).synchronize()
+        return out_host

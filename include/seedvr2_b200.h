@@ -113,11 +113,18 @@ int svr2_window_attn_worklist(const int32_t* win_table_host, int n_windows, int 
  *   q,k,v_pack [P, heads, 128] bf16;  win_table / work: DEVICE copies of the plan's tables;
  *   out_vid [L, heads*128] bf16 in ORIGINAL token order;
  *   txt_part [n_windows, Lt, heads*128] bf16 workspace (per-window text rows);  out_txt [Lt, heads*128] bf16 = mean
- *   over windows (na.py:414).
+ *   over windows (na.py:414), or NULL to leave the pooling to svr2_txt_pool_fwd.
  */
 int svr2_window_attn_fwd(const void* q_pack, const void* k_pack, const void* v_pack, const int32_t* win_table,
                          const int32_t* work, int n_work, int n_windows, int T, int H, int W, int txt_len, int heads,
                          int64_t P, void* out_vid, void* txt_part, void* out_txt, void* stream);
+
+/*
+ * Text pooling on its own: out_txt[j] = mean over windows of txt_part[w, j]  (na.py:414 — unconcat_coalesce's
+ * `.mean(1)` over the per-window copies of the text rows; bf16 rows, fp32 accumulate, bf16 result).
+ * svr2_window_attn_fwd runs it itself unless out_txt is NULL.
+ */
+int svr2_txt_pool_fwd(const void* txt_part, void* out_txt, int n_windows, int txt_len, int heads, void* stream);
 
 /*
  * Overlap crossfade between neighbouring temporal segments (Hann for overlap >= 3, linear below), fp32.
