@@ -3,9 +3,9 @@
 // (modulation.py:65-118) plus the residual adds of mmsr_block.py:114,126.
 //
 // HBM-bound.  Algorithmic bytes (bf16): modnorm 4*L*D, gate_residual 6*L*D, fused pair 8*L*D.
-// One warp owns one row, the row lives in registers as packed bf16 (lossless: every value is bf16 already), all global
-// accesses are 16-byte vectors, consecutive lanes touch consecutive 16 B.  The (embA + paramB) sums are formed once per
-// CTA in shared memory; CTAs are persistent (grid = k * #SM) and stride over rows.
+// A thread owns 8 fixed columns, rows live in registers as packed bf16 (lossless: every value is bf16 already), all
+// global accesses are 16-byte vectors, consecutive lanes touch consecutive 16 B.  The (embA + paramB) sums are formed
+// once per CTA in registers; CTAs are persistent (grid = resident CTAs x #SM) and stride over groups of kRows rows.
 //
 // Numerics: the reference runs op by op in bf16 — ATen computes each op in fp32 and rounds the result to bf16.  Every
 // such rounding point is reproduced with bf16r(), so results match the reference's bf16 path to the
@@ -14,99 +14,105 @@
 
 namespace svr2 {
 
-constexpr int kWarpsPerCta = 8;
+// Thread t of a CTA owns columns [8t, 8t+8) of EVERY row the CTA touches (D/8 threads, rounded up to a warp), so the
+// (embA + paramB) vectors live in registers for the CTA's lifetime and a row costs each thread exactly one 16-byte load
+// (two when the gate/residual is fused) and one (two) 16-byte store.  A CTA walks kRows rows per iteration — kRows
+// independent loads in flight per thread — and the row sums are reduced with warp shuffles + one __syncthreads per
+// iteration (double-buffered partials).  Few registers -> 3+ CTAs per SM -> >= 60 KB of loads in flight per SM.
+constexpr int kMaxWarps = 16;     // D <= 4096
 
-template <int MAXCH, bool FUSE_GATE>
-__global__ void __launch_bounds__(kWarpsPerCta * 32)
+template <bool FUSE_GATE, int kRows>
+__global__ void __launch_bounds__(kMaxWarps * 32, 2)
 modnorm_kernel(const __nv_bfloat16* __restrict__ x,       // FUSE_GATE: h (branch output), else the row to normalise
                const __nv_bfloat16* __restrict__ resid,   // FUSE_GATE only
                const __nv_bfloat16* __restrict__ emb, const __nv_bfloat16* __restrict__ gateB,
                const __nv_bfloat16* __restrict__ shiftB, const __nv_bfloat16* __restrict__ scaleB,
                __nv_bfloat16* __restrict__ out,           // FUSE_GATE only: gated residual sum
                __nv_bfloat16* __restrict__ y, int64_t L, int D, int gate_layer, int mod_layer, float eps, int has_mod) {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    __nv_bfloat16* s_scale = reinterpret_cast<__nv_bfloat16*>(smem_raw);
-    __nv_bfloat16* s_shift = s_scale + D;
-    __nv_bfloat16* s_gate = s_shift + D;
-    for (int d = threadIdx.x; d < D; d += blockDim.x) {
-        if (has_mod) {
-            const float shA = __bfloat162float(emb[d * 6 + mod_layer * 3 + 0]);
-            const float scA = __bfloat162float(emb[d * 6 + mod_layer * 3 + 1]);
-            s_shift[d] = __float2bfloat16_rn(shA + __bfloat162float(shiftB[d]));
-            s_scale[d] = __float2bfloat16_rn(scA + __bfloat162float(scaleB[d]));
-        }
-        if (FUSE_GATE) {
-            const float gA = __bfloat162float(emb[d * 6 + gate_layer * 3 + 2]);
-            s_gate[d] = __float2bfloat16_rn(gA + __bfloat162float(gateB[d]));
-        }
-    }
-    __syncthreads();
-
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const float inv_d = 1.0f / (float)D;
-    for (int64_t row = (int64_t)blockIdx.x * kWarpsPerCta + warp; row < L; row += (int64_t)gridDim.x * kWarpsPerCta) {
-        const __nv_bfloat16* xr = x + row * D;
-        bf16x8 v[MAXCH];
+    __shared__ float s_part[2][kRows][kMaxWarps];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, n_warps = blockDim.x >> 5;
+    const int col = threadIdx.x * 8;
+    const bool act = col < D;
+    bf16x8 sc_p, sh_p, g_p;      // (embA + paramB), rounded to bf16 like the reference's tensor add; kept packed
+    {
+        float sc[8], sh[8], g[8];
 #pragma unroll
-        for (int c = 0; c < MAXCH; ++c) {
-            const int col = c * 256 + lane * 8;
-            if (col < D) v[c] = ldg8_stream(xr + col);
-        }
-        if (FUSE_GATE) {
-            const __nv_bfloat16* rr = resid + row * D;
-            bf16x8 r[MAXCH];
+        for (int i = 0; i < 8; ++i) { sc[i] = 1.f; sh[i] = 0.f; g[i] = 1.f; }
+        if (act) {
 #pragma unroll
-            for (int c = 0; c < MAXCH; ++c) {
-                const int col = c * 256 + lane * 8;
-                if (col < D) r[c] = ldg8_stream(rr + col);
-            }
-#pragma unroll
-            for (int c = 0; c < MAXCH; ++c) {
-                const int col = c * 256 + lane * 8;
-                if (col < D) {
-                    float h[8], rf[8], g[8];
-                    unpack8(v[c], h);
-                    unpack8(r[c], rf);
-                    unpack8(*reinterpret_cast<const bf16x8*>(s_gate + col), g);
-#pragma unroll
-                    for (int i = 0; i < 8; ++i) h[i] = bf16r(h[i] * g[i]) + rf[i];   // mul_ rounds, then the add rounds (pack8)
-                    v[c] = pack8(h);
-                    stg8(out + row * D + col, v[c]);
-                }
-            }
-        }
-        float ss = 0.f;
-#pragma unroll
-        for (int c = 0; c < MAXCH; ++c) {
-            const int col = c * 256 + lane * 8;
-            if (col < D) {
-                float f[8];
-                unpack8(v[c], f);
-#pragma unroll
-                for (int i = 0; i < 8; ++i) ss += bf16r(f[i] * f[i]);   // input.pow(2) is a bf16 tensor
-            }
-        }
-        ss = warp_sum(ss);
-        const float var = bf16r(ss * inv_d);          // .mean() -> bf16
-        const float rms = bf16r(sqrtf(bf16r(var + eps)));
-#pragma unroll
-        for (int c = 0; c < MAXCH; ++c) {
-            const int col = c * 256 + lane * 8;
-            if (col < D) {
-                float f[8];
-                unpack8(v[c], f);
+            for (int i = 0; i < 8; ++i) {
+                const int d = col + i;
                 if (has_mod) {
-                    float sc[8], sh[8];
-                    unpack8(*reinterpret_cast<const bf16x8*>(s_scale + col), sc);
-                    unpack8(*reinterpret_cast<const bf16x8*>(s_shift + col), sh);
-#pragma unroll
-                    for (int i = 0; i < 8; ++i) f[i] = bf16r(bf16r(__fdiv_rn(f[i], rms)) * sc[i]) + sh[i];
-                } else {
-#pragma unroll
-                    for (int i = 0; i < 8; ++i) f[i] = __fdiv_rn(f[i], rms);
+                    sh[i] = __bfloat162float(emb[d * 6 + mod_layer * 3 + 0]) + __bfloat162float(shiftB[d]);
+                    sc[i] = __bfloat162float(emb[d * 6 + mod_layer * 3 + 1]) + __bfloat162float(scaleB[d]);
                 }
-                stg8(y + row * D + col, pack8(f));
+                if (FUSE_GATE) g[i] = __bfloat162float(emb[d * 6 + gate_layer * 3 + 2]) + __bfloat162float(gateB[d]);
             }
+        }
+        sc_p = pack8(sc); sh_p = pack8(sh); g_p = pack8(g);
+    }
+    const float inv_d = 1.0f / (float)D;
+    int buf = 0;
+    for (int64_t row0 = (int64_t)blockIdx.x * kRows; row0 < L; row0 += (int64_t)gridDim.x * kRows, buf ^= 1) {
+        bf16x8 v[kRows], r[kRows];
+#pragma unroll
+        for (int k = 0; k < kRows; ++k) {
+            const bool ok = act && (row0 + k < L);
+            if (ok) {
+                v[k] = ldg8_stream(x + (row0 + k) * D + col);
+                if (FUSE_GATE) r[k] = ldg8_stream(resid + (row0 + k) * D + col);
+            } else {
+#pragma unroll
+                for (int i = 0; i < 4; ++i) v[k].v[i] = __floats2bfloat162_rn(0.f, 0.f);
+            }
+        }
+        float ss[kRows];
+#pragma unroll
+        for (int k = 0; k < kRows; ++k) {
+            float f[8];
+            unpack8(v[k], f);
+            if (FUSE_GATE) {
+                if (act && (row0 + k < L)) {
+                    float rf[8], g[8];
+                    unpack8(r[k], rf);
+                    unpack8(g_p, g);
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) f[i] = bf16r(f[i] * g[i]) + rf[i];   // mul_ rounds, then the add rounds (pack8)
+                    v[k] = pack8(f);
+                    stg8(out + (row0 + k) * D + col, v[k]);                          // re-read by the next GEMM epilogue chain: keep in L2
+                    unpack8(v[k], f);
+                }
+            }
+            float a = 0.f;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) a += bf16r(f[i] * f[i]);                      // input.pow(2) is a bf16 tensor
+            ss[k] = warp_sum(a);
+        }
+        if (lane == 0) {
+#pragma unroll
+            for (int k = 0; k < kRows; ++k) s_part[buf][k][warp] = ss[k];
+        }
+        __syncthreads();
+#pragma unroll
+        for (int k = 0; k < kRows; ++k) {
+            if (!(act && (row0 + k < L))) continue;
+            float tot = 0.f;
+            for (int w = 0; w < n_warps; ++w) tot += s_part[buf][k][w];
+            const float var = bf16r(tot * inv_d);                                     // .mean() -> bf16
+            const float rms = bf16r(sqrtf(bf16r(var + eps)));
+            float f[8];
+            unpack8(v[k], f);
+            if (has_mod) {
+                float sc[8], sh[8];
+                unpack8(sc_p, sc);
+                unpack8(sh_p, sh);
+#pragma unroll
+                for (int i = 0; i < 8; ++i) f[i] = bf16r(bf16r(__fdiv_rn(f[i], rms)) * sc[i]) + sh[i];
+            } else {
+#pragma unroll
+                for (int i = 0; i < 8; ++i) f[i] = __fdiv_rn(f[i], rms);
+            }
+            stg8(y + (row0 + k) * D + col, pack8(f));
         }
     }
 }
@@ -156,24 +162,23 @@ static int launch_modnorm(const void* x, const void* resid, const void* emb, con
                           const void* scaleB, void* out, void* y, int64_t L, int D, int gate_layer, int mod_layer,
                           float eps, int has_mod, cudaStream_t st, const char* name) {
     if (L == 0) return SVR2_OK;
-    const int64_t want = (L + kWarpsPerCta - 1) / kWarpsPerCta;
-    const int64_t cap = (int64_t)sm_count() * 6;     // 6 CTAs x 8 warps = 48 warps / SM resident
+    const int threads = ((D / 8) + 31) / 32 * 32;
+    constexpr int kRows = FUSE ? 2 : 4;          // same bytes in flight per thread either way (the fused kernel loads h and resid)
+    static int occ[kMaxWarps + 1] = {0};          // resident CTAs per SM for this block size (queried once)
+    const int wi = threads / 32;
+    if (occ[wi] == 0) {
+        int n = 0;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, modnorm_kernel<FUSE, kRows>, threads, 0) != cudaSuccess || n <= 0) n = 2;
+        occ[wi] = n;
+    }
+    const int64_t want = (L + kRows - 1) / kRows;
+    const int64_t cap = (int64_t)sm_count() * occ[wi];
     const int grid = (int)(want < cap ? want : cap);
-    const size_t smem = (size_t)3 * D * sizeof(__nv_bfloat16);
-#define SVR2_LAUNCH_MN(MAXCH)                                                                                       \
-    do {                                                                                                             \
-        auto k = modnorm_kernel<MAXCH, FUSE>;                                                                        \
-        if (smem > 48 * 1024) cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);       \
-        k<<<grid, kWarpsPerCta * 32, smem, st>>>((const __nv_bfloat16*)x, (const __nv_bfloat16*)resid,               \
-                                                 (const __nv_bfloat16*)emb, (const __nv_bfloat16*)gateB,             \
-                                                 (const __nv_bfloat16*)shiftB, (const __nv_bfloat16*)scaleB,         \
-                                                 (__nv_bfloat16*)out, (__nv_bfloat16*)y, L, D, gate_layer, mod_layer, \
-                                                 eps, has_mod);                                                      \
-    } while (0)
-    if (D <= 1024) SVR2_LAUNCH_MN(4);
-    else if (D <= 3072) SVR2_LAUNCH_MN(12);
-    else SVR2_LAUNCH_MN(16);
-#undef SVR2_LAUNCH_MN
+    modnorm_kernel<FUSE, kRows><<<grid, threads, 0, st>>>((const __nv_bfloat16*)x, (const __nv_bfloat16*)resid,
+                                                   (const __nv_bfloat16*)emb, (const __nv_bfloat16*)gateB,
+                                                   (const __nv_bfloat16*)shiftB, (const __nv_bfloat16*)scaleB,
+                                                   (__nv_bfloat16*)out, (__nv_bfloat16*)y, L, D, gate_layer, mod_layer,
+                                                   eps, has_mod);
     SVR2_CHECK_LAUNCH(name);
     return SVR2_OK;
 }
