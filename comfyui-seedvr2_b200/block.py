@@ -105,7 +105,7 @@ class _SwiGLU(nn.Module):      # reference mlp.py:46-62
         self.proj_in = nn.Linear(dim, hidden, bias=False)
 
     def forward(self, x):
-        return self.proj_out(F.silu(self.proj_in_gate(x)) * self.proj_in(x))
+        return self.proj_out(ops.swiglu(self.proj_in_gate(x), self.proj_in(x)))
 
 
 class _GeluMLP(nn.Module):     # reference mlp.py:28-43

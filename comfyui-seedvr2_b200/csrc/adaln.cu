@@ -69,23 +69,22 @@ modnorm_kernel(const __nv_bfloat16* __restrict__ x,       // FUSE_GATE: h (branc
         float ss[kRows];
 #pragma unroll
         for (int k = 0; k < kRows; ++k) {
-            float f[8];
-            unpack8(v[k], f);
             if (FUSE_GATE) {
                 if (act && (row0 + k < L)) {
-                    float rf[8], g[8];
+                    float f[8], rf[8];
+                    unpack8(mul8(v[k], g_p), f);                                     // mul_ rounds to bf16 ...
                     unpack8(r[k], rf);
-                    unpack8(g_p, g);
 #pragma unroll
-                    for (int i = 0; i < 8; ++i) f[i] = bf16r(f[i] * g[i]) + rf[i];   // mul_ rounds, then the add rounds (pack8)
+                    for (int i = 0; i < 8; ++i) f[i] += rf[i];                       // ... then the add rounds (pack8)
                     v[k] = pack8(f);
-                    stg8(out + (row0 + k) * D + col, v[k]);                          // re-read by the next GEMM epilogue chain: keep in L2
-                    unpack8(v[k], f);
+                    stg8(out + (row0 + k) * D + col, v[k]);
                 }
             }
+            float f[8];
+            unpack8(mul8(v[k], v[k]), f);                                            // input.pow(2) is a bf16 tensor
             float a = 0.f;
 #pragma unroll
-            for (int i = 0; i < 8; ++i) a += bf16r(f[i] * f[i]);                      // input.pow(2) is a bf16 tensor
+            for (int i = 0; i < 8; ++i) a += f[i];
             ss[k] = warp_sum(a);
         }
         if (lane == 0) {
@@ -100,17 +99,17 @@ modnorm_kernel(const __nv_bfloat16* __restrict__ x,       // FUSE_GATE: h (branc
             for (int w = 0; w < n_warps; ++w) tot += s_part[buf][k][w];
             const float var = bf16r(tot * inv_d);                                     // .mean() -> bf16
             const float rms = bf16r(sqrtf(bf16r(var + eps)));
+            const float rcp = __frcp_rn(rms);
             float f[8];
             unpack8(v[k], f);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) f[i] = div_rcp(f[i], rms, rcp);
             if (has_mod) {
-                float sc[8], sh[8];
-                unpack8(sc_p, sc);
+                float sh[8];
+                unpack8(mul8(pack8(f), sc_p), f);                                     // (x / rms) -> bf16, * scale -> bf16
                 unpack8(sh_p, sh);
 #pragma unroll
-                for (int i = 0; i < 8; ++i) f[i] = bf16r(bf16r(__fdiv_rn(f[i], rms)) * sc[i]) + sh[i];
-            } else {
-#pragma unroll
-                for (int i = 0; i < 8; ++i) f[i] = __fdiv_rn(f[i], rms);
+                for (int i = 0; i < 8; ++i) f[i] += sh[i];
             }
             stg8(y + (row0 + k) * D + col, pack8(f));
         }
@@ -124,10 +123,14 @@ gate_residual_kernel(const __nv_bfloat16* __restrict__ h, const __nv_bfloat16* _
                      __nv_bfloat16* __restrict__ out, int64_t L, int D, int layer, int has_gate) {
     const int col = threadIdx.x * 8;
     if (col >= D) return;
-    float g[8];
+    bf16x8 g_p;
+    {
+        float g[8];
 #pragma unroll
-    for (int i = 0; i < 8; ++i)
-        g[i] = has_gate ? bf16r(__bfloat162float(emb[(col + i) * 6 + layer * 3 + 2]) + __bfloat162float(gateB[col + i])) : 1.f;
+        for (int i = 0; i < 8; ++i)
+            g[i] = has_gate ? __bfloat162float(emb[(col + i) * 6 + layer * 3 + 2]) + __bfloat162float(gateB[col + i]) : 1.f;
+        g_p = pack8(g);       // gateA + gateB is a bf16 tensor in the reference
+    }
     int64_t row = blockIdx.x;
     const int64_t step = gridDim.x;
     for (; row + 3 * step < L; row += 4 * step) {     // 8 independent 16-B loads in flight per thread
@@ -140,20 +143,54 @@ gate_residual_kernel(const __nv_bfloat16* __restrict__ h, const __nv_bfloat16* _
 #pragma unroll
         for (int u = 0; u < 4; ++u) {
             float a[8], b[8];
-            unpack8(hv[u], a);
+            unpack8(has_gate ? mul8(hv[u], g_p) : hv[u], a);
             unpack8(rv[u], b);
 #pragma unroll
-            for (int i = 0; i < 8; ++i) a[i] = (has_gate ? bf16r(a[i] * g[i]) : a[i]) + b[i];
+            for (int i = 0; i < 8; ++i) a[i] += b[i];
             stg8_stream(out + (row + u * step) * D + col, pack8(a));
         }
     }
     for (; row < L; row += step) {
         float a[8], b[8];
-        unpack8(ldg8_stream(h + row * D + col), a);
+        const bf16x8 hv = ldg8_stream(h + row * D + col);
+        unpack8(has_gate ? mul8(hv, g_p) : hv, a);
         unpack8(ldg8_stream(resid + row * D + col), b);
 #pragma unroll
-        for (int i = 0; i < 8; ++i) a[i] = (has_gate ? bf16r(a[i] * g[i]) : a[i]) + b[i];
+        for (int i = 0; i < 8; ++i) a[i] += b[i];
         stg8_stream(out + row * D + col, pack8(a));
+    }
+}
+
+// out = silu(gate) * up  — the SwiGLU activation between proj_in_gate/proj_in and proj_out (reference mlp.py:60-62:
+// `F.silu(self.proj_in_gate(x)) * self.proj_in(x)`, two ATen kernels = 5 [L,hidden] passes; here 3).  silu is rounded to
+// bf16 before the product like the reference's intermediate tensor.  HBM-bound: 6 B per element.
+__global__ void __launch_bounds__(256)
+swiglu_kernel(const __nv_bfloat16* __restrict__ gate, const __nv_bfloat16* __restrict__ up,
+              __nv_bfloat16* __restrict__ out, int64_t n8) {
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    for (; i + 3 * stride < n8; i += 4 * stride) {       // 8 independent 16-B loads in flight per thread
+        bf16x8 g[4], u[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            g[k] = ldg8_stream(gate + (i + k * stride) * 8);
+            u[k] = ldg8_stream(up + (i + k * stride) * 8);
+        }
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            float f[8];
+            unpack8(g[k], f);
+#pragma unroll
+            for (int e = 0; e < 8; ++e) f[e] = __fdividef(f[e], 1.0f + __expf(-f[e]));
+            stg8(out + (i + k * stride) * 8, mul8(pack8(f), u[k]));
+        }
+    }
+    for (; i < n8; i += stride) {
+        float f[8];
+        unpack8(ldg8_stream(gate + i * 8), f);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) f[e] = __fdividef(f[e], 1.0f + __expf(-f[e]));
+        stg8(out + i * 8, mul8(pack8(f), ldg8_stream(up + i * 8)));
     }
 }
 
@@ -221,5 +258,19 @@ extern "C" int svr2_gate_residual_fwd(const void* h, const void* resid, const vo
         (const __nv_bfloat16*)h, (const __nv_bfloat16*)resid, (const __nv_bfloat16*)emb, (const __nv_bfloat16*)gateB,
         (__nv_bfloat16*)out, L, D, layer, has_gate);
     SVR2_CHECK_LAUNCH("svr2_gate_residual_fwd");
+    return SVR2_OK;
+}
+
+extern "C" int svr2_swiglu_fwd(const void* gate, const void* up, void* out, int64_t n, void* stream) {
+    SVR2_CHECK_ARG(gate && up && out, "svr2_swiglu_fwd: null pointer");
+    SVR2_CHECK_ARG(n >= 0 && n % 8 == 0, "svr2_swiglu_fwd: element count %lld must be a multiple of 8", (long long)n);
+    if (n == 0) return SVR2_OK;
+    const int64_t n8 = n / 8;
+    int64_t grid = (n8 + 256 * 4 - 1) / (256 * 4);
+    const int64_t cap = (int64_t)svr2::sm_count() * 8;
+    if (grid > cap) grid = cap;
+    svr2::swiglu_kernel<<<(unsigned)grid, 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)gate, (const __nv_bfloat16*)up,
+                                                                           (__nv_bfloat16*)out, n8);
+    SVR2_CHECK_LAUNCH("svr2_swiglu_fwd");
     return SVR2_OK;
 }

@@ -72,6 +72,23 @@ __device__ __forceinline__ bf16x8 pack8(const float* f) {
     return r;
 }
 
+// Element-wise bf16 product, rounded once to bf16.  The exact product of two bf16 values fits in fp32 (16 significant
+// bits), so HMUL2.BF16 equals ATen's "compute in fp32, round the result to bf16" bit for bit — at half the instructions
+// of unpack / FMUL / round.  (Additions are NOT done this way: fp32-add-then-round double-rounds, HADD2.BF16 may not.)
+__device__ __forceinline__ bf16x8 mul8(const bf16x8& a, const bf16x8& b) {
+    bf16x8 r;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) r.v[i] = __hmul2(a.v[i], b.v[i]);
+    return r;
+}
+// x / d with d's reciprocal precomputed: one Newton step on the residual gives the correctly rounded fp32 quotient
+// (the core of the IEEE division sequence without its special-case handling; operands here are finite and normal).
+__device__ __forceinline__ float div_rcp(float x, float d, float rcp) {
+    const float q = x * rcp;
+    const float r = fmaf(-q, d, x);
+    return fmaf(r, rcp, q);
+}
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

@@ -9,8 +9,10 @@
 //   concat_win (na.py:320-424)                              -> output is already the packed varlen layout
 // Output: q,k,v [P, heads, 128] bf16, sequence k = [video rows of window k (row-major t,h,w) ; Lt text rows].
 //
-// HBM-bound: reads 3*heads*256 B per packed row, writes the same.  One CTA per packed row; a half-warp owns one
-// (q|k|v, head) slice of 128 values as 16-byte vectors, so every access is a fully coalesced 256-B segment.
+// HBM-bound: reads 3*heads*256 B per packed row, writes the same.  One CTA per two packed rows; a half-warp owns up to
+// five (q|k|v, head) slices of 128 values as 16-byte vectors (every access a fully coalesced 256-B segment) and issues
+// all of its loads before any arithmetic; products that the reference rounds to bf16 use HMUL2.BF16 (exact), the
+// division is one reciprocal + a Newton step.
 #include "common.cuh"
 
 namespace svr2 {
@@ -23,101 +25,134 @@ __device__ __forceinline__ float torch_linspace_m1_p1(int idx, int n) {
                          : __fsub_rn(1.0f, __fmul_rn(step, (float)(n - idx - 1)));
 }
 
-__global__ void __launch_bounds__(128)
+constexpr int kRowsPerCta = 2;     // packed rows per CTA
+constexpr int kMaxItems = 5;       // (q|k|v, head) slices per half-warp: 16 half-warps x 5 >= 3 * 24 heads
+constexpr int kPackThreads = 256;
+
+// Per-row bookkeeping every thread derives redundantly (uniform loads of the tiny L1-resident window table).
+struct PackRow {
+    const __nv_bfloat16* src;   // qkv row of the source token (video) or text token
+    int valid, is_txt, n_rot;
+};
+
+__global__ void __launch_bounds__(kPackThreads)
 qkv_pack_kernel(const __nv_bfloat16* __restrict__ qkv_vid, const __nv_bfloat16* __restrict__ qkv_txt,
                 const __nv_bfloat16* __restrict__ wq_vid, const __nv_bfloat16* __restrict__ wk_vid,
                 const __nv_bfloat16* __restrict__ wq_txt, const __nv_bfloat16* __restrict__ wk_txt,
                 const float* __restrict__ freqs, int n_freqs, int rope_kind, const int32_t* __restrict__ tab,
                 int n_windows, int H, int W, int txt_len, int heads, float eps, __nv_bfloat16* __restrict__ qp,
-                __nv_bfloat16* __restrict__ kp, __nv_bfloat16* __restrict__ vp) {
-    __shared__ float s_cos[64], s_sin[64];
-    const int row = blockIdx.x;
-    // window of this packed row: last window whose row_start <= row (uniform across the CTA, table is L1/L2 resident)
-    int lo = 0, hi = n_windows - 1;
-    while (lo < hi) {
-        const int mid = (lo + hi + 1) >> 1;
-        if (__ldg(tab + mid * SVR2_WIN_FIELDS + 6) <= row) lo = mid; else hi = mid - 1;
-    }
-    const Win w = load_win(tab, lo);
-    const int j = row - w.row_start;
-    const bool is_txt = j >= w.n_vid;
-    int lt = 0, lh = 0, lw = 0;
-    const __nv_bfloat16* src;
-    if (is_txt) {
-        src = qkv_txt + (int64_t)(j - w.n_vid) * 3 * heads * SVR2_HEAD_DIM;
-    } else {
-        const int64_t tok = win_token(w, j, H, W, &lt, &lh, &lw);
-        src = qkv_vid + tok * 3 * heads * SVR2_HEAD_DIM;
-    }
-    const int n_rot_pairs = (rope_kind == SVR2_ROPE_3B_MM || (rope_kind == SVR2_ROPE_7B_PIX && !is_txt)) ? 3 * n_freqs : 0;
-    if (threadIdx.x < 64) {
-        const int p = threadIdx.x;
-        float c = 1.f, s = 0.f;
-        if (p < n_rot_pairs) {
-            const int axis = p / n_freqs, fi = p - axis * n_freqs;
-            const float f = __ldg(freqs + fi);
-            if (rope_kind == SVR2_ROPE_3B_MM) {
-                // video: positions (Lt + t, h, w) inside the window (rope.py:172); text row r: (r, r, r) (rope.py:173)
-                const int pos = is_txt ? (j - w.n_vid) : (axis == 0 ? txt_len + lt : (axis == 1 ? lh : lw));
-                const float ang = __fmul_rn((float)pos, f);
-                c = cosf(ang);
-                s = sinf(ang);
-            } else {
-                // 7B: linspace(-1,1,n) over the window's own extent; the angle AND cos/sin are bf16 tensors
-                // (freqs.to(q.dtype), dit_7b/rope.py:85; freqs.cos() of a bf16 tensor is bf16)
-                const int n = axis == 0 ? w.nt : (axis == 1 ? w.nh : w.nw);
-                const int idx = axis == 0 ? lt : (axis == 1 ? lh : lw);
-                const float ang = bf16r(__fmul_rn(torch_linspace_m1_p1(idx, n), f));
-                c = bf16r(cosf(ang));
-                s = bf16r(sinf(ang));
-            }
+                __nv_bfloat16* __restrict__ kp, __nv_bfloat16* __restrict__ vp, int64_t P) {
+    __shared__ float s_cos[kRowsPerCta][64], s_sin[kRowsPerCta][64];
+    const int hl = threadIdx.x & 15;              // lane inside the half-warp: owns elements [8*hl, 8*hl+8)
+    const int hw_id = threadIdx.x >> 4;           // 16 half-warps per CTA
+    const int col = hl * 8;
+    const int n_items = 3 * heads;                // item = kind * heads + head; source offset = item * 128
+    const int64_t qkv_stride = (int64_t)n_items * SVR2_HEAD_DIM;
+
+    PackRow pr[kRowsPerCta];
+    bf16x8 raw[kRowsPerCta][kMaxItems];
+#pragma unroll
+    for (int r = 0; r < kRowsPerCta; ++r) {
+        const int64_t row = (int64_t)blockIdx.x * kRowsPerCta + r;
+        pr[r].valid = row < P;
+        pr[r].is_txt = 0; pr[r].n_rot = 0; pr[r].src = qkv_vid;
+        if (!pr[r].valid) continue;
+        // window of this packed row: last window whose row_start <= row
+        int lo = 0, hi = n_windows - 1;
+        while (lo < hi) {
+            const int mid = (lo + hi + 1) >> 1;
+            if (__ldg(tab + mid * SVR2_WIN_FIELDS + 6) <= row) lo = mid; else hi = mid - 1;
         }
-        s_cos[p] = c;
-        s_sin[p] = s;
+        const Win w = load_win(tab, lo);
+        const int j = (int)row - w.row_start;
+        const bool is_txt = j >= w.n_vid;
+        int lt = 0, lh = 0, lw = 0;
+        if (is_txt) {
+            pr[r].src = qkv_txt + (int64_t)(j - w.n_vid) * qkv_stride;
+        } else {
+            pr[r].src = qkv_vid + win_token(w, j, H, W, &lt, &lh, &lw) * qkv_stride;
+        }
+        pr[r].is_txt = is_txt;
+        pr[r].n_rot = (rope_kind == SVR2_ROPE_3B_MM || (rope_kind == SVR2_ROPE_7B_PIX && !is_txt)) ? 3 * n_freqs : 0;
+        // all of this thread's loads for the row go out before any arithmetic
+#pragma unroll
+        for (int it = 0; it < kMaxItems; ++it) {
+            const int item = hw_id + it * 16;
+            if (item < n_items) raw[r][it] = ldg8_stream(pr[r].src + item * SVR2_HEAD_DIM + col);
+        }
+        // cos/sin of the row's rotary pairs: threads [64r, 64r+64) — overlaps the loads above
+        const int p = (int)threadIdx.x - 64 * r;
+        if (p >= 0 && p < 64) {
+            float c = 1.f, sn = 0.f;
+            if (p < pr[r].n_rot) {
+                const int axis = p / n_freqs, fi = p - axis * n_freqs;
+                const float f = __ldg(freqs + fi);
+                if (rope_kind == SVR2_ROPE_3B_MM) {
+                    // video: positions (Lt + t, h, w) inside the window (rope.py:172); text row r: (r, r, r) (rope.py:173)
+                    const int pos = is_txt ? (j - w.n_vid) : (axis == 0 ? txt_len + lt : (axis == 1 ? lh : lw));
+                    const float ang = __fmul_rn((float)pos, f);
+                    c = cosf(ang);
+                    sn = sinf(ang);
+                } else {
+                    // 7B: linspace(-1,1,n) over the window's own extent; the angle AND cos/sin are bf16 tensors
+                    // (freqs.to(q.dtype), dit_7b/rope.py:85; freqs.cos() of a bf16 tensor is bf16)
+                    const int n = axis == 0 ? w.nt : (axis == 1 ? w.nh : w.nw);
+                    const int idx = axis == 0 ? lt : (axis == 1 ? lh : lw);
+                    const float ang = bf16r(__fmul_rn(torch_linspace_m1_p1(idx, n), f));
+                    c = bf16r(cosf(ang));
+                    sn = bf16r(sinf(ang));
+                }
+            }
+            s_cos[r][p] = c;        // pairs beyond n_rot rotate by (1, 0): identity, branch-free below
+            s_sin[r][p] = sn;
+        }
     }
     __syncthreads();
 
-    const int hl = threadIdx.x & 15;              // lane inside the half-warp: owns elements [8*hl, 8*hl+8)
-    const int hw_id = threadIdx.x >> 4;           // 8 half-warps per CTA
-    const int col = hl * 8;
     const unsigned half_mask = 0xFFFFu << (threadIdx.x & 16);
-    float wq[8], wk[8];
-    unpack8(ldg8((is_txt ? wq_txt : wq_vid) + col), wq);
-    unpack8(ldg8((is_txt ? wk_txt : wk_vid) + col), wk);
-    const int64_t drow = (int64_t)row * heads * SVR2_HEAD_DIM;
-    const int n_items = 3 * heads;                // item = kind * heads + head; source offset = item * 128
-    for (int it = hw_id; it < n_items; it += 8) {
-        const int kind = it / heads, head = it - kind * heads;
-        const bf16x8 raw = ldg8_stream(src + it * SVR2_HEAD_DIM + col);
-        __nv_bfloat16* dst = (kind == 0 ? qp : (kind == 1 ? kp : vp)) + drow + head * SVR2_HEAD_DIM + col;
-        if (kind == 2) {                          // v: gather only
-            stg8(dst, raw);
-            continue;
-        }
-        float x[8];
-        unpack8(raw, x);
-        float ss = 0.f;
+    const bf16x8 wqv = ldg8(wq_vid + col), wkv = ldg8(wk_vid + col);
+    const bf16x8 wqt = txt_len ? ldg8(wq_txt + col) : wqv, wkt = txt_len ? ldg8(wk_txt + col) : wkv;
 #pragma unroll
-        for (int i = 0; i < 8; ++i) ss += bf16r(x[i] * x[i]);
+    for (int r = 0; r < kRowsPerCta; ++r) {
+        if (!pr[r].valid) continue;              // uniform across the CTA
+        const int64_t drow = ((int64_t)blockIdx.x * kRowsPerCta + r) * heads * SVR2_HEAD_DIM;
+        float cs[4], sn[4];
 #pragma unroll
-        for (int o = 8; o > 0; o >>= 1) ss += __shfl_xor_sync(half_mask, ss, o);     // the two halves may diverge
-        const float var = bf16r(ss * (1.0f / SVR2_HEAD_DIM));
-        const float rms = bf16r(sqrtf(bf16r(var + eps)));
-        const float* wgt = kind == 0 ? wq : wk;
+        for (int i = 0; i < 4; ++i) { cs[i] = s_cos[r][hl * 4 + i]; sn[i] = s_sin[r][hl * 4 + i]; }
 #pragma unroll
-        for (int i = 0; i < 8; ++i) x[i] = bf16r(bf16r(__fdiv_rn(x[i], rms)) * wgt[i]);
-        // interleaved-pair rotation in fp32, mul and add rounded separately like the two ATen ops
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-            const int p = hl * 4 + i;
-            if (p < n_rot_pairs) {
-                const float c = s_cos[p], s = s_sin[p];
-                const float x0 = x[2 * i], x1 = x[2 * i + 1];
-                x[2 * i] = __fadd_rn(__fmul_rn(x0, c), __fmul_rn(-x1, s));
-                x[2 * i + 1] = __fadd_rn(__fmul_rn(x1, c), __fmul_rn(x0, s));
+        for (int it = 0; it < kMaxItems; ++it) {
+            const int item = hw_id + it * 16;
+            if (item >= n_items) continue;       // uniform across the half-warp
+            const int kind = item / heads, head = item - kind * heads;
+            __nv_bfloat16* dst = (kind == 0 ? qp : (kind == 1 ? kp : vp)) + drow + head * SVR2_HEAD_DIM + col;
+            if (kind == 2) {                     // v: gather only
+                stg8(dst, raw[r][it]);
+                continue;
             }
+            float x[8], sq[8];
+            unpack8(raw[r][it], x);
+            unpack8(mul8(raw[r][it], raw[r][it]), sq);          // x.pow(2) is a bf16 tensor
+            float ss = 0.f;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) ss += sq[i];
+#pragma unroll
+            for (int o = 8; o > 0; o >>= 1) ss += __shfl_xor_sync(half_mask, ss, o);     // the two halves may diverge
+            const float var = bf16r(ss * (1.0f / SVR2_HEAD_DIM));
+            const float rms = bf16r(sqrtf(bf16r(var + eps)));
+            const float rcp = __frcp_rn(rms);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) x[i] = div_rcp(x[i], rms, rcp);
+            const bf16x8 wgt = kind == 0 ? (pr[r].is_txt ? wqt : wqv) : (pr[r].is_txt ? wkt : wkv);
+            unpack8(mul8(pack8(x), wgt), x);                    // (x / rms) -> bf16, * weight -> bf16
+            // interleaved-pair rotation in fp32, mul and add rounded separately like the two ATen ops
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const float x0 = x[2 * i], x1 = x[2 * i + 1];
+                x[2 * i] = __fadd_rn(__fmul_rn(x0, cs[i]), __fmul_rn(-x1, sn[i]));
+                x[2 * i + 1] = __fadd_rn(__fmul_rn(x1, cs[i]), __fmul_rn(x0, sn[i]));
+            }
+            stg8(dst, pack8(x));
         }
-        stg8(dst, pack8(x));
     }
 }
 
@@ -135,11 +170,13 @@ extern "C" int svr2_qkv_pack_fwd(const void* qkv_vid, const void* qkv_txt, const
     SVR2_CHECK_ARG(rope_kind == SVR2_ROPE_NONE || (freqs && n_freqs > 0 && 3 * n_freqs <= 64),
                    "svr2_qkv_pack_fwd: need 0 < 3*n_freqs <= 64 rotary pairs (got n_freqs=%d)", n_freqs);
     (void)T;
-    svr2::qkv_pack_kernel<<<(unsigned)P, 128, 0, (cudaStream_t)stream>>>(
+    SVR2_CHECK_ARG(3 * heads <= 16 * svr2::kMaxItems, "svr2_qkv_pack_fwd: at most %d heads", 16 * svr2::kMaxItems / 3);
+    const unsigned grid = (unsigned)((P + svr2::kRowsPerCta - 1) / svr2::kRowsPerCta);
+    svr2::qkv_pack_kernel<<<grid, svr2::kPackThreads, 0, (cudaStream_t)stream>>>(
         (const __nv_bfloat16*)qkv_vid, (const __nv_bfloat16*)qkv_txt, (const __nv_bfloat16*)wq_vid,
         (const __nv_bfloat16*)wk_vid, (const __nv_bfloat16*)wq_txt, (const __nv_bfloat16*)wk_txt, freqs, n_freqs,
         rope_kind, win_table, n_windows, H, W, txt_len, heads, eps, (__nv_bfloat16*)q_pack, (__nv_bfloat16*)k_pack,
-        (__nv_bfloat16*)v_pack);
+        (__nv_bfloat16*)v_pack, P);
     SVR2_CHECK_LAUNCH("svr2_qkv_pack_fwd");
     return SVR2_OK;
 }

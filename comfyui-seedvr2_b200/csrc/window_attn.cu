@@ -53,7 +53,19 @@ struct Params {
     int H, W, txt_len, heads;
     __nv_bfloat16* out_vid;
     __nv_bfloat16* txt_part;
+    long long* trace;      // debug timeline (svr2_debug_attn_trace): kTraceSlots clock64 stamps per CTA, or nullptr
+    int trace_ctas;
 };
+
+constexpr int kTraceSlots = 64;
+// slot map: 0 entry, 1 setup done, 2 Q+K0 landed (MMA warp), 3 O final seen (group 0), 4 epilogue stores issued (group 0),
+// 5 CTA end, 6 smid, 7 n_kv, 8+j S(j) ready seen by group 0, 24+j P(j) published by group 0, 40+j group-1 S(j) ready
+__device__ __forceinline__ void trace_stamp(const Params& p, int slot) {
+    if (p.trace != nullptr) {
+        const int cta = blockIdx.y * gridDim.x + blockIdx.x;
+        if (cta < p.trace_ctas && slot < kTraceSlots) p.trace[(long long)cta * kTraceSlots + slot] = clock64();
+    }
+}
 
 __device__ __forceinline__ uint32_t pack2(float lo, float hi) {
     __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
@@ -88,6 +100,7 @@ window_attn_tc_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
     const int n_kv = (seq + BN - 1) / BN;
 
     if (threadIdx.x == 0) {
+        trace_stamp(p, 0);
         for (int i = 0; i < 2; ++i) {
             mbar_init(bar(BAR_QFULL + i), 1);
             mbar_init(bar(BAR_SFULL + i), 1);
@@ -110,6 +123,18 @@ window_attn_tc_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem = *tmem_slot;
+    if (threadIdx.x == 0) {
+        trace_stamp(p, 1);
+        if (p.trace != nullptr) {
+            const int cta = blockIdx.y * gridDim.x + blockIdx.x;
+            if (cta < p.trace_ctas) {
+                unsigned smid;
+                asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+                p.trace[(long long)cta * kTraceSlots + 6] = smid;
+                p.trace[(long long)cta * kTraceSlots + 7] = n_kv;
+            }
+        }
+    }
 
     if (warp == 8) {
         // ------------------------------------------------------------------ TMA producer
@@ -152,6 +177,7 @@ window_attn_tc_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
             for (int i = 0; i < nq; ++i) mbar_wait(bar(BAR_QFULL + i), 0);
             mbar_wait(bar(BAR_KVFULL + 0), 0);
             tc_fence_after();
+            trace_stamp(p, 2);
             for (int i = 0; i < nq; ++i) {
                 issue_qk(i, sRing);
                 tc_commit(bar(BAR_SFULL + i));
@@ -187,6 +213,7 @@ window_attn_tc_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
         for (int j = 0; j < n_kv; ++j) {
             mbar_wait(bar(BAR_SFULL + i), j & 1);
             tc_fence_after();
+            if ((threadIdx.x & 127) == 0 && j < 16) trace_stamp(p, (i == 0 ? 8 : 40) + j);
             uint32_t sv[128];
             tmem_ld32(tS, sv);
             tmem_ld32(tS + 32, sv + 32);
@@ -243,10 +270,12 @@ window_attn_tc_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
             tc_wait_st();
             tc_fence_before();
             mbar_arrive(bar(BAR_PREADY + i));
+            if (threadIdx.x == 0 && j < 16) trace_stamp(p, 24 + j);
         }
         // ---- epilogue: O_i / l -> bf16 -> swizzled staging tile (the Q_i buffer) -> coalesced 256-B row stores
         mbar_wait(bar(BAR_OFINAL + i), 0);
         tc_fence_after();
+        if (threadIdx.x == 0) trace_stamp(p, 3);
         const float inv = 1.0f / l;
         unsigned char* stage = gbase + i * TILE_BYTES;
 #pragma unroll
@@ -286,9 +315,11 @@ window_attn_tc_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
             const uint4 u = *reinterpret_cast<const uint4*>(stage + r * 256 + (((ch & 8) | ((ch ^ r) & 7)) << 4));
             if (d != 0ull) *reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(d) + ch * 8) = u;
         }
+        if (threadIdx.x == 0) trace_stamp(p, 4);
     }
     tc_fence_before();
     __syncthreads();
+    if (threadIdx.x == 0) trace_stamp(p, 5);
     if (warp == 9) {
         __syncwarp();
         tmem_dealloc(tmem, TMEM_COLS);
@@ -339,6 +370,9 @@ int make_tmap(CUtensorMap* m, const void* ptr, int64_t P, int heads) {
     return SVR2_OK;
 }
 
+long long* g_trace = nullptr;
+int g_trace_ctas = 0;
+
 int launch_window_attn_tc(const void* q, const void* k, const void* v, const int32_t* tab, const int32_t* work,
                           int n_work, int H, int W, int txt_len, int heads, int64_t P, void* out_vid, void* txt_part,
                           cudaStream_t st) {
@@ -360,6 +394,7 @@ int launch_window_attn_tc(const void* q, const void* k, const void* v, const int
     tc_attn::Params p;
     p.tab = tab; p.work = work; p.H = H; p.W = W; p.txt_len = txt_len; p.heads = heads;
     p.out_vid = (__nv_bfloat16*)out_vid; p.txt_part = (__nv_bfloat16*)txt_part;
+    p.trace = g_trace; p.trace_ctas = g_trace_ctas;
     dim3 grid(n_work, heads);
     tc_attn::window_attn_tc_kernel<<<grid, tc_attn::NTHREADS, tc_attn::SMEM_BYTES, st>>>(tq, tk, tv, p);
     SVR2_CHECK_LAUNCH("svr2_window_attn_fwd(tcgen05)");
@@ -374,6 +409,13 @@ int launch_window_attn_tc(const void* q, const void* k, const void* v, const int
 
 #include <algorithm>
 #include <vector>
+
+namespace svr2 { namespace { extern long long* g_trace; extern int g_trace_ctas; } }
+extern "C" int svr2_debug_attn_trace(void* trace_buf, int n_ctas) {
+    svr2::g_trace = (long long*)trace_buf;
+    svr2::g_trace_ctas = trace_buf ? n_ctas : 0;
+    return svr2::tc_attn::kTraceSlots;
+}
 
 extern "C" int svr2_window_attn_worklist(const int32_t* win_table_host, int n_windows, int txt_len, int32_t* work,
                                          int max_items, int64_t* n_items) {

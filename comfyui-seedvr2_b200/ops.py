@@ -134,6 +134,19 @@ def gate_residual_modnorm(h: torch.Tensor, resid: torch.Tensor, emb: torch.Tenso
 
 
 @torch._dynamo.disable
+def swiglu(gate: torch.Tensor, up: torch.Tensor) -> torch.Tensor:
+    """silu(gate) * up (reference mlp.py:60-62), one pass."""
+    _need(gate, "gate"); _need(up, "up")
+    if gate.shape != up.shape:
+        raise RuntimeError("swiglu: shape mismatch")
+    out = torch.empty_like(gate)
+    if gate.numel():
+        _call("svr2_swiglu_fwd", 1, gate.device, _lib.lib().svr2_swiglu_fwd, gate.data_ptr(), up.data_ptr(), out.data_ptr(),
+              gate.numel(), _stream(gate))
+    return out
+
+
+@torch._dynamo.disable
 def qkv_pack(plan: WindowPlan, qkv_vid: torch.Tensor, qkv_txt: torch.Tensor, wq_vid, wk_vid, wq_txt, wk_txt,
              freqs: Optional[torch.Tensor], rope_kind: int, heads: int, eps: float):
     """-> (q, k, v) packed [P, heads, 128] bf16: q/k RMSNorm + RoPE + window partition + text interleave."""

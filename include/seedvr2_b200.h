@@ -84,6 +84,13 @@ int svr2_gate_residual_modnorm_fwd(const void* h, const void* resid, const void*
                                    int64_t L, int D, int layer, float eps, void* stream);
 
 /*
+ * SwiGLU activation:  out = silu(gate) * up, silu rounded to bf16 before the product.
+ * Replaces `F.silu(self.proj_in_gate(x)) * self.proj_in(x)` (src/models/dit_3b/mlp.py:60-62) — two ATen kernels.
+ * gate/up/out bf16, n elements (multiple of 8), out may alias gate or up.
+ */
+int svr2_swiglu_fwd(const void* gate, const void* up, void* out, int64_t n, void* stream);
+
+/*
  * q/k RMSNorm (affine, per head) + 3D RoPE + window partition + text interleave, one pass over qkv.
  * Replaces window_partition index_select (na.py:637, mmattn.py:199), norm_q/norm_k (mmattn.py:207-208,
  * normalization.py:88-109), the text repeat (mmattn.py:223-236), RoPE (dit_3b/rope.py:92-127, dit_7b/rope.py:73-91 +
@@ -118,6 +125,13 @@ int svr2_window_attn_worklist(const int32_t* win_table_host, int n_windows, int 
 int svr2_window_attn_fwd(const void* q_pack, const void* k_pack, const void* v_pack, const int32_t* win_table,
                          const int32_t* work, int n_work, int n_windows, int T, int H, int W, int txt_len, int heads,
                          int64_t P, void* out_vid, void* txt_part, void* out_txt, void* stream);
+
+/*
+ * Debug hook (no reference counterpart): point the attention kernel at a device buffer of n_ctas * 64 int64 slots and
+ * every CTA records clock64 stamps of its pipeline phases (slot map in csrc/window_attn.cu).  NULL switches it off.
+ * Returns the number of slots per CTA.  Used by scripts/attn_trace.py to read the per-CTA timeline.
+ */
+int svr2_debug_attn_trace(void* trace_buf, int n_ctas);
 
 /*
  * Text pooling on its own: out_txt[j] = mean over windows of txt_part[w, j]  (na.py:414 — unconcat_coalesce's

@@ -87,6 +87,18 @@ def test_gate_residual(svr2, cuda, L, D):
     _close_bf16(y, oblock.ada_in(oblock.rmsnorm(ref_out, 1e-5), emb, 1, shift, scale), "fused modnorm")
 
 
+@pytest.mark.parametrize("L,Hd", [(58, 6912), (1000, 6912), (3, 8), (4099, 256)])
+def test_swiglu(svr2, cuda, L, Hd):
+    """silu(gate) * up vs the reference's two bf16 ATen ops (mlp.py:60-62).  The kernel uses ex2.approx / fast division, so
+    a bf16 rounding may flip on a few elements: <= 1 bf16 ulp, < 0.1 % of elements."""
+    g = torch.Generator().manual_seed(L)
+    a = (2 * torch.randn(L, Hd, generator=g)).bfloat16().to(cuda)
+    b = torch.randn(L, Hd, generator=g).bfloat16().to(cuda)
+    out = svr2.ops.swiglu(a, b)
+    ref = F.silu(a) * b
+    _close_bf16(out, ref, "swiglu", max_ulp_frac=1e-3)
+
+
 # ----------------------------------------------------------------------------------------------- qkv pack
 def _pack_case(model, grid, shifted, heads, seed, txt_len=cases.TXT_LEN):
     g = torch.Generator().manual_seed(seed)

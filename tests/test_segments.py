@@ -1,0 +1,73 @@
+"""Temporal-segment partitioner (comfyui-seedvr2_b200/segments.py): integer split arithmetic vs the oracle restatement of
+inference_cli.py:1087-1135, and the halo exchange + gather over a world-size-2/3 gloo group on CPU (host logic only: the
+crossfade itself is injected — the CUDA kernel svr2_halo_blend is checked in tests/test_gpu_kernels.py)."""
+import os
+import socket
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from oracle import partition
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+@pytest.mark.parametrize("total,n,overlap", [(121, 8, 4), (121, 2, 4), (33, 4, 0), (7, 8, 2), (100, 3, 3), (1, 1, 4), (240, 8, 4)])
+def test_segment_ranges_match_oracle(svr2, total, n, overlap):
+    from seedvr2_b200 import segments
+    assert segments.segment_ranges(total, n, overlap, 5) == partition.segment_ranges(total, n, overlap, 5)
+    r = segments.segment_ranges(total, n, overlap)
+    owned = [b - a - (overlap if i < n - 1 and b - a > 0 else 0) for i, (a, b) in enumerate(r)]
+    assert r[0][0] == 0 and r[-1][1] == total
+    assert all(r[i + 1][0] <= r[i][1] for i in range(n - 1))
+
+
+def test_preloaded_chunks(svr2):
+    from seedvr2_b200 import segments
+    # inference_cli.py:1118-1135 by hand: total 100, 4 ranks, overlap 4, batch 5 -> chunk = ceil((25+4)/5)*5 = 30, stride 26
+    assert segments.chunk_ranges_preloaded(100, 4, 4, 5) == [(0, 30), (26, 56), (52, 82), (78, 100)]
+    assert segments.chunk_ranges_preloaded(10, 3, 0) == [(0, 4), (4, 8), (8, 10)]          # torch.chunk
+    assert [segments.padded_batch_frames(n) for n in (1, 2, 5, 19, 20, 21, 33)] == [1, 5, 5, 21, 21, 21, 33]
+
+
+def _worker(rank, world, port, lens, overlap, out_path):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    import seedvr2_b200  # noqa: F401
+    from seedvr2_b200 import segments
+    g = torch.Generator().manual_seed(100 + rank)
+    frames = torch.rand(lens[rank], 6, 8, 3, generator=g)
+    out = segments.halo_exchange_and_gather(frames.clone(), overlap, blend=partition.blend)
+    if rank == 0:
+        torch.save(out, out_path)
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("lens,overlap", [([12, 9], 4), ([10, 8, 9], 3), ([12, 9], 0), ([5, 9, 6], 4), ([9, 2, 9], 4)])
+def test_halo_exchange_gloo(svr2, tmp_path, lens, overlap):
+    """World size 2 and 3 on CPU/gloo: the distributed stitch equals the reference parent loop (oracle.partition.stitch) on
+    the same per-rank chunks, including the short-segment cases that fall back to the sequential order."""
+    world = len(lens)
+    ctx = mp.get_context("spawn")
+    out_path = str(tmp_path / "stitched.pt")
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, world, port, lens, overlap, out_path)) for r in range(world)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(timeout=120)
+        assert p.exitcode == 0
+    got = torch.load(out_path)
+    chunks = [torch.rand(n, 6, 8, 3, generator=torch.Generator().manual_seed(100 + r)) for r, n in enumerate(lens)]
+    ref = partition.stitch(chunks, overlap)
+    assert got.shape == ref.shape
+    assert torch.equal(got, ref)
