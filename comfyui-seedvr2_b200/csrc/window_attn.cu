@@ -331,6 +331,12 @@ window_attn_tc_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
 
 // ------------------------------------------------------------------------------------------------ host side
 namespace svr2 {
+long long* g_trace = nullptr;      // svr2_debug_attn_trace
+int g_trace_ctas = 0;
+int make_tmap(CUtensorMap* m, const void* ptr, int64_t P, int heads);
+int launch_window_attn_tc2(const void* q, const void* k, const void* v, const int32_t* tab, const int32_t* work,
+                           int n_work, int H, int W, int txt_len, int heads, int64_t P, void* out_vid, void* txt_part,
+                           cudaStream_t st);
 namespace {
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
@@ -348,6 +354,8 @@ EncodeTiledFn get_encode_fn() {
     }
     return fn;
 }
+
+}  // namespace
 
 // [P, heads, 128] bf16 viewed as a 3-D tensor (d, head, row); box = 64 d x 1 head x 128 rows, 128-byte swizzle.
 int make_tmap(CUtensorMap* m, const void* ptr, int64_t P, int heads) {
@@ -370,8 +378,7 @@ int make_tmap(CUtensorMap* m, const void* ptr, int64_t P, int heads) {
     return SVR2_OK;
 }
 
-long long* g_trace = nullptr;
-int g_trace_ctas = 0;
+namespace {
 
 int launch_window_attn_tc(const void* q, const void* k, const void* v, const int32_t* tab, const int32_t* work,
                           int n_work, int H, int W, int txt_len, int heads, int64_t P, void* out_vid, void* txt_part,
@@ -410,7 +417,6 @@ int launch_window_attn_tc(const void* q, const void* k, const void* v, const int
 #include <algorithm>
 #include <vector>
 
-namespace svr2 { namespace { extern long long* g_trace; extern int g_trace_ctas; } }
 extern "C" int svr2_debug_attn_trace(void* trace_buf, int n_ctas) {
     svr2::g_trace = (long long*)trace_buf;
     svr2::g_trace_ctas = trace_buf ? n_ctas : 0;
@@ -447,12 +453,15 @@ extern "C" int svr2_window_attn_fwd(const void* q_pack, const void* k_pack, cons
                    "svr2_window_attn_fwd: bad sizes");
     (void)T;
     cudaStream_t st = (cudaStream_t)stream;
-    // SVR2_ATTN_IMPL=mma selects the legacy mma.sync comparator (bring-up / A-B debugging only).
+    // Product path: the persistent tcgen05 kernel (window_attn_v2.cu).  SVR2_ATTN_IMPL=v1 selects the first-generation
+    // one-CTA-per-item tcgen05 kernel and =mma the legacy mma.sync comparator — A/B debugging aids only, both CUDA.
     const char* e = getenv("SVR2_ATTN_IMPL");
-    const int impl = (e && strcmp(e, "mma") == 0) ? 1 : 0;
+    const int impl = (e && strcmp(e, "mma") == 0) ? 1 : ((e && strcmp(e, "v1") == 0) ? 2 : 0);
     int rc = impl == 1
                  ? svr2::launch_window_attn_mma(q_pack, k_pack, v_pack, win_table, work, n_work, H, W, txt_len, heads, out_vid, txt_part, st)
-                 : svr2::launch_window_attn_tc(q_pack, k_pack, v_pack, win_table, work, n_work, H, W, txt_len, heads, P, out_vid, txt_part, st);
+             : impl == 2
+                 ? svr2::launch_window_attn_tc(q_pack, k_pack, v_pack, win_table, work, n_work, H, W, txt_len, heads, P, out_vid, txt_part, st)
+                 : svr2::launch_window_attn_tc2(q_pack, k_pack, v_pack, win_table, work, n_work, H, W, txt_len, heads, P, out_vid, txt_part, st);
     if (rc != SVR2_OK) return rc;
     if (out_txt == nullptr) return SVR2_OK;      // caller pools the text rows itself with svr2_txt_pool_fwd
     return svr2::launch_txt_pool(txt_part, out_txt, n_windows, txt_len, heads, st);
