@@ -11,8 +11,8 @@
 //
 // Work item = (window, pair of 128-row query tiles, head); items are sorted longest sequence first and CTA b takes
 // items b, b+G, b+2G, ...   Roles (14 warps, 448 threads):
-//   warps 0-3   softmax group 0 (query tile 0): one thread per query row; S is read from TMEM twice in 32-column chunks
-//               (pass 1 row max, pass 2 exp2 + bf16 P written back over S) so no thread ever holds a whole row
+//   warps 0-3   softmax group 0 (query tile 0): one thread per query row; S is read from TMEM ONCE in 32-column chunks
+//               (exp2 against a lagging reference max + bf16 P written back over S) so no thread ever holds a whole row
 //   warps 4-7   softmax group 1 (query tile 1)
 //   warps 8-11  epilogue: O/l -> bf16 -> swizzled staging tile -> coalesced 256-B row stores to the token's ORIGINAL
 //               position (window reverse) or the per-window text buffer; frees O for the next item as soon as it is read
@@ -46,7 +46,8 @@ constexpr int OFF_BAR = OFF_L + 2 * 2 * 128 * 4;
 constexpr int SMEM_BYTES = OFF_BAR + 256;              // 231,680 B of the 232,448 B a CTA may opt in to
 constexpr uint32_t TMEM_COLS = 512;
 constexpr float kScaleLog2 = 0.08838834764831845f * 1.4426950408889634f;   // 1/sqrt(128) * log2(e)
-constexpr float kRescaleThreshold = 8.0f;   // lazy rescale: tolerate P up to 2^8 before touching O
+constexpr float kRescaleThreshold = 8.0f;   // lazy rescale: the reference lags the running max by up to 2^8 between tiles
+constexpr float kMaxExponent = 100.0f;      // P <= 2^100: a row can never overflow bf16 / the fp32 sums (128 * 2^100 << 2^127)
 
 // barrier slots (8 bytes each)
 enum { BAR_QFULL = 0, BAR_QEMPTY = 2, BAR_SFULL = 4, BAR_PREADY = 6, BAR_OFINAL = 8, BAR_OEMPTY = 10, BAR_LREADY = 12,
@@ -63,7 +64,15 @@ struct Params {
     long long* trace;      // debug timeline (svr2_debug_attn_trace) or nullptr
     int trace_ctas;
 };
-constexpr int kTraceSlots = 64;   // 0 entry, 1 setup done, 5 end, 6 smid, 7 items done, 8+n: MMA thread starts item n (n < 56)
+// 0 entry, 1 setup done, 5 end, 6 smid, 7 items done; for the CTA's first kTraceItems items n, at 8 + 9n:
+// +0 MMA thread starts the item (Q and K0 landed)   +1 softmax-0 sees S(0)   +2 softmax-0 published P(0)
+// +3 softmax-0 sees S(last)   +4 softmax-0 published P(last)   +5 epilogue sees O_0 final   +6 tile-0 stores issued
+// +7 tile-1 stores issued   +8 TMA thread issued the item's last K/V load
+constexpr int kTraceSlots = 64, kTraceItems = 4;
+// fine stamps of item 2, key tile 1 (steady state): 44-51 softmax-0 thread 0 (S seen, chunk-0 landed, after chunks 0..3, after
+// wait::st, after arrive), 52-55 MMA thread (P0 ready, tile-0 MMAs issued, P1 ready, tile-1 MMAs issued), 56-58 epilogue tile 0
+// (O final seen, staged, stored)
+#define SVR2_FINE(slot) do { if (p.trace != nullptr && fine) trace_at(p, slot, clock64()); } while (0)
 
 // Everything a role needs to know about one work item; every role decodes it identically.
 struct Item {
@@ -114,38 +123,78 @@ __device__ __forceinline__ float chunk_max(const uint32_t* v, int n_valid) {
     }
     return fmaxf(fmaxf(m0, m1), fmaxf(m2, m3));
 }
-// P = exp2(s * k - mb) for one chunk, packed to bf16 pairs; returns the chunk's row sum
-__device__ __forceinline__ float chunk_exp(const uint32_t* v, uint32_t* pk, float mb, int n_valid) {
+// packed fp32 pairs (Blackwell FFMA2 / FADD2): two lanes of arithmetic per issue slot
+__device__ __forceinline__ uint64_t pack_f2(float lo, float hi) {
+    uint64_t r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ void unpack_f2(uint64_t v, float& lo, float& hi) {
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ uint64_t fma_f2(uint64_t a, uint64_t b, uint64_t c) {
+    uint64_t d;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+    return d;
+}
+__device__ __forceinline__ uint64_t add_f2(uint64_t a, uint64_t b) {
+    uint64_t d;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+    return d;
+}
+
+// P = exp2(s * k - mb) for one full chunk, packed to bf16 pairs; returns the chunk's row sum.  3 issue slots per element:
+// FFMA2 (half), MUFU.EX2, F2FP (half), FADD2 (half) + the FMNMX3 (half) of chunk_max.  The caller guarantees
+// s * k - mb <= kMaxExponent for every element (warp vote on the chunk max), so there is no per-element clamp.
+__device__ __forceinline__ float chunk_exp(const uint32_t* v, uint32_t* pk, float mb) {
+    const uint64_t kk = pack_f2(kScaleLog2, kScaleLog2), nmb = pack_f2(-mb, -mb);
+    uint64_t acc0 = pack_f2(0.f, 0.f), acc1 = acc0;
+#pragma unroll
+    for (int c = 0; c < 16; c += 2) {
+        float x0, x1, x2, x3;
+        unpack_f2(fma_f2(pack_f2(__uint_as_float(v[2 * c]), __uint_as_float(v[2 * c + 1])), kk, nmb), x0, x1);
+        unpack_f2(fma_f2(pack_f2(__uint_as_float(v[2 * c + 2]), __uint_as_float(v[2 * c + 3])), kk, nmb), x2, x3);
+        const float p0 = ex2(x0), p1 = ex2(x1), p2 = ex2(x2), p3 = ex2(x3);
+        pk[c] = pack2(p0, p1);
+        pk[c + 1] = pack2(p2, p3);
+        acc0 = add_f2(acc0, pack_f2(p0, p1));
+        acc1 = add_f2(acc1, pack_f2(p2, p3));
+    }
+    float s0, s1;
+    unpack_f2(add_f2(acc0, acc1), s0, s1);
+    return s0 + s1;
+}
+// The rare general form: columns >= n_valid masked to zero (last chunk of a sequence) and the exponent clamped.
+__device__ __forceinline__ float chunk_exp_slow(const uint32_t* v, uint32_t* pk, float mb, int n_valid) {
     float r0 = 0.f, r1 = 0.f;
-    if (n_valid >= 32) {
 #pragma unroll
-        for (int c = 0; c < 16; ++c) {
-            const float p0 = ex2(fmaf(__uint_as_float(v[2 * c]), kScaleLog2, -mb));
-            const float p1 = ex2(fmaf(__uint_as_float(v[2 * c + 1]), kScaleLog2, -mb));
-            r0 += p0;
-            r1 += p1;
-            pk[c] = pack2(p0, p1);
-        }
-    } else {
-#pragma unroll
-        for (int c = 0; c < 16; ++c) {
-            float p0 = ex2(fmaf(__uint_as_float(v[2 * c]), kScaleLog2, -mb));
-            float p1 = ex2(fmaf(__uint_as_float(v[2 * c + 1]), kScaleLog2, -mb));
-            p0 = (2 * c < n_valid) ? p0 : 0.f;
-            p1 = (2 * c + 1 < n_valid) ? p1 : 0.f;
-            r0 += p0;
-            r1 += p1;
-            pk[c] = pack2(p0, p1);
-        }
+    for (int c = 0; c < 16; ++c) {
+        float p0 = ex2(fminf(fmaf(__uint_as_float(v[2 * c]), kScaleLog2, -mb), kMaxExponent));
+        float p1 = ex2(fminf(fmaf(__uint_as_float(v[2 * c + 1]), kScaleLog2, -mb), kMaxExponent));
+        p0 = (2 * c < n_valid) ? p0 : 0.f;
+        p1 = (2 * c + 1 < n_valid) ? p1 : 0.f;
+        r0 += p0;
+        r1 += p1;
+        pk[c] = pack2(p0, p1);
     }
     return r0 + r1;
+}
+// one chunk: running max bookkeeping + P; `cm` = this chunk's row max (already masked)
+__device__ __forceinline__ float chunk_softmax(const uint32_t* v, uint32_t* pk, float mb, float cm, int n_valid) {
+    const bool danger = fmaf(cm, kScaleLog2, -mb) > kMaxExponent;       // reference lags by more than 2^100: never in practice
+    if (n_valid >= 32 && !__any_sync(0xffffffffu, danger)) return chunk_exp(v, pk, mb);
+    return chunk_exp_slow(v, pk, mb, n_valid);
 }
 
 __device__ __forceinline__ void trace_at(const Params& p, int slot, long long v) {
     if (p.trace != nullptr && (int)blockIdx.x < p.trace_ctas && slot < kTraceSlots)
         p.trace[(long long)blockIdx.x * kTraceSlots + slot] = v;
 }
+__device__ __forceinline__ void trace_item(const Params& p, int n, int what) {
+    if (p.trace != nullptr && n < kTraceItems) trace_at(p, 8 + 9 * n + what, clock64());
+}
 
+// 14 warps = 4+4+3+3 per SM sub-partition; a sub-partition's 16 K registers / 4 warps caps a thread at 128 registers
 __global__ void __launch_bounds__(NTHREADS, 1)
 window_attn_tc2_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_k,
                        const __grid_constant__ CUtensorMap tm_v, const Params p) {
@@ -201,7 +250,8 @@ window_attn_tc2_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
         // ------------------------------------------------------------------ TMA producer (runs ahead across items)
         if (lane == 0) {
             uint32_t kv_n = 0, c[2] = {0, 0};
-            for (int item = blockIdx.x; item < p.n_items; item += gridDim.x) {
+            int n_it = 0;
+            for (int item = blockIdx.x; item < p.n_items; item += gridDim.x, ++n_it) {
                 const Item it = decode_item(p, item);
                 for (int i = 0; i < it.nq; ++i) {
                     const int row = it.w.row_start + it.q0 + i * BM;
@@ -220,6 +270,7 @@ window_attn_tc2_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
                     tma_load_3d(sRing + st * TILE_BYTES, map, bar(BAR_KVFULL + st), 0, it.head, row);
                     tma_load_3d(sRing + st * TILE_BYTES + BOX_BYTES, map, bar(BAR_KVFULL + st), 64, it.head, row);
                 }
+                trace_item(p, n_it, 8);
             }
         }
     } else if (warp == 13) {
@@ -250,7 +301,7 @@ window_attn_tc2_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
                     const uint32_t st = kv_c % STAGES;
                     mbar_wait(bar(BAR_KVFULL + st), (kv_c / STAGES) & 1);
                     tc_fence_after();
-                    if (n_done < kTraceSlots - 8) trace_at(p, 8 + n_done, clock64());
+                    trace_item(p, n_done, 0);
                     for (int i = 0; i < it.nq; ++i) {
                         issue_qk(i, sRing + st * TILE_BYTES, cols(0));
                         tc_commit(bar(BAR_SFULL + i));
@@ -264,8 +315,10 @@ window_attn_tc2_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
                     const uint32_t stV = kv_c % STAGES, stK = (kv_c + 1) % STAGES;
                     mbar_wait(bar(BAR_KVFULL + stV), (kv_c / STAGES) & 1);
                     if (has_next) mbar_wait(bar(BAR_KVFULL + stK), ((kv_c + 1) / STAGES) & 1);
+                    const bool fine = n_done == 2 && j == 1;
                     for (int i = 0; i < it.nq; ++i) {
                         mbar_wait(bar(BAR_PREADY + i), s[i] & 1);
+                        SVR2_FINE(52 + 2 * i);
                         ++s[i];
                         if (j == 0) mbar_wait(bar(BAR_OEMPTY + i), (c[i] & 1) ^ 1);   // epilogue drained O_i of the previous item
                         tc_fence_after();
@@ -277,6 +330,7 @@ window_attn_tc2_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
                         } else {
                             tc_commit(bar(BAR_OFINAL + i));
                         }
+                        SVR2_FINE(53 + 2 * i);
                     }
                     tc_commit(bar(BAR_KVEMPTY + stV));
                     ++kv_c;
@@ -295,10 +349,12 @@ window_attn_tc2_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
         const uint32_t lane_off = (uint32_t)(quad * 32) << 16;
         const uint32_t tS = tmem + lane_off + i * 128, tO = tmem + lane_off + 256 + i * 128;
         uint32_t s_cnt = 0, c_cnt = 0;
+        int n_it = -1;
         for (int item = blockIdx.x; item < p.n_items; item += gridDim.x) {
             const Item it = decode_item(p, item);
+            ++n_it;
             if (i >= it.nq) continue;
-            float m = -INFINITY, l = 0.f;
+            float m = -INFINITY, m_seen = -INFINITY, l = 0.f;
             for (int j = 0; j < it.n_kv; ++j) {
                 const bool last = j == it.n_kv - 1;
                 const int n_ch = (last ? it.last_cols : BN) >> 5;         // 32-column chunks of this key tile
@@ -306,30 +362,24 @@ window_attn_tc2_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
                 mbar_wait(bar(BAR_SFULL + i), s_cnt & 1);
                 ++s_cnt;
                 tc_fence_after();
-                uint32_t a[32], b[32];
-                // ---- pass 1: row max (two chunks in flight)
-                float mx = -INFINITY;
-                tmem_ld32(tS, a);
-                if (n_ch > 1) tmem_ld32(tS + 32, b);
-                tc_wait_ld();
-                mx = chunk_max(a, valid);
-                if (n_ch > 1) mx = fmaxf(mx, chunk_max(b, valid - 32));
-                if (n_ch > 2) {
-                    tmem_ld32(tS + 64, a);
-                    if (n_ch > 3) tmem_ld32(tS + 96, b);
-                    tc_wait_ld();
-                    mx = fmaxf(mx, chunk_max(a, valid - 64));
-                    if (n_ch > 3) mx = fmaxf(mx, chunk_max(b, valid - 96));
+                if (threadIdx.x == 0) {
+                    if (j == 0) trace_item(p, n_it, 1);
+                    if (last) trace_item(p, n_it, 3);
                 }
-                // first chunk of pass 2 goes out now; the O rescale (rare) and the max bookkeeping overlap it
+                // S is read from TMEM exactly ONCE (TMEM -> registers moves 64 B/clk/SM: one 128x128 fp32 tile costs as many
+                // cycles as its two MMAs), chunk by chunk with the next chunk in flight.  The exponent reference `m` is
+                // therefore not the exact row max of this tile: it is the running max of the previous tiles (first tile:
+                // the max of its first 32 columns).  Softmax is shift invariant, bf16/fp32 precision is relative, and the
+                // exponent is clamped far below overflow, so the result is the same; the true running max `m_seen` is
+                // tracked alongside and `m` catches up lazily (rescaling O and l) once it lags by more than 2^8.
+                const bool fine = threadIdx.x == 0 && n_it == 2 && j == 1;
+                SVR2_FINE(44);
+                uint32_t a[32], b[32];
                 tmem_ld32(tS, a);
-                const float m_new = fmaxf(m, mx);
-                if (j == 0) {
-                    m = m_new;
-                } else {
-                    const bool need = (m_new - m) * kScaleLog2 > kRescaleThreshold;
+                if (j > 0) {
+                    const bool need = (m_seen - m) * kScaleLog2 > kRescaleThreshold;
                     if (__any_sync(0xffffffffu, need)) {                  // warp-uniform: tcgen05.ld/st are warp collectives
-                        const float m_use = need ? m_new : m;
+                        const float m_use = need ? m_seen : m;            // SFULL(j) implies O += P(j-1) V(j-1) has completed
                         const float alpha = ex2((m - m_use) * kScaleLog2);
                         l *= alpha;
                         m = m_use;
@@ -344,35 +394,54 @@ window_attn_tc2_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
                         }
                     }
                 }
-                const float mb = m * kScaleLog2;
-                // ---- pass 2: P = exp2(s k - m k) as bf16 over the first columns of S, chunk by chunk, next chunk in flight
                 uint32_t pk[16];
-                float rs;
+                float rs, cm;
                 tc_wait_ld();
+                SVR2_FINE(45);
                 if (n_ch > 1) tmem_ld32(tS + 32, b);
-                rs = chunk_exp(a, pk, mb, valid);
+                cm = chunk_max(a, valid);
+                if (j == 0) m = cm;
+                const float mb = m * kScaleLog2;
+                rs = chunk_softmax(a, pk, mb, cm, valid);
                 tmem_st16(tS, pk);
+                SVR2_FINE(46);
                 if (n_ch > 1) {
                     tc_wait_ld();
                     if (n_ch > 2) tmem_ld32(tS + 64, a);
-                    rs += chunk_exp(b, pk, mb, valid - 32);
+                    const float c1 = chunk_max(b, valid - 32);
+                    cm = fmaxf(cm, c1);
+                    rs += chunk_softmax(b, pk, mb, c1, valid - 32);
                     tmem_st16(tS + 16, pk);
+                    SVR2_FINE(47);
                 }
                 if (n_ch > 2) {
                     tc_wait_ld();
                     if (n_ch > 3) tmem_ld32(tS + 96, b);
-                    rs += chunk_exp(a, pk, mb, valid - 64);
+                    const float c2 = chunk_max(a, valid - 64);
+                    cm = fmaxf(cm, c2);
+                    rs += chunk_softmax(a, pk, mb, c2, valid - 64);
                     tmem_st16(tS + 32, pk);
+                    SVR2_FINE(48);
                 }
                 if (n_ch > 3) {
                     tc_wait_ld();
-                    rs += chunk_exp(b, pk, mb, valid - 96);
+                    const float c3 = chunk_max(b, valid - 96);
+                    cm = fmaxf(cm, c3);
+                    rs += chunk_softmax(b, pk, mb, c3, valid - 96);
                     tmem_st16(tS + 48, pk);
+                    SVR2_FINE(49);
                 }
+                m_seen = fmaxf(m_seen, cm);
                 l += rs;
                 tc_wait_st();
+                SVR2_FINE(50);
                 tc_fence_before();
                 mbar_arrive(bar(BAR_PREADY + i));
+                SVR2_FINE(51);
+                if (threadIdx.x == 0) {
+                    if (j == 0) trace_item(p, n_it, 2);
+                    if (last) trace_item(p, n_it, 4);
+                }
             }
             // publish the row sum for the epilogue warps (double-buffered by item parity)
             l_buf[((c_cnt & 1) * 2 + i) * 128 + row] = l;
@@ -386,13 +455,17 @@ window_attn_tc2_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
         unsigned char* stage = smem + OFF_STAGE;
         const int64_t row_stride = (int64_t)p.heads * D;
         uint32_t c[2] = {0, 0};
-        for (int item = blockIdx.x; item < p.n_items; item += gridDim.x) {
+        int n_it = 0;
+        for (int item = blockIdx.x; item < p.n_items; item += gridDim.x, ++n_it) {
             const Item it = decode_item(p, item);
             for (int i = 0; i < it.nq; ++i) {
                 const uint32_t tO = tmem + lane_off + 256 + i * 128;
                 mbar_wait(bar(BAR_LREADY + i), c[i] & 1);
                 mbar_wait(bar(BAR_OFINAL + i), c[i] & 1);
                 tc_fence_after();
+                if (threadIdx.x == 256 && i == 0) trace_item(p, n_it, 5);
+                const bool fine = threadIdx.x == 256 && i == 0 && n_it == 2;
+                SVR2_FINE(56);
                 const float inv = 1.0f / l_buf[((c[i] & 1) * 2 + i) * 128 + row];
 #pragma unroll
                 for (int c4 = 0; c4 < 4; ++c4) {
@@ -425,6 +498,7 @@ window_attn_tc2_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
                     dst = (unsigned long long)(p.txt_part + ((int64_t)it.wi * p.txt_len + (jrow - it.w.n_vid)) * row_stride + it.head * D);
                 }
                 __syncwarp();
+                SVR2_FINE(57);
                 const int ch = lane & 15;
 #pragma unroll 4
                 for (int t = 0; t < 16; ++t) {
@@ -435,6 +509,8 @@ window_attn_tc2_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
                     if (d != 0ull) *reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(d) + ch * 8) = u;
                 }
                 __syncwarp();                                           // staging rows of this warp are free again
+                SVR2_FINE(58);
+                if (threadIdx.x == 256) trace_item(p, n_it, 6 + i);
                 ++c[i];
             }
         }

@@ -1,5 +1,6 @@
-"""Per-CTA timeline of the window-attention kernel (debug): python scripts/attn_trace.py [c1|c2] [swin]"""
-import os, sys, ctypes
+"""Per-CTA timeline of the persistent window-attention kernel (debug hook svr2_debug_attn_trace):
+python scripts/attn_trace.py [c1|c2|c3] [swin]"""
+import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np
 import torch
@@ -17,41 +18,48 @@ q, k, v = (torch.randn(P, heads, 128, generator=g, device=dev).bfloat16() for _ 
 for _ in range(3):
     svr2.ops.window_attn(plan, q, k, v, heads)
 torch.cuda.synchronize()
-n_ctas = plan.work.shape[0] * heads
+n_ctas = 148
 L = svr2._lib.lib()
 slots = L.svr2_debug_attn_trace(None, 0)
 buf = torch.zeros(n_ctas, slots, dtype=torch.int64, device=dev)
 L.svr2_debug_attn_trace(buf.data_ptr(), n_ctas)
-e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-e0.record()
+timer = svr2.ops.KernelTimer(only={"svr2_window_attn_fwd"})
+svr2.ops.set_timer(timer)
 svr2.ops.window_attn(plan, q, k, v, heads)
-e1.record()
 torch.cuda.synchronize()
+svr2.ops.set_timer(None)
 L.svr2_debug_attn_trace(None, 0)
-t = buf.cpu().numpy()
-print(f"{name} shifted={shifted}: {n_ctas} CTAs, kernel+pool {e0.elapsed_time(e1)*1e3:.1f} us, flops {plan.attention_flops(heads)/1e9:.1f} G")
-nkv = t[:, 7]
-for nk in sorted(set(nkv.tolist())):
-    m = nkv == nk
-    tt = t[m]
-    ent = tt[:, 0]
-    def col(s):
-        return (tt[:, s] - ent)
-    print(f"-- n_kv={nk}: {m.sum()} CTAs;  median cycles since entry:")
-    print(f"   setup done {np.median(col(1)):.0f} | Q+K0 landed {np.median(col(2)):.0f} | O final {np.median(col(3)):.0f} | stores issued {np.median(col(4)):.0f} | end {np.median(col(5)):.0f}")
-    s_ready = [np.median(col(8 + j)) for j in range(min(nk, 16))]
-    p_pub = [np.median(col(24 + j)) for j in range(min(nk, 16))]
-    s1 = [np.median(col(40 + j)) for j in range(min(nk, 16))]
-    print("   S0(j) ready:", [int(x) for x in s_ready])
-    print("   P0(j) done :", [int(x) for x in p_pub])
-    print("   S1(j) ready:", [int(x) for x in s1])
-# per-SM occupancy: gaps between consecutive CTAs on one SM
-sm = t[:, 6]
-gaps = []
-for s_ in np.unique(sm):
-    rows = t[sm == s_]
-    rows = rows[np.argsort(rows[:, 0])]
-    gaps += list(rows[1:, 0] - rows[:-1, 5])
-print(f"gap between a CTA's end and the next CTA's entry on the same SM: median {np.median(gaps):.0f} cycles, mean {np.mean(gaps):.0f}")
-dur = t[:, 5] - t[:, 0]
-print(f"CTA lifetime cycles: median {np.median(dur):.0f} mean {dur.mean():.0f}; CTAs per SM ~{n_ctas/148:.1f}")
+ms = timer.summary()["svr2_window_attn_fwd"][1]
+fl = plan.attention_flops(heads)
+print(f"{name} shifted={shifted}: {plan.work.shape[0] * heads} items, kernel {ms*1e3:.1f} us, {fl/ms/1e9:.0f} TFLOP/s (with trace stores)")
+t = buf.cpu().numpy().astype(np.float64)
+ent = t[:, 0]
+print(f"setup done {np.median(t[:,1]-ent):.0f} | CTA end {np.median(t[:,5]-ent):.0f} cycles | items per CTA median {np.median(t[:,7]):.0f}")
+names = ["MMA start", "S0(0) seen", "P0(0) pub", "S0(last) seen", "P0(last) pub", "O0 final seen", "tile0 stored", "tile1 stored", "TMA last KV issued"]
+for n in range(4):
+    base = 8 + 9 * n
+    st = t[:, base]
+    ok = st > 0
+    if not ok.any():
+        continue
+    line = f"item {n}: start @ {np.median(st[ok]-ent[ok]):.0f}"
+    if n > 0:
+        prev = t[:, base - 9]
+        line += f" (period {np.median((st-prev)[ok]):.0f})"
+    for w in range(1, 9):
+        x = t[:, base + w]
+        m = ok & (x > 0)
+        if m.any():
+            line += f" | {names[w]} {np.median((x-st)[m]):+.0f}"
+    print(line)
+
+fine = t[:, 44:59]
+ok = (fine[:, 0] > 0)
+if ok.any():
+    f = fine[ok]
+    rel = lambda k: np.median(f[:, k] - f[:, 0])
+    print("fine (item 2, key tile 1), cycles after softmax-0 saw S:")
+    print("  softmax-0: chunk0 landed %+d | after chunk 0 %+d | 1 %+d | 2 %+d | 3 %+d | wait::st %+d | arrived %+d" % tuple(rel(k) for k in range(1, 8)))
+    print("  MMA thread: P0 ready %+d | tile-0 MMAs issued %+d | P1 ready %+d | tile-1 MMAs issued %+d" % tuple(rel(k) for k in range(8, 12)))
+    e = f[:, 12:15]
+    print("  epilogue tile 0: O final -> staged %+d -> stored %+d" % (np.median(e[:, 1] - e[:, 0]), np.median(e[:, 2] - e[:, 0])))
