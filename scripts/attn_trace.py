@@ -53,13 +53,13 @@ for n in range(4):
             line += f" | {names[w]} {np.median((x-st)[m]):+.0f}"
     print(line)
 
-fine = t[:, 44:59]
-ok = (fine[:, 0] > 0)
+
+names_f = ["S seen", "S in regs", "max done", "token", "exp2 done", "wait::st", "P published", "next S seen"]
+f = t[:, 44:60]
+ok = (f[:, :8] > 0).all(axis=1) & (f[:, 8:14] > 0).all(axis=1)
 if ok.any():
-    f = fine[ok]
-    rel = lambda k: np.median(f[:, k] - f[:, 0])
-    print("fine (item 2, key tile 1), cycles after softmax-0 saw S:")
-    print("  softmax-0: chunk0 landed %+d | after chunk 0 %+d | 1 %+d | 2 %+d | 3 %+d | wait::st %+d | arrived %+d" % tuple(rel(k) for k in range(1, 8)))
-    print("  MMA thread: P0 ready %+d | tile-0 MMAs issued %+d | P1 ready %+d | tile-1 MMAs issued %+d" % tuple(rel(k) for k in range(8, 12)))
-    e = f[:, 12:15]
-    print("  epilogue tile 0: O final -> staged %+d -> stored %+d" % (np.median(e[:, 1] - e[:, 0]), np.median(e[:, 2] - e[:, 0])))
+    f = f[ok]; ref = f[:, 0]
+    print("fine softmax-0 (item 2, half tile 3), cycles after it saw S(3): " + " | ".join(f"{names_f[k]} {np.median(f[:, k] - ref):+.0f}" for k in range(8)))
+    lab = ["P(2) seen", "h=2 issued", "P(3) seen", "h=3 issued", "P(4) seen", "h=4 issued"]
+    print("fine MMA warp tile 0: " + " | ".join(f"{lab[k]} {np.median(f[:, 8 + k] - ref):+.0f}" for k in range(6)))
+    print("softmax-0 reaches the S(4) wait at %+d; S(4) already complete at that moment in %.0f%% of CTAs" % (np.median(t[ok, 60] - ref), 100 * np.mean(t[ok, 61])))
