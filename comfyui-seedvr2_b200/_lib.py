@@ -9,7 +9,7 @@ import subprocess
 from ctypes import POINTER, c_char_p, c_float, c_int, c_int32, c_int64, c_void_p
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libseedvr2_b200.so")
+LIB_PATH = os.environ.get("SVR2_LIB") or os.path.join(_HERE, "libseedvr2_b200.so")   # SVR2_LIB: kernel experiments
 CSRC = os.path.join(_HERE, "csrc")
 
 # name -> (restype, argtypes); must list EVERY symbol of include/seedvr2_b200.h (tests/test_cabi.py checks this)

@@ -29,14 +29,19 @@ __device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
         : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
     return ok != 0;
 }
-// Bounded wait: a protocol bug traps (the launch fails with an error) instead of hanging the GPU.
+// Bounded wait: a protocol bug traps (the launch fails with "unspecified launch failure") instead of hanging the GPU.
+// The default build traps silently: a printf here gives every wait a stack frame, and local-memory traffic next to the
+// waits of a register-starved role is an L2 round trip (this kernel leaves the L1 ~20 KB).  Build with -DSVR2_DEBUG_WAIT to
+// get the block / thread / barrier of the wait that timed out.
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
     if (mbar_try_wait(bar, parity)) return;
     const long long t0 = clock64();
     while (!mbar_try_wait(bar, parity)) {
-        if (clock64() - t0 > 4000000000LL) {   // ~2 s at 2 GHz
+        if (clock64() - t0 > 40000000000LL) {   // ~20 s: instrumented profiler passes run orders of magnitude slower
+#ifdef SVR2_DEBUG_WAIT
             printf("svr2: mbarrier timeout (block %d,%d thread %d bar 0x%x parity %u)\n", blockIdx.x, blockIdx.y,
                    threadIdx.x, bar, parity);
+#endif
             __trap();
         }
     }
@@ -126,6 +131,14 @@ __device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t* v) {
         ::"r"(taddr), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]),
           "r"(v[8]), "r"(v[9]), "r"(v[10]), "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15])
         : "memory");
+}
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t* v) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+        "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+          "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+        : "r"(taddr) : "memory");
 }
 // named barrier among `nthreads` threads (a subset of warps of the CTA)
 __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {

@@ -54,12 +54,11 @@ for n in range(4):
     print(line)
 
 
-names_f = ["S seen", "S in regs", "max done", "token", "exp2 done", "wait::st", "P published", "next S seen"]
-f = t[:, 44:60]
-ok = (f[:, :8] > 0).all(axis=1) & (f[:, 8:14] > 0).all(axis=1)
+f = t[:, 44:64]
+ok = (f > 0).all(axis=1)
 if ok.any():
     f = f[ok]; ref = f[:, 0]
-    print("fine softmax-0 (item 2, half tile 3), cycles after it saw S(3): " + " | ".join(f"{names_f[k]} {np.median(f[:, k] - ref):+.0f}" for k in range(8)))
-    lab = ["P(2) seen", "h=2 issued", "P(3) seen", "h=3 issued", "P(4) seen", "h=4 issued"]
-    print("fine MMA warp tile 0: " + " | ".join(f"{lab[k]} {np.median(f[:, 8 + k] - ref):+.0f}" for k in range(6)))
-    print("softmax-0 reaches the S(4) wait at %+d; S(4) already complete at that moment in %.0f%% of CTAs" % (np.median(t[ok, 60] - ref), 100 * np.mean(t[ok, 61])))
+    order = [0, 6, 7, 8, 1, 2, 9, 3, 4, 5]
+    nm = {0: "S seen", 6: "ld#1 issued", 7: "ld#4 issued", 8: "wait::ld passed", 1: "s[31] readable", 2: "max done", 9: "chunk 0 exp+st", 3: "all exp+st issued", 4: "st complete", 5: "P published"}
+    for i in range(2):
+        print(f"fine softmax-{i} (item 2, key tile 1), cycles after softmax-0 saw S: " + " | ".join(f"{nm[k]} {np.median(f[:, 10*i+k] - ref):+.0f}" for k in order))
