@@ -50,18 +50,29 @@ constexpr int TILE_BYTES = BM * D * 2;    // 32768
 constexpr int BOX_BYTES = TILE_BYTES / 2; // 128 rows x 64 cols bf16
 constexpr int STAGES = 4;
 constexpr int NTHREADS = 512;
-constexpr int REGS_CTRL = 72, REGS_EPI = 72, REGS_SOFTMAX = 184;   // per sub-partition: 32 * (56 + 88 + 2 * 184) = 16384
+#ifndef SVR2_REGS
+#define SVR2_REGS 72, 72, 184
+#endif
+constexpr int kRegs[3] = {SVR2_REGS};
+constexpr int REGS_CTRL = kRegs[0], REGS_EPI = kRegs[1], REGS_SOFTMAX = kRegs[2];   // per sub-partition: 32 * (56 + 88 + 2 * 184) = 16384
 constexpr int OFF_RING = 2 * TILE_BYTES;
 constexpr int OFF_STAGE = OFF_RING + STAGES * TILE_BYTES;
 constexpr int OFF_L = OFF_STAGE + TILE_BYTES;          // float l[2 parities][2 tiles][128 rows]
 constexpr int OFF_BAR = OFF_L + 2 * 2 * 128 * 4;
 constexpr int SMEM_BYTES = OFF_BAR + 256;              // 231,680 B of the 232,448 B a CTA may opt in to
 constexpr uint32_t TMEM_COLS = 512;
+#ifndef SVR2_FMA8
+#define SVR2_FMA8 3
+#endif
+constexpr int kFmaEighths = SVR2_FMA8;              // of every 8 exp2 pairs, this many are evaluated on the FMA pipe (softmax_row.cuh)
 constexpr float kRescaleThreshold = 8.0f;   // lazy rescale: tolerate P up to 2^8 before touching O
 
 // barrier slots (8 bytes each), per query tile i: slot + i
 enum { BAR_QFULL = 0, BAR_QEMPTY = 2, BAR_SFULL = 4, BAR_PREADY = 6, BAR_OFINAL = 8, BAR_OEMPTY = 10, BAR_LREADY = 12,
-       BAR_KVFULL = 14, BAR_KVEMPTY = 14 + STAGES, BAR_COUNT = 14 + 2 * STAGES };
+       BAR_TURN = 14, BAR_KVFULL = 16, BAR_KVEMPTY = 16 + STAGES, BAR_COUNT = 16 + 2 * STAGES };
+#ifndef SVR2_TURNS
+#define SVR2_TURNS 1
+#endif
 static_assert(BAR_COUNT * 8 + 8 <= 256, "barrier block too small");
 
 struct Params {
@@ -79,9 +90,8 @@ struct Params {
 // +3 softmax-0 sees S(last)   +4 softmax-0 published P(last)   +5 epilogue sees O_0 final   +6 tile-0 stores issued
 // +7 tile-1 stores issued   +8 TMA thread issued the item's last K/V load
 constexpr int kTraceSlots = 64, kTraceItems = 4;
-// fine stamps for the CTA's third item, key tile 1: softmax group i at 44 + 6i (S seen, S in registers, max done, exp2 +
-// P stores issued, stores complete, P published), MMA warp i at 56 + 2i (P seen, MMAs issued)
-#define SVR2_FINE(k) do { asm volatile("mov.u32 %0, %%clock;" : "=r"(ts[k])); } while (0)
+// step stamps for the CTA's third item, key tiles j < 4: softmax group i saw S(j) at 44 + 8i + 2j, published P(j) at 45 + 8i + 2j;
+// MMA warp i finished issuing the step-j MMAs at 60 + 2i (j = 1 only: slots are scarce)
 
 // Everything a role needs to know about one work item; every role decodes it identically.
 struct Item {
@@ -112,20 +122,28 @@ __device__ __forceinline__ void warp_wait(uint32_t bar, uint32_t parity) {
     if ((threadIdx.x & 31) == 0) mbar_wait(bar, parity);
     __syncwarp();
 }
-#define SOFTMAX_WAIT(b, par) do { if (SVR2_EXP == 1 || SVR2_EXP == 3) warp_wait(b, par); else mbar_wait(b, par); } while (0)
-#define OTHER_WAIT(b, par) do { if (SVR2_EXP == 3) warp_wait(b, par); else mbar_wait(b, par); } while (0)
+#define SOFTMAX_WAIT(b, par) mbar_wait(b, par)
+#define OTHER_WAIT(b, par) mbar_wait(b, par)
 
 template <int N> __device__ __forceinline__ void reg_alloc() { asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(N)); }
 template <int N> __device__ __forceinline__ void reg_dealloc() { asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(N)); }
 
+// The timeline hooks exist only in the kTrace instantiation (launched while svr2_debug_attn_trace is armed): the
+// production kernel carries none of their code — the roles' instruction streams have to share a 32-KB instruction cache.
+template <bool kTrace>
 __device__ __forceinline__ void trace_at(const Params& p, int slot, long long v) {
-    if (p.trace != nullptr && (int)blockIdx.x < p.trace_ctas && slot < kTraceSlots)
-        p.trace[(long long)blockIdx.x * kTraceSlots + slot] = v;
+    if constexpr (kTrace) {
+        if ((int)blockIdx.x < p.trace_ctas && slot < kTraceSlots) p.trace[(long long)blockIdx.x * kTraceSlots + slot] = v;
+    }
 }
+template <bool kTrace>
 __device__ __forceinline__ void trace_item(const Params& p, int n, int what) {
-    if (p.trace != nullptr && n < kTraceItems) trace_at(p, 8 + 9 * n + what, clock64());
+    if constexpr (kTrace) {
+        if (n < kTraceItems) trace_at<kTrace>(p, 8 + 9 * n + what, clock64());
+    }
 }
 
+template <bool kTrace>
 __global__ void __launch_bounds__(NTHREADS, 1)
 window_attn_tc2_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_k,
                        const __grid_constant__ CUtensorMap tm_v, const Params p) {
@@ -144,7 +162,7 @@ window_attn_tc2_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
             printf("svr2: dynamic shared memory base 0x%x is not 1024-B aligned\n", base);
             __trap();
         }
-        trace_at(p, 0, clock64());
+        trace_at<kTrace>(p, 0, clock64());
         for (int i = 0; i < 2; ++i) {
             mbar_init(bar(BAR_QFULL + i), 1);
             mbar_init(bar(BAR_QEMPTY + i), 1);
@@ -153,10 +171,11 @@ window_attn_tc2_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
             mbar_init(bar(BAR_OFINAL + i), 1);
             mbar_init(bar(BAR_OEMPTY + i), 128);
             mbar_init(bar(BAR_LREADY + i), 128);
+            mbar_init(bar(BAR_TURN + i), 128);
         }
         for (int s = 0; s < STAGES; ++s) {
             mbar_init(bar(BAR_KVFULL + s), 1);
-            mbar_init(bar(BAR_KVEMPTY + s), 2);       // one commit per MMA warp (two from warp 1 when tile 1 is absent)
+            mbar_init(bar(BAR_KVEMPTY + s), 2);       // one commit per MMA warp
         }
         fence_mbar_init();
     }
@@ -171,10 +190,12 @@ window_attn_tc2_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
     tc_fence_after();
     const uint32_t tmem = *tmem_slot;
     if (threadIdx.x == 0) {
-        unsigned smid;
-        asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
-        trace_at(p, 1, clock64());
-        trace_at(p, 6, smid);
+        if constexpr (kTrace) {
+            unsigned smid;
+            asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+            trace_at<kTrace>(p, 1, clock64());
+            trace_at<kTrace>(p, 6, smid);
+        }
     }
 
     if (warp < 4) {
@@ -204,7 +225,7 @@ window_attn_tc2_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
                         tma_load_3d(sRing + st * TILE_BYTES, map, bar(BAR_KVFULL + st), 0, it.head, row);
                         tma_load_3d(sRing + st * TILE_BYTES + BOX_BYTES, map, bar(BAR_KVFULL + st), 64, it.head, row);
                     }
-                    trace_item(p, n_it, 8);
+                    trace_item<kTrace>(p, n_it, 8);
                 }
             }
         } else if (warp <= 2) {
@@ -243,21 +264,25 @@ window_attn_tc2_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
             auto ring_par = [&](uint32_t idx) { return ((kv0 + idx) / STAGES) & 1u; };
             for (int item = blockIdx.x; item < p.n_items; item += gridDim.x, ++n_done) {
                 const Item it = decode_item(p, item);
-                if (i >= it.nq) {                       // tile 1 absent: warp 1 releases the K/V tiles for both warps
+                if (i >= it.nq) {
+                    // Query tile 1 absent.  This warp still walks the item's K/V fills — waits for each one and releases it
+                    // with an (empty) commit.  Skipping ahead instead would let it test a ring barrier two phases early,
+                    // where the parity aliases and an unfinished fill reads as complete.
+                    for (uint32_t n = 0; n < 2u * it.n_kv; ++n) {
+                        OTHER_WAIT(bar(BAR_KVFULL + ring_slot(n)), ring_par(n));
+                        if (elect_one()) tc_commit(bar(BAR_KVEMPTY + ring_slot(n)));
+                        __syncwarp();
+                    }
                     kv0 += 2 * it.n_kv;
                     continue;
                 }
-                const bool both = it.nq == 1;
                 auto cols = [&](int j) { return j == it.n_kv - 1 ? it.last_cols : BN; };
-                auto release = [&](uint32_t idx) {
-                    tc_commit(bar(BAR_KVEMPTY + ring_slot(idx)));
-                    if (both) tc_commit(bar(BAR_KVEMPTY + ring_slot(idx)));
-                };
+                auto release = [&](uint32_t idx) { tc_commit(bar(BAR_KVEMPTY + ring_slot(idx))); };
                 OTHER_WAIT(bar(BAR_QFULL + i), cq & 1);
                 OTHER_WAIT(bar(BAR_KVFULL + ring_slot(0)), ring_par(0));
                 tc_fence_after();
                 if (elect_one()) {
-                    if (i == 0) trace_item(p, n_done, 0);
+                    if (i == 0) trace_item<kTrace>(p, n_done, 0);
                     issue_qk(sRing + ring_slot(0) * TILE_BYTES, cols(0));
                     tc_commit(bar(BAR_SFULL + i));
                     if (it.n_kv == 1) tc_commit(bar(BAR_QEMPTY + i));                    // that was the last read of Q_i
@@ -291,7 +316,7 @@ window_attn_tc2_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
                 kv0 += 2 * it.n_kv;
                 ++cq;
             }
-            if (lane == 0 && i == 0) trace_at(p, 7, n_done);
+            if (lane == 0 && i == 0) trace_at<kTrace>(p, 7, n_done);
         }
     } else if (warp < 8) {
         reg_dealloc<REGS_EPI>();
@@ -310,9 +335,9 @@ window_attn_tc2_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
                 OTHER_WAIT(bar(BAR_LREADY + i), cc & 1);
                 OTHER_WAIT(bar(BAR_OFINAL + i), cc & 1);
                 tc_fence_after();
-                if (threadIdx.x == 128 && i == 0) trace_item(p, n_it, 5);
+                if (threadIdx.x == 128 && i == 0) trace_item<kTrace>(p, n_it, 5);
                 const float inv = 1.0f / l_buf[((cc & 1) * 2 + i) * 128 + row];
-#pragma unroll
+#pragma unroll 1
                 for (int c4 = 0; c4 < 4; ++c4) {
                     uint32_t ov[32];
                     tmem_ld32(tO + c4 * 32, ov);
@@ -353,7 +378,7 @@ window_attn_tc2_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
                     if (d != 0ull) *reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(d) + ch * 8) = u;
                 }
                 __syncwarp();                                           // staging rows of this warp are free again
-                if (threadIdx.x == 128) trace_item(p, n_it, 6 + i);
+                if (threadIdx.x == 128) trace_item<kTrace>(p, n_it, 6 + i);
                 if (i) ++c1; else ++c0;
             }
         }
@@ -367,47 +392,57 @@ window_attn_tc2_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
         const bool tracer = (threadIdx.x & 127) == 0 && i == 0;
         uint32_t sf = 0;            // SFULL_i phases consumed
         uint32_t c_cnt = 0;
+        // Taking turns.  Left alone the two groups fall into lockstep: both run their softmax step at once, fighting for the
+        // exp2 unit and the issue slots (~2600 cycles each instead of ~1300), then both wait while their MMAs run one after
+        // the other.  BAR_TURN + g completes once per softmax step of group g (after its last exp2 is issued); a group
+        // starts a step only after the other group finished the step that precedes it in the order (item, key tile, group).
+        // That staggers the groups by one softmax step, so one tile's MMAs run under the other tile's softmax.  The turn is
+        // a scheduling hint only: a stale parity after single-tile items lets a group start early, never blocks it.
+        uint32_t other_steps = 0;   // steps of the other group in the items before this one
         int n_it = -1;
         for (int item = blockIdx.x; item < p.n_items; item += gridDim.x) {
             const Item it = decode_item(p, item);
             ++n_it;
-            if (i >= it.nq) continue;
+            if (i >= it.nq) {
+                other_steps += it.n_kv;
+                continue;
+            }
             float m = -INFINITY, l = 0.f;
             for (int j = 0; j < it.n_kv; ++j, ++sf) {
+                if (SVR2_TURNS) {
+                    // group 1 follows group 0's step j of this item; group 0 follows group 1's previous step
+                    const uint32_t k = i ? other_steps + j : other_steps + (it.nq == 2 ? j : 0) - 1;
+                    if (k != 0xffffffffu) mbar_wait(bar(BAR_TURN + (i ^ 1)), k & 1u);
+                }
                 const bool last = j == it.n_kv - 1;
                 const int nch = (last ? it.last_cols : BN) >> 5;            // 32-column chunks in this key tile (warp-uniform)
                 const int valid = it.seq - j * BN;                          // key columns >= valid are beyond the sequence
-                const bool fine = p.trace != nullptr && (threadIdx.x & 127) == 0 && n_it == 2 && j == 1;
-                uint32_t ts[10];
+                const bool fine = kTrace && (threadIdx.x & 127) == 0 && n_it == 2 && j < 4;
                 SOFTMAX_WAIT(bar(BAR_SFULL + i), sf & 1u);
-                if (SVR2_EXP != 2) tc_fence_after();
-                SVR2_FINE(0);
+                tc_fence_after();
+                if (fine) trace_at<kTrace>(p, 44 + 8 * i + 2 * j, clock64());
                 if (tracer) {
-                    if (j == 0) trace_item(p, n_it, 1);
-                    if (last) trace_item(p, n_it, 3);
+                    if (j == 0) trace_item<kTrace>(p, n_it, 1);
+                    if (last) trace_item<kTrace>(p, n_it, 3);
                 }
-                uint32_t s[128];                                            // the whole S row: ONE TMEM round trip per tile
-                tmem_ld32(tS, s);
-                SVR2_FINE(6);
-                if (nch > 1) tmem_ld32(tS + 32, s + 32);
-                if (nch > 2) tmem_ld32(tS + 64, s + 64);
-                if (nch > 3) tmem_ld32(tS + 96, s + 96);
-                SVR2_FINE(7);
+                // The whole S row in registers: ONE TMEM round trip per key tile.  Register block b holds chunk nch - 4 + b,
+                // so the chunk with the end of the sequence is always block 3 and the masking code exists once.
+                uint32_t s[128];
+                const uint32_t tS3 = tS + 32 * (nch - 1);
+                if (nch > 3) tmem_ld32(tS3 - 96, s);
+                if (nch > 2) tmem_ld32(tS3 - 64, s + 32);
+                if (nch > 1) tmem_ld32(tS3 - 32, s + 64);
+                tmem_ld32(tS3, s + 96);
                 tc_wait_ld();
-                SVR2_FINE(8);
-                { uint32_t d; asm volatile("mov.u32 %0, %1;" : "=r"(d) : "r"(s[31])); }
-                SVR2_FINE(1);
-                if (valid < nch * 32) {                                     // only in the last key tile of a sequence
-                    const int c = nch - 1;                                  // trimming leaves the tail inside the last chunk
-                    if (c == 0) mask_chunk(s, valid);
-                    else if (c == 1) mask_chunk(s + 32, valid - 32);
-                    else if (c == 2) mask_chunk(s + 64, valid - 64);
-                    else mask_chunk(s + 96, valid - 96);
-                }
-                float mx = chunk_max(s);
-                if (nch > 1) mx = fmaxf(mx, chunk_max(s + 32));
-                if (nch > 2) mx = fmaxf(mx, chunk_max(s + 64));
-                if (nch > 3) mx = fmaxf(mx, chunk_max(s + 96));
+                if (valid < nch * 32) mask_chunk(s + 96, valid - 32 * (nch - 1));      // only in the last key tile of a sequence
+                float m8[8];
+#pragma unroll
+                for (int q = 0; q < 8; ++q) m8[q] = -INFINITY;
+                if (nch > 3) chunk_max8(m8, s);
+                if (nch > 2) chunk_max8(m8, s + 32);
+                if (nch > 1) chunk_max8(m8, s + 64);
+                chunk_max8(m8, s + 96);
+                const float mx = fmaxf(max3(m8[0], m8[1], m8[2]), max3(max3(m8[3], m8[4], m8[5]), m8[6], m8[7]));
                 if (j == 0) {
                     m = mx;
                 } else {
@@ -431,49 +466,42 @@ window_attn_tc2_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
                     }
                 }
                 const float mb = m * kScaleLog2;
-                SVR2_FINE(2);
-                // bf16 P overwrites the front of S_i chunk by chunk (the whole row is already in registers)
-                float rs;
-                {
+                // bf16 P overwrites the front of S_i chunk by chunk (the whole row is already in registers); kFmaEighths/8 of the
+                // exponentials run on the FMA pipe, the rest on MUFU
+                const uint32_t tP3 = tS + 16 * (nch - 1);
+                float rs = 0.f;
+                if (nch > 3) {
                     uint32_t pk[16];
-                    rs = chunk_exp(s, pk, mb);
-                    tmem_st16(tS, pk);
-                }
-                SVR2_FINE(9);
-                if (nch > 1) {
-                    uint32_t pk[16];
-                    rs += chunk_exp(s + 32, pk, mb);
-                    tmem_st16(tS + 16, pk);
+                    rs = chunk_exp_mix<kFmaEighths>(s, pk, mb);
+                    tmem_st16(tP3 - 48, pk);
                 }
                 if (nch > 2) {
                     uint32_t pk[16];
-                    rs += chunk_exp(s + 64, pk, mb);
-                    tmem_st16(tS + 32, pk);
+                    rs += chunk_exp_mix<kFmaEighths>(s + 32, pk, mb);
+                    tmem_st16(tP3 - 32, pk);
                 }
-                if (nch > 3) {
+                if (nch > 1) {
                     uint32_t pk[16];
-                    rs += chunk_exp(s + 96, pk, mb);
-                    tmem_st16(tS + 48, pk);
+                    rs += chunk_exp_mix<kFmaEighths>(s + 64, pk, mb);
+                    tmem_st16(tP3 - 16, pk);
+                }
+                {
+                    uint32_t pk[16];
+                    rs += chunk_exp_mix<kFmaEighths>(s + 96, pk, mb);
+                    tmem_st16(tP3, pk);
                 }
                 l += rs;
-                SVR2_FINE(3);
+                if (SVR2_TURNS) mbar_arrive(bar(BAR_TURN + i));
                 tc_wait_st();
-                SVR2_FINE(4);
                 tc_fence_before();
                 mbar_arrive(bar(BAR_PREADY + i));
-                SVR2_FINE(5);
-                if (fine) {
-                    const long long c64 = clock64();
-                    uint32_t now;
-                    asm volatile("mov.u32 %0, %%clock;" : "=r"(now));
-#pragma unroll
-                    for (int k = 0; k < 10; ++k) trace_at(p, 44 + 10 * i + k, c64 - (long long)(uint32_t)(now - ts[k]));
-                }
+                if (fine) trace_at<kTrace>(p, 45 + 8 * i + 2 * j, clock64());
                 if (tracer) {
-                    if (j == 0) trace_item(p, n_it, 2);
-                    if (last) trace_item(p, n_it, 4);
+                    if (j == 0) trace_item<kTrace>(p, n_it, 2);
+                    if (last) trace_item<kTrace>(p, n_it, 4);
                 }
             }
+            other_steps += (i == 1 || it.nq == 2) ? it.n_kv : 0;
             // publish the row sum for the epilogue warps (double-buffered by item parity)
             l_buf[((c_cnt & 1) * 2 + i) * 128 + row] = l;
             mbar_arrive(bar(BAR_LREADY + i));
@@ -482,7 +510,7 @@ window_attn_tc2_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
     }
     tc_fence_before();
     __syncthreads();
-    if (threadIdx.x == 0) trace_at(p, 5, clock64());
+    if (threadIdx.x == 0) trace_at<kTrace>(p, 5, clock64());
     if (warp == 1) {
         __syncwarp();
         tmem_dealloc(tmem, TMEM_COLS);
@@ -508,8 +536,11 @@ int launch_window_attn_tc2(const void* q, const void* k, const void* v, const in
     if ((rc = make_tmap(&tv, v, P, heads)) != SVR2_OK) return rc;
     static bool attr_set = false;
     if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(tc2::window_attn_tc2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        cudaError_t e = cudaFuncSetAttribute(tc2::window_attn_tc2_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              tc2::SMEM_BYTES);
+        if (e == cudaSuccess)
+            e = cudaFuncSetAttribute(tc2::window_attn_tc2_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     tc2::SMEM_BYTES);
         if (e != cudaSuccess) {
             set_error("svr2_window_attn_fwd: cannot reserve %d B shared memory: %s", tc2::SMEM_BYTES, cudaGetErrorString(e));
             return SVR2_E_CUDA;
@@ -523,7 +554,8 @@ int launch_window_attn_tc2(const void* q, const void* k, const void* v, const in
     p.trace = g_trace; p.trace_ctas = g_trace_ctas;
     const int sms = sm_count();
     const int grid = p.n_items < sms ? p.n_items : sms;       // one persistent CTA per SM
-    tc2::window_attn_tc2_kernel<<<grid, tc2::NTHREADS, tc2::SMEM_BYTES, st>>>(tq, tk, tv, p);
+    if (p.trace != nullptr) tc2::window_attn_tc2_kernel<true><<<grid, tc2::NTHREADS, tc2::SMEM_BYTES, st>>>(tq, tk, tv, p);
+    else tc2::window_attn_tc2_kernel<false><<<grid, tc2::NTHREADS, tc2::SMEM_BYTES, st>>>(tq, tk, tv, p);
     SVR2_CHECK_LAUNCH("svr2_window_attn_fwd(tcgen05, persistent)");
     return SVR2_OK;
 }

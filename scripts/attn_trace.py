@@ -15,7 +15,7 @@ plan = svr2.get_plan(grid, (4, 3, 3), shifted, 58)
 P = plan.packed_rows
 g = torch.Generator(device="cuda").manual_seed(0)
 q, k, v = (torch.randn(P, heads, 128, generator=g, device=dev).bfloat16() for _ in range(3))
-for _ in range(3):
+for _ in range(20):      # let the clocks settle
     svr2.ops.window_attn(plan, q, k, v, heads)
 torch.cuda.synchronize()
 n_ctas = 148
@@ -54,11 +54,15 @@ for n in range(4):
     print(line)
 
 
-f = t[:, 44:64]
-ok = (f > 0).all(axis=1)
+f = t[:, 44:60]
+ok = (f[:, :4] > 0).all(axis=1)
 if ok.any():
-    f = f[ok]; ref = f[:, 0]
-    order = [0, 6, 7, 8, 1, 2, 9, 3, 4, 5]
-    nm = {0: "S seen", 6: "ld#1 issued", 7: "ld#4 issued", 8: "wait::ld passed", 1: "s[31] readable", 2: "max done", 9: "chunk 0 exp+st", 3: "all exp+st issued", 4: "st complete", 5: "P published"}
+    ref = t[ok, 8 + 9 * 2]           # item 2: MMA start
     for i in range(2):
-        print(f"fine softmax-{i} (item 2, key tile 1), cycles after softmax-0 saw S: " + " | ".join(f"{nm[k]} {np.median(f[:, 10*i+k] - ref):+.0f}" for k in order))
+        parts = []
+        for j in range(4):
+            a, b = t[ok, 44 + 8 * i + 2 * j], t[ok, 45 + 8 * i + 2 * j]
+            m = (a > 0) & (b > 0)
+            if m.any():
+                parts.append(f"j={j}: S seen {np.median((a - ref)[m]):+.0f}, P published {np.median((b - ref)[m]):+.0f} (softmax {np.median((b - a)[m]):.0f})")
+        print(f"item 2, tile {i}: " + " | ".join(parts))
