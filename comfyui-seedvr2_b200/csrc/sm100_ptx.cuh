@@ -51,13 +51,29 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
     // passes slow polls and progress down alike (a 2-s clock bound fired under ncu).  2^28 failed polls are >= 3 s.
 #pragma unroll 1
     for (uint32_t n = 0; !mbar_try_wait(bar, parity); ++n) {
-        if (n > (1u << 28)) {
 #ifdef SVR2_DEBUG_WAIT
-            printf("svr2: mbarrier timeout (block %d,%d thread %d bar 0x%x parity %u)\n", blockIdx.x, blockIdx.y,
-                   threadIdx.x, bar, parity);
-#endif
+        if (n > (1u << 22)) {      // report, leave the other stuck threads time to report too, then fail the launch
+            // the attention kernels keep their barriers in a 256-B aligned block: slots of 8 B, then (debug builds) progress
+            // words at +200.  Bit b of `done0` = barrier b has completed a phase of parity 0 last (its current parity is 1).
+            const uint32_t blk = bar & ~0xffu;
+            uint32_t done0 = 0, w[12];
+            for (int b = 0; b < 24; ++b) {
+                uint32_t ok;
+                asm volatile("{\n\t.reg .pred p;\n\tmbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                             : "=r"(ok) : "r"(blk + 8u * b), "r"(0u) : "memory");
+                done0 |= ok << b;
+            }
+            for (int k = 0; k < 12; ++k) asm volatile("ld.volatile.shared.u32 %0, [%1];" : "=r"(w[k]) : "r"(blk + 200u + 4u * k));
+            printf("svr2: mbarrier timeout (block %d thread %d slot %u parity %u) parity-0-done mask 0x%06x progress tma %x mma %x %x epi %x "
+                   "sm0 %x %x %x %x sm1 %x %x %x %x\n", blockIdx.x, threadIdx.x, (bar & 0xffu) >> 3, parity, done0, w[0], w[1], w[2],
+                   w[3], w[4], w[5], w[6], w[7], w[8], w[9], w[10], w[11]);
+            const long long t0 = clock64();
+            while (clock64() - t0 < 2000000000LL) {}
             __trap();
         }
+#else
+        if (n > (1u << 28)) __trap();
+#endif
     }
 }
 

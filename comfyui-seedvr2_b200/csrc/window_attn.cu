@@ -335,6 +335,9 @@ long long* g_trace = nullptr;      // svr2_debug_attn_trace
 int g_trace_ctas = 0;
 int make_tmap(CUtensorMap* m, const void* ptr, int64_t P, int heads);
 int launch_window_attn_tc2(const void* q, const void* k, const void* v, const int32_t* tab, const int32_t* work,
+                           int n_work, int n_windows, int H, int W, int txt_len, int heads, int64_t P, void* out_vid,
+                           void* txt_part, cudaStream_t st);
+int launch_window_attn_tc3(const void* q, const void* k, const void* v, const int32_t* tab, const int32_t* work,
                            int n_work, int H, int W, int txt_len, int heads, int64_t P, void* out_vid, void* txt_part,
                            cudaStream_t st);
 namespace {
@@ -453,15 +456,19 @@ extern "C" int svr2_window_attn_fwd(const void* q_pack, const void* k_pack, cons
                    "svr2_window_attn_fwd: bad sizes");
     (void)T;
     cudaStream_t st = (cudaStream_t)stream;
-    // Product path: the persistent tcgen05 kernel (window_attn_v2.cu).  SVR2_ATTN_IMPL=v1 selects the first-generation
-    // one-CTA-per-item tcgen05 kernel and =mma the legacy mma.sync comparator — A/B debugging aids only, both CUDA.
+    // Product path: the persistent tcgen05 kernel of window_attn_v2.cu (generation 4).  SVR2_ATTN_IMPL selects another
+    // generation for A/B runs — v3 (generation 5: both softmax warpgroups on one query tile, column-split; correct, not
+    // faster), v1 (one CTA per item) or mma (the legacy mma.sync comparator).  Every one is a CUDA kernel of this library.
     const char* e = getenv("SVR2_ATTN_IMPL");
-    const int impl = (e && strcmp(e, "mma") == 0) ? 1 : ((e && strcmp(e, "v1") == 0) ? 2 : 0);
-    int rc = impl == 1
-                 ? svr2::launch_window_attn_mma(q_pack, k_pack, v_pack, win_table, work, n_work, H, W, txt_len, heads, out_vid, txt_part, st)
-             : impl == 2
-                 ? svr2::launch_window_attn_tc(q_pack, k_pack, v_pack, win_table, work, n_work, H, W, txt_len, heads, P, out_vid, txt_part, st)
-                 : svr2::launch_window_attn_tc2(q_pack, k_pack, v_pack, win_table, work, n_work, H, W, txt_len, heads, P, out_vid, txt_part, st);
+    int rc;
+    if (e && strcmp(e, "mma") == 0)
+        rc = svr2::launch_window_attn_mma(q_pack, k_pack, v_pack, win_table, work, n_work, H, W, txt_len, heads, out_vid, txt_part, st);
+    else if (e && strcmp(e, "v1") == 0)
+        rc = svr2::launch_window_attn_tc(q_pack, k_pack, v_pack, win_table, work, n_work, H, W, txt_len, heads, P, out_vid, txt_part, st);
+    else if (e && strcmp(e, "v3") == 0)
+        rc = svr2::launch_window_attn_tc3(q_pack, k_pack, v_pack, win_table, work, n_work, H, W, txt_len, heads, P, out_vid, txt_part, st);
+    else
+        rc = svr2::launch_window_attn_tc2(q_pack, k_pack, v_pack, win_table, work, n_work, n_windows, H, W, txt_len, heads, P, out_vid, txt_part, st);
     if (rc != SVR2_OK) return rc;
     if (out_txt == nullptr) return SVR2_OK;      // caller pools the text rows itself with svr2_txt_pool_fwd
     return svr2::launch_txt_pool(txt_part, out_txt, n_windows, txt_len, heads, st);

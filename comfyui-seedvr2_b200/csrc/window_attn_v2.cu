@@ -33,6 +33,7 @@
 // TMEM map (columns): S0 [0,128)  S1 [128,256)  O0 [256,384)  O1 [384,512);  P_i aliases the first 64 columns of S_i.
 // SMEM map: Q0 | Q1 | ring[4] | staging (32 KB each) | row sums l[2][2][128] | mbarriers.
 #include <cuda.h>
+#include <cstdlib>
 
 #include "common.cuh"
 #include "sm100_ptx.cuh"
@@ -69,9 +70,15 @@ constexpr float kRescaleThreshold = 8.0f;   // lazy rescale: tolerate P up to 2^
 
 // barrier slots (8 bytes each), per query tile i: slot + i
 enum { BAR_QFULL = 0, BAR_QEMPTY = 2, BAR_SFULL = 4, BAR_PREADY = 6, BAR_OFINAL = 8, BAR_OEMPTY = 10, BAR_LREADY = 12,
-       BAR_TURN = 14, BAR_KVFULL = 16, BAR_KVEMPTY = 16 + STAGES, BAR_COUNT = 16 + 2 * STAGES };
+       BAR_KVFULL = 14, BAR_KVEMPTY = 14 + STAGES, BAR_COUNT = 14 + 2 * STAGES };
 #ifndef SVR2_TURNS
-#define SVR2_TURNS 1
+#define SVR2_TURNS 0      // measured: the bounded counter version gains nothing (see the comment in the softmax role); kept for experiments
+#endif
+#ifndef SVR2_TURN_BOUND
+#define SVR2_TURN_BOUND 4096      // cycles a group waits for its turn at most
+#endif
+#ifndef SVR2_TURN_SLEEP
+#define SVR2_TURN_SLEEP 20        // ns between polls of the turn counter
 #endif
 static_assert(BAR_COUNT * 8 + 8 <= 256, "barrier block too small");
 
@@ -84,6 +91,7 @@ struct Params {
     __nv_bfloat16* txt_part;
     long long* trace;      // debug timeline (svr2_debug_attn_trace) or nullptr
     int trace_ctas;
+    int turns;             // softmax groups take turns (short sequences) or run freely (long ones)
 };
 // 0 entry, 1 setup done, 5 end, 6 smid, 7 items done; for the CTA's first kTraceItems items n, at 8 + 9n:
 // +0 MMA warp 0 starts the item (Q and K0 landed)   +1 softmax-0 sees S(0)   +2 softmax-0 published P(0)
@@ -122,6 +130,11 @@ __device__ __forceinline__ void warp_wait(uint32_t bar, uint32_t parity) {
     if ((threadIdx.x & 31) == 0) mbar_wait(bar, parity);
     __syncwarp();
 }
+#ifdef SVR2_DEBUG_WAIT
+#define DBG_PROGRESS(role, val) do { if ((threadIdx.x & 31) == 0) reinterpret_cast<volatile uint32_t*>(smem + OFF_BAR + 200)[role] = (uint32_t)(val); } while (0)
+#else
+#define DBG_PROGRESS(role, val) do { } while (0)
+#endif
 #define SOFTMAX_WAIT(b, par) mbar_wait(b, par)
 #define OTHER_WAIT(b, par) mbar_wait(b, par)
 
@@ -153,6 +166,7 @@ window_attn_tc2_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
     const uint32_t sBar = base + OFF_BAR;
     float* l_buf = reinterpret_cast<float*>(smem + OFF_L);
     volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(smem + OFF_BAR + BAR_COUNT * 8);
+    volatile uint32_t* turn_cnt = reinterpret_cast<volatile uint32_t*>(smem + OFF_BAR + 248);   // softmax steps finished, x4 warps, per group
     auto bar = [&](int slot) { return sBar + 8u * (uint32_t)slot; };
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -171,12 +185,13 @@ window_attn_tc2_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
             mbar_init(bar(BAR_OFINAL + i), 1);
             mbar_init(bar(BAR_OEMPTY + i), 128);
             mbar_init(bar(BAR_LREADY + i), 128);
-            mbar_init(bar(BAR_TURN + i), 128);
         }
         for (int s = 0; s < STAGES; ++s) {
             mbar_init(bar(BAR_KVFULL + s), 1);
             mbar_init(bar(BAR_KVEMPTY + s), 2);       // one commit per MMA warp
         }
+        turn_cnt[0] = 0;
+        turn_cnt[1] = 0;
         fence_mbar_init();
     }
     if (warp == 1) tmem_alloc(smem_u32(const_cast<uint32_t*>(tmem_slot)), TMEM_COLS);
@@ -217,6 +232,7 @@ window_attn_tc2_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
                         if (i) ++c1; else ++c0;
                     }
                     for (int n = 0; n < 2 * it.n_kv; ++n, ++kv_n) {           // ring order K0 V0 K1 V1 ...
+                        DBG_PROGRESS(0, (n_it << 12) | (it.nq << 8) | n);
                         const uint32_t st = kv_n % STAGES, use = kv_n / STAGES;
                         const CUtensorMap* map = (n & 1) ? &tm_v : &tm_k;
                         const int row = it.w.row_start + (n >> 1) * BN;
@@ -269,6 +285,7 @@ window_attn_tc2_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
                     // with an (empty) commit.  Skipping ahead instead would let it test a ring barrier two phases early,
                     // where the parity aliases and an unfinished fill reads as complete.
                     for (uint32_t n = 0; n < 2u * it.n_kv; ++n) {
+                        DBG_PROGRESS(1 + i, 0x80000000u | (n_done << 12) | n);
                         OTHER_WAIT(bar(BAR_KVFULL + ring_slot(n)), ring_par(n));
                         if (elect_one()) tc_commit(bar(BAR_KVEMPTY + ring_slot(n)));
                         __syncwarp();
@@ -291,6 +308,7 @@ window_attn_tc2_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
                 __syncwarp();
                 for (int j = 0; j < it.n_kv; ++j) {
                     const bool more = j + 1 < it.n_kv;
+                    DBG_PROGRESS(1 + i, (n_done << 12) | (it.nq << 8) | j);
                     OTHER_WAIT(bar(BAR_KVFULL + ring_slot(2 * j + 1)), ring_par(2 * j + 1));              // V_j
                     if (more) OTHER_WAIT(bar(BAR_KVFULL + ring_slot(2 * j + 2)), ring_par(2 * j + 2));    // K_{j+1}
                     OTHER_WAIT(bar(BAR_PREADY + i), pr & 1u);
@@ -316,6 +334,7 @@ window_attn_tc2_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
                 kv0 += 2 * it.n_kv;
                 ++cq;
             }
+            DBG_PROGRESS(1 + i, 0xffff0000u | n_done);
             if (lane == 0 && i == 0) trace_at<kTrace>(p, 7, n_done);
         }
     } else if (warp < 8) {
@@ -332,6 +351,7 @@ window_attn_tc2_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
             for (int i = 0; i < it.nq; ++i) {
                 const uint32_t cc = i ? c1 : c0;
                 const uint32_t tO = tmem + lane_off + 256 + i * 128;
+                if (quad == 0) DBG_PROGRESS(3, (n_it << 12) | (it.nq << 8) | i);
                 OTHER_WAIT(bar(BAR_LREADY + i), cc & 1);
                 OTHER_WAIT(bar(BAR_OFINAL + i), cc & 1);
                 tc_fence_after();
@@ -394,10 +414,11 @@ window_attn_tc2_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
         uint32_t c_cnt = 0;
         // Taking turns.  Left alone the two groups fall into lockstep: both run their softmax step at once, fighting for the
         // exp2 unit and the issue slots (~2600 cycles each instead of ~1300), then both wait while their MMAs run one after
-        // the other.  BAR_TURN + g completes once per softmax step of group g (after its last exp2 is issued); a group
-        // starts a step only after the other group finished the step that precedes it in the order (item, key tile, group).
-        // That staggers the groups by one softmax step, so one tile's MMAs run under the other tile's softmax.  The turn is
-        // a scheduling hint only: a stale parity after single-tile items lets a group start early, never blocks it.
+        // the other.  turn_cnt[g] counts the softmax steps group g's warps have finished (bumped after the last exp2 is
+        // issued); a group starts a step only after the other group finished the step that precedes it in the order
+        // (item, key tile, group).  That staggers the groups by one softmax step, so one tile's MMAs run under the other
+        // tile's softmax.  The turn is a scheduling hint and must never be able to block: it is a monotonic counter (an
+        // mbarrier phase can be missed by a slow warp — that deadlocked an earlier version) and the wait is bounded.
         uint32_t other_steps = 0;   // steps of the other group in the items before this one
         int n_it = -1;
         for (int item = blockIdx.x; item < p.n_items; item += gridDim.x) {
@@ -409,15 +430,23 @@ window_attn_tc2_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
             }
             float m = -INFINITY, l = 0.f;
             for (int j = 0; j < it.n_kv; ++j, ++sf) {
-                if (SVR2_TURNS) {
+                if (SVR2_TURNS && p.turns) {
                     // group 1 follows group 0's step j of this item; group 0 follows group 1's previous step
-                    const uint32_t k = i ? other_steps + j : other_steps + (it.nq == 2 ? j : 0) - 1;
-                    if (k != 0xffffffffu) mbar_wait(bar(BAR_TURN + (i ^ 1)), k & 1u);
+                    const uint32_t need = 4u * (i ? other_steps + j + 1 : other_steps + (it.nq == 2 ? j : 0));
+                    uint32_t t0;
+                    asm volatile("mov.u32 %0, %%clock;" : "=r"(t0));
+                    while (turn_cnt[i ^ 1] < need) {
+                        uint32_t t1;
+                        asm volatile("mov.u32 %0, %%clock;" : "=r"(t1));
+                        if (t1 - t0 > (uint32_t)SVR2_TURN_BOUND) break;
+                        if (SVR2_TURN_SLEEP) __nanosleep(SVR2_TURN_SLEEP);
+                    }
                 }
                 const bool last = j == it.n_kv - 1;
                 const int nch = (last ? it.last_cols : BN) >> 5;            // 32-column chunks in this key tile (warp-uniform)
                 const int valid = it.seq - j * BN;                          // key columns >= valid are beyond the sequence
                 const bool fine = kTrace && (threadIdx.x & 127) == 0 && n_it == 2 && j < 4;
+                DBG_PROGRESS(4 + 4 * i + quad, (n_it << 12) | (it.nq << 8) | j);
                 SOFTMAX_WAIT(bar(BAR_SFULL + i), sf & 1u);
                 tc_fence_after();
                 if (fine) trace_at<kTrace>(p, 44 + 8 * i + 2 * j, clock64());
@@ -491,7 +520,7 @@ window_attn_tc2_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
                     tmem_st16(tP3, pk);
                 }
                 l += rs;
-                if (SVR2_TURNS) mbar_arrive(bar(BAR_TURN + i));
+                if (SVR2_TURNS && p.turns && lane == 0) atomicAdd(const_cast<uint32_t*>(&turn_cnt[i]), 1u);
                 tc_wait_st();
                 tc_fence_before();
                 mbar_arrive(bar(BAR_PREADY + i));
@@ -527,8 +556,8 @@ extern int g_trace_ctas;
 int make_tmap(CUtensorMap* m, const void* ptr, int64_t P, int heads);
 
 int launch_window_attn_tc2(const void* q, const void* k, const void* v, const int32_t* tab, const int32_t* work,
-                           int n_work, int H, int W, int txt_len, int heads, int64_t P, void* out_vid, void* txt_part,
-                           cudaStream_t st) {
+                           int n_work, int n_windows, int H, int W, int txt_len, int heads, int64_t P, void* out_vid,
+                           void* txt_part, cudaStream_t st) {
     CUtensorMap tq, tk, tv;
     int rc;
     if ((rc = make_tmap(&tq, q, P, heads)) != SVR2_OK) return rc;
@@ -552,6 +581,13 @@ int launch_window_attn_tc2(const void* q, const void* k, const void* v, const in
     p.H = H; p.W = W; p.txt_len = txt_len; p.heads = heads;
     p.out_vid = (__nv_bfloat16*)out_vid; p.txt_part = (__nv_bfloat16*)txt_part;
     p.trace = g_trace; p.trace_ctas = g_trace_ctas;
+    // Turn-taking staggers the two query tiles from the first key tile on: +7 % at 4 key tiles per sequence (2048^2 stills),
+    // but -5 % at 39 (720p, 33 frames), where the groups find their own rhythm and the enforced order only adds waits.
+    // SVR2_ATTN_TURNS=0/1 overrides the choice (A/B runs).
+    {
+        const char* e = getenv("SVR2_ATTN_TURNS");
+        p.turns = e ? (e[0] != '0') : (P / n_windows <= 8 * tc2::BN);      // mean sequence length
+    }
     const int sms = sm_count();
     const int grid = p.n_items < sms ? p.n_items : sms;       // one persistent CTA per SM
     if (p.trace != nullptr) tc2::window_attn_tc2_kernel<true><<<grid, tc2::NTHREADS, tc2::SMEM_BYTES, st>>>(tq, tk, tv, p);

@@ -130,15 +130,77 @@ class NaDiTStack(nn.Module):
 
     @torch.no_grad()
     def forward_host(self, vid_host: torch.Tensor, txt_host: torch.Tensor, grid: Tuple[int, int, int], timestep: float,
-                     out_host: torch.Tensor, device: torch.device) -> torch.Tensor:
+                     out_host: torch.Tensor, device: torch.device, graphed: bool = True) -> torch.Tensor:
         """End-to-end call with HOST buffers (what a pipeline stage hands over): pinned host latents/text are copied to
         the device, one NaDiT forward runs, the predicted latent is copied back into the pinned ``out_host``.
-        Stream-ordered on the current stream; returns ``out_host`` after the copy-back completed."""
-        vid = vid_host.to(device, non_blocking=True)
-        txt = txt_host.to(device, non_blocking=True)
-        ts = torch.tensor([[txt.shape[0]]], dtype=torch.long)
-        t = torch.full((1,), float(timestep), dtype=torch.float32, device=device)
-        out = self.forward(vid, txt, None, ts, t, grid=grid)
+        Stream-ordered on the current stream; returns ``out_host`` after the copy-back completed.
+        ``graphed`` replays the CUDA graph of this (grid, text length) — captured on first use — instead of launching
+        the ~1,500 kernels of a forward one by one."""
+        if graphed:
+            g = self.graph_for(grid, txt_host.shape[0], device, vid_host.dtype)
+            g.vid.copy_(vid_host, non_blocking=True)
+            g.txt.copy_(txt_host, non_blocking=True)
+            g.timestep.fill_(float(timestep))
+            out = g.replay()
+        else:
+            vid = vid_host.to(device, non_blocking=True)
+            txt = txt_host.to(device, non_blocking=True)
+            ts = torch.tensor([[txt.shape[0]]], dtype=torch.long)
+            t = torch.full((1,), float(timestep), dtype=torch.float32, device=device)
+            out = self.forward(vid, txt, None, ts, t, grid=grid)
         out_host.copy_(out, non_blocking=True)
         torch.cuda.current_stream(device).synchronize()
         return out_host
+
+    def graph_for(self, grid: Tuple[int, int, int], txt_len: int, device: torch.device,
+                  dtype: torch.dtype = torch.bfloat16) -> "GraphedForward":
+        """The captured forward for one (latent grid, text length); cached — a video pipeline sees a handful of shapes."""
+        cache = self.__dict__.setdefault("_graphs", {})
+        key = (tuple(grid), int(txt_len), str(device), dtype)
+        if key not in cache:
+            cache[key] = GraphedForward(self, grid, txt_len, device, dtype)
+        return cache[key]
+
+
+class GraphedForward:
+    """One NaDiT forward captured as a CUDA graph on static input / output buffers.
+
+    A forward at 2048x2048 is ~1,500 launches, many of them the text branch's few-microsecond kernels; launched one by
+    one from Python the GPU idles ~13 % of the step between them (profiles/r01_launch_list_*).  The reference has the
+    same shape of problem and answers it with ``torch.compile`` (model_configuration.py:1217-1219); here the launches
+    are already hand-written kernels, so the answer is stream capture: no tracing, no recompilation, one launch.
+    Everything the forward touches is stream-ordered on the capture stream (the C-ABI takes the stream explicitly) and
+    the window plan is resolved at capture time, so the graph holds no host work.
+
+    ``vid`` / ``txt`` / ``timestep`` are the static inputs (write them, then ``replay()``); the returned tensor is the
+    static output, overwritten by the next replay."""
+
+    def __init__(self, stack: "NaDiTStack", grid: Tuple[int, int, int], txt_len: int, device: torch.device,
+                 dtype: torch.dtype = torch.bfloat16, warmup: int = 2):
+        from . import ops
+        T2, H2, W2 = grid
+        c = stack.cfg
+        self.grid = tuple(grid)
+        self.vid = torch.zeros(T2 * H2 * W2, c["vid_in_channels"], dtype=dtype, device=device)
+        self.txt = torch.zeros(txt_len, c["txt_in_dim"], dtype=dtype, device=device)
+        self.timestep = torch.zeros(1, dtype=torch.float32, device=device)
+        self.txt_shape = torch.tensor([[txt_len]], dtype=torch.long)
+        cur = torch.cuda.current_stream(device)
+        side = torch.cuda.Stream(device)
+        side.wait_stream(cur)
+        with torch.cuda.stream(side), torch.no_grad():      # plans, cuBLAS workspaces, func attributes: all settled here
+            for _ in range(warmup):
+                stack.forward(self.vid, self.txt, None, self.txt_shape, self.timestep, grid=self.grid)
+        cur.wait_stream(side)
+        torch.cuda.synchronize(device)
+        n0 = ops.launch_count()
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph), torch.no_grad():
+            self.out = stack.forward(self.vid, self.txt, None, self.txt_shape, self.timestep, grid=self.grid)
+        self.launches_per_replay = ops.launch_count() - n0      # kernels of libseedvr2_b200.so inside the graph
+
+    def replay(self) -> torch.Tensor:
+        from . import ops
+        self.graph.replay()
+        ops.count_launches(self.launches_per_replay)
+        return self.out
