@@ -22,8 +22,9 @@ SIGNATURES = {
     "svr2_gate_residual_fwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_void_p]),
     "svr2_gate_residual_modnorm_fwd": (c_int, [c_void_p] * 8 + [c_int64, c_int, c_int, c_float, c_void_p]),
     "svr2_swiglu_fwd": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_void_p]),
-    "svr2_qkv_pack_fwd": (c_int, [c_void_p] * 7 + [c_int, c_int, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int,
+    "svr2_qkv_pack_fwd": (c_int, [c_void_p] * 7 + [c_int, c_int, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int,
                                   c_float, c_void_p, c_void_p, c_void_p, c_int64, c_void_p]),
+    "svr2_pack_rowmap": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p, c_int64, c_void_p]),
     "svr2_window_attn_worklist": (c_int, [POINTER(c_int32), c_int, c_int, POINTER(c_int32), c_int, POINTER(c_int64)]),
     "svr2_window_attn_fwd": (c_int, [c_void_p] * 5 + [c_int] * 7 + [c_int64, c_void_p, c_void_p, c_void_p, c_void_p]),
     "svr2_debug_attn_trace": (c_int, [c_void_p, c_int]),

@@ -9,10 +9,13 @@
 //   concat_win (na.py:320-424)                              -> output is already the packed varlen layout
 // Output: q,k,v [P, heads, 128] bf16, sequence k = [video rows of window k (row-major t,h,w) ; Lt text rows].
 //
-// HBM-bound: reads 3*heads*256 B per packed row, writes the same.  One CTA per two packed rows; a half-warp owns up to
-// five (q|k|v, head) slices of 128 values as 16-byte vectors (every access a fully coalesced 256-B segment) and issues
-// all of its loads before any arithmetic; products that the reference rounds to bf16 use HMUL2.BF16 (exact), the
-// division is one reciprocal + a Newton step.
+// HBM-bound: reads 3*heads*256 B per packed row, writes the same.  One CTA per packed row; a half-warp owns up to five
+// (q|k|v, head) slices of 128 values as 16-byte vectors (every access a fully coalesced 256-B segment) and issues all of
+// its loads before any arithmetic; products that the reference rounds to bf16 use HMUL2.BF16 (exact), the division is
+// one reciprocal + a Newton step.  Where the row comes from is read from the plan's packed-row map (svr2_pack_rowmap).
+// Measured (profiles/r01_run9_*): the kernel is latency bound, not issue bound — one row per CTA at 48 registers
+// (5 CTAs = 40 warps per SM) runs at 3.6 TB/s, two rows per CTA at 74 registers (3 CTAs) at 3.1 TB/s, and a version with
+// 30 % fewer instructions but 96-120 registers (2 CTAs) at 2.7 TB/s.
 #include "common.cuh"
 
 namespace svr2 {
@@ -25,7 +28,7 @@ __device__ __forceinline__ float torch_linspace_m1_p1(int idx, int n) {
                          : __fsub_rn(1.0f, __fmul_rn(step, (float)(n - idx - 1)));
 }
 
-constexpr int kRowsPerCta = 2;     // packed rows per CTA
+constexpr int kRowsPerCta = 1;     // packed rows per CTA (the code below is written for 1 or 2)
 constexpr int kMaxItems = 5;       // (q|k|v, head) slices per half-warp: 16 half-warps x 5 >= 3 * 24 heads
 constexpr int kPackThreads = 256;
 
@@ -35,12 +38,13 @@ struct PackRow {
     int valid, is_txt, n_rot;
 };
 
-__global__ void __launch_bounds__(kPackThreads)
+__global__ void __launch_bounds__(kPackThreads, 5)
 qkv_pack_kernel(const __nv_bfloat16* __restrict__ qkv_vid, const __nv_bfloat16* __restrict__ qkv_txt,
                 const __nv_bfloat16* __restrict__ wq_vid, const __nv_bfloat16* __restrict__ wk_vid,
                 const __nv_bfloat16* __restrict__ wq_txt, const __nv_bfloat16* __restrict__ wk_txt,
                 const float* __restrict__ freqs, int n_freqs, int rope_kind, const int32_t* __restrict__ tab,
-                int n_windows, int H, int W, int txt_len, int heads, float eps, __nv_bfloat16* __restrict__ qp,
+                const int4* __restrict__ row_map, int n_windows, int H, int W, int txt_len, int heads, float eps,
+                __nv_bfloat16* __restrict__ qp,
                 __nv_bfloat16* __restrict__ kp, __nv_bfloat16* __restrict__ vp, int64_t P) {
     __shared__ float s_cos[kRowsPerCta][64], s_sin[kRowsPerCta][64];
     const int hl = threadIdx.x & 15;              // lane inside the half-warp: owns elements [8*hl, 8*hl+8)
@@ -57,20 +61,36 @@ qkv_pack_kernel(const __nv_bfloat16* __restrict__ qkv_vid, const __nv_bfloat16* 
         pr[r].valid = row < P;
         pr[r].is_txt = 0; pr[r].n_rot = 0; pr[r].src = qkv_vid;
         if (!pr[r].valid) continue;
-        // window of this packed row: last window whose row_start <= row
-        int lo = 0, hi = n_windows - 1;
-        while (lo < hi) {
-            const int mid = (lo + hi + 1) >> 1;
-            if (__ldg(tab + mid * SVR2_WIN_FIELDS + 6) <= row) lo = mid; else hi = mid - 1;
-        }
-        const Win w = load_win(tab, lo);
-        const int j = (int)row - w.row_start;
-        const bool is_txt = j >= w.n_vid;
-        int lt = 0, lh = 0, lw = 0;
-        if (is_txt) {
-            pr[r].src = qkv_txt + (int64_t)(j - w.n_vid) * qkv_stride;
+        bool is_txt;
+        int lt = 0, lh = 0, lw = 0, txt_row = 0, wnt = 1, wnh = 1, wnw = 1;
+        if (row_map != nullptr) {
+            // the plan's row map (svr2_pack_rowmap): one 16-B load instead of a search of the window table
+            const int4 m = __ldg(row_map + row);
+            is_txt = m.x < 0;
+            txt_row = -(m.x + 1);
+            lt = m.y & 0xffff; lh = (m.y >> 16) & 0xffff; lw = m.z;
+            pr[r].src = is_txt ? qkv_txt + (int64_t)txt_row * qkv_stride : qkv_vid + (int64_t)m.x * qkv_stride;
+            if (rope_kind == SVR2_ROPE_7B_PIX && !is_txt) {
+                const int32_t* t = tab + m.w * SVR2_WIN_FIELDS;
+                wnt = __ldg(t + 3); wnh = __ldg(t + 4); wnw = __ldg(t + 5);
+            }
         } else {
-            pr[r].src = qkv_vid + win_token(w, j, H, W, &lt, &lh, &lw) * qkv_stride;
+            // window of this packed row: last window whose row_start <= row
+            int lo = 0, hi = n_windows - 1;
+            while (lo < hi) {
+                const int mid = (lo + hi + 1) >> 1;
+                if (__ldg(tab + mid * SVR2_WIN_FIELDS + 6) <= row) lo = mid; else hi = mid - 1;
+            }
+            const Win w = load_win(tab, lo);
+            const int j = (int)row - w.row_start;
+            is_txt = j >= w.n_vid;
+            txt_row = j - w.n_vid;
+            wnt = w.nt; wnh = w.nh; wnw = w.nw;
+            if (is_txt) {
+                pr[r].src = qkv_txt + (int64_t)txt_row * qkv_stride;
+            } else {
+                pr[r].src = qkv_vid + win_token(w, j, H, W, &lt, &lh, &lw) * qkv_stride;
+            }
         }
         pr[r].is_txt = is_txt;
         pr[r].n_rot = (rope_kind == SVR2_ROPE_3B_MM || (rope_kind == SVR2_ROPE_7B_PIX && !is_txt)) ? 3 * n_freqs : 0;
@@ -89,14 +109,14 @@ qkv_pack_kernel(const __nv_bfloat16* __restrict__ qkv_vid, const __nv_bfloat16* 
                 const float f = __ldg(freqs + fi);
                 if (rope_kind == SVR2_ROPE_3B_MM) {
                     // video: positions (Lt + t, h, w) inside the window (rope.py:172); text row r: (r, r, r) (rope.py:173)
-                    const int pos = is_txt ? (j - w.n_vid) : (axis == 0 ? txt_len + lt : (axis == 1 ? lh : lw));
+                    const int pos = is_txt ? txt_row : (axis == 0 ? txt_len + lt : (axis == 1 ? lh : lw));
                     const float ang = __fmul_rn((float)pos, f);
                     c = cosf(ang);
                     sn = sinf(ang);
                 } else {
                     // 7B: linspace(-1,1,n) over the window's own extent; the angle AND cos/sin are bf16 tensors
                     // (freqs.to(q.dtype), dit_7b/rope.py:85; freqs.cos() of a bf16 tensor is bf16)
-                    const int n = axis == 0 ? w.nt : (axis == 1 ? w.nh : w.nw);
+                    const int n = axis == 0 ? wnt : (axis == 1 ? wnh : wnw);
                     const int idx = axis == 0 ? lt : (axis == 1 ? lh : lw);
                     const float ang = bf16r(__fmul_rn(torch_linspace_m1_p1(idx, n), f));
                     c = bf16r(cosf(ang));
@@ -156,12 +176,48 @@ qkv_pack_kernel(const __nv_bfloat16* __restrict__ qkv_vid, const __nv_bfloat16* 
     }
 }
 
+// one thread per packed row: the search every qkv_pack CTA used to repeat, done once per plan
+__global__ void pack_rowmap_kernel(const int32_t* __restrict__ tab, int n_windows, int H, int W, int4* __restrict__ row_map,
+                                   int64_t P) {
+    const int64_t row = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (row >= P) return;
+    int lo = 0, hi = n_windows - 1;
+    while (lo < hi) {
+        const int mid = (lo + hi + 1) >> 1;
+        if (__ldg(tab + mid * SVR2_WIN_FIELDS + 6) <= row) lo = mid; else hi = mid - 1;
+    }
+    const Win w = load_win(tab, lo);
+    const int j = (int)row - w.row_start;
+    int4 m = make_int4(0, 0, 0, lo);
+    if (j >= w.n_vid) {
+        m.x = -(1 + (j - w.n_vid));
+    } else {
+        int lt, lh, lw;
+        m.x = (int)win_token(w, j, H, W, &lt, &lh, &lw);
+        m.y = lt | (lh << 16);
+        m.z = lw;
+    }
+    row_map[row] = m;
+}
+
 }  // namespace svr2
+
+extern "C" int svr2_pack_rowmap(const int32_t* win_table, int n_windows, int T, int H, int W, int txt_len, int32_t* row_map,
+                                int64_t P, void* stream) {
+    SVR2_CHECK_ARG(win_table && row_map && n_windows > 0 && P > 0 && P < ((int64_t)1 << 31), "svr2_pack_rowmap: bad arguments");
+    SVR2_CHECK_ARG(T > 0 && H > 0 && W > 0 && T < 65536 && H < 65536 && (int64_t)T * H * W < ((int64_t)1 << 31) && txt_len >= 0,
+                   "svr2_pack_rowmap: grid %dx%dx%d out of range", T, H, W);
+    svr2::pack_rowmap_kernel<<<(unsigned)((P + 255) / 256), 256, 0, (cudaStream_t)stream>>>(win_table, n_windows, H, W,
+                                                                                             (int4*)row_map, P);
+    SVR2_CHECK_LAUNCH("svr2_pack_rowmap");
+    return SVR2_OK;
+}
 
 extern "C" int svr2_qkv_pack_fwd(const void* qkv_vid, const void* qkv_txt, const void* wq_vid, const void* wk_vid,
                                  const void* wq_txt, const void* wk_txt, const float* freqs, int n_freqs, int rope_kind,
-                                 const int32_t* win_table, int n_windows, int T, int H, int W, int txt_len, int heads,
-                                 float eps, void* q_pack, void* k_pack, void* v_pack, int64_t P, void* stream) {
+                                 const int32_t* win_table, const int32_t* row_map, int n_windows, int T, int H, int W,
+                                 int txt_len, int heads, float eps, void* q_pack, void* k_pack, void* v_pack, int64_t P,
+                                 void* stream) {
     SVR2_CHECK_ARG(qkv_vid && wq_vid && wk_vid && win_table && q_pack && k_pack && v_pack, "svr2_qkv_pack_fwd: null pointer");
     SVR2_CHECK_ARG(txt_len == 0 || (qkv_txt && wq_txt && wk_txt), "svr2_qkv_pack_fwd: text inputs missing");
     SVR2_CHECK_ARG(heads > 0 && n_windows > 0 && P > 0 && P < ((int64_t)1 << 31), "svr2_qkv_pack_fwd: bad sizes");
@@ -175,7 +231,7 @@ extern "C" int svr2_qkv_pack_fwd(const void* qkv_vid, const void* qkv_txt, const
     svr2::qkv_pack_kernel<<<grid, svr2::kPackThreads, 0, (cudaStream_t)stream>>>(
         (const __nv_bfloat16*)qkv_vid, (const __nv_bfloat16*)qkv_txt, (const __nv_bfloat16*)wq_vid,
         (const __nv_bfloat16*)wk_vid, (const __nv_bfloat16*)wq_txt, (const __nv_bfloat16*)wk_txt, freqs, n_freqs,
-        rope_kind, win_table, n_windows, H, W, txt_len, heads, eps, (__nv_bfloat16*)q_pack, (__nv_bfloat16*)k_pack,
+        rope_kind, win_table, (const int4*)row_map, n_windows, H, W, txt_len, heads, eps, (__nv_bfloat16*)q_pack, (__nv_bfloat16*)k_pack,
         (__nv_bfloat16*)v_pack, P);
     SVR2_CHECK_LAUNCH("svr2_qkv_pack_fwd");
     return SVR2_OK;

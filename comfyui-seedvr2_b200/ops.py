@@ -174,8 +174,9 @@ def qkv_pack(plan: WindowPlan, qkv_vid: torch.Tensor, qkv_txt: torch.Tensor, wq_
     d = plan.on(dev)
     _call("svr2_qkv_pack_fwd", 1, dev, _lib.lib().svr2_qkv_pack_fwd,
           qkv_vid.data_ptr(), qkv_txt.data_ptr(), wq_vid.data_ptr(), wk_vid.data_ptr(), wq_txt.data_ptr(),
-          wk_txt.data_ptr(), _ptr(freqs), n_freqs, rope_kind, d["table"].data_ptr(), plan.n_windows, T, H, W,
-          plan.txt_len, heads, float(eps), q.data_ptr(), k.data_ptr(), v.data_ptr(), P, _stream(qkv_vid))
+          wk_txt.data_ptr(), _ptr(freqs), n_freqs, rope_kind, d["table"].data_ptr(), plan.row_map(dev).data_ptr(),
+          plan.n_windows, T, H, W, plan.txt_len, heads, float(eps), q.data_ptr(), k.data_ptr(), v.data_ptr(), P,
+          _stream(qkv_vid))
     return q, k, v
 
 

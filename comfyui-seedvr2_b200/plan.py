@@ -88,6 +88,22 @@ class WindowPlan:
             self._dev[device] = d
         return d
 
+    def row_map(self, device: torch.device) -> torch.Tensor:
+        """[P, 4] int32 packed-row map (svr2_pack_rowmap), built once per plan and device: source row, local (t, h, w),
+        window — what every svr2_qkv_pack_fwd CTA would otherwise search the window table for."""
+        d = self.on(device)
+        if "row_map" not in d:
+            if torch.device(device).type != "cuda":
+                raise RuntimeError("svr2_pack_rowmap runs on a CUDA device only (no CPU fallback)")
+            rm = torch.empty(self.packed_rows, 4, dtype=torch.int32, device=device)
+            T, H, W = self.grid
+            with torch.cuda.device(device):
+                stream = torch.cuda.current_stream(device).cuda_stream
+                _lib.check(_lib.lib().svr2_pack_rowmap(d["table"].data_ptr(), self.n_windows, T, H, W, self.txt_len,
+                                                       rm.data_ptr(), self.packed_rows, stream), "svr2_pack_rowmap")
+            d["row_map"] = rm
+        return d["row_map"]
+
     def index_tensors(self, device: torch.device):
         """(tgt_idx, src_idx, window_shape, cu_seqlens) on `device`, computed by svr2_window_index (bit-exact)."""
         d = self.on(device)

@@ -98,11 +98,21 @@ int svr2_swiglu_fwd(const void* gate, const void* up, void* out, int64_t n, void
  * [P, heads, 128]: sequence k = [video rows of window k ; all Lt text rows].
  *   qkv_vid [L, 3, heads, 128] bf16 (token order), qkv_txt [Lt, 3, heads, 128] bf16
  *   wq_vid,wk_vid,wq_txt,wk_txt [128] bf16;  freqs fp32 [n_freqs] = the checkpoint buffer attn.rope.rope.freqs
+ *   row_map: svr2_pack_rowmap's table for this plan, or NULL (every CTA then finds its rows' windows itself — slower)
  */
 int svr2_qkv_pack_fwd(const void* qkv_vid, const void* qkv_txt, const void* wq_vid, const void* wk_vid,
                       const void* wq_txt, const void* wk_txt, const float* freqs, int n_freqs, int rope_kind,
-                      const int32_t* win_table, int n_windows, int T, int H, int W, int txt_len, int heads,
-                      float eps, void* q_pack, void* k_pack, void* v_pack, int64_t P, void* stream);
+                      const int32_t* win_table, const int32_t* row_map, int n_windows, int T, int H, int W, int txt_len,
+                      int heads, float eps, void* q_pack, void* k_pack, void* v_pack, int64_t P, void* stream);
+
+/*
+ * Packed-row map of a window plan, computed once per plan on the device (pure integer): for packed row r
+ *   row_map[r] = { source (video token index >= 0, or -(1 + text row)), local t | local h << 16, local w, window }.
+ * It is the per-row form of na.window_idx (na.py:616-641) + the text repeat order (mmattn.py:223-236); svr2_qkv_pack_fwd
+ * reads it instead of searching the window table in every CTA.   row_map [P][4] int32 on the device.
+ */
+int svr2_pack_rowmap(const int32_t* win_table, int n_windows, int T, int H, int W, int txt_len, int32_t* row_map,
+                     int64_t P, void* stream);
 
 /*
  * Work list for svr2_window_attn_fwd, host side, pure integer: one item = (window, pair of 128-row query tiles), items

@@ -151,6 +151,36 @@ def test_qkv_pack(svr2, cuda, model, grid, shifted, heads):
         assert float((d > 0).float().mean()) < 5e-3, f"{nm}: {float((d > 0).float().mean())} of elements differ"
 
 
+@pytest.mark.parametrize("model,grid,shifted,heads", [("3b", (1, 32, 32), True, 3), ("7b", (5, 17, 30), True, 3), ("3b", (2, 20, 36), False, 2)])
+def test_qkv_pack_row_map_equals_table_search(svr2, cuda, model, grid, shifted, heads):
+    """The plan's packed-row map (svr2_pack_rowmap) is an integer restatement of the per-CTA window search: both paths of
+    svr2_qkv_pack_fwd must give bit-identical q, k, v; the map itself is checked against the oracle's window index."""
+    qkv_v, qkv_t, w, freqs = _pack_case(model, grid, shifted, heads, 7)
+    plan = svr2.get_plan(grid, (4, 3, 3), shifted, cases.TXT_LEN)
+    kind = svr2.ops.ROPE_3B_MM if model == "3b" else svr2.ops.ROPE_7B_PIX
+    dq, dt = qkv_v.to(cuda), qkv_t.to(cuda)
+    dw = [t.to(cuda) for t in w]
+    fr = freqs.to(cuda)
+    q1, k1, v1 = svr2.ops.qkv_pack(plan, dq, dt, *dw, fr, kind, heads, 1e-5)
+    L = svr2._lib.lib()
+    P = plan.packed_rows
+    q0, k0, v0 = (torch.empty(P, heads, 128, dtype=torch.bfloat16, device=cuda) for _ in range(3))
+    T, H, W = grid
+    rc = L.svr2_qkv_pack_fwd(dq.data_ptr(), dt.data_ptr(), *[t.data_ptr() for t in dw], fr.data_ptr(), fr.numel(), kind,
+                             plan.on(cuda)["table"].data_ptr(), None, plan.n_windows, T, H, W, plan.txt_len, heads, 1e-5,
+                             q0.data_ptr(), k0.data_ptr(), v0.data_ptr(), P, torch.cuda.current_stream().cuda_stream)
+    svr2._lib.check(rc, "svr2_qkv_pack_fwd")
+    torch.cuda.synchronize()
+    for a, b, nm in ((q0, q1, "q"), (k0, k1, "k"), (v0, v1, "v")):
+        assert torch.equal(a, b), f"{nm}: row-map path differs from the table-search path"
+    rm = plan.row_map(cuda).cpu().numpy()
+    tgt = geometry.window_index(T, H, W, plan.window, plan.shifted, plan.txt_len)[0]      # video token of every window slot
+    vid_rows = rm[:, 0] >= 0
+    assert np.array_equal(rm[vid_rows, 0], tgt), "video rows of the map are na.window_idx in packed order"
+    txt = -(rm[~vid_rows, 0] + 1)
+    assert np.array_equal(txt, np.tile(np.arange(plan.txt_len), plan.n_windows)), "text rows repeat 0..Lt-1 per window"
+
+
 # ----------------------------------------------------------------------------------------------- window attention
 def _sdpa_reference(plan, q, k, v, heads):
     """fp32 per-window attention on the packed layout (the reference's pytorch_varlen_attention semantics)."""
