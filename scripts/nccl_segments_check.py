@@ -1,0 +1,33 @@
+"""NCCL check of the temporal-segment halo exchange on real GPUs (run under torchrun):
+every rank makes its deterministic output segment, halo_exchange_and_gather stitches on rank 0, and rank 0 compares with the
+sequential parent loop (segments.stitch_sequential) on the same chunks — the reference's order, inference_cli.py:1163-1198."""
+import os, sys
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+import torch.distributed as dist
+import seedvr2_b200 as svr2
+from seedvr2_b200 import segments
+
+rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+torch.cuda.set_device(local)
+dev = torch.device("cuda", local)
+dist.init_process_group("nccl", device_id=dev)
+ok = True
+for total, overlap, hw in ((41, 4, (36, 64)), (23, 2, (20, 20)), (16, 0, (8, 8)), (9, 3, (8, 8))):
+    ranges = segments.segment_ranges(total, world, overlap)
+    def chunk(r):
+        s, e = ranges[r]
+        g = torch.Generator().manual_seed(100 + r)
+        return torch.rand(e - s, hw[0], hw[1], 3, generator=g)
+    mine = chunk(rank).to(dev)
+    out = segments.halo_exchange_and_gather(mine, overlap)
+    if rank == 0:
+        ref = segments.stitch_sequential([chunk(r).to(dev) for r in range(world)], overlap)
+        same = out.shape == ref.shape and torch.equal(out, ref)
+        ok &= bool(same)
+        print(f"total {total} overlap {overlap} world {world}: stitched {tuple(out.shape)} {'== sequential parent loop (bit-exact)' if same else 'MISMATCH'}")
+dist.barrier()
+if rank == 0:
+    print("NCCL segments check", "PASSED" if ok else "FAILED")
+dist.destroy_process_group()
+sys.exit(0 if ok else 1)
