@@ -66,6 +66,16 @@ constexpr uint32_t TMEM_COLS = 512;
 #define SVR2_FMA8 3
 #endif
 constexpr int kFmaEighths = SVR2_FMA8;              // of every 8 exp2 pairs, this many are evaluated on the FMA pipe (softmax_row.cuh)
+// Exponent reference of a row, in the log2 domain.  Default: the exact scaled row max (P <= 1, the rounding pattern of the
+// reference's fp32 softmax).  SVR2_INT_REF=1 rounds it UP to an integer, which makes every lazy rescale an exact power of two;
+// measured: it does NOT make the result independent of the tiling (the FFMA that forms s k - c rounds differently for a
+// different c), and it moved three block outputs by one bf16 ulp against the golden vectors — kept off.
+#ifndef SVR2_INT_REF
+#define SVR2_INT_REF 0
+#endif
+__device__ __forceinline__ float ref_of(float row_max) {
+    return SVR2_INT_REF ? ceilf(row_max * kScaleLog2) : row_max * kScaleLog2;
+}
 constexpr float kRescaleThreshold = 8.0f;   // lazy rescale: tolerate P up to 2^8 before touching O
 
 // barrier slots (8 bytes each), per query tile i: slot + i
@@ -473,14 +483,14 @@ window_attn_tc2_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
                 chunk_max8(m8, s + 96);
                 const float mx = fmaxf(max3(m8[0], m8[1], m8[2]), max3(max3(m8[3], m8[4], m8[5]), m8[6], m8[7]));
                 if (j == 0) {
-                    m = mx;
+                    m = ref_of(mx);
                 } else {
                     // lazy rescale: O_i and l keep the old reference until the row max has moved by more than 2^8
-                    const bool need = (mx - m) * kScaleLog2 > kRescaleThreshold;
+                    const bool need = mx * kScaleLog2 - m > kRescaleThreshold;
                     if (__any_sync(0xffffffffu, need)) {                    // warp-uniform: tcgen05.ld/st are warp collectives
                         // S_i(j) was committed after P_i V(j-1): O_i is quiescent until this thread publishes P(j)
-                        const float m_new = need ? mx : m;
-                        const float alpha = ex2((m - m_new) * kScaleLog2);
+                        const float m_new = need ? ref_of(mx) : m;
+                        const float alpha = ex2(m - m_new);                    // an exact power of two
                         l *= alpha;
                         m = m_new;
 #pragma unroll 1
@@ -494,7 +504,7 @@ window_attn_tc2_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
                         }
                     }
                 }
-                const float mb = m * kScaleLog2;
+                const float mb = m;
                 // bf16 P overwrites the front of S_i chunk by chunk (the whole row is already in registers); kFmaEighths/8 of the
                 // exponentials run on the FMA pipe, the rest on MUFU
                 const uint32_t tP3 = tS + 16 * (nch - 1);

@@ -205,7 +205,7 @@ ATTN_CASES = [((2, 20, 36), False, 2), ((1, 32, 32), True, 3), ((5, 17, 30), Tru
               ((9, 30, 54), False, 1), ((3, 46, 81), True, 1)]
 
 
-@pytest.mark.parametrize("impl", ["tcgen05", "v3", "v1", "mma"])
+@pytest.mark.parametrize("impl", ["tcgen05", "v4", "v3", "v1", "mma"])
 @pytest.mark.parametrize("grid,shifted,heads", ATTN_CASES)
 def test_window_attn_vs_fp32(svr2, cuda, monkeypatch, impl, grid, shifted, heads):
     monkeypatch.setenv("SVR2_ATTN_IMPL", impl)
