@@ -71,12 +71,7 @@ modnorm_kernel(const __nv_bfloat16* __restrict__ x,       // FUSE_GATE: h (branc
         for (int k = 0; k < kRows; ++k) {
             if (FUSE_GATE) {
                 if (act && (row0 + k < L)) {
-                    float f[8], rf[8];
-                    unpack8(mul8(v[k], g_p), f);                                     // mul_ rounds to bf16 ...
-                    unpack8(r[k], rf);
-#pragma unroll
-                    for (int i = 0; i < 8; ++i) f[i] += rf[i];                       // ... then the add rounds (pack8)
-                    v[k] = pack8(f);
+                    v[k] = add8_rn(mul8_rn(v[k], g_p), r[k]);                         // mul_ rounds to bf16, then the add rounds
                     stg8(out + (row0 + k) * D + col, v[k]);
                 }
             }
@@ -104,14 +99,9 @@ modnorm_kernel(const __nv_bfloat16* __restrict__ x,       // FUSE_GATE: h (branc
             unpack8(v[k], f);
 #pragma unroll
             for (int i = 0; i < 8; ++i) f[i] = div_rcp(f[i], rms, rcp);
-            if (has_mod) {
-                float sh[8];
-                unpack8(mul8(pack8(f), sc_p), f);                                     // (x / rms) -> bf16, * scale -> bf16
-                unpack8(sh_p, sh);
-#pragma unroll
-                for (int i = 0; i < 8; ++i) f[i] += sh[i];
-            }
-            stg8(y + (row0 + k) * D + col, pack8(f));
+            bf16x8 yv = pack8(f);                                                     // (x / rms) -> bf16
+            if (has_mod) yv = add8_rn(mul8_rn(yv, sc_p), sh_p);                       // * scale -> bf16, + shift -> bf16
+            stg8(y + (row0 + k) * D + col, yv);
         }
     }
 }
@@ -142,22 +132,12 @@ gate_residual_kernel(const __nv_bfloat16* __restrict__ h, const __nv_bfloat16* _
         }
 #pragma unroll
         for (int u = 0; u < 4; ++u) {
-            float a[8], b[8];
-            unpack8(has_gate ? mul8(hv[u], g_p) : hv[u], a);
-            unpack8(rv[u], b);
-#pragma unroll
-            for (int i = 0; i < 8; ++i) a[i] += b[i];
-            stg8_stream(out + (row + u * step) * D + col, pack8(a));
+            stg8_stream(out + (row + u * step) * D + col, add8_rn(has_gate ? mul8_rn(hv[u], g_p) : hv[u], rv[u]));
         }
     }
     for (; row < L; row += step) {
-        float a[8], b[8];
         const bf16x8 hv = ldg8_stream(h + row * D + col);
-        unpack8(has_gate ? mul8(hv, g_p) : hv, a);
-        unpack8(ldg8_stream(resid + row * D + col), b);
-#pragma unroll
-        for (int i = 0; i < 8; ++i) a[i] += b[i];
-        stg8_stream(out + row * D + col, pack8(a));
+        stg8_stream(out + row * D + col, add8_rn(has_gate ? mul8_rn(hv, g_p) : hv, ldg8_stream(resid + row * D + col)));
     }
 }
 

@@ -81,6 +81,23 @@ __device__ __forceinline__ bf16x8 mul8(const bf16x8& a, const bf16x8& b) {
     for (int i = 0; i < 4; ++i) r.v[i] = __hmul2(a.v[i], b.v[i]);
     return r;
 }
+// a * b and a + b as the reference's bf16 tensor ops compute them (fp32 result rounded once to bf16) on packed pairs.
+// The product of two bf16 values is exact in fp32; their sum is exact in fp32 unless the exponents are > 16 bits apart,
+// where the small operand cannot reach the bf16 rounding boundary either way — so HMUL2.BF16 / HADD2.BF16 give the same
+// bits as "fp32 op, then round".  The _rn intrinsics keep the compiler from contracting the pair into one HFMA2 (which
+// would round once instead of twice).
+__device__ __forceinline__ bf16x8 mul8_rn(const bf16x8& a, const bf16x8& b) {
+    bf16x8 r;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) r.v[i] = __hmul2_rn(a.v[i], b.v[i]);
+    return r;
+}
+__device__ __forceinline__ bf16x8 add8_rn(const bf16x8& a, const bf16x8& b) {
+    bf16x8 r;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) r.v[i] = __hadd2_rn(a.v[i], b.v[i]);
+    return r;
+}
 // x / d with d's reciprocal precomputed: one Newton step on the residual gives the correctly rounded fp32 quotient
 // (the core of the IEEE division sequence without its special-case handling; operands here are finite and normal).
 __device__ __forceinline__ float div_rcp(float x, float d, float rcp) {
