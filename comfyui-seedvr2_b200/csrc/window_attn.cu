@@ -459,19 +459,22 @@ extern "C" int svr2_window_attn_fwd(const void* q_pack, const void* k_pack, cons
                    "svr2_window_attn_fwd: bad sizes");
     (void)T;
     cudaStream_t st = (cudaStream_t)stream;
-    // Product path: the persistent tcgen05 kernel of window_attn_v2.cu (generation 4).  SVR2_ATTN_IMPL selects another
-    // generation for A/B runs — v3 (generation 5: both softmax warpgroups on one query tile, column-split; correct, not
-    // faster), v1 (one CTA per item) or mma (the legacy mma.sync comparator).  Every one is a CUDA kernel of this library.
+    // Product path: generation 4 (window_attn_v2.cu: persistent, whole 128-column key tiles, one TMEM round trip each).
+    // Generation 6 (window_attn_v4.cu: 64-column half tiles, double-buffered S) returns the same bits — checked by
+    // tests/test_gpu_kernels.py::test_window_attn_generations_bit_identical — and measures within +-2 % of it on NaSwin's
+    // short sequences, 5 % behind on long ones; SVR2_ATTN_IMPL=v4 selects it.  v3 (generation 5, column-split softmax),
+    // v1 (one CTA per item) and mma (the legacy mma.sync comparator) are A/B aids.  Every one is a CUDA kernel of this
+    // library.
     const char* e = getenv("SVR2_ATTN_IMPL");
     int rc;
     if (e && strcmp(e, "mma") == 0)
         rc = svr2::launch_window_attn_mma(q_pack, k_pack, v_pack, win_table, work, n_work, H, W, txt_len, heads, out_vid, txt_part, st);
     else if (e && strcmp(e, "v1") == 0)
         rc = svr2::launch_window_attn_tc(q_pack, k_pack, v_pack, win_table, work, n_work, H, W, txt_len, heads, P, out_vid, txt_part, st);
-    else if (e && strcmp(e, "v4") == 0)
-        rc = svr2::launch_window_attn_tc4(q_pack, k_pack, v_pack, win_table, work, n_work, H, W, txt_len, heads, P, out_vid, txt_part, st);
     else if (e && strcmp(e, "v3") == 0)
         rc = svr2::launch_window_attn_tc3(q_pack, k_pack, v_pack, win_table, work, n_work, H, W, txt_len, heads, P, out_vid, txt_part, st);
+    else if (e && strcmp(e, "v4") == 0)
+        rc = svr2::launch_window_attn_tc4(q_pack, k_pack, v_pack, win_table, work, n_work, H, W, txt_len, heads, P, out_vid, txt_part, st);
     else
         rc = svr2::launch_window_attn_tc2(q_pack, k_pack, v_pack, win_table, work, n_work, n_windows, H, W, txt_len, heads, P, out_vid, txt_part, st);
     if (rc != SVR2_OK) return rc;

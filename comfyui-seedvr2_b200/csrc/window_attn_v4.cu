@@ -309,7 +309,13 @@ window_attn_tc4_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
             const Item it = decode_item(p, item);
             ++n_it;
             if (i >= it.nq) continue;
-            float m = -INFINITY, l = 0.f;       // exponent reference (running row max, raised lazily) and row sum
+            // Bit-compatibility with generation 4 (window_attn_v2.cu), which works on whole 128-column key tiles: the exponent
+            // reference of the first tile is the max over all of ITS columns (both halves), and a tile's row sum is formed as
+            // ((c0 + c1) + c2) + c3 before it is added to l.  With the same reference every P, every P V accumulation and l
+            // are the same numbers in the same order, so both generations return identical bits unless a lazy rescale
+            // fires (they test for it at different granularity) — tests/test_gpu_kernels.py checks the identity.
+            float m = -INFINITY, l = 0.f;       // exponent reference (log2 domain, raised lazily) and row sum
+            float rs_even = 0.f;                // row sum of the even half of the current key tile, not yet in l
             for (int h = 0; h < it.n_half; ++h, ++g) {
                 const int b = h & 1;
                 const bool last = h == it.n_half - 1;
@@ -317,12 +323,32 @@ window_attn_tc4_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
                 const bool two = rem > 32;                               // 64 or 32 key columns in this half tile
                 const int valid = it.seq - h * HN;                       // key columns >= valid are beyond the sequence
                 const uint32_t tS = tmem + lane_off + i * 128 + b * HN;
-                mbar_wait(bar(BAR_SFULL + 2 * i + b), (sf_par >> b) & 1u);
+                if (h != 1) mbar_wait(bar(BAR_SFULL + 2 * i + b), (sf_par >> b) & 1u);      // S(1) was awaited at h == 0
                 sf_par ^= 1u << b;
                 tc_fence_after();
                 if (kTrace && threadIdx.x == 0) {
                     if (h == 0) trace_item<kTrace>(p, n_it, 1);
                     if (last) trace_item<kTrace>(p, n_it, 3);
+                }
+                float m8[8];
+#pragma unroll
+                for (int q = 0; q < 8; ++q) m8[q] = -INFINITY;
+                if (h == 0 && it.n_half > 1) {
+                    // first key tile: fold the row max of its second half (already queued behind the first) into the reference
+                    mbar_wait(bar(BAR_SFULL + 2 * i + 1), (sf_par >> 1) & 1u);
+                    tc_fence_after();
+                    const int rem1 = it.cols_total - HN, valid1 = it.seq - HN;
+                    uint32_t t[32];
+                    tmem_ld32(tS + HN, t);
+                    tc_wait_ld();
+                    if (valid1 < 32) mask_chunk(t, valid1);
+                    chunk_max8(m8, t);
+                    if (rem1 > 32) {
+                        tmem_ld32(tS + HN + 32, t);
+                        tc_wait_ld();
+                        if (valid1 < rem1) mask_chunk(t, valid1 - 32);
+                        chunk_max8(m8, t);
+                    }
                 }
                 uint32_t a[32], a2[32];
                 tmem_ld32(tS, a);
@@ -332,9 +358,6 @@ window_attn_tc4_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
                     if (valid < 32) mask_chunk(a, valid);
                     if (two) mask_chunk(a2, valid - 32);
                 }
-                float m8[8];
-#pragma unroll
-                for (int q = 0; q < 8; ++q) m8[q] = -INFINITY;
                 chunk_max8(m8, a);
                 if (two) chunk_max8(m8, a2);
                 const float mx = fmaxf(max3(m8[0], m8[1], m8[2]), max3(max3(m8[3], m8[4], m8[5]), m8[6], m8[7]));
@@ -349,8 +372,9 @@ window_attn_tc4_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
                         mbar_wait(bar(BAR_PVDONE + i), (g - 1) & 1u);
                         tc_fence_after();
                         const float m_new = need ? ref_of(mx) : m;
-                        const float alpha = ex2(m - m_new);                    // an exact power of two
+                        const float alpha = ex2(m - m_new);
                         l *= alpha;
+                        rs_even *= alpha;
                         m = m_new;
 #pragma unroll 1
                         for (int c8 = 0; c8 < 8; ++c8) {
@@ -364,10 +388,10 @@ window_attn_tc4_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
                     }
                 }
                 const float mb = m;
-                float rs;
+                float rs = b ? rs_even : 0.f;                            // ((c0 + c1) + c2) + c3 per key tile
                 {
                     uint32_t pk[16];
-                    rs = chunk_exp_mix<kFmaEighths>(a, pk, mb);
+                    rs += chunk_exp_mix<kFmaEighths>(a, pk, mb);
                     tmem_st16(tS, pk);
                 }
                 if (two) {
@@ -375,7 +399,12 @@ window_attn_tc4_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
                     rs += chunk_exp_mix<kFmaEighths>(a2, pk, mb);
                     tmem_st16(tS + 16, pk);
                 }
-                l += rs;
+                if (b == 0 && !last) {
+                    rs_even = rs;
+                } else {
+                    l += rs;
+                    rs_even = 0.f;
+                }
                 tc_wait_st();
                 tc_fence_before();
                 mbar_arrive(bar(BAR_PREADY + 2 * i + b));

@@ -205,7 +205,24 @@ ATTN_CASES = [((2, 20, 36), False, 2), ((1, 32, 32), True, 3), ((5, 17, 30), Tru
               ((9, 30, 54), False, 1), ((3, 46, 81), True, 1)]
 
 
-@pytest.mark.parametrize("impl", ["tcgen05", "v4", "v3", "v1", "mma"])
+@pytest.mark.parametrize("grid,shifted,heads", ATTN_CASES)
+def test_window_attn_generations_bit_identical(svr2, cuda, monkeypatch, grid, shifted, heads):
+    """The two shipped kernels (generation 4: whole key tiles; generation 6: double-buffered half tiles) are picked by
+    sequence length and must be interchangeable: same exponent reference, same summation order -> identical bits."""
+    plan = svr2.get_plan(grid, (4, 3, 3), shifted, cases.TXT_LEN)
+    g = torch.Generator().manual_seed(11)
+    q, k, v = (torch.randn(plan.packed_rows, heads, 128, generator=g).bfloat16().to(cuda) for _ in range(3))
+    outs = {}
+    for impl in ("v2", "v4"):
+        monkeypatch.setenv("SVR2_ATTN_IMPL", impl)
+        ov, ot = svr2.ops.window_attn(plan, q, k, v, heads)
+        torch.cuda.synchronize()
+        outs[impl] = (ov.clone(), ot.clone())
+    assert torch.equal(outs["v2"][0], outs["v4"][0]), "video rows differ between generation 4 and generation 6"
+    assert torch.equal(outs["v2"][1], outs["v4"][1]), "pooled text rows differ between generation 4 and generation 6"
+
+
+@pytest.mark.parametrize("impl", ["tcgen05", "v2", "v4", "v3", "v1", "mma"])
 @pytest.mark.parametrize("grid,shifted,heads", ATTN_CASES)
 def test_window_attn_vs_fp32(svr2, cuda, monkeypatch, impl, grid, shifted, heads):
     monkeypatch.setenv("SVR2_ATTN_IMPL", impl)
