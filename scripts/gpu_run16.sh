@@ -1,2 +1,2 @@
 #!/bin/bash
-timeout 600 python -m pytest tests -m gpu -q -x 2>&1 | tail -2
+timeout 600 python -m pytest tests/test_gpu_stack.py -m gpu -q -x 2>&1 | tail -8
