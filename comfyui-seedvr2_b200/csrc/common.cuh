@@ -36,6 +36,14 @@ struct __align__(16) bf16x8 {
 // reference's bf16 path (ATen computes in fp32 and stores bf16).
 __device__ __forceinline__ float bf16r(float x) { return __bfloat162float(__float2bfloat16_rn(x)); }
 
+// register selects the compiler cannot turn into an indexed local-memory array
+__device__ __forceinline__ uint32_t sel_u32(bool c, uint32_t a, uint32_t b) {
+    uint32_t r;
+    asm("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %1, 0;\n\tselp.u32 %0, %2, %3, p;\n\t}" : "=r"(r) : "r"((uint32_t)c), "r"(a), "r"(b));
+    return r;
+}
+__device__ __forceinline__ int sel_i32(bool c, int a, int b) { return (int)sel_u32(c, (uint32_t)a, (uint32_t)b); }
+
 __device__ __forceinline__ bf16x8 ldg8(const __nv_bfloat16* p) {
     bf16x8 r;
     *reinterpret_cast<uint4*>(&r) = __ldg(reinterpret_cast<const uint4*>(p));

@@ -109,15 +109,15 @@ qkv_pack_kernel(const __nv_bfloat16* __restrict__ qkv_vid, const __nv_bfloat16* 
                 const float f = __ldg(freqs + fi);
                 if (rope_kind == SVR2_ROPE_3B_MM) {
                     // video: positions (Lt + t, h, w) inside the window (rope.py:172); text row r: (r, r, r) (rope.py:173)
-                    const int pos = is_txt ? txt_row : (axis == 0 ? txt_len + lt : (axis == 1 ? lh : lw));
+                    const int pos = is_txt ? txt_row : sel_i32(axis == 0, txt_len + lt, sel_i32(axis == 1, lh, lw));
                     const float ang = __fmul_rn((float)pos, f);
                     c = cosf(ang);
                     sn = sinf(ang);
                 } else {
                     // 7B: linspace(-1,1,n) over the window's own extent; the angle AND cos/sin are bf16 tensors
                     // (freqs.to(q.dtype), dit_7b/rope.py:85; freqs.cos() of a bf16 tensor is bf16)
-                    const int n = axis == 0 ? wnt : (axis == 1 ? wnh : wnw);
-                    const int idx = axis == 0 ? lt : (axis == 1 ? lh : lw);
+                    const int n = sel_i32(axis == 0, wnt, sel_i32(axis == 1, wnh, wnw));
+                    const int idx = sel_i32(axis == 0, lt, sel_i32(axis == 1, lh, lw));
                     const float ang = bf16r(__fmul_rn(torch_linspace_m1_p1(idx, n), f));
                     c = bf16r(cosf(ang));
                     sn = bf16r(sinf(ang));
@@ -130,20 +130,26 @@ qkv_pack_kernel(const __nv_bfloat16* __restrict__ qkv_vid, const __nv_bfloat16* 
     __syncthreads();
 
     const unsigned half_mask = 0xFFFFu << (threadIdx.x & 16);
-    const bf16x8 wqv = ldg8(wq_vid + col), wkv = ldg8(wk_vid + col);
-    const bf16x8 wqt = txt_len ? ldg8(wq_txt + col) : wqv, wkt = txt_len ? ldg8(wk_txt + col) : wkv;
 #pragma unroll
     for (int r = 0; r < kRowsPerCta; ++r) {
         if (!pr[r].valid) continue;              // uniform across the CTA
         const int64_t drow = ((int64_t)blockIdx.x * kRowsPerCta + r) * heads * SVR2_HEAD_DIM;
+        // the row's norm weights (video or text set): two L1-resident 16-B loads, selected by pointer
+        const uint4 wq = __ldg(reinterpret_cast<const uint4*>((pr[r].is_txt ? wq_txt : wq_vid) + col));
+        const uint4 wk = __ldg(reinterpret_cast<const uint4*>((pr[r].is_txt ? wk_txt : wk_vid) + col));
         float cs[4], sn[4];
 #pragma unroll
         for (int i = 0; i < 4; ++i) { cs[i] = s_cos[r][hl * 4 + i]; sn[i] = s_sin[r][hl * 4 + i]; }
 #pragma unroll
         for (int it = 0; it < kMaxItems; ++it) {
             const int item = hw_id + it * 16;
-            if (item >= n_items) continue;       // uniform across the half-warp
-            const int kind = item / heads, head = item - kind * heads;
+            // q | k | v without an integer division; kind 3 = no slice for this half-warp
+            const int kind = item >= n_items ? 3 : (item >= heads) + (item >= 2 * heads);
+            // both half-warps on the same path -> the row-sum butterfly can use the full mask (a computed mask costs a
+            // MATCH / REDUX preamble per shuffle); all 32 lanes reach this line in every iteration
+            const bool uni = __shfl_xor_sync(0xffffffffu, kind, 16) == kind;
+            if (kind == 3) continue;             // uniform across the half-warp
+            const int head = item - kind * heads;
             __nv_bfloat16* dst = (kind == 0 ? qp : (kind == 1 ? kp : vp)) + drow + head * SVR2_HEAD_DIM + col;
             if (kind == 2) {                     // v: gather only
                 stg8(dst, raw[r][it]);
@@ -155,14 +161,22 @@ qkv_pack_kernel(const __nv_bfloat16* __restrict__ qkv_vid, const __nv_bfloat16* 
             float ss = 0.f;
 #pragma unroll
             for (int i = 0; i < 8; ++i) ss += sq[i];
+            if (uni) {
 #pragma unroll
-            for (int o = 8; o > 0; o >>= 1) ss += __shfl_xor_sync(half_mask, ss, o);     // the two halves may diverge
+                for (int o = 8; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);   // xor < 16 stays inside a half-warp
+            } else {
+#pragma unroll
+                for (int o = 8; o > 0; o >>= 1) ss += __shfl_xor_sync(half_mask, ss, o);     // the two halves diverged
+            }
             const float var = bf16r(ss * (1.0f / SVR2_HEAD_DIM));
             const float rms = bf16r(sqrtf(bf16r(var + eps)));
             const float rcp = __frcp_rn(rms);
 #pragma unroll
             for (int i = 0; i < 8; ++i) x[i] = div_rcp(x[i], rms, rcp);
-            const bf16x8 wgt = kind == 0 ? (pr[r].is_txt ? wqt : wqv) : (pr[r].is_txt ? wkt : wkv);
+            // field-wise selects (selp): a struct-valued ?: would go through local memory
+            bf16x8 wgt;
+            *reinterpret_cast<uint4*>(&wgt) = make_uint4(sel_u32(kind == 0, wq.x, wk.x), sel_u32(kind == 0, wq.y, wk.y),
+                                                         sel_u32(kind == 0, wq.z, wk.z), sel_u32(kind == 0, wq.w, wk.w));
             unpack8(mul8(pack8(x), wgt), x);                    // (x / rms) -> bf16, * weight -> bf16
             // interleaved-pair rotation in fp32, mul and add rounded separately like the two ATen ops
 #pragma unroll
