@@ -15,7 +15,11 @@
 // one reciprocal + a Newton step.  Where the row comes from is read from the plan's packed-row map (svr2_pack_rowmap).
 // Measured (profiles/r01_run9_*): the kernel is latency bound, not issue bound — one row per CTA at 48 registers
 // (5 CTAs = 40 warps per SM) runs at 3.6 TB/s, two rows per CTA at 74 registers (3 CTAs) at 3.1 TB/s, and a version with
-// 30 % fewer instructions but 96-120 registers (2 CTAs) at 2.7 TB/s.
+// 30 % fewer instructions but 96-120 registers (2 CTAs) at 2.7 TB/s.  A persistent variant that stages whole rows through
+// shared memory with 1-D bulk copies (3 stages x 4 rows, 512 threads) was correct but slower (149.5 us against 136.2 us at
+// C1): with the loads off the critical path the kernel is issue bound — ~5,200 warp instructions per row, 63 % issue-slot
+// use with 4 warps per scheduler (profiles/r01_qkv_pack_staged_experiment.txt) — so the exact-rounding arithmetic, not the
+// memory system, sets the floor (~85 us of issue at IPC 1 against 84 us of HBM time).
 #include "common.cuh"
 
 namespace svr2 {
@@ -26,6 +30,72 @@ __device__ __forceinline__ float torch_linspace_m1_p1(int idx, int n) {
     const float step = __fdiv_rn(2.0f, (float)(n - 1));
     return (idx < n / 2) ? __fadd_rn(-1.0f, __fmul_rn(step, (float)idx))
                          : __fsub_rn(1.0f, __fmul_rn(step, (float)(n - idx - 1)));
+}
+
+// cos / sin of rotary pair p of one packed row; pairs at or beyond n_rot rotate by (1, 0) = identity
+__device__ __forceinline__ void rope_pair(int rope_kind, int p, int n_rot, int n_freqs, const float* __restrict__ freqs,
+                                          bool is_txt, int txt_row, int txt_len, int lt, int lh, int lw, int wnt, int wnh,
+                                          int wnw, float* c_out, float* s_out) {
+    float c = 1.f, sn = 0.f;
+    if (p < n_rot) {
+        const int axis = p / n_freqs, fi = p - axis * n_freqs;
+        const float f = __ldg(freqs + fi);
+        if (rope_kind == SVR2_ROPE_3B_MM) {
+            // video: positions (Lt + t, h, w) inside the window (rope.py:172); text row r: (r, r, r) (rope.py:173)
+            const int pos = is_txt ? txt_row : sel_i32(axis == 0, txt_len + lt, sel_i32(axis == 1, lh, lw));
+            const float ang = __fmul_rn((float)pos, f);
+            c = cosf(ang);
+            sn = sinf(ang);
+        } else {
+            // 7B: linspace(-1,1,n) over the window's own extent; the angle AND cos/sin are bf16 tensors
+            // (freqs.to(q.dtype), dit_7b/rope.py:85; freqs.cos() of a bf16 tensor is bf16)
+            const int n = sel_i32(axis == 0, wnt, sel_i32(axis == 1, wnh, wnw));
+            const int idx = sel_i32(axis == 0, lt, sel_i32(axis == 1, lh, lw));
+            const float ang = bf16r(__fmul_rn(torch_linspace_m1_p1(idx, n), f));
+            c = bf16r(cosf(ang));
+            sn = bf16r(sinf(ang));
+        }
+    }
+    *c_out = c;
+    *s_out = sn;
+}
+
+// One (q|k, head) slice of 128 values held by a half-warp, 8 per thread: RMSNorm over the slice with the reference's bf16
+// rounding points (normalization.py:88-109), affine weight, interleaved-pair rotation (apply_rotary_emb).
+__device__ __forceinline__ bf16x8 norm_rope_slice(const bf16x8& raw, bool is_q, const uint4& wq, const uint4& wk,
+                                                  const float* cs, const float* sn, float eps, bool full_mask,
+                                                  unsigned half_mask) {
+    float x[8], sq[8];
+    unpack8(raw, x);
+    unpack8(mul8(raw, raw), sq);                        // x.pow(2) is a bf16 tensor
+    float ss = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) ss += sq[i];
+    if (full_mask) {     // both half-warps of the warp are here: no computed-mask (MATCH / REDUX) preamble per shuffle
+#pragma unroll
+        for (int o = 8; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);   // xor < 16 stays inside a half-warp
+    } else {
+#pragma unroll
+        for (int o = 8; o > 0; o >>= 1) ss += __shfl_xor_sync(half_mask, ss, o);
+    }
+    const float var = bf16r(ss * (1.0f / SVR2_HEAD_DIM));
+    const float rms = bf16r(sqrtf(bf16r(var + eps)));
+    const float rcp = __frcp_rn(rms);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) x[i] = div_rcp(x[i], rms, rcp);
+    // field-wise selects (selp): a struct-valued ?: would go through local memory
+    bf16x8 wgt;
+    *reinterpret_cast<uint4*>(&wgt) = make_uint4(sel_u32(is_q, wq.x, wk.x), sel_u32(is_q, wq.y, wk.y),
+                                                 sel_u32(is_q, wq.z, wk.z), sel_u32(is_q, wq.w, wk.w));
+    unpack8(mul8(pack8(x), wgt), x);                    // (x / rms) -> bf16, * weight -> bf16
+    // interleaved-pair rotation in fp32, mul and add rounded separately like the two ATen ops
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const float x0 = x[2 * i], x1 = x[2 * i + 1];
+        x[2 * i] = __fadd_rn(__fmul_rn(x0, cs[i]), __fmul_rn(-x1, sn[i]));
+        x[2 * i + 1] = __fadd_rn(__fmul_rn(x1, cs[i]), __fmul_rn(x0, sn[i]));
+    }
+    return pack8(x);
 }
 
 constexpr int kRowsPerCta = 1;     // packed rows per CTA (the code below is written for 1 or 2)
@@ -103,26 +173,8 @@ qkv_pack_kernel(const __nv_bfloat16* __restrict__ qkv_vid, const __nv_bfloat16* 
         // cos/sin of the row's rotary pairs: threads [64r, 64r+64) — overlaps the loads above
         const int p = (int)threadIdx.x - 64 * r;
         if (p >= 0 && p < 64) {
-            float c = 1.f, sn = 0.f;
-            if (p < pr[r].n_rot) {
-                const int axis = p / n_freqs, fi = p - axis * n_freqs;
-                const float f = __ldg(freqs + fi);
-                if (rope_kind == SVR2_ROPE_3B_MM) {
-                    // video: positions (Lt + t, h, w) inside the window (rope.py:172); text row r: (r, r, r) (rope.py:173)
-                    const int pos = is_txt ? txt_row : sel_i32(axis == 0, txt_len + lt, sel_i32(axis == 1, lh, lw));
-                    const float ang = __fmul_rn((float)pos, f);
-                    c = cosf(ang);
-                    sn = sinf(ang);
-                } else {
-                    // 7B: linspace(-1,1,n) over the window's own extent; the angle AND cos/sin are bf16 tensors
-                    // (freqs.to(q.dtype), dit_7b/rope.py:85; freqs.cos() of a bf16 tensor is bf16)
-                    const int n = sel_i32(axis == 0, wnt, sel_i32(axis == 1, wnh, wnw));
-                    const int idx = sel_i32(axis == 0, lt, sel_i32(axis == 1, lh, lw));
-                    const float ang = bf16r(__fmul_rn(torch_linspace_m1_p1(idx, n), f));
-                    c = bf16r(cosf(ang));
-                    sn = bf16r(sinf(ang));
-                }
-            }
+            float c, sn;
+            rope_pair(rope_kind, p, pr[r].n_rot, n_freqs, freqs, is_txt, txt_row, txt_len, lt, lh, lw, wnt, wnh, wnw, &c, &sn);
             s_cos[r][p] = c;        // pairs beyond n_rot rotate by (1, 0): identity, branch-free below
             s_sin[r][p] = sn;
         }
@@ -155,40 +207,11 @@ qkv_pack_kernel(const __nv_bfloat16* __restrict__ qkv_vid, const __nv_bfloat16* 
                 stg8(dst, raw[r][it]);
                 continue;
             }
-            float x[8], sq[8];
-            unpack8(raw[r][it], x);
-            unpack8(mul8(raw[r][it], raw[r][it]), sq);          // x.pow(2) is a bf16 tensor
-            float ss = 0.f;
-#pragma unroll
-            for (int i = 0; i < 8; ++i) ss += sq[i];
-            if (uni) {
-#pragma unroll
-                for (int o = 8; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);   // xor < 16 stays inside a half-warp
-            } else {
-#pragma unroll
-                for (int o = 8; o > 0; o >>= 1) ss += __shfl_xor_sync(half_mask, ss, o);     // the two halves diverged
-            }
-            const float var = bf16r(ss * (1.0f / SVR2_HEAD_DIM));
-            const float rms = bf16r(sqrtf(bf16r(var + eps)));
-            const float rcp = __frcp_rn(rms);
-#pragma unroll
-            for (int i = 0; i < 8; ++i) x[i] = div_rcp(x[i], rms, rcp);
-            // field-wise selects (selp): a struct-valued ?: would go through local memory
-            bf16x8 wgt;
-            *reinterpret_cast<uint4*>(&wgt) = make_uint4(sel_u32(kind == 0, wq.x, wk.x), sel_u32(kind == 0, wq.y, wk.y),
-                                                         sel_u32(kind == 0, wq.z, wk.z), sel_u32(kind == 0, wq.w, wk.w));
-            unpack8(mul8(pack8(x), wgt), x);                    // (x / rms) -> bf16, * weight -> bf16
-            // interleaved-pair rotation in fp32, mul and add rounded separately like the two ATen ops
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                const float x0 = x[2 * i], x1 = x[2 * i + 1];
-                x[2 * i] = __fadd_rn(__fmul_rn(x0, cs[i]), __fmul_rn(-x1, sn[i]));
-                x[2 * i + 1] = __fadd_rn(__fmul_rn(x1, cs[i]), __fmul_rn(x0, sn[i]));
-            }
-            stg8(dst, pack8(x));
+            stg8(dst, norm_rope_slice(raw[r][it], kind == 0, wq, wk, cs, sn, eps, uni, half_mask));
         }
     }
 }
+
 
 // one thread per packed row: the search every qkv_pack CTA used to repeat, done once per plan
 __global__ void pack_rowmap_kernel(const int32_t* __restrict__ tab, int n_windows, int H, int W, int4* __restrict__ row_map,
