@@ -93,12 +93,12 @@ modnorm_kernel(const __nv_bfloat16* __restrict__ x,       // FUSE_GATE: h (branc
             float tot = 0.f;
             for (int w = 0; w < n_warps; ++w) tot += s_part[buf][k][w];
             const float var = bf16r(tot * inv_d);                                     // .mean() -> bf16
-            const float rms = bf16r(sqrtf(bf16r(var + eps)));
-            const float rcp = __frcp_rn(rms);
+            const float rms = bf16r(sqrt_approx(bf16r(var + eps)));
+            const float rcp = rcp_approx(rms);
             float f[8];
             unpack8(v[k], f);
 #pragma unroll
-            for (int i = 0; i < 8; ++i) f[i] = div_rcp(f[i], rms, rcp);
+            for (int i = 0; i < 8; ++i) f[i] = f[i] * rcp;       // rounds to the same bf16 as x / rms (common.cuh)
             bf16x8 yv = pack8(f);                                                     // (x / rms) -> bf16
             if (has_mod) yv = add8_rn(mul8_rn(yv, sc_p), sh_p);                       // * scale -> bf16, + shift -> bf16
             stg8(y + (row0 + k) * D + col, yv);

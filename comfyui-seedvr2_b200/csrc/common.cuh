@@ -106,12 +106,20 @@ __device__ __forceinline__ bf16x8 add8_rn(const bf16x8& a, const bf16x8& b) {
     for (int i = 0; i < 4; ++i) r.v[i] = __hadd2_rn(a.v[i], b.v[i]);
     return r;
 }
-// x / d with d's reciprocal precomputed: one Newton step on the residual gives the correctly rounded fp32 quotient
-// (the core of the IEEE division sequence without its special-case handling; operands here are finite and normal).
-__device__ __forceinline__ float div_rcp(float x, float d, float rcp) {
-    const float q = x * rcp;
-    const float r = fmaf(-q, d, x);
-    return fmaf(r, rcp, q);
+// bf16(fp32(x / d)) for bf16-valued x and d, without the division.  The quotient of two 8-bit significands is never a
+// bf16 rounding midpoint (its odd part would have to exceed 8 bits) and lies at least 2^-17 (relative) away from one, so
+// x * rcp with rcp within a few fp32 ulps of 1/d rounds to the same bf16 value as the reference's correctly rounded fp32
+// division followed by its bf16 store.  The same holds for sqrt of a bf16 value (distance >= 2^-19).  Both checked
+// exhaustively over all significand pairs with the approximation perturbed by +-2 / +-4 ulps (tests/test_oracle_golden.py).
+__device__ __forceinline__ float rcp_approx(float d) {
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(d));
+    return r;
+}
+__device__ __forceinline__ float sqrt_approx(float v) {
+    float r;
+    asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(v));
+    return r;
 }
 
 __device__ __forceinline__ float warp_sum(float v) {

@@ -79,10 +79,10 @@ __device__ __forceinline__ bf16x8 norm_rope_slice(const bf16x8& raw, bool is_q, 
         for (int o = 8; o > 0; o >>= 1) ss += __shfl_xor_sync(half_mask, ss, o);
     }
     const float var = bf16r(ss * (1.0f / SVR2_HEAD_DIM));
-    const float rms = bf16r(sqrtf(bf16r(var + eps)));
-    const float rcp = __frcp_rn(rms);
+    const float rms = bf16r(sqrt_approx(bf16r(var + eps)));
+    const float rcp = rcp_approx(rms);
 #pragma unroll
-    for (int i = 0; i < 8; ++i) x[i] = div_rcp(x[i], rms, rcp);
+    for (int i = 0; i < 8; ++i) x[i] = x[i] * rcp;       // rounds to the same bf16 as x / rms (common.cuh)
     // field-wise selects (selp): a struct-valued ?: would go through local memory
     bf16x8 wgt;
     *reinterpret_cast<uint4*>(&wgt) = make_uint4(sel_u32(is_q, wq.x, wk.x), sel_u32(is_q, wq.y, wk.y),

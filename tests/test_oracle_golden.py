@@ -72,3 +72,37 @@ def test_partition_split_and_blend():
     a, b = torch.ones(4, 2, 2, 3), torch.zeros(4, 2, 2, 3)
     out = partition.stitch([torch.cat([torch.ones(6, 2, 2, 3), a]), torch.cat([b, torch.zeros(5, 2, 2, 3)])], 4)
     assert out.shape[0] == 15 and float(out[:8].min()) == 1.0 and float(out[8:].max()) == 0.0
+
+
+def _bf16_round(x):
+    """round-to-nearest-even fp32 -> bf16, returned as fp32 (what every bf16 ATen op does on store)"""
+    u = np.asarray(x, dtype=np.float32).view(np.uint32).astype(np.uint64)
+    return ((u + 0x7FFF + ((u >> 16) & 1)) & 0xFFFF0000).astype(np.uint32).view(np.float32)
+
+
+def _nudge(x, ulps):
+    return (np.asarray(x, dtype=np.float32).view(np.uint32).astype(np.int64) + ulps).astype(np.uint32).view(np.float32)
+
+
+def test_rmsnorm_division_free_rounding_lemma():
+    """The CUDA RMSNorm paths (csrc/common.cuh rcp_approx / sqrt_approx) replace the reference's fp32 division and sqrt
+    (normalization.py:88-109: x / sqrt(mean + eps) on bf16 tensors) by x * rcp.approx(rms) and sqrt.approx.  That is only
+    legitimate if the bf16 result is identical for EVERY input; the quotient / root of 8-bit significands never sits
+    within a few fp32 ulps of a bf16 rounding midpoint.  Checked exhaustively over all significand pairs (exponents only
+    shift), with the approximations perturbed by more than the PTX error bounds (rcp.approx: 1 ulp, sqrt.approx: 2^-23)."""
+    man = np.arange(128, 256, dtype=np.float32)
+    for ex in (-20, -7, -1, 0, 3, 11):
+        x = (man * np.float32(2.0) ** ex).astype(np.float32)[:, None]
+        for ed in (-9, -3, 0, 2, 5):
+            d = (man * np.float32(2.0) ** ed).astype(np.float32)[None, :]
+            ref = _bf16_round((x / d).astype(np.float32))
+            rcp = (np.float32(1) / d).astype(np.float32)
+            for ulps in (-2, -1, 0, 1, 2):
+                got = _bf16_round((x * _nudge(rcp, ulps)).astype(np.float32))
+                assert np.array_equal(got, ref), (ex, ed, ulps)
+    for e in range(-30, 10):
+        v = (man * np.float32(2.0) ** e).astype(np.float32)
+        root = np.sqrt(v).astype(np.float32)
+        ref = _bf16_round(root)
+        for ulps in range(-4, 5):
+            assert np.array_equal(_bf16_round(_nudge(root, ulps)), ref), (e, ulps)
