@@ -154,3 +154,64 @@ GEOMETRY_GRIDS = [
     (33, 9, 7), (1, 200, 3), (1, 3, 200), (30, 15, 27), (31, 15, 27), (8, 64, 64), (1, 67, 119),
 ]
 GEOMETRY_FULL_LIMIT = 4096   # grids with <= this many tokens store full index arrays, larger ones store sha256
+
+
+# ---- whole-NaDiT cases (the glue either side of the block loop) --------------------------------
+@dataclass
+class StackCase:
+    name: str
+    model: str                      # "3b" | "7b"
+    dim: int
+    heads: int
+    num_layers: int
+    mm_layers: int                  # 3B: layers < mm_layers use separate vid/txt weights (dit_3b/nadit.py:149-151)
+    latent_grid: Tuple[int, int, int]   # T, 2H, 2W (before the (1,2,2) patching)
+    txt_in_dim: int = 160
+    txt_len: int = TXT_LEN
+    timestep: float = 1000.0        # one-step trailing schedule, T=1000 (configs_3b/main.yaml:68)
+    seed: int = 0
+    in_scale: float = 1.0           # latents + noise are unit normal (infer.py:56,341)
+    txt_scale: float = 0.25
+
+
+STACK_CASES = [
+    # 2 separate + 2 shared layers, last layer vid_only, win/swin alternating, vid_out_norm + vid_out_ada (quirk Q1)
+    StackCase("3b_4layer", "3b", 256, 2, 4, 2, (2, 40, 72), seed=21),
+    # 7B: separate weights everywhere, GELU MLP with biases, pixel RoPE on video only, no output norm
+    StackCase("7b_4layer", "7b", 256, 2, 4, 0, (3, 34, 60), seed=22),
+]
+
+
+def stack_kwargs(c: StackCase) -> Dict:
+    """Constructor arguments of the reference NaDiT (configs_3b/main.yaml:11-36, configs_7b/main.yaml:11-33), narrowed."""
+    methods = ["720pwin_by_size_bysize", "720pswin_by_size_bysize"] * (c.num_layers // 2)
+    common = dict(vid_in_channels=33, vid_out_channels=16, vid_dim=c.dim, txt_in_dim=c.txt_in_dim, txt_dim=c.dim,
+                  emb_dim=6 * c.dim, heads=c.heads, head_dim=128, expand_ratio=4, norm="fusedrms", norm_eps=1e-5,
+                  ada="single", qk_bias=False, qk_norm="fusedrms", patch_size=[1, 2, 2], num_layers=c.num_layers,
+                  block_type=["mmdit_sr"] * c.num_layers, window=[(4, 3, 3)] * c.num_layers, window_method=methods)
+    if c.model == "3b":
+        return dict(common, mm_layers=c.mm_layers, mlp_type="swiglu", patch_type="v1", rope_type="mmrope3d",
+                    rope_dim=128, msa_type=None, mca_type=None, vid_out_norm="fusedrms")
+    return dict(common, qk_rope=True, shared_mlp=False, shared_qkv=False, mlp_type="normal")
+
+
+def stack_params(c: StackCase, shapes: Dict[str, Tuple[int, ...]]) -> Dict[str, torch.Tensor]:
+    """Deterministic parameters for every state-dict entry; `shapes` comes from the module being filled (the golden
+    generator asserts the reference NaDiT and NaDiTStack expose the same names and shapes)."""
+    return {k: draw_param(k, s, c.seed, c.model) for k, s in shapes.items()}
+
+
+def stack_inputs(c: StackCase):
+    """vid [T*2H*2W, 33] (16 noise + 16 condition + 1 mask channels, infer.py:56,341), txt [Lt, txt_in_dim]."""
+    T, H2, W2 = c.latent_grid
+    vid = (c.in_scale * torch.randn(T * H2 * W2, 33, generator=_gen(c.seed, "stack.vid"))).bfloat16().float()
+    txt = (c.txt_scale * torch.randn(c.txt_len, c.txt_in_dim, generator=_gen(c.seed, "stack.txt"))).bfloat16().float()
+    return vid, txt
+
+
+def psnr(a: torch.Tensor, ref: torch.Tensor) -> float:
+    """PSNR in dB of `a` against `ref`, peak = the reference's value range (the output is a latent, not [0,1] pixels)."""
+    ref = ref.double()
+    mse = float(((a.double() - ref) ** 2).mean())
+    peak = float(ref.max() - ref.min())
+    return float("inf") if mse == 0 else 10.0 * math.log10(peak * peak / mse)

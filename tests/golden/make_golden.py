@@ -4,6 +4,9 @@ read-only at /root/reference) in the build container.  Run once:  python tests/g
 The reference has no tests or fixtures of its own, so these files ARE the pin for the oracle:
   geometry.json     window bounds / window_shape / cu_seqlens / index arrays (or their sha256) from the reference's
                     window.py + na.window_idx for every grid in cases.GEOMETRY_GRIDS, both window methods
+  stack_<case>.pt   output of the reference NaDiT.forward (whole model, narrowed width/depth; fp32 and bf16 CPU) on
+                    cases.stack_inputs with cases.stack_params; also asserts that the product's NaDiTStack exposes the
+                    reference NaDiT's state-dict names and shapes
   block_<case>.pt   outputs of the reference NaMMSRTransformerBlock (fp32 CPU, and bf16 CPU) on cases.block_inputs
                     with cases.block_params loaded through load_state_dict (which also pins the state-dict contract)
 Needs: /root/reference, oracle/shim (third-party restatements).  Never runs on the GPU box.
@@ -141,7 +144,52 @@ def gen_blocks():
         }, os.path.join(HERE, f"block_{c.name}.pt"))
 
 
+def gen_stacks():
+    """Whole NaDiT.forward of the real reference (dit_3b/nadit.py:171-248, dit_7b/nadit.py:152-191)."""
+    import seedvr2_b200
+    from oracle import nadit as onadit
+    for c in cases.STACK_CASES:
+        if c.model == "3b":
+            from src.models.dit_3b.nadit import NaDiT
+        else:
+            from src.models.dit_7b.nadit import NaDiT
+        ref = NaDiT(**cases.stack_kwargs(c)).eval()
+        shapes = {k: tuple(v.shape) for k, v in ref.state_dict().items()}
+        ours = seedvr2_b200.stack.NaDiTStack(c.model, num_layers=c.num_layers, vid_dim=c.dim, heads=c.heads,
+                                             mm_layers=c.mm_layers, txt_in_dim=c.txt_in_dim)
+        mine = {k: tuple(v.shape) for k, v in ours.state_dict().items()}
+        assert mine == shapes, f"NaDiTStack state dict differs from the reference NaDiT for {c.name}:\n" \
+                               f"{sorted(set(mine.items()) ^ set(shapes.items()))}"
+        params = cases.stack_params(c, shapes)
+        ref.load_state_dict(params, strict=True)
+        vid, txt = cases.stack_inputs(c)
+        vid_shape = torch.tensor([list(c.latent_grid)]); txt_shape = torch.tensor([[c.txt_len]])
+        ts = torch.tensor([c.timestep])
+        kw = dict(disable_cache=False) if c.model == "3b" else {}      # 7B keeps its default (disable_cache=True, quirk Q2)
+        with torch.no_grad():
+            o32 = ref(vid.clone(), txt.clone(), vid_shape.clone(), txt_shape.clone(), ts, **kw).vid_sample
+            ref16 = ref.bfloat16()
+            for m in ref16.modules():                    # checkpoint rope buffers stay fp32 in the product too
+                if hasattr(m, "freqs") and isinstance(getattr(m, "freqs"), torch.Tensor):
+                    m.freqs.data = cases.rope_freqs(c.model)
+            o16 = ref16(vid.bfloat16(), txt.bfloat16(), vid_shape.clone(), txt_shape.clone(), ts, **kw).vid_sample
+            okw = dict(dim=c.dim, heads=c.heads, num_layers=c.num_layers, mm_layers=c.mm_layers)
+            oo32 = onadit.nadit_forward(c.model, params, vid, txt, c.latent_grid, c.timestep, **okw)
+            p16 = {k: (v if k.endswith("rope.freqs") else v.bfloat16()) for k, v in params.items()}
+            oo16 = onadit.nadit_forward(c.model, p16, vid.bfloat16(), txt.bfloat16(), c.latent_grid, c.timestep, **okw)
+        print(f"{c.name}: out {tuple(o32.shape)} |out| max {float(o32.abs().max()):.3f} rms {float(o32.pow(2).mean().sqrt()):.3f}"
+              f" | oracle-vs-ref fp32 {float((oo32 - o32).abs().max()):.3e} bf16 {float((oo16.float() - o16.float()).abs().max()):.3e}"
+              f" | ref bf16-vs-fp32 max {float((o16.float() - o32).abs().max()):.3e} PSNR {cases.psnr(o16.float(), o32):.1f} dB")
+        torch.save({"case": c.name, "in_digest": {"vid": cases.tensor_digest(vid), "txt": cases.tensor_digest(txt)},
+                    "out_fp32": o32, "out_bf16": o16}, os.path.join(HERE, f"stack_{c.name}.pt"))
+
+
 if __name__ == "__main__":
     torch.manual_seed(0)
-    gen_geometry()
-    gen_blocks()
+    what = sys.argv[1:] or ["geometry", "blocks", "stacks"]
+    if "geometry" in what:
+        gen_geometry()
+    if "blocks" in what:
+        gen_blocks()
+    if "stacks" in what:
+        gen_stacks()

@@ -106,3 +106,27 @@ def test_rmsnorm_division_free_rounding_lemma():
         ref = _bf16_round(root)
         for ulps in range(-4, 5):
             assert np.array_equal(_bf16_round(_nudge(root, ulps)), ref), (e, ulps)
+
+
+@pytest.mark.parametrize("case", cases.STACK_CASES, ids=lambda c: c.name)
+def test_nadit_forward_matches_reference(case):
+    """Whole NaDiT.forward (dit_3b/nadit.py:171-248 incl. quirk Q1, dit_7b/nadit.py:152-191): oracle/nadit.py against the
+    output of the real reference model (tests/golden/stack_*.pt)."""
+    from oracle import nadit as onadit
+    import seedvr2_b200
+    gold = torch.load(os.path.join(GOLD, f"stack_{case.name}.pt"))
+    vid, txt = cases.stack_inputs(case)
+    assert gold["in_digest"] == {"vid": cases.tensor_digest(vid), "txt": cases.tensor_digest(txt)}
+    st = seedvr2_b200.stack.NaDiTStack(case.model, num_layers=case.num_layers, vid_dim=case.dim, heads=case.heads,
+                                       mm_layers=case.mm_layers, txt_in_dim=case.txt_in_dim)
+    params = cases.stack_params(case, {k: tuple(v.shape) for k, v in st.state_dict().items()})
+    kw = dict(dim=case.dim, heads=case.heads, num_layers=case.num_layers, mm_layers=case.mm_layers)
+    with torch.no_grad():
+        o32 = onadit.nadit_forward(case.model, params, vid, txt, case.latent_grid, case.timestep, **kw)
+        p16 = {k: (v if k.endswith("rope.freqs") else v.bfloat16()) for k, v in params.items()}
+        o16 = onadit.nadit_forward(case.model, p16, vid.bfloat16(), txt.bfloat16(), case.latent_grid, case.timestep, **kw)
+    assert float((o32 - gold["out_fp32"]).abs().max()) < 1e-4
+    assert cases.psnr(o16.float(), gold["out_bf16"].float()) > 80.0      # same ops, same order: bit-equal where run
+    # the north star's decoded-output bar applied to the reference's OWN bf16 path: it must clear 45 dB for the
+    # bar to be meaningful at these magnitudes
+    assert cases.psnr(gold["out_bf16"].float(), gold["out_fp32"]) > 45.0
