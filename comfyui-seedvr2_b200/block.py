@@ -123,6 +123,20 @@ def _bf16(t: torch.Tensor) -> torch.Tensor:
     return t if t.dtype == torch.bfloat16 else t.to(torch.bfloat16)
 
 
+def _joined(a: torch.Tensor, b: torch.Tensor) -> Optional[torch.Tensor]:
+    """[a; b] as ONE tensor without a copy when `b`'s rows directly follow `a`'s in the same storage, else None.
+    Shared-weight layers (3B layers >= mm_layers, mm.py:59-74 routes vid and txt through the same ``.all`` module) apply
+    the same row-wise function to both branches; run on the joined rows that is one GEMM / one launch instead of two
+    ("vid+txt concatenated for shared-weight layers") and the weights are read once."""
+    if a.dim() != 2 or b.dim() != 2 or a.shape[1] != b.shape[1] or a.dtype != b.dtype or a.device != b.device:
+        return None
+    if not (a.is_contiguous() and b.is_contiguous()) or a.numel() == 0 or b.numel() == 0:
+        return None
+    if a.untyped_storage().data_ptr() != b.untyped_storage().data_ptr() or b.storage_offset() != a.storage_offset() + a.numel():
+        return None
+    return torch.as_strided(a, (a.shape[0] + b.shape[0], a.shape[1]), (a.shape[1], 1))
+
+
 class _GridMemo:
     """vid_shape lives on the GPU (na.py:97); reading it is a D2H sync the reference pays several times per layer.
     The same tensor OBJECT flows through all blocks of a forward, so one sync per forward is enough — also for 7B,
@@ -173,8 +187,13 @@ class NaSwinAttentionB200(nn.Module):
 
     def core(self, vid: torch.Tensor, txt: torch.Tensor, plan: WindowPlan):
         """proj_qkv -> pack (norm+rope+partition) -> window attention; returns attention outputs BEFORE proj_out."""
-        vqkv = F.linear(vid, _bf16(self.proj_qkv.pick("vid").weight))
-        tqkv = F.linear(txt, _bf16(self.proj_qkv.pick("txt").weight))
+        both = _joined(vid, txt) if self.proj_qkv.shared_weights else None
+        if both is not None:
+            qkv = F.linear(both, _bf16(self.proj_qkv.all.weight))
+            vqkv, tqkv = qkv[:vid.shape[0]], qkv[vid.shape[0]:]
+        else:
+            vqkv = F.linear(vid, _bf16(self.proj_qkv.pick("vid").weight))
+            tqkv = F.linear(txt, _bf16(self.proj_qkv.pick("txt").weight))
         if self.rope is not None:
             freqs = self.rope.rope.freqs
             if freqs.dtype != torch.float32:
@@ -191,6 +210,10 @@ class NaSwinAttentionB200(nn.Module):
         grid, txt_len = _GridMemo.read(vid_shape, txt_shape)
         plan = get_plan(grid, self.window, self.shifted, txt_len)
         ov, ot = self.core(vid, txt, plan)
+        both = _joined(ov, ot) if self.proj_out.shared_weights else None
+        if both is not None:
+            o = F.linear(both, _bf16(self.proj_out.all.weight), _bf16(self.proj_out.all.bias))
+            return o[:ov.shape[0]], o[ov.shape[0]:]
         po_v, po_t = self.proj_out.pick("vid"), self.proj_out.pick("txt")
         return (F.linear(ov, _bf16(po_v.weight), _bf16(po_v.bias)), F.linear(ot, _bf16(po_t.weight), _bf16(po_t.bias)))
 
@@ -220,6 +243,23 @@ class _BlockBase(nn.Module):
         vid, txt = vid.contiguous(), txt.contiguous()
         eps = self.norm_eps
         av, at = self._ada("vid"), (None if self.txt_tail_skipped else self._ada("txt"))
+        L = vid.shape[0]
+
+        if av is at and self.mlp.shared_weights:
+            # Shared-weight layer: ada / mlp (and attn) hold ONE module for both branches, so every row-wise step runs once
+            # on the joined rows [vid; txt].  The joined tensor is free when the previous layer produced it; the first
+            # shared layer pays one copy.
+            x = _joined(vid, txt)
+            if x is None:
+                x = torch.cat([vid, txt])
+            a = ops.modnorm(x, e, _bf16(av.attn_shift), _bf16(av.attn_scale), 0, eps)
+            o_v, o_t = self.attn(a[:L], a[L:], vid_shape, txt_shape, cache)
+            o = _joined(o_v, o_t)
+            if o is None:       # a wrapper around attn.forward returned copies (compatibility.py:437-522)
+                o = torch.cat([o_v, o_t])
+            x1, m = ops.gate_residual_modnorm(o, x, e, _bf16(av.attn_gate), _bf16(av.mlp_shift), _bf16(av.mlp_scale), eps)
+            x2 = ops.gate_residual(self.mlp.all(m), x1, e, _bf16(av.mlp_gate), 1)
+            return x2[:L], x2[L:], vid_shape, txt_shape
 
         # --- attention half
         a_v = ops.modnorm(vid, e, _bf16(av.attn_shift), _bf16(av.attn_scale), 0, eps)

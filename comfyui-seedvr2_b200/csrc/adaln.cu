@@ -21,14 +21,15 @@ namespace svr2 {
 // iteration (double-buffered partials).  Few registers -> 3+ CTAs per SM -> >= 60 KB of loads in flight per SM.
 constexpr int kMaxWarps = 16;     // D <= 4096
 
-template <bool FUSE_GATE, int kRows>
+template <bool FUSE_GATE, int kRows, bool AFFINE = false>
 __global__ void __launch_bounds__(kMaxWarps * 32, 2)
 modnorm_kernel(const __nv_bfloat16* __restrict__ x,       // FUSE_GATE: h (branch output), else the row to normalise
                const __nv_bfloat16* __restrict__ resid,   // FUSE_GATE only
                const __nv_bfloat16* __restrict__ emb, const __nv_bfloat16* __restrict__ gateB,
                const __nv_bfloat16* __restrict__ shiftB, const __nv_bfloat16* __restrict__ scaleB,
                __nv_bfloat16* __restrict__ out,           // FUSE_GATE only: gated residual sum
-               __nv_bfloat16* __restrict__ y, int64_t L, int D, int gate_layer, int mod_layer, float eps, int has_mod) {
+               __nv_bfloat16* __restrict__ y, int64_t L, int D, int gate_layer, int mod_layer, float eps, int has_mod,
+               const __nv_bfloat16* __restrict__ normW = nullptr) {   // AFFINE only: RMSNorm weight (vid_out_norm)
     __shared__ float s_part[2][kRows][kMaxWarps];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, n_warps = blockDim.x >> 5;
     const int col = threadIdx.x * 8;
@@ -50,6 +51,10 @@ modnorm_kernel(const __nv_bfloat16* __restrict__ x,       // FUSE_GATE: h (branc
             }
         }
         sc_p = pack8(sc); sh_p = pack8(sh); g_p = pack8(g);
+    }
+    bf16x8 w_p;
+    if (AFFINE) {
+        if (act) w_p = ldg8_stream(normW + col);
     }
     const float inv_d = 1.0f / (float)D;
     int buf = 0;
@@ -100,6 +105,7 @@ modnorm_kernel(const __nv_bfloat16* __restrict__ x,       // FUSE_GATE: h (branc
 #pragma unroll
             for (int i = 0; i < 8; ++i) f[i] = f[i] * rcp;       // rounds to the same bf16 as x / rms (common.cuh)
             bf16x8 yv = pack8(f);                                                     // (x / rms) -> bf16
+            if (AFFINE) yv = mul8_rn(yv, w_p);                                        // * weight -> bf16 (normalization.py:108)
             if (has_mod) yv = add8_rn(mul8_rn(yv, sc_p), sh_p);                       // * scale -> bf16, + shift -> bf16
             stg8(y + (row0 + k) * D + col, yv);
         }
@@ -211,6 +217,26 @@ extern "C" int svr2_modnorm_fwd(const void* x, const void* emb, const void* shif
     SVR2_CHECK_ARG(!has_mod || (shiftB && scaleB && emb), "svr2_modnorm_fwd: emb, shiftB and scaleB go together");
     return svr2::launch_modnorm<false>(x, nullptr, emb, nullptr, shiftB, scaleB, nullptr, y, L, D, 0, layer, eps,
                                        has_mod, (cudaStream_t)stream, "svr2_modnorm_fwd");
+}
+
+// RMSNorm WITH elementwise-affine weight, then the "in" modulation: the model's output norm + vid_out_ada
+// (reference dit_3b/nadit.py:233-244; CustomRMSNorm normalization.py:88-109 with weight; quirk Q1 — the caller passes
+// layer 0, the attn-layer (shift, scale) pair the reference's cache hands to vid_out_ada).
+extern "C" int svr2_modnorm_affine_fwd(const void* x, const void* weight, const void* emb, const void* shiftB,
+                                       const void* scaleB, void* y, int64_t L, int D, int layer, float eps, void* stream) {
+    SVR2_CHECK_ARG(x && y && weight, "svr2_modnorm_affine_fwd: null x/y/weight");
+    SVR2_CHECK_ARG(L >= 0 && D > 0 && D % 8 == 0 && D <= 4096, "svr2_modnorm_affine_fwd: D=%d must be a multiple of 8, <= 4096", D);
+    SVR2_CHECK_ARG(layer == 0 || layer == 1, "svr2_modnorm_affine_fwd: layer must be 0 (attn) or 1 (mlp)");
+    const int has_mod = (shiftB != nullptr || scaleB != nullptr || emb != nullptr) ? 1 : 0;
+    SVR2_CHECK_ARG(!has_mod || (shiftB && scaleB && emb), "svr2_modnorm_affine_fwd: emb, shiftB and scaleB go together");
+    if (L == 0) return SVR2_OK;
+    const int threads = ((D / 8) + 31) / 32 * 32;
+    const int64_t want = (L + 3) / 4, cap = (int64_t)svr2::sm_count() * 2;
+    svr2::modnorm_kernel<false, 4, true><<<(int)(want < cap ? want : cap), threads, 0, (cudaStream_t)stream>>>(
+        (const __nv_bfloat16*)x, nullptr, (const __nv_bfloat16*)emb, nullptr, (const __nv_bfloat16*)shiftB,
+        (const __nv_bfloat16*)scaleB, nullptr, (__nv_bfloat16*)y, L, D, 0, layer, eps, has_mod, (const __nv_bfloat16*)weight);
+    SVR2_CHECK_LAUNCH("svr2_modnorm_affine_fwd");
+    return SVR2_OK;
 }
 
 extern "C" int svr2_gate_residual_modnorm_fwd(const void* h, const void* resid, const void* emb, const void* gateB,

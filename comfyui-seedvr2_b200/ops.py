@@ -41,6 +41,11 @@ class KernelTimer:
         return {k: (len(v), sum(a.elapsed_time(b) for a, b in v)) for k, v in self.records.items()}
 
 
+    def durations(self):
+        """{name: [ms of every launch]} — call after torch.cuda.synchronize()."""
+        return {k: [a.elapsed_time(b) for a, b in v] for k, v in self.records.items()}
+
+
 _timer: Optional[KernelTimer] = None
 _launches = 0      # kernels of libseedvr2_b200.so launched by this process (bench.py's `gpu_launches`)
 
@@ -103,6 +108,22 @@ def modnorm(x: torch.Tensor, emb: Optional[torch.Tensor], shift_b: Optional[torc
     if L:
         _call("svr2_modnorm_fwd", 1, x.device, _lib.lib().svr2_modnorm_fwd, x.data_ptr(), _ptr(emb), _ptr(shift_b),
               _ptr(scale_b), y.data_ptr(), L, D, layer, float(eps), _stream(x))
+    return y
+
+
+@torch._dynamo.disable
+def modnorm_affine(x: torch.Tensor, weight: torch.Tensor, emb: Optional[torch.Tensor], shift_b: Optional[torch.Tensor],
+                   scale_b: Optional[torch.Tensor], layer: int, eps: float) -> torch.Tensor:
+    """y = rmsnorm(x) * weight * (scaleA + scaleB) + (shiftA + shiftB): the model's output norm + output modulation."""
+    _need(x, "x"); _need(weight, "weight")
+    L, D = x.shape
+    y = torch.empty_like(x)
+    for n, t in (("emb", emb), ("shift_b", shift_b), ("scale_b", scale_b)):
+        if t is not None:
+            _need(t, n)
+    if L:
+        _call("svr2_modnorm_affine_fwd", 1, x.device, _lib.lib().svr2_modnorm_affine_fwd, x.data_ptr(), weight.data_ptr(),
+              _ptr(emb), _ptr(shift_b), _ptr(scale_b), y.data_ptr(), L, D, layer, float(eps), _stream(x))
     return y
 
 
@@ -189,9 +210,10 @@ def window_attn(plan: WindowPlan, q: torch.Tensor, k: torch.Tensor, v: torch.Ten
             raise RuntimeError(f"window_attn: `{n}` has shape {tuple(t.shape)}, expected {(plan.packed_rows, heads, 128)}")
     dev = q.device
     T, H, W = plan.grid
-    out_vid = torch.empty(plan.n_tokens, heads * 128, dtype=torch.bfloat16, device=dev)
+    # one buffer, video rows then text rows: shared-weight layers run proj_out on it as ONE GEMM (block._joined)
+    out = torch.empty(plan.n_tokens + plan.txt_len, heads * 128, dtype=torch.bfloat16, device=dev)
+    out_vid, out_txt = out[:plan.n_tokens], out[plan.n_tokens:]
     txt_part = torch.empty(plan.n_windows, plan.txt_len, heads * 128, dtype=torch.bfloat16, device=dev)
-    out_txt = torch.empty(plan.txt_len, heads * 128, dtype=torch.bfloat16, device=dev)
     d = plan.on(dev)
     # attention and text pooling are two kernels; they are launched separately so the attention kernel can be timed alone
     _call("svr2_window_attn_fwd", 1, dev, _lib.lib().svr2_window_attn_fwd,

@@ -118,10 +118,10 @@ class NaDiTStack(nn.Module):
         if self.vid_out_norm is not None:
             # CustomRMSNorm affine (normalization.py:88-109) then vid_out_ada; quirk Q1: the cache hands it the ATTN
             # (shift, scale) of `emb` (dit_3b/nadit.py:236-244) — reproduced, not fixed.
-            var = x.pow(2).mean(dim=-1, keepdim=True)
-            x = x / torch.sqrt(var + 1e-5) * self.vid_out_norm.weight
-            e = emb.reshape(1, -1, 2, 3)[:, :, 0, :]
-            x = x * (e[..., 1] + self.vid_out_ada.out_scale) + (e[..., 0] + self.vid_out_ada.out_shift)
+            from . import ops
+            from .block import _bf16
+            x = ops.modnorm_affine(x.contiguous(), _bf16(self.vid_out_norm.weight), _bf16(emb).reshape(-1).contiguous(),
+                                   _bf16(self.vid_out_ada.out_shift), _bf16(self.vid_out_ada.out_scale), 0, 1e-5)
         x = self.vid_out.proj(x)
         # "T H W (t h w c) -> (T t)(H h)(W w) c"  (patch/patch_v1.py:121)
         co = x.shape[-1] // (ph * pw)

@@ -68,6 +68,16 @@ int svr2_modnorm_fwd(const void* x, const void* emb, const void* shiftB, const v
                      int64_t L, int D, int layer, float eps, void* stream);
 
 /*
+ * RMSNorm WITH elementwise-affine weight + adaLN "in" modulation:  y = rmsnorm(x) * weight * (scaleA + scaleB) + (shiftA + shiftB)
+ * Replaces the model's output norm + output modulation: `vid_out_norm` (CustomRMSNorm with weight, normalization.py:88-109)
+ * followed by `vid_out_ada(..., layer="out", mode="in")` (src/models/dit_3b/nadit.py:233-244).  Cache-key quirk Q1: the
+ * reference's cache hands vid_out_ada the ATTN-layer (shift, scale) of emb, so the caller passes layer 0.
+ *   weight [D] bf16; the rest as svr2_modnorm_fwd.
+ */
+int svr2_modnorm_affine_fwd(const void* x, const void* weight, const void* emb, const void* shiftB, const void* scaleB,
+                            void* y, int64_t L, int D, int layer, float eps, void* stream);
+
+/*
  * Gate + residual:  out = h * (gateA + gateB) + resid      (modulation.py:111-116 + mmsr_block.py:114,126)
  * gateB NULL with emb NULL means plain residual add (vid_only text branch).  h/resid/out [L,D] bf16, out may alias h.
  */

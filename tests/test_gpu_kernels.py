@@ -73,6 +73,17 @@ def test_modnorm(svr2, cuda, L, D, layer):
     _close_bf16(y0, oblock.rmsnorm(x, 1e-5), "rmsnorm only")
 
 
+@pytest.mark.parametrize("L,D", [(58, 128), (1000, 2560), (4099, 256)])
+def test_modnorm_affine(svr2, cuda, L, D):
+    """Output norm (RMSNorm with weight) + output modulation with the attn-layer pair (quirk Q1), dit_3b/nadit.py:233-244."""
+    x, _, emb, shift, scale, _ = _ada_inputs(L, D, 300, cuda)
+    w = (1 + 0.1 * torch.randn(D, generator=torch.Generator().manual_seed(7))).bfloat16().to(cuda)
+    y = svr2.ops.modnorm_affine(x, w, emb.reshape(-1), shift, scale, 0, 1e-5)
+    ref = oblock.ada_in(oblock.rmsnorm(x, 1e-5, w), emb, 0, shift, scale)
+    _close_bf16(y, ref, "modnorm_affine")
+    _close_bf16(svr2.ops.modnorm_affine(x, w, None, None, None, 0, 1e-5), oblock.rmsnorm(x, 1e-5, w), "affine rmsnorm only")
+
+
 @pytest.mark.parametrize("L,D", [(58, 128), (1000, 2560), (333, 3072), (4099, 256)])
 def test_gate_residual(svr2, cuda, L, D):
     x, r, emb, shift, scale, gate = _ada_inputs(L, D, 7, cuda)
