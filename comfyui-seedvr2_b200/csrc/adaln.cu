@@ -10,6 +10,8 @@
 // Numerics: the reference runs op by op in bf16 — ATen computes each op in fp32 and rounds the result to bf16.  Every
 // such rounding point is reproduced with bf16r(), so results match the reference's bf16 path to the
 // last bit except for the fp32 summation order inside mean().
+#include <cstdlib>
+
 #include "common.cuh"
 
 namespace svr2 {
@@ -21,7 +23,7 @@ namespace svr2 {
 // iteration (double-buffered partials).  Few registers -> 3+ CTAs per SM -> >= 60 KB of loads in flight per SM.
 constexpr int kMaxWarps = 16;     // D <= 4096
 
-template <bool FUSE_GATE, int kRows, bool AFFINE = false>
+template <bool FUSE_GATE, int kRows, bool AFFINE = false, bool PREFETCH = true>
 __global__ void __launch_bounds__(kMaxWarps * 32, 2)
 modnorm_kernel(const __nv_bfloat16* __restrict__ x,       // FUSE_GATE: h (branch output), else the row to normalise
                const __nv_bfloat16* __restrict__ resid,   // FUSE_GATE only
@@ -58,18 +60,32 @@ modnorm_kernel(const __nv_bfloat16* __restrict__ x,       // FUSE_GATE: h (branc
     }
     const float inv_d = 1.0f / (float)D;
     int buf = 0;
-    for (int64_t row0 = (int64_t)blockIdx.x * kRows; row0 < L; row0 += (int64_t)gridDim.x * kRows, buf ^= 1) {
+    // Software pipeline: the loads of the NEXT row group are issued before this group's reduction, barrier and stores, so a
+    // CTA always has kRows (x2 when fused) 16-byte loads per thread in flight instead of alternating load / store phases.
+    bf16x8 nv[kRows], nr[kRows];
+    auto fetch = [&](int64_t row0) {
+#pragma unroll
+        for (int k = 0; k < kRows; ++k) {
+            if (act && (row0 + k < L)) {
+                nv[k] = ldg8_stream(x + (row0 + k) * D + col);
+                if (FUSE_GATE) nr[k] = ldg8_stream(resid + (row0 + k) * D + col);
+            } else {
+#pragma unroll
+                for (int i = 0; i < 4; ++i) nv[k].v[i] = __floats2bfloat162_rn(0.f, 0.f);
+            }
+        }
+    };
+    const int64_t stride = (int64_t)gridDim.x * kRows;
+    fetch((int64_t)blockIdx.x * kRows);
+    for (int64_t row0 = (int64_t)blockIdx.x * kRows; row0 < L; row0 += stride, buf ^= 1) {
         bf16x8 v[kRows], r[kRows];
 #pragma unroll
         for (int k = 0; k < kRows; ++k) {
-            const bool ok = act && (row0 + k < L);
-            if (ok) {
-                v[k] = ldg8_stream(x + (row0 + k) * D + col);
-                if (FUSE_GATE) r[k] = ldg8_stream(resid + (row0 + k) * D + col);
-            } else {
-#pragma unroll
-                for (int i = 0; i < 4; ++i) v[k].v[i] = __floats2bfloat162_rn(0.f, 0.f);
-            }
+            v[k] = nv[k];
+            if (FUSE_GATE) r[k] = nr[k];
+        }
+        if (PREFETCH) {
+            if (row0 + stride < L) fetch(row0 + stride);
         }
         float ss[kRows];
 #pragma unroll
@@ -108,6 +124,9 @@ modnorm_kernel(const __nv_bfloat16* __restrict__ x,       // FUSE_GATE: h (branc
             if (AFFINE) yv = mul8_rn(yv, w_p);                                        // * weight -> bf16 (normalization.py:108)
             if (has_mod) yv = add8_rn(mul8_rn(yv, sc_p), sh_p);                       // * scale -> bf16, + shift -> bf16
             stg8(y + (row0 + k) * D + col, yv);
+        }
+        if (!PREFETCH) {
+            if (row0 + stride < L) fetch(row0 + stride);      // A/B variant: load / compute / store phases alternate
         }
     }
 }
@@ -197,11 +216,11 @@ static int launch_modnorm(const void* x, const void* resid, const void* emb, con
     const int64_t want = (L + kRows - 1) / kRows;
     const int64_t cap = (int64_t)sm_count() * occ[wi];
     const int grid = (int)(want < cap ? want : cap);
-    modnorm_kernel<FUSE, kRows><<<grid, threads, 0, st>>>((const __nv_bfloat16*)x, (const __nv_bfloat16*)resid,
-                                                   (const __nv_bfloat16*)emb, (const __nv_bfloat16*)gateB,
-                                                   (const __nv_bfloat16*)shiftB, (const __nv_bfloat16*)scaleB,
-                                                   (__nv_bfloat16*)out, (__nv_bfloat16*)y, L, D, gate_layer, mod_layer,
-                                                   eps, has_mod);
+    static const bool prefetch = [] { const char* e = getenv("SVR2_MODNORM_PREFETCH"); return !(e && e[0] == '0'); }();
+    auto kern = prefetch ? modnorm_kernel<FUSE, kRows, false, true> : modnorm_kernel<FUSE, kRows, false, false>;
+    kern<<<grid, threads, 0, st>>>((const __nv_bfloat16*)x, (const __nv_bfloat16*)resid, (const __nv_bfloat16*)emb,
+                                   (const __nv_bfloat16*)gateB, (const __nv_bfloat16*)shiftB, (const __nv_bfloat16*)scaleB,
+                                   (__nv_bfloat16*)out, (__nv_bfloat16*)y, L, D, gate_layer, mod_layer, eps, has_mod, nullptr);
     SVR2_CHECK_LAUNCH(name);
     return SVR2_OK;
 }
