@@ -337,6 +337,9 @@ int make_tmap(CUtensorMap* m, const void* ptr, int64_t P, int heads);
 int launch_window_attn_tc2(const void* q, const void* k, const void* v, const int32_t* tab, const int32_t* work,
                            int n_work, int n_windows, int H, int W, int txt_len, int heads, int64_t P, void* out_vid,
                            void* txt_part, cudaStream_t st);
+int launch_window_attn_tc5(const void* q, const void* k, const void* v, const int32_t* tab, const int32_t* work,
+                           int n_work, int n_windows, int H, int W, int txt_len, int heads, int64_t P, void* out_vid,
+                           void* txt_part, cudaStream_t st);
 int launch_window_attn_tc4(const void* q, const void* k, const void* v, const int32_t* tab, const int32_t* work,
                            int n_work, int H, int W, int txt_len, int heads, int64_t P, void* out_vid, void* txt_part,
                            cudaStream_t st);
@@ -473,6 +476,8 @@ extern "C" int svr2_window_attn_fwd(const void* q_pack, const void* k_pack, cons
         rc = svr2::launch_window_attn_tc(q_pack, k_pack, v_pack, win_table, work, n_work, H, W, txt_len, heads, P, out_vid, txt_part, st);
     else if (e && strcmp(e, "v3") == 0)
         rc = svr2::launch_window_attn_tc3(q_pack, k_pack, v_pack, win_table, work, n_work, H, W, txt_len, heads, P, out_vid, txt_part, st);
+    else if (e && strcmp(e, "v5") == 0)
+        rc = svr2::launch_window_attn_tc5(q_pack, k_pack, v_pack, win_table, work, n_work, n_windows, H, W, txt_len, heads, P, out_vid, txt_part, st);
     else if (e && strcmp(e, "v4") == 0)
         rc = svr2::launch_window_attn_tc4(q_pack, k_pack, v_pack, win_table, work, n_work, H, W, txt_len, heads, P, out_vid, txt_part, st);
     else

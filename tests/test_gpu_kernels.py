@@ -218,22 +218,35 @@ ATTN_CASES = [((2, 20, 36), False, 2), ((1, 32, 32), True, 3), ((5, 17, 30), Tru
 
 @pytest.mark.parametrize("grid,shifted,heads", ATTN_CASES)
 def test_window_attn_generations_bit_identical(svr2, cuda, monkeypatch, grid, shifted, heads):
-    """The two shipped kernels (generation 4: whole key tiles; generation 6: double-buffered half tiles) are picked by
-    sequence length and must be interchangeable: same exponent reference, same summation order -> identical bits."""
+    """Generation 7 (one query tile per item, S and P double-buffered, two warpgroups on alternate key tiles), generation 4
+    (two query tiles, whole key tiles) and generation 6 (double-buffered half tiles) use the same exponent reference, lazy
+    rescale rule and summation order: their outputs must be identical bit for bit."""
     plan = svr2.get_plan(grid, (4, 3, 3), shifted, cases.TXT_LEN)
     g = torch.Generator().manual_seed(11)
     q, k, v = (torch.randn(plan.packed_rows, heads, 128, generator=g).bfloat16().to(cuda) for _ in range(3))
-    outs = {}
-    for impl in ("v2", "v4"):
+
+    def run(impl, q):
         monkeypatch.setenv("SVR2_ATTN_IMPL", impl)
         ov, ot = svr2.ops.window_attn(plan, q, k, v, heads)
         torch.cuda.synchronize()
-        outs[impl] = (ov.clone(), ot.clone())
-    assert torch.equal(outs["v2"][0], outs["v4"][0]), "video rows differ between generation 4 and generation 6"
-    assert torch.equal(outs["v2"][1], outs["v4"][1]), "pooled text rows differ between generation 4 and generation 6"
+        return ov.clone(), ot.clone()
+
+    base = run("v2", q)
+    for other in ("v4", "v5", "v5", "v5"):          # repeated launches of generation 7 must also agree with each other
+        ov, ot = run(other, q)
+        assert torch.equal(base[0], ov), f"video rows differ between generation 4 (v2) and {other}"
+        assert torch.equal(base[1], ot), f"pooled text rows differ between generation 4 (v2) and {other}"
+    # rows whose maximum jumps from key tile to key tile exercise the lazy rescale of O, where generation 7 hands the
+    # reference exponent and the row sum from warpgroup to warpgroup (generation 6 takes row maxima per half tile and is
+    # only bit-compatible while no rescale fires)
+    q2 = q.clone()
+    q2[: plan.packed_rows // 2] *= 6.0
+    base = run("v2", q2)
+    ov, ot = run("v5", q2)
+    assert torch.equal(base[0], ov) and torch.equal(base[1], ot), "generation 7 differs from generation 4 under lazy rescales"
 
 
-@pytest.mark.parametrize("impl", ["tcgen05", "v2", "v4", "v3", "v1", "mma"])
+@pytest.mark.parametrize("impl", ["tcgen05", "v5", "v2", "v4", "v3", "v1", "mma"])
 @pytest.mark.parametrize("grid,shifted,heads", ATTN_CASES)
 def test_window_attn_vs_fp32(svr2, cuda, monkeypatch, impl, grid, shifted, heads):
     monkeypatch.setenv("SVR2_ATTN_IMPL", impl)
