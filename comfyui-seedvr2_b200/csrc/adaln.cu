@@ -33,6 +33,7 @@ modnorm_kernel(const __nv_bfloat16* __restrict__ x,       // FUSE_GATE: h (branc
                __nv_bfloat16* __restrict__ y, int64_t L, int D, int gate_layer, int mod_layer, float eps, int has_mod,
                const __nv_bfloat16* __restrict__ normW = nullptr) {   // AFFINE only: RMSNorm weight (vid_out_norm)
     __shared__ float s_part[2][kRows][kMaxWarps];
+    __shared__ __align__(16) float s_tot[2][4];      // row totals of the current group (kRows <= 4)
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, n_warps = blockDim.x >> 5;
     const int col = threadIdx.x * 8;
     const bool act = col < D;
@@ -96,23 +97,32 @@ modnorm_kernel(const __nv_bfloat16* __restrict__ x,       // FUSE_GATE: h (branc
                     stg8(out + (row0 + k) * D + col, v[k]);
                 }
             }
-            float f[8];
-            unpack8(mul8(v[k], v[k]), f);                                            // input.pow(2) is a bf16 tensor
-            float a = 0.f;
-#pragma unroll
-            for (int i = 0; i < 8; ++i) a += f[i];
-            ss[k] = warp_sum(a);
+            float a = quad_sum_bf16x8(mul8(v[k], v[k]));                             // input.pow(2) is a bf16 tensor; fp32 sum
+            a += __shfl_xor_sync(0xffffffffu, a, 4);
+            a += __shfl_xor_sync(0xffffffffu, a, 8);
+            a += __shfl_xor_sync(0xffffffffu, a, 16);
+            ss[k] = a;
         }
         if (lane == 0) {
 #pragma unroll
             for (int k = 0; k < kRows; ++k) s_part[buf][k][warp] = ss[k];
         }
         __syncthreads();
+        // second level: warp k adds the n_warps partials of row k (one lane per partial, a 4-step butterfly) and publishes the
+        // total; everybody then reads the kRows totals with one 16-byte load.  Letting every thread add all partials itself
+        // cost ~10 FADD + 10 uniform branches per row and thread — a quarter of this issue-bound kernel's instructions.
+        for (int k = warp; k < kRows; k += n_warps) {       // (a CTA of a narrow D has fewer warps than rows)
+            float t = lane < n_warps ? s_part[buf][k][lane] : 0.f;
+#pragma unroll
+            for (int o = 8; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
+            if (lane == 0) s_tot[buf][k] = t;
+        }
+        __syncthreads();
+        const float4 tot4 = *reinterpret_cast<const float4*>(s_tot[buf]);
 #pragma unroll
         for (int k = 0; k < kRows; ++k) {
             if (!(act && (row0 + k < L))) continue;
-            float tot = 0.f;
-            for (int w = 0; w < n_warps; ++w) tot += s_part[buf][k][w];
+            const float tot = k == 0 ? tot4.x : (k == 1 ? tot4.y : (k == 2 ? tot4.z : tot4.w));
             const float var = bf16r(tot * inv_d);                                     // .mean() -> bf16
             const float rms = bf16r(sqrt_approx(bf16r(var + eps)));
             const float rcp = rcp_approx(rms);

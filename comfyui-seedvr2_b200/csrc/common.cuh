@@ -122,6 +122,22 @@ __device__ __forceinline__ float sqrt_approx(float v) {
     return r;
 }
 
+// Sum of the 8 bf16 values held by each of the 4 lanes of a quad (lanes 4q .. 4q+3), in fp32, in ONE instruction: the four
+// registers are the A fragment of mma.sync.m16n8k16 (a0, a2 -> row q, a1, a3 -> row q + 8) and B is all ones, so D[q][*] +
+// D[q+8][*] is the quad's total.  Replaces 8 conversions + 8 FADD + 2 butterfly steps of a row-sum — the RMSNorm kernels are
+// issue bound, not memory bound (profiles/r01_run25_ncu_elementwise_c1.txt).  Products with 1.0 are exact and the accumulation
+// is fp32; like any change of summation order it can move a sum by an fp32 ulp.  The whole warp must be converged.
+__device__ __forceinline__ float quad_sum_bf16x8(const bf16x8& v) {
+    const uint4 a = *reinterpret_cast<const uint4*>(&v);
+    float c0, c1, c2, c3;
+    const uint32_t ones = 0x3F803F80u;
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%8}, {%9,%9,%9,%9};"
+                 : "=f"(c0), "=f"(c1), "=f"(c2), "=f"(c3)
+                 : "r"(a.x), "r"(a.y), "r"(a.z), "r"(a.w), "r"(ones), "f"(0.f));
+    (void)c1; (void)c3;
+    return c0 + c2;
+}
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

@@ -63,21 +63,14 @@ __device__ __forceinline__ void rope_pair(int rope_kind, int p, int n_rot, int n
 // One (q|k, head) slice of 128 values held by a half-warp, 8 per thread: RMSNorm over the slice with the reference's bf16
 // rounding points (normalization.py:88-109), affine weight, interleaved-pair rotation (apply_rotary_emb).
 __device__ __forceinline__ bf16x8 norm_rope_slice(const bf16x8& raw, bool is_q, const uint4& wq, const uint4& wk,
-                                                  const float* cs, const float* sn, float eps, bool full_mask,
-                                                  unsigned half_mask) {
-    float x[8], sq[8];
+                                                  const float* cs, const float* sn, float eps) {
+    float x[8];
     unpack8(raw, x);
-    unpack8(mul8(raw, raw), sq);                        // x.pow(2) is a bf16 tensor
-    float ss = 0.f;
-#pragma unroll
-    for (int i = 0; i < 8; ++i) ss += sq[i];
-    if (full_mask) {     // both half-warps of the warp are here: no computed-mask (MATCH / REDUX) preamble per shuffle
-#pragma unroll
-        for (int o = 8; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);   // xor < 16 stays inside a half-warp
-    } else {
-#pragma unroll
-        for (int o = 8; o > 0; o >>= 1) ss += __shfl_xor_sync(half_mask, ss, o);
-    }
+    // x.pow(2) is a bf16 tensor; its fp32 sum over the half-warp's 128 values: one HMMA per quad + two butterfly steps
+    // (both half-warps of a warp are always on this path together: q|k slices end at an even item index)
+    float ss = quad_sum_bf16x8(mul8(raw, raw));
+    ss += __shfl_xor_sync(0xffffffffu, ss, 4);
+    ss += __shfl_xor_sync(0xffffffffu, ss, 8);
     const float var = bf16r(ss * (1.0f / SVR2_HEAD_DIM));
     const float rms = bf16r(sqrt_approx(bf16r(var + eps)));
     const float rcp = rcp_approx(rms);
@@ -108,7 +101,10 @@ struct PackRow {
     int valid, is_txt, n_rot;
 };
 
-__global__ void __launch_bounds__(kPackThreads, 5)
+#ifndef SVR2_PACK_MINB
+#define SVR2_PACK_MINB 5      // resident CTAs per SM the register budget is sized for
+#endif
+__global__ void __launch_bounds__(kPackThreads, SVR2_PACK_MINB)
 qkv_pack_kernel(const __nv_bfloat16* __restrict__ qkv_vid, const __nv_bfloat16* __restrict__ qkv_txt,
                 const __nv_bfloat16* __restrict__ wq_vid, const __nv_bfloat16* __restrict__ wk_vid,
                 const __nv_bfloat16* __restrict__ wq_txt, const __nv_bfloat16* __restrict__ wk_txt,
@@ -181,7 +177,6 @@ qkv_pack_kernel(const __nv_bfloat16* __restrict__ qkv_vid, const __nv_bfloat16* 
     }
     __syncthreads();
 
-    const unsigned half_mask = 0xFFFFu << (threadIdx.x & 16);
 #pragma unroll
     for (int r = 0; r < kRowsPerCta; ++r) {
         if (!pr[r].valid) continue;              // uniform across the CTA
@@ -197,9 +192,8 @@ qkv_pack_kernel(const __nv_bfloat16* __restrict__ qkv_vid, const __nv_bfloat16* 
             const int item = hw_id + it * 16;
             // q | k | v without an integer division; kind 3 = no slice for this half-warp
             const int kind = item >= n_items ? 3 : (item >= heads) + (item >= 2 * heads);
-            // both half-warps on the same path -> the row-sum butterfly can use the full mask (a computed mask costs a
-            // MATCH / REDUX preamble per shuffle); all 32 lanes reach this line in every iteration
-            const bool uni = __shfl_xor_sync(0xffffffffu, kind, 16) == kind;
+            // the q|k -> v boundary (item 2 * heads) is even and the two half-warps of a warp hold items (2m, 2m+1): a warp is
+            // never split between the norm path and the others, so the row-sum HMMA below always sees a converged warp
             if (kind == 3) continue;             // uniform across the half-warp
             const int head = item - kind * heads;
             __nv_bfloat16* dst = (kind == 0 ? qp : (kind == 1 ? kp : vp)) + drow + head * SVR2_HEAD_DIM + col;
@@ -207,7 +201,7 @@ qkv_pack_kernel(const __nv_bfloat16* __restrict__ qkv_vid, const __nv_bfloat16* 
                 stg8(dst, raw[r][it]);
                 continue;
             }
-            stg8(dst, norm_rope_slice(raw[r][it], kind == 0, wq, wk, cs, sn, eps, uni, half_mask));
+            stg8(dst, norm_rope_slice(raw[r][it], kind == 0, wq, wk, cs, sn, eps));
         }
     }
 }
