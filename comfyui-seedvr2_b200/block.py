@@ -14,6 +14,7 @@ What differs is how the work is done: GEMMs stay torch/cuBLAS calls; everything 
 """
 import math
 import os
+import weakref
 from typing import Callable, Optional, Tuple
 
 import torch
@@ -127,9 +128,22 @@ class _GeluMLP(nn.Module):     # reference mlp.py:28-43
         return self.proj_out(h)
 
 
+_cast_cache = {}      # id(tensor) -> (weakref, version, data_ptr, device, bf16 copy)
+
+
 def _bf16(t: torch.Tensor) -> torch.Tensor:
-    """Parameters are used as bf16.  Checkpoints loaded with assign=True may be fp16/fp32: cast on use."""
-    return t if t.dtype == torch.bfloat16 else t.to(torch.bfloat16)
+    """Parameters are used as bf16.  Checkpoints loaded with ``assign=True`` keep the file's dtype (fp16 / fp32 / fp8,
+    model_loader.py:809, model_registry.py:34-49; the reference casts such parameters per call, modulation.py:95-107): they
+    are cast ONCE, lazily, and the copy is reused until the parameter is replaced, modified in place or moved (BlockSwap)."""
+    if t.dtype == torch.bfloat16:
+        return t
+    key = id(t)
+    hit = _cast_cache.get(key)
+    if hit is not None and hit[0]() is t and hit[1] == t._version and hit[2] == t.data_ptr() and hit[3] == t.device:
+        return hit[4]
+    c = t.detach().to(torch.bfloat16)
+    _cast_cache[key] = (weakref.ref(t, lambda _r, k=key: _cast_cache.pop(k, None)), t._version, t.data_ptr(), t.device, c)
+    return c
 
 
 def _joined(a: torch.Tensor, b: torch.Tensor) -> Optional[torch.Tensor]:

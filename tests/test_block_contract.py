@@ -55,3 +55,18 @@ def test_unsupported_configs_raise(svr2):
     with pytest.raises(NotImplementedError):
         svr2.NaMMSRTransformerBlockB200(vid_dim=128, txt_dim=128, emb_dim=768, heads=2, head_dim=128, expand_ratio=4,
                                         window=(4, 3, 3), window_method="win")
+
+
+def test_non_bf16_parameters_are_cast_once(svr2):
+    """assign=True keeps the checkpoint's dtype (fp16 / fp32 / fp8 files, model_loader.py:809): the blocks use a bf16 copy made
+    once, refreshed when the parameter is replaced, written in place or moved."""
+    from seedvr2_b200.block import _bf16
+    p = torch.nn.Parameter(torch.randn(8, 8).half())
+    a = _bf16(p)
+    assert a.dtype == torch.bfloat16 and _bf16(p) is a
+    with torch.no_grad():
+        p.mul_(2)
+    b = _bf16(p)
+    assert b is not a and torch.equal(b, p.detach().to(torch.bfloat16))
+    q = torch.nn.Parameter(torch.randn(4).bfloat16())
+    assert _bf16(q) is q

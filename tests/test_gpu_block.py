@@ -62,3 +62,23 @@ def test_block_vs_reference_golden(svr2, cuda, case):
         rep = cache.cache["emb_repeat_0_vid"]
         assert rep.shape == (vid.shape[0], case.dim, 3)
         assert torch.equal(rep[0], emb.reshape(1, -1, 2, 3)[0, :, 0, :])
+
+
+def test_block_with_fp16_checkpoint_parameters(svr2, cuda):
+    """A checkpoint loaded with assign=True keeps its dtype (the shipped files are fp16, model_registry.py:34-49); the pipeline
+    then runs the model under bf16 autocast.  The block casts such parameters to bf16 once and must give the same output as
+    with bf16 parameters (the test parameters are bf16-representable, so fp16 holds them exactly)."""
+    case = cases.BLOCK_CASES[1]
+    outs = []
+    for dt in (torch.bfloat16, torch.float16):
+        with torch.device("meta"):
+            blk = make_block(svr2, case)
+        sd = {k: (v if k.endswith("freqs") else v.to(dt)).to(cuda) for k, v in cases.block_params(case).items()}
+        blk.load_state_dict(sd, strict=True, assign=True)
+        vid, txt, emb = (t.bfloat16().to(cuda) for t in cases.block_inputs(case))
+        with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16):
+            v, t, _, _ = blk(vid=vid, txt=txt, vid_shape=torch.tensor([list(case.grid)], device=cuda),
+                             txt_shape=torch.tensor([[case.txt_len]], device=cuda), emb=emb, cache=None)
+        torch.cuda.synchronize()
+        outs.append((v.clone(), t.clone()))
+    assert torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][1], outs[1][1])

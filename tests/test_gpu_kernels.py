@@ -261,7 +261,8 @@ def test_window_attn_vs_fp32(svr2, cuda, monkeypatch, impl, grid, shifted, heads
     assert float(dv) <= 2e-2 and float(dt) <= 2e-2, f"{impl}: vid {float(dv)} txt {float(dt)}"   # north-star tolerance
 
 
-@pytest.mark.parametrize("grid,shifted,heads", [((1, 128, 128), False, 20), ((1, 128, 128), True, 20), ((9, 90, 160), True, 4)])
+@pytest.mark.parametrize("grid,shifted,heads", [((1, 128, 128), False, 20), ((1, 128, 128), True, 20), ((9, 90, 160), True, 4),
+                                                ((31, 68, 120), False, 2), ((6, 68, 120), True, 3), ((10, 135, 240), True, 1)])
 def test_window_attn_full_size_properties(svr2, cuda, monkeypatch, grid, shifted, heads):
     """BASELINE-size runs checked through size-independent properties:
     (1) V = ones -> every output row is exactly softmax-normalised (1.0): masking + all tiles + scatter coverage;
