@@ -33,6 +33,7 @@ WORKLOADS = {
     "c1": ("3b", (1, 256, 256), 1, "SeedVR2-3B 1 frame 2048x2048 image upscale"),
     "c2": ("3b", (9, 180, 320), 33, "SeedVR2-3B 33 frames 2560x1440"),
     "c3": ("7b", (31, 136, 240), 121, "SeedVR2-7B 121 frames 1920x1080"),
+    "c4": ("7b", (10, 270, 480), 37, "SeedVR2-7B 33+4-frame streaming chunk at 3840x2160"),
     "c3r": ("7b", (6, 136, 240), 21, "SeedVR2-7B 21-frame per-rank segment of the 121-frame 1080p video at 8 GPUs"),
 }
 TXT_LEN, TXT_DIM = 58, 5120

@@ -108,7 +108,8 @@ class _SwiGLU(nn.Module):      # reference mlp.py:46-62
         self.proj_in = nn.Linear(dim, hidden, bias=False)
 
     def forward(self, x):
-        return self.proj_out(ops.swiglu(self.proj_in_gate(x), self.proj_in(x)))
+        h = ops.swiglu(F.linear(x, _bf16(self.proj_in_gate.weight)), F.linear(x, _bf16(self.proj_in.weight)))
+        return F.linear(h, _bf16(self.proj_out.weight))
 
 
 class _GeluMLP(nn.Module):     # reference mlp.py:28-43
@@ -124,8 +125,8 @@ class _GeluMLP(nn.Module):     # reference mlp.py:28-43
             # GELU then sees the fp32 accumulator instead of its bf16 rounding; the block golden tests hold the bound.
             h = torch._addmm_activation(_bf16(self.proj_in.bias), x, _bf16(self.proj_in.weight).t(), use_gelu=True)
         else:
-            h = F.gelu(self.proj_in(x), approximate="tanh")
-        return self.proj_out(h)
+            h = F.gelu(F.linear(x, _bf16(self.proj_in.weight), _bf16(self.proj_in.bias)), approximate="tanh")
+        return F.linear(h, _bf16(self.proj_out.weight), _bf16(self.proj_out.bias))
 
 
 _cast_cache = {}      # id(tensor) -> (weakref, version, data_ptr, device, bf16 copy)

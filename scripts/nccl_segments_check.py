@@ -26,6 +26,25 @@ for total, overlap, hw in ((41, 4, (36, 64)), (23, 2, (20, 20)), (16, 0, (8, 8))
         same = out.shape == ref.shape and torch.equal(out, ref)
         ok &= bool(same)
         print(f"total {total} overlap {overlap} world {world}: stitched {tuple(out.shape)} {'== sequential parent loop (bit-exact)' if same else 'MISMATCH'}")
+# timing at BASELINE config C3: 121 frames of 1920x1080 RGB fp32 split over the ranks with overlap 4: neighbour halo
+# over NVLink + blend kernel + gather to rank 0, device-timed, max over ranks
+total, overlap = 121, 4
+ranges = segments.segment_ranges(total, world, overlap)
+s_, e_ = ranges[rank]
+mine = torch.rand(e_ - s_, 1080, 1920, 3, device=dev)
+for it in range(3):
+    dist.barrier(); torch.cuda.synchronize()
+    t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0.record()
+    out = segments.halo_exchange_and_gather(mine, overlap)
+    t1.record(); torch.cuda.synchronize()
+    ms = torch.tensor([t0.elapsed_time(t1)], device=dev)
+    dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    if rank == 0 and it == 2:
+        halo_mb = overlap * 1080 * 1920 * 3 * 4 / 1e6
+        print(f"C3 stitch (121 x 1080p fp32, overlap 4, world {world}): {float(ms):.2f} ms = halo {halo_mb:.0f} MB per neighbour pair + blend + "
+              f"gather of {out.shape[0]} frames ({out.numel() * 4 / 1e9:.2f} GB) to rank 0")
+    del out
 dist.barrier()
 if rank == 0:
     print("NCCL segments check", "PASSED" if ok else "FAILED")
