@@ -340,6 +340,9 @@ int launch_window_attn_tc2(const void* q, const void* k, const void* v, const in
 int launch_window_attn_tc5(const void* q, const void* k, const void* v, const int32_t* tab, const int32_t* work,
                            int n_work, int n_windows, int H, int W, int txt_len, int heads, int64_t P, void* out_vid,
                            void* txt_part, cudaStream_t st);
+int launch_window_attn_tc6(const void* q, const void* k, const void* v, const int32_t* tab, const int32_t* work,
+                           int n_work, int n_windows, int H, int W, int txt_len, int heads, int64_t P, void* out_vid,
+                           void* txt_part, cudaStream_t st);
 int launch_window_attn_tc4(const void* q, const void* k, const void* v, const int32_t* tab, const int32_t* work,
                            int n_work, int H, int W, int txt_len, int heads, int64_t P, void* out_vid, void* txt_part,
                            cudaStream_t st);
@@ -366,8 +369,8 @@ EncodeTiledFn get_encode_fn() {
 
 }  // namespace
 
-// [P, heads, 128] bf16 viewed as a 3-D tensor (d, head, row); box = 64 d x 1 head x 128 rows, 128-byte swizzle.
-int make_tmap(CUtensorMap* m, const void* ptr, int64_t P, int heads) {
+// [P, heads, 128] bf16 viewed as a 3-D tensor (d, head, row); box = 64 d x 1 head x box_rows rows, 128-byte swizzle.
+int make_tmap_box(CUtensorMap* m, const void* ptr, int64_t P, int heads, int box_rows) {
     EncodeTiledFn enc = get_encode_fn();
     if (!enc) {
         set_error("svr2_window_attn_fwd: cuTensorMapEncodeTiled not available from the driver");
@@ -375,7 +378,7 @@ int make_tmap(CUtensorMap* m, const void* ptr, int64_t P, int heads) {
     }
     const cuuint64_t gdim[3] = {(cuuint64_t)SVR2_HEAD_DIM, (cuuint64_t)heads, (cuuint64_t)P};
     const cuuint64_t gstr[2] = {(cuuint64_t)SVR2_HEAD_DIM * 2, (cuuint64_t)heads * SVR2_HEAD_DIM * 2};
-    const cuuint32_t box[3] = {64, 1, 128};
+    const cuuint32_t box[3] = {64, 1, (cuuint32_t)box_rows};
     const cuuint32_t estr[3] = {1, 1, 1};
     const CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(ptr), gdim, gstr, box, estr,
                            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
@@ -386,6 +389,7 @@ int make_tmap(CUtensorMap* m, const void* ptr, int64_t P, int heads) {
     }
     return SVR2_OK;
 }
+int make_tmap(CUtensorMap* m, const void* ptr, int64_t P, int heads) { return make_tmap_box(m, ptr, P, heads, 128); }
 
 namespace {
 
@@ -462,12 +466,14 @@ extern "C" int svr2_window_attn_fwd(const void* q_pack, const void* k_pack, cons
                    "svr2_window_attn_fwd: bad sizes");
     (void)T;
     cudaStream_t st = (cudaStream_t)stream;
-    // Product path: generation 4 (window_attn_v2.cu: persistent, whole 128-column key tiles, one TMEM round trip each).
-    // Generation 6 (window_attn_v4.cu: 64-column half tiles, double-buffered S) returns the same bits — checked by
-    // tests/test_gpu_kernels.py::test_window_attn_generations_bit_identical — and measures within +-2 % of it on NaSwin's
-    // short sequences, 5 % behind on long ones; SVR2_ATTN_IMPL=v4 selects it.  v3 (generation 5, column-split softmax),
-    // v1 (one CTA per item) and mma (the legacy mma.sync comparator) are A/B aids.  Every one is a CUDA kernel of this
-    // library.
+    // Product path, two kernels with identical output bits (tests/test_gpu_kernels.py::test_window_attn_generations_bit_identical):
+    //  * sequences of up to ~4 key tiles (stills, small windows: mean packed length <= 576 rows): generation 8
+    //    (window_attn_v6.cu) — CTA pairs with tcgen05.mma.cta_group::2, one query tile per CTA, S and P double-buffered, the
+    //    pipeline runs across item boundaries.  In the power-capped C1 step: 151.5 us against 163.7 us per launch (run 42);
+    //  * longer sequences: generation 4 (window_attn_v2.cu) — two query tiles per CTA share every K/V tile; 2 % ahead at C2,
+    //    equal at the C3 per-rank size.
+    // v3 / v4 / v5 (generations 5-7), v1 (one CTA per item) and mma (the legacy mma.sync comparator) are A/B aids; "v2" /
+    // "v6" force one of the two product kernels.  Every one is a CUDA kernel of this library.
     const char* e = getenv("SVR2_ATTN_IMPL");
     int rc;
     if (e && strcmp(e, "mma") == 0)
@@ -476,10 +482,16 @@ extern "C" int svr2_window_attn_fwd(const void* q_pack, const void* k_pack, cons
         rc = svr2::launch_window_attn_tc(q_pack, k_pack, v_pack, win_table, work, n_work, H, W, txt_len, heads, P, out_vid, txt_part, st);
     else if (e && strcmp(e, "v3") == 0)
         rc = svr2::launch_window_attn_tc3(q_pack, k_pack, v_pack, win_table, work, n_work, H, W, txt_len, heads, P, out_vid, txt_part, st);
+    else if (e && strcmp(e, "v6") == 0)
+        rc = svr2::launch_window_attn_tc6(q_pack, k_pack, v_pack, win_table, work, n_work, n_windows, H, W, txt_len, heads, P, out_vid, txt_part, st);
     else if (e && strcmp(e, "v5") == 0)
         rc = svr2::launch_window_attn_tc5(q_pack, k_pack, v_pack, win_table, work, n_work, n_windows, H, W, txt_len, heads, P, out_vid, txt_part, st);
     else if (e && strcmp(e, "v4") == 0)
         rc = svr2::launch_window_attn_tc4(q_pack, k_pack, v_pack, win_table, work, n_work, H, W, txt_len, heads, P, out_vid, txt_part, st);
+    else if (e && strcmp(e, "v2") == 0)
+        rc = svr2::launch_window_attn_tc2(q_pack, k_pack, v_pack, win_table, work, n_work, n_windows, H, W, txt_len, heads, P, out_vid, txt_part, st);
+    else if (P <= (int64_t)576 * n_windows)
+        rc = svr2::launch_window_attn_tc6(q_pack, k_pack, v_pack, win_table, work, n_work, n_windows, H, W, txt_len, heads, P, out_vid, txt_part, st);
     else
         rc = svr2::launch_window_attn_tc2(q_pack, k_pack, v_pack, win_table, work, n_work, n_windows, H, W, txt_len, heads, P, out_vid, txt_part, st);
     if (rc != SVR2_OK) return rc;

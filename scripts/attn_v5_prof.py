@@ -1,7 +1,7 @@
 """Where generation 7 (SVR2_ATTN_IMPL=v5) spends its cycles: per-role wait counters of CTA 0 (kProf instantiation, armed
 through svr2_debug_attn_trace).  python scripts/attn_v5_prof.py [c1|c2|c3] [swin]"""
 import os, sys
-os.environ["SVR2_ATTN_IMPL"] = "v5"
+os.environ.setdefault("SVR2_ATTN_IMPL", "v5")      # v5 (generation 7) or v6 (generation 8: wg rows of CTA 1 follow)
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 import seedvr2_b200 as svr2
@@ -36,6 +36,17 @@ for wg in (0, 1):
     print(f"softmax warpgroup {wg}: {a[0]} steps, {tot} cycles = {tot / steps:.0f} per step | waits per step: S full {a[2] / steps:.0f}, "
           f"m(g-1) {a[3] / steps:.0f}, P buffer free {a[4] / steps:.0f}, l(g-1) {a[5] / steps:.0f}, O drained {a[6] / steps:.0f} | "
           f"working {busy / steps:.0f} per step ({100 * busy / tot:.0f} %) | rescales {a[7]}")
+if os.environ["SVR2_ATTN_IMPL"] == "v6":
+    for wg in (0, 1):
+        a = t[24 + 8 * wg: 32 + 8 * wg]
+        steps, tot = max(a[0], 1), max(a[1], 1)
+        busy = tot - sum(a[2:7])
+        print(f"CTA 1 softmax warpgroup {wg}: {a[0]} steps, {tot / steps:.0f} per step | waits: S full {a[2] / steps:.0f}, m {a[3] / steps:.0f}, "
+              f"P buffer free {a[4] / steps:.0f}, l {a[5] / steps:.0f}, O drained {a[6] / steps:.0f} | working {busy / steps:.0f}")
+if os.environ["SVR2_ATTN_IMPL"] == "v6":
+    for wg in (0, 1):
+        ph, steps = t[40 + 4 * wg: 44 + 4 * wg], max(t[8 * wg], 1)
+        print(f"CTA 0 warpgroup {wg} phases per step: ld S {ph[0] / steps:.0f} | mask + row max {ph[1] / steps:.0f} | exp2 + pack + st issue {ph[2] / steps:.0f} | wait::st {ph[3] / steps:.0f}")
 a = t[16:24]
 steps, tot = max(a[0], 1), max(a[1], 1)
 print(f"MMA warp: {a[0]} steps, {tot} cycles = {tot / steps:.0f} per step | waits per step: S in registers {a[2] / steps:.0f}, K tile {a[3] / steps:.0f}, "
