@@ -298,6 +298,12 @@ def run_ours(args):
     attn_flops = attention_flops_per_forward(svr2, model, tok_grid, layers, heads)      # per forward
     attn_ms_per_launch = attn_ms / max(attn_n, 1)
     achieved_tf = (attn_flops / layers) / (attn_ms_per_launch * 1e-3) / 1e12 if attn_n else 0.0
+    plans = [svr2.get_plan(tok_grid, (4, 3, 3), sh, TXT_LEN) for sh in (False, True)]
+    forced = os.environ.get("SVR2_ATTN_IMPL")
+    short = all(pl.packed_rows <= 576 * pl.n_windows for pl in plans)          # the library's dispatch rule (window_attn.cu)
+    attn_kernel = (f"forced SVR2_ATTN_IMPL={forced}" if forced else
+                   "generation 8, window_attn_tc6_kernel: CTA pairs, tcgen05.mma.cta_group::2 + TMA + TMEM" if short else
+                   "generation 4, window_attn_tc2_kernel: TMA + tcgen05 + TMEM")
     traffic = None
     try:
         with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
@@ -305,7 +311,7 @@ def run_ours(args):
     except Exception:
         pass
     roofline = {
-        "kernel": "svr2_window_attn_fwd (window_attn_tc_kernel: TMA + tcgen05 + TMEM)", "bound": "tensor",
+        "kernel": "svr2_window_attn_fwd (" + attn_kernel + ")", "bound": "tensor",
         "achieved": achieved_tf, "peak": pk["bf16_tflops_sustained"], "unit": "TFLOP/s",
         "frac": achieved_tf / pk["bf16_tflops_sustained"], "frac_of_burst_peak": achieved_tf / pk["bf16_tflops"],
         "peak_source": pk_src + ", sustained bf16 figure (kernel timed inside a long step)",
