@@ -452,6 +452,8 @@ window_attn_tc6_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
         long long prof_acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
         long long ph_acc[4] = {0, 0, 0, 0};          // kProf: cycles in ld S | mask + max | exp2 + pack + st issue | wait::st
         long long ph_t = 0;
+        long long x_acc[6] = {0, 0, 0, 0, 0, 0};     // kProf: glue between the phases (see scripts/attn_v5_prof.py)
+        long long x_t = 0;
         const long long prof_t0 = kProf ? clock64() : 0;
         Cursor c;
         cur_init(p, walk, c);
@@ -464,6 +466,7 @@ window_attn_tc6_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
             const int valid = it.seq - j * BN;
             const uint32_t par = (g >> 1) & 1u;
             const uint32_t ppar = ((g - 1) >> 1) & 1u;
+            if constexpr (kProf) { if (x_t != 0) x_acc[5] += clock64() - x_t; }
             PROF_WAIT(2, mbar_wait(bar(BAR_SFULL + b), par));
             if constexpr (kProf) prof_acc[0] += 1;
             tc_fence_after();
@@ -479,6 +482,7 @@ window_attn_tc6_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive_cluster(sloaded_g);              // Q K^T(g+2) may overwrite S[b] (counted over both CTAs)
+            if constexpr (kProf) { const long long t = clock64(); x_acc[1] += t - ph_t; ph_t = t; }
             if (valid < nch * 32) mask_chunk(s + 96, valid - 32 * (nch - 1));
             float m8[8];
 #pragma unroll
@@ -490,6 +494,7 @@ window_attn_tc6_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
             const float mx = fmaxf(max3(m8[0], m8[1], m8[2]), max3(max3(m8[3], m8[4], m8[5]), m8[6], m8[7]));
             if constexpr (kProf) { if (mx > -1e30f) ph_acc[1] += clock64() - ph_t; }
             if (g > 0) PROF_WAIT(3, mbar_wait(bar(BAR_MPUB + ob), ppar));
+            if constexpr (kProf) x_t = clock64();
             float m, alpha = 1.0f;
             if (j == 0) {
                 m = ref_of(mx);
@@ -516,6 +521,7 @@ window_attn_tc6_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
             }
             m_sh[row] = m;
             mbar_arrive(bar(BAR_MPUB + b));
+            if constexpr (kProf) x_acc[2] += clock64() - x_t;
             // P[b] is free once P V(g-2) has read it.  (Waiting later, in front of the first store of P, costs registers the
             // step does not have: the spills made the step 450 cycles longer, run 38.)
             if (g >= 2) PROF_WAIT(4, mbar_wait(bar(BAR_PVDONE + b), (par ^ 1u)));
@@ -545,11 +551,13 @@ window_attn_tc6_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
             }
             if constexpr (kProf) { if (rs >= 0.f) { const long long t = clock64(); ph_acc[2] += t - ph_t; ph_t = t; } }
             tc_wait_st();
-            if constexpr (kProf) ph_acc[3] += clock64() - ph_t;
+            if constexpr (kProf) { const long long t = clock64(); ph_acc[3] += t - ph_t; ph_t = t; }
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive_cluster(pready_g);
+            if constexpr (kProf) x_acc[3] += clock64() - ph_t;
             if (g > 0) PROF_WAIT(5, mbar_wait(bar(BAR_LPUB + ob), ppar));
+            if constexpr (kProf) x_t = clock64();
             float l = 0.f;
             if (j > 0) l = l_sh[row];
             l *= alpha;
@@ -561,12 +569,14 @@ window_attn_tc6_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
             }
             l_sh[row] = l;
             mbar_arrive(bar(BAR_LPUB + b));
+            if constexpr (kProf) { const long long t = clock64(); x_acc[4] += t - x_t; x_t = t; }
         }
         if constexpr (kProf) {
             if (blockIdx.x < 2 && (threadIdx.x & 127) == 0 && p.prof != nullptr) {
                 prof_acc[1] = clock64() - prof_t0;
                 for (int q = 0; q < 8; ++q) p.prof[(blockIdx.x == 0 ? 0 : 24) + 8 * wg + q] = prof_acc[q];
                 if (blockIdx.x == 0) for (int q = 0; q < 4; ++q) p.prof[40 + 4 * wg + q] = ph_acc[q];
+                if (blockIdx.x == 0) for (int q = 0; q < 6; ++q) p.prof[48 + 8 * wg + q] = x_acc[q];
             }
         }
     }

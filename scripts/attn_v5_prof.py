@@ -47,6 +47,9 @@ if os.environ["SVR2_ATTN_IMPL"] == "v6":
     for wg in (0, 1):
         ph, steps = t[40 + 4 * wg: 44 + 4 * wg], max(t[8 * wg], 1)
         print(f"CTA 0 warpgroup {wg} phases per step: ld S {ph[0] / steps:.0f} | mask + row max {ph[1] / steps:.0f} | exp2 + pack + st issue {ph[2] / steps:.0f} | wait::st {ph[3] / steps:.0f}")
+        x = t[48 + 8 * wg: 54 + 8 * wg]
+        print(f"CTA 0 warpgroup {wg} glue per step: S-loaded fence + remote arrive {x[1] / steps:.0f} | m hand-over {x[2] / steps:.0f} | "
+              f"P-ready fence + remote arrive {x[3] / steps:.0f} | l hand-over {x[4] / steps:.0f} | cursor to next step {x[5] / steps:.0f}")
 a = t[16:24]
 steps, tot = max(a[0], 1), max(a[1], 1)
 print(f"MMA warp: {a[0]} steps, {tot} cycles = {tot / steps:.0f} per step | waits per step: S in registers {a[2] / steps:.0f}, K tile {a[3] / steps:.0f}, "
