@@ -1,9 +1,11 @@
 #!/bin/bash
-# build_variant.sh <name> <nvcc -D flags...> : experimental build of the attention kernel -> csrc/build/variants/lib_<name>.so
+# build_variant.sh <name> <source.cu> <nvcc -D flags...> : experimental build of one kernel file -> csrc/build/variants/lib_<name>.so
+# (all other objects come from the regular build; select the library with SVR2_LIB=<path>)
 set -e
-C=/root/repo/comfyui-seedvr2_b200/csrc
-name=$1; shift
+name=$1; src=$2; shift 2
+C=$(dirname $0)/../comfyui-seedvr2_b200/csrc
 mkdir -p $C/build/variants
-nvcc -O3 -std=c++17 -lineinfo -gencode arch=compute_100a,code=sm_100a -Xcompiler -fPIC --expt-relaxed-constexpr -Xptxas -v -I$C "$@" -c $C/window_attn_v2.cu -o $C/build/variants/$name.o 2> $C/build/variants/$name.log
-nvcc -shared -gencode arch=compute_100a,code=sm_100a -o $C/build/variants/lib_$name.so $C/build/api.o $C/build/window_index.o $C/build/adaln.o $C/build/qkv_pack.o $C/build/window_attn_mma.o $C/build/window_attn.o $C/build/window_attn_v3.o $C/build/window_attn_v4.o $C/build/window_attn_v5.o $C/build/variants/$name.o $C/build/halo_blend.o -lcudart
+nvcc -O3 -std=c++17 -lineinfo -gencode arch=compute_100a,code=sm_100a -Xcompiler -fPIC --expt-relaxed-constexpr -Xptxas -v -I$C "$@" -c $C/$src -o $C/build/variants/$name.o 2> $C/build/variants/$name.log
+objs=$(ls $C/build/*.o | grep -v "/${src%.cu}.o")
+nvcc -shared -gencode arch=compute_100a,code=sm_100a -o $C/build/variants/lib_$name.so $objs $C/build/variants/$name.o -lcudart
 echo "$name: $(grep -A1 'ILb0' $C/build/variants/$name.log | grep spill)"

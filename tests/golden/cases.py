@@ -215,3 +215,42 @@ def psnr(a: torch.Tensor, ref: torch.Tensor) -> float:
     mse = float(((a.double() - ref) ** 2).mean())
     peak = float(ref.max() - ref.min())
     return float("inf") if mse == 0 else 10.0 * math.log10(peak * peak / mse)
+
+
+# ---- one-step SR call either side of the DiT forward -----------------------------------------------------
+@dataclass(frozen=True)
+class SamplerCase:
+    name: str
+    grid: Tuple[int, int, int]          # latent grid (t, h, w) before patching
+    dtype: str                          # "bf16" | "fp32": the pipeline's compute dtype (sampler state and latents)
+    latent_noise_scale: float
+    seed: int
+    channels: int = 16
+
+
+SAMPLER_CASES = [
+    SamplerCase("bf16_plain", (3, 6, 10), "bf16", 0.0, 31),
+    SamplerCase("bf16_image", (1, 8, 8), "bf16", 0.0, 32),
+    SamplerCase("bf16_latent_noise", (3, 6, 10), "bf16", 0.25, 33),
+    SamplerCase("bf16_latent_noise_image", (1, 12, 16), "bf16", 1.0, 34),
+    SamplerCase("fp32_latent_noise", (2, 4, 6), "fp32", 0.5, 35),
+]
+
+
+def sampler_inputs(c: SamplerCase):
+    """latent, base noise and augmentation noise as generation_phases.py:676-679 builds them, plus the fixed matrix of the
+    stand-in DiT.  Values scaled so that x_t - pred exercises bf16 rounding."""
+    dt = torch.bfloat16 if c.dtype == "bf16" else torch.float32
+    g = torch.Generator().manual_seed(c.seed)
+    shape = (*c.grid, c.channels)
+    latent = (torch.randn(shape, generator=g) * 1.3).to(dt)
+    base_noise = torch.randn(shape, generator=g).to(dt)
+    aug_noise = base_noise * 0.1 + torch.randn(shape, generator=g).to(dt) * 0.05
+    mix = (torch.randn(2 * c.channels + 1, c.channels, generator=g) * 0.2).to(dt)
+    return latent, base_noise, aug_noise, mix
+
+
+def standin_dit(mix: torch.Tensor):
+    """A deterministic stand-in for the DiT: pred = vid @ mix (in the compute dtype), so the golden pins the channel order
+    of the concat and the endpoint arithmetic without a model."""
+    return lambda vid, timestep: (vid.float() @ mix.float()).to(vid.dtype)

@@ -9,6 +9,8 @@ The reference has no tests or fixtures of its own, so these files A
                     reference NaDiT's state-dict names and shapes
   block_<case>.pt   outputs of the reference NaMMSRTransformerBlock (fp32 CPU, and bf16 CPU) on cases.block_inputs
                     with cases.block_params loaded through load_state_dict (which also pins the state-dict contract)
+  sampler_<case>.pt condition, DiT input and one-step endpoint from the real VideoDiffusionInfer + EulerSampler with a
+                    stand-in DiT (cases.SAMPLER_CASES)
 Needs: /root/reference, oracle/shim (third-party restatements).  Never runs on the GPU box.
 """
 import hashlib
@@ -184,12 +186,64 @@ def gen_stacks():
                     "out_fp32": o32, "out_bf16": o16}, os.path.join(HERE, f"stack_{c.name}.pt"))
 
 
+def gen_sampler():
+    """The one-step SR call around the DiT forward, run through the REAL VideoDiffusionInfer / EulerSampler /
+    LinearInterpolationSchedule / UniformTrailingSamplingTimesteps with a stand-in DiT (cases.standin_dit)."""
+    from types import SimpleNamespace
+
+    from src.common.diffusion.samplers.euler import EulerSampler
+    from src.common.diffusion.schedules.lerp import LinearInterpolationSchedule
+    from src.common.diffusion.timesteps.sampling.trailing import UniformTrailingSamplingTimesteps
+    from src.common.diffusion.types import PredictionType
+    from src.core.infer import VideoDiffusionInfer
+
+    for c in cases.SAMPLER_CASES:
+        dt = torch.bfloat16 if c.dtype == "bf16" else torch.float32
+        latent, base_noise, aug_noise, mix = cases.sampler_inputs(c)
+        runner = object.__new__(VideoDiffusionInfer)
+        runner.config = SimpleNamespace(
+            diffusion=SimpleNamespace(timesteps={"transform": True}, cfg=SimpleNamespace(scale=1.0, rescale=0.0, get=lambda k, d=None: d)),
+            vae=SimpleNamespace(model={}))
+        runner.schedule = LinearInterpolationSchedule(T=1000.0)                      # configs_3b/main.yaml:66-68
+        runner.sampling_timesteps = UniformTrailingSamplingTimesteps(T=1000.0, steps=1, shift=1.0, device="cpu", dtype=dt)
+        runner.sampler = EulerSampler(schedule=runner.schedule, timesteps=runner.sampling_timesteps,
+                                      prediction_type=PredictionType.v_lerp)
+        runner.sampler.get_progress_bar = lambda: SimpleNamespace(update=lambda: None)
+        seen = {}
+        fake = cases.standin_dit(mix)
+
+        def dit(vid, txt, vid_shape, txt_shape, timestep):
+            seen["vid"], seen["timestep"], seen["vid_shape"] = vid.clone(), timestep.clone(), vid_shape.clone()
+            return SimpleNamespace(vid_sample=fake(vid, timestep))
+        runner.dit = dit
+
+        # generation_phases.py:685-701
+        def _add_noise(x, aug):
+            if c.latent_noise_scale == 0.0:
+                return x
+            t = torch.tensor([1000.0], dtype=dt) * c.latent_noise_scale
+            shape = torch.tensor(x.shape[1:])[None]
+            t = runner.timestep_transform(t, shape)
+            return runner.schedule.forward(x, aug, t)
+        blur = _add_noise(latent, aug_noise)
+        condition = runner.get_condition(base_noise, task="sr", latent_blur=blur)
+        txt = torch.zeros(58, 8, dtype=dt)
+        out = runner.inference(noises=[base_noise], conditions=[condition], texts_pos=[txt], texts_neg=[txt])
+        assert len(out) == 1 and out[0].shape == latent.shape
+        torch.save({"latent_blur": blur, "condition": condition, "dit_input": seen["vid"], "timestep": seen["timestep"],
+                    "vid_shape": seen["vid_shape"], "x0": out[0]}, os.path.join(HERE, f"sampler_{c.name}.pt"))
+        print(f"sampler_{c.name}.pt: input {tuple(seen['vid'].shape)} {seen['vid'].dtype} timestep {seen['timestep'].tolist()} "
+              f"x0 {out[0].dtype} blur dtype {blur.dtype}")
+
+
 if __name__ == "__main__":
     torch.manual_seed(0)
-    what = sys.argv[1:] or ["geometry", "blocks", "stacks"]
+    what = sys.argv[1:] or ["geometry", "blocks", "stacks", "sampler"]
     if "geometry" in what:
         gen_geometry()
     if "blocks" in what:
         gen_blocks()
     if "stacks" in what:
         gen_stacks()
+    if "sampler" in what:
+        gen_sampler()

@@ -130,3 +130,21 @@ def test_nadit_forward_matches_reference(case):
     # the north star's decoded-output bar applied to the reference's OWN bf16 path: it must clear 45 dB for the
     # bar to be meaningful at these magnitudes
     assert cases.psnr(gold["out_bf16"].float(), gold["out_fp32"]) > 45.0
+
+
+# ---- one-step SR call around the DiT forward ---------------------------------------------------------------
+@pytest.mark.parametrize("case", cases.SAMPLER_CASES, ids=lambda c: c.name)
+def test_sampler_oracle_matches_reference(case):
+    """oracle/sampler.py against the real VideoDiffusionInfer.get_condition / timestep_transform / inference + EulerSampler
+    (tests/golden/sampler_*.pt): condition, DiT input (channel order of the concat) and x_0, bit for bit."""
+    from oracle import sampler as osamp
+    gold = torch.load(os.path.join(GOLD, f"sampler_{case.name}.pt"))
+    latent, base_noise, aug_noise, mix = cases.sampler_inputs(case)
+    blur = osamp.add_noise(latent, aug_noise, case.latent_noise_scale)
+    assert blur.dtype == gold["latent_blur"].dtype and torch.equal(blur, gold["latent_blur"])
+    cond = osamp.sr_condition(base_noise, blur)
+    assert torch.equal(cond, gold["condition"])
+    vid, x0 = osamp.one_step(cases.standin_dit(mix), base_noise, cond)
+    assert torch.equal(vid, gold["dit_input"])
+    assert x0.dtype == gold["x0"].dtype and torch.equal(x0, gold["x0"])
+    assert gold["timestep"].tolist() == [1000.0] and gold["vid_shape"].tolist() == [list(case.grid)]
