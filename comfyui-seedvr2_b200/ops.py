@@ -237,3 +237,41 @@ def halo_blend(prev_tail: torch.Tensor, cur_head: torch.Tensor, overlap: int, ou
     _call("svr2_halo_blend", 1, prev_tail.device, _lib.lib().svr2_halo_blend, prev_tail.data_ptr(), cur_head.data_ptr(),
           out.data_ptr(), int(overlap), frame, _stream(prev_tail))
     return out
+
+
+@torch._dynamo.disable
+def sr_input(noise: torch.Tensor, latent: torch.Tensor, aug_noise: Optional[torch.Tensor] = None,
+             A: float = 1.0, B: float = 0.0, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """[N, 2C+1] bf16 DiT input = [noise | A*latent + B*aug_noise (or latent when aug_noise is None) | 1]
+    (infer.py:54-78,341; generation_phases.py:685-693).  noise / latent / aug_noise: [..., C] with N = prod(leading dims)."""
+    _need(noise, "noise"); _need(latent, "latent")
+    if aug_noise is not None:
+        _need(aug_noise, "aug_noise")
+        if aug_noise.shape != latent.shape:
+            raise RuntimeError("sr_input: aug_noise must have the latent's shape")
+    if noise.shape != latent.shape:
+        raise RuntimeError(f"sr_input: noise {tuple(noise.shape)} and latent {tuple(latent.shape)} differ")
+    C = noise.shape[-1]
+    N = noise.numel() // C
+    if out is None:
+        out = torch.empty(N, 2 * C + 1, dtype=torch.bfloat16, device=noise.device)
+    else:
+        _need(out, "out")
+        if out.shape != (N, 2 * C + 1):
+            raise RuntimeError(f"sr_input: out must be [{N}, {2 * C + 1}]")
+    _call("svr2_sr_input_fwd", 1, noise.device, _lib.lib().svr2_sr_input_fwd, noise.data_ptr(), latent.data_ptr(), _ptr(aug_noise),
+          float(A), float(B), int(aug_noise is not None), out.data_ptr(), N, C, _stream(noise))
+    return out
+
+
+@torch._dynamo.disable
+def v_lerp_endpoint(x_t: torch.Tensor, pred: torch.Tensor, A: float = 0.0, B: float = 1.0,
+                    out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """bf16 (x_t - B*pred) / (A + B), every op rounded to bf16 (samplers/base.py:88-98, schedules/base.py:107-109)."""
+    _need(x_t, "x_t"); _need(pred, "pred")
+    if x_t.numel() != pred.numel():
+        raise RuntimeError("v_lerp_endpoint: x_t and pred differ in size")
+    out = torch.empty_like(x_t) if out is None else _need(out, "out")
+    _call("svr2_v_lerp_endpoint_fwd", 1, x_t.device, _lib.lib().svr2_v_lerp_endpoint_fwd, x_t.data_ptr(), pred.data_ptr(),
+          float(A), float(B), out.data_ptr(), x_t.numel(), _stream(x_t))
+    return out

@@ -168,6 +168,24 @@ int svr2_txt_pool_fwd(const void* txt_part, void* out_txt, int n_windows, int tx
 int svr2_halo_blend(const float* prev_tail, const float* cur_head, float* out, int overlap, int64_t frame_elems,
                     void* stream);
 
+/*
+ * DiT input of the one-step super-resolution call, bf16:  out[n, 0:C] = noise[n], out[n, C:2C] = blurred latent[n],
+ * out[n, 2C] = 1.   Replaces get_condition(task="sr") (src/core/infer.py:54-78) + torch.cat([x_t, latents_cond], -1)
+ * (src/core/infer.py:341) and, when augment != 0, the latent-noise augmentation
+ * latent_blur = A*latent + B*aug_noise (src/core/generation_phases.py:685-693 -> schedules/base.py:82-87; A = 1 - t/T,
+ * B = t/T after timestep_transform, fp32 in the reference, rounded to bf16 once).  augment == 0: aug_noise may be NULL.
+ */
+int svr2_sr_input_fwd(const void* noise, const void* latent, const void* aug_noise, float A, float B, int augment,
+                      void* out, int64_t n_rows, int channels, void* stream);
+
+/*
+ * Endpoint of the Euler sampler for prediction type v_lerp, bf16 sampler state (every op rounds to bf16):
+ * out = (x_t - B*pred) / (A + B).   Replaces EulerSampler.get_endpoint (src/common/diffusion/samplers/base.py:88-98) ->
+ * Schedule.convert_from_pred (src/common/diffusion/schedules/base.py:107-109).  One-step schedule: A = 0, B = 1.
+ * out may alias x_t or pred.
+ */
+int svr2_v_lerp_endpoint_fwd(const void* x_t, const void* pred, float A, float B, void* out, int64_t n, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
