@@ -31,6 +31,7 @@ SIGNATURES = {
     "svr2_debug_attn_trace": (c_int, [c_void_p, c_int]),
     "svr2_txt_pool_fwd": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
     "svr2_halo_blend": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int64, c_void_p]),
+    "svr2_segment_stitch_peer": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int64, c_void_p]),
     "svr2_sr_input_fwd": (c_int, [c_void_p, c_void_p, c_void_p, c_float, c_float, c_int, c_void_p, c_int64, c_int, c_void_p]),
     "svr2_v_lerp_endpoint_fwd": (c_int, [c_void_p, c_void_p, c_float, c_float, c_void_p, c_int64, c_void_p]),
 }

@@ -21,16 +21,42 @@ __device__ __forceinline__ float prev_weight(int f, int overlap) {
     return (f < overlap / 2) ? 1.0f + step * (float)f : 0.0f - step * (float)(overlap - 1 - f);
 }
 
+// one expression for every kernel that blends, so that they round identically
+__device__ __forceinline__ float4 blend4(const float4 a, const float4 b, float wp, float wc) {
+    float4 r;
+    r.x = a.x * wp + b.x * wc; r.y = a.y * wp + b.y * wc; r.z = a.z * wp + b.z * wc; r.w = a.w * wp + b.w * wc;
+    return r;
+}
+
+// Halo exchange + crossfade + gather in ONE kernel over peer memory.  `mine` is this rank's segment, `prev_tail` the previous
+// rank's last `head` frames (a peer mapping: NVLink loads), `out` this rank's slot in the ROOT's stitched video (a peer
+// mapping for every rank but the root: NVLink stores).  Output frame f < head is the crossfade of prev_tail[f] and mine[f];
+// output frame f >= head is mine[first_body + f - head].  blockIdx.y = output frame.
+__global__ void __launch_bounds__(256) segment_stitch_peer_kernel(const float4* __restrict__ mine, const float4* __restrict__ prev_tail,
+                                                                 float4* __restrict__ out, int head, int first_body,
+                                                                 int64_t n4_per_frame) {
+    const int f = blockIdx.y;
+    float4* dst = out + (int64_t)f * n4_per_frame;
+    if (f < head) {
+        const float wp = prev_weight(f, head), wc = 1.0f - wp;
+        const float4* a = prev_tail + (int64_t)f * n4_per_frame;
+        const float4* b = mine + (int64_t)f * n4_per_frame;
+        for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4_per_frame; i += (int64_t)gridDim.x * blockDim.x)
+            dst[i] = blend4(a[i], b[i], wp, wc);
+    } else {
+        const float4* b = mine + (int64_t)(first_body + f - head) * n4_per_frame;
+        for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4_per_frame; i += (int64_t)gridDim.x * blockDim.x)
+            dst[i] = b[i];
+    }
+}
+
 __global__ void __launch_bounds__(256) halo_blend_kernel(const float4* __restrict__ prev, const float4* __restrict__ cur,
                                                          float4* __restrict__ out, int overlap, int64_t n4_per_frame) {
     const int f = blockIdx.y;
     const float wp = prev_weight(f, overlap), wc = 1.0f - wp;
     const int64_t base = (int64_t)f * n4_per_frame;
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4_per_frame; i += (int64_t)gridDim.x * blockDim.x) {
-        const float4 a = prev[base + i], b = cur[base + i];
-        float4 r;
-        r.x = a.x * wp + b.x * wc; r.y = a.y * wp + b.y * wc; r.z = a.z * wp + b.z * wc; r.w = a.w * wp + b.w * wc;
-        out[base + i] = r;
+        out[base + i] = blend4(prev[base + i], cur[base + i], wp, wc);
     }
 }
 
@@ -49,5 +75,24 @@ extern "C" int svr2_halo_blend(const float* prev_tail, const float* cur_head, fl
     svr2::halo_blend_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>((const float4*)prev_tail, (const float4*)cur_head,
                                                                     (float4*)out, overlap, n4);
     SVR2_CHECK_LAUNCH("svr2_halo_blend");
+    return SVR2_OK;
+}
+
+extern "C" int svr2_segment_stitch_peer(const float* mine, const float* prev_tail, float* out, int head, int first_body,
+                                        int n_body, int64_t frame_elems, void* stream) {
+    SVR2_CHECK_ARG(mine && out, "svr2_segment_stitch_peer: null pointer");
+    SVR2_CHECK_ARG(head >= 0 && first_body >= 0 && n_body >= 0 && head + n_body <= 65535 && frame_elems > 0 && frame_elems % 4 == 0,
+                   "svr2_segment_stitch_peer: bad frame counts (%d head, %d body from %d) or frame_elems %% 4 != 0 (%lld)", head, n_body,
+                   first_body, (long long)frame_elems);
+    SVR2_CHECK_ARG(head == 0 || prev_tail, "svr2_segment_stitch_peer: head frames need the previous segment's tail");
+    if (head + n_body == 0) return SVR2_OK;
+    const int64_t n4 = frame_elems / 4;
+    int64_t gx = (n4 + 255) / 256;
+    const int64_t cap = (int64_t)svr2::sm_count() * 8;
+    if (gx > cap) gx = cap;
+    dim3 grid((unsigned)gx, head + n_body);
+    svr2::segment_stitch_peer_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>((const float4*)mine, (const float4*)prev_tail, (float4*)out,
+                                                                             head, first_body, n4);
+    SVR2_CHECK_LAUNCH("svr2_segment_stitch_peer");
     return SVR2_OK;
 }

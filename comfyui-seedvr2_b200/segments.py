@@ -145,3 +145,66 @@ def _gather_ragged(frames, lens, frame_shape, rank, world, group, g):
         for w in dist.batch_isend_irecv(ops_):
             w.wait()
     return parts
+
+
+# ---- the same stitch as ONE kernel per rank over peer memory -----------------------------------------------------------------
+def stitch_layout(lens: Sequence[int], overlap: int) -> List[Tuple[int, int, int, int]]:
+    """Per rank (out_offset, head, first_body, n_body) of the stitched video for segments of ``lens`` frames:
+    ``head`` frames are crossfades with the previous segment's tail, then ``n_body`` frames are copied from
+    ``first_body`` on; every segment but the last drops its final ``overlap`` frames (inference_cli.py:1163-1198).
+    Only defined where the sequential loop's result does not depend on its order: every segment >= 2 * overlap frames."""
+    n = len(lens)
+    if overlap < 0 or any(l < max(2 * overlap, 1) for l in lens):
+        raise ValueError("stitch_layout: every segment needs at least max(2 * overlap, 1) frames")
+    out, off = [], 0
+    for r, l in enumerate(lens):
+        head = overlap if r > 0 else 0
+        body = l - head - (overlap if r < n - 1 else 0)
+        out.append((off, head, head, body))
+        off += head + body
+    return out
+
+
+class PeerStitcher:
+    """Halo exchange + crossfade + gather as one kernel per rank (``svr2_segment_stitch_peer``): every rank reads its
+    predecessor's tail and writes its frames into the root's video through NVLink peer mappings of two symmetric-memory
+    buffers; the only other device work is a signal-pad barrier on either side.  The producer writes its segment into
+    ``segment_buffer()``; ``stitch(lens)`` returns the stitched video on rank 0 (a view of the root buffer), None elsewhere.
+    Symmetric memory is torch.distributed plumbing (CUDA VMM handles exchanged through the process group's store)."""
+
+    def __init__(self, max_segment_frames: int, total_out_frames: int, frame_shape: Tuple[int, ...], device: torch.device,
+                 group: Optional[dist.ProcessGroup] = None):
+        import torch.distributed._symmetric_memory as symm
+        self.group = group if group is not None else dist.group.WORLD
+        self.rank, self.world = dist.get_rank(self.group), dist.get_world_size(self.group)
+        self.frame_shape = tuple(frame_shape)
+        self.frame_elems = 1
+        for d in self.frame_shape:
+            self.frame_elems *= d
+        if self.frame_elems % 4:
+            raise ValueError("PeerStitcher: frame element count must be a multiple of 4")
+        self.seg = symm.empty((max_segment_frames,) + self.frame_shape, dtype=torch.float32, device=device)
+        self.out = symm.empty((total_out_frames,) + self.frame_shape, dtype=torch.float32, device=device)
+        self.h_seg = symm.rendezvous(self.seg, self.group)
+        self.h_out = symm.rendezvous(self.out, self.group)
+
+    def segment_buffer(self) -> torch.Tensor:
+        return self.seg
+
+    def stitch(self, lens: Sequence[int], overlap: int) -> Optional[torch.Tensor]:
+        from . import _lib, ops
+        lay = stitch_layout(lens, overlap)
+        off, head, first_body, n_body = lay[self.rank]
+        total = lay[-1][0] + lay[-1][1] + lay[-1][3]
+        if lens[self.rank] > self.seg.shape[0] or total > self.out.shape[0]:
+            raise ValueError("PeerStitcher: buffers too small for these segments")
+        fb = self.frame_elems * 4
+        prev_tail = None
+        if head:
+            prev_tail = int(self.h_seg.buffer_ptrs[self.rank - 1]) + (lens[self.rank - 1] - head) * fb
+        out_ptr = int(self.h_out.buffer_ptrs[0]) + off * fb
+        self.h_seg.barrier(channel=0)                  # every rank's segment is complete before anyone reads a tail
+        ops._call("svr2_segment_stitch_peer", 1, self.seg.device, _lib.lib().svr2_segment_stitch_peer, self.seg.data_ptr(),
+                  prev_tail, out_ptr, head, first_body, n_body, self.frame_elems, ops._stream(self.seg))
+        self.h_out.barrier(channel=0)                  # every rank's frames have landed in the root's buffer
+        return self.out[:total] if self.rank == 0 else None

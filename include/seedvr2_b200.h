@@ -169,6 +169,21 @@ int svr2_halo_blend(const float* prev_tail, const float* cur_head, float* out, i
                     void* stream);
 
 /*
+ * Halo exchange + crossfade + gather of one rank's temporal segment in ONE kernel over peer memory (NVLink loads / stores).
+ * Replaces, for this rank, the parent process's stitch loop (inference_cli.py:1163-1198) and the shared-memory / queue
+ * hand-over of the worker results (inference_cli.py:1021,1148-1153).
+ *   mine       this rank's segment [frames, frame_elems] fp32 (local)
+ *   prev_tail  the previous rank's LAST `head` frames (peer mapping of its segment buffer), NULL when head == 0
+ *   out        this rank's first output frame inside the root's stitched video (peer mapping unless this rank is the root)
+ *   out[f] = prev_tail[f]*w[f] + mine[f]*(1-w[f])  for f < head  (w as svr2_halo_blend with overlap = head),
+ *   out[head + g] = mine[first_body + g]            for g < n_body.
+ * The caller orders the launch after every rank finished producing its segment and tells the root when all ranks are done
+ * (a barrier on either side; comfyui-seedvr2_b200/segments.py uses the symmetric-memory signal pads).
+ */
+int svr2_segment_stitch_peer(const float* mine, const float* prev_tail, float* out, int head, int first_body, int n_body,
+                             int64_t frame_elems, void* stream);
+
+/*
  * DiT input of the one-step super-resolution call, bf16:  out[n, 0:C] = noise[n], out[n, C:2C] = blurred latent[n],
  * out[n, 2C] = 1.   Replaces get_condition(task="sr") (src/core/infer.py:54-78) + torch.cat([x_t, latents_cond], -1)
  * (src/core/infer.py:341) and, when augment != 0, the latent-noise augmentation

@@ -71,3 +71,23 @@ def test_halo_exchange_gloo(svr2, tmp_path, lens, overlap):
     ref = partition.stitch(chunks, overlap)
     assert got.shape == ref.shape
     assert torch.equal(got, ref)
+
+
+@pytest.mark.parametrize("lens,overlap", [((20, 19, 19, 15), 4), ((8, 8), 4), ((5, 7, 6), 2), ((3, 3, 3), 0), ((9,), 3),
+                                          ((16, 15, 15, 15, 15, 15, 15, 15), 4)])
+def test_stitch_layout_places_frames_like_the_sequential_loop(svr2, lens, overlap):
+    """Host arithmetic of the peer-memory stitch (segments.stitch_layout) against the parent loop restated in
+    segments.stitch_sequential (inference_cli.py:1163-1198): same length, copied frames in the same places, crossfades where
+    the loop blends."""
+    import torch
+    from seedvr2_b200 import segments
+    chunks = [torch.arange(l, dtype=torch.float32).view(l, 1, 1, 1).expand(l, 1, 1, 4) + 1000.0 * r for r, l in enumerate(lens)]
+    ref = segments.stitch_sequential(chunks, overlap, blend=lambda p, c, o: torch.full_like(c, -1.0))
+    lay = segments.stitch_layout(lens, overlap)
+    total = lay[-1][0] + lay[-1][1] + lay[-1][3]
+    assert total == ref.shape[0]
+    for r, (off, head, first_body, n_body) in enumerate(lay):
+        assert bool((ref[off:off + head] == -1.0).all())
+        assert torch.equal(ref[off + head: off + head + n_body], chunks[r][first_body:first_body + n_body])
+    with pytest.raises(ValueError):
+        segments.stitch_layout((6, 3, 6), 2)           # a segment shorter than 2 * overlap: order-dependent, not offered
