@@ -343,6 +343,8 @@ int launch_window_attn_tc5(const void* q, const void* k, const void* v, const in
 int launch_window_attn_tc6(const void* q, const void* k, const void* v, const int32_t* tab, const int32_t* work,
                            int n_work, int n_windows, int H, int W, int txt_len, int heads, int64_t P, void* out_vid,
                            void* txt_part, cudaStream_t st);
+int launch_window_attn_tc7(const void* q, const void* k, const void* v, const int32_t* tab, const int32_t* work4, int n_work4,
+                           int H, int W, int txt_len, int heads, int64_t P, void* out_vid, void* txt_part, cudaStream_t st);
 int launch_window_attn_tc4(const void* q, const void* k, const void* v, const int32_t* tab, const int32_t* work,
                            int n_work, int H, int W, int txt_len, int heads, int64_t P, void* out_vid, void* txt_part,
                            cudaStream_t st);
@@ -438,12 +440,19 @@ extern "C" int svr2_debug_attn_trace(void* trace_buf, int n_ctas) {
 
 extern "C" int svr2_window_attn_worklist(const int32_t* win_table_host, int n_windows, int txt_len, int32_t* work,
                                          int max_items, int64_t* n_items) {
-    SVR2_CHECK_ARG(win_table_host && n_items && n_windows > 0 && txt_len >= 0, "svr2_window_attn_worklist: bad arguments");
+    return svr2_window_attn_worklist_tiles(win_table_host, n_windows, txt_len, 2, work, max_items, n_items);
+}
+
+extern "C" int svr2_window_attn_worklist_tiles(const int32_t* win_table_host, int n_windows, int txt_len, int tiles_per_item,
+                                               int32_t* work, int max_items, int64_t* n_items) {
+    SVR2_CHECK_ARG(win_table_host && n_items && n_windows > 0 && txt_len >= 0 && tiles_per_item > 0 && tiles_per_item <= 64,
+                   "svr2_window_attn_worklist: bad arguments");
+    const int rows_per_item = 128 * tiles_per_item;
     struct Item { int seq, win, qp; };
     std::vector<Item> items;
     for (int i = 0; i < n_windows; ++i) {
         const int seq = win_table_host[i * SVR2_WIN_FIELDS + 7] + txt_len;
-        for (int qp = 0; qp * 256 < seq; ++qp) items.push_back({seq, i, qp});
+        for (int qp = 0; qp * rows_per_item < seq; ++qp) items.push_back({seq, i, qp});
     }
     // longest sequences first (LPT): the ragged shifted-window remnants fill the tail of the last wave
     std::stable_sort(items.begin(), items.end(), [](const Item& a, const Item& b) { return a.seq > b.seq; });
@@ -458,8 +467,9 @@ extern "C" int svr2_window_attn_worklist(const int32_t* win_table_host, int n_wi
 }
 
 extern "C" int svr2_window_attn_fwd(const void* q_pack, const void* k_pack, const void* v_pack, const int32_t* win_table,
-                                    const int32_t* work, int n_work, int n_windows, int T, int H, int W, int txt_len,
-                                    int heads, int64_t P, void* out_vid, void* txt_part, void* out_txt, void* stream) {
+                                    const int32_t* work, int n_work, const int32_t* work4, int n_work4, int n_windows, int T,
+                                    int H, int W, int txt_len, int heads, int64_t P, void* out_vid, void* txt_part,
+                                    void* out_txt, void* stream) {
     SVR2_CHECK_ARG(q_pack && k_pack && v_pack && win_table && work && out_vid, "svr2_window_attn_fwd: null pointer");
     SVR2_CHECK_ARG(txt_len == 0 || txt_part, "svr2_window_attn_fwd: text workspace missing");
     SVR2_CHECK_ARG(n_work > 0 && n_windows > 0 && heads > 0 && heads <= 65535 && P > 0 && P < ((int64_t)1 << 31),
@@ -482,7 +492,10 @@ extern "C" int svr2_window_attn_fwd(const void* q_pack, const void* k_pack, cons
         rc = svr2::launch_window_attn_tc(q_pack, k_pack, v_pack, win_table, work, n_work, H, W, txt_len, heads, P, out_vid, txt_part, st);
     else if (e && strcmp(e, "v3") == 0)
         rc = svr2::launch_window_attn_tc3(q_pack, k_pack, v_pack, win_table, work, n_work, H, W, txt_len, heads, P, out_vid, txt_part, st);
-    else if (e && strcmp(e, "v6") == 0)
+    else if (e && strcmp(e, "v7") == 0) {
+        SVR2_CHECK_ARG(work4 && n_work4 > 0, "svr2_window_attn_fwd: SVR2_ATTN_IMPL=v7 needs the 4-tile work list");
+        rc = svr2::launch_window_attn_tc7(q_pack, k_pack, v_pack, win_table, work4, n_work4, H, W, txt_len, heads, P, out_vid, txt_part, st);
+    } else if (e && strcmp(e, "v6") == 0)
         rc = svr2::launch_window_attn_tc6(q_pack, k_pack, v_pack, win_table, work, n_work, n_windows, H, W, txt_len, heads, P, out_vid, txt_part, st);
     else if (e && strcmp(e, "v5") == 0)
         rc = svr2::launch_window_attn_tc5(q_pack, k_pack, v_pack, win_table, work, n_work, n_windows, H, W, txt_len, heads, P, out_vid, txt_part, st);

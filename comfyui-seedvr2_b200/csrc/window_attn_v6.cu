@@ -22,6 +22,7 @@
 #include <cstdlib>
 
 #include "common.cuh"
+#include "sm100_pair.cuh"
 #include "sm100_ptx.cuh"
 #include "softmax_row.cuh"
 
@@ -29,6 +30,7 @@ namespace svr2 {
 namespace tc6 {
 
 using namespace ptx;
+using namespace pairx;
 using namespace rowsm;
 
 constexpr int D = SVR2_HEAD_DIM;          // 128
@@ -126,69 +128,6 @@ __device__ __forceinline__ void cur_next_item(const Params& p, const Walk& w, Cu
 
 template <int N> __device__ __forceinline__ void reg_alloc() { asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(N)); }
 template <int N> __device__ __forceinline__ void reg_dealloc() { asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(N)); }
-
-// ---- pair-wide primitives ------------------------------------------------------------------------------------------
-__device__ __forceinline__ uint32_t cluster_rank() {
-    uint32_t r;
-    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
-    return r;
-}
-__device__ __forceinline__ void cluster_sync_all() {
-    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
-    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
-}
-// shared::cluster address of the same shared-memory offset in CTA `rank` of the cluster
-__device__ __forceinline__ uint32_t mapa(uint32_t addr, uint32_t rank) {
-    uint32_t r;
-    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
-    return r;
-}
-// Arrival on a barrier of another CTA of the cluster.  Default semantics (release at CTA scope), as CUTLASS's
-// ClusterBarrier::arrive(cta_id) issues it: what crosses the pair here are tcgen05 operations, ordered by the
-// tcgen05.fence::before/after_thread_sync pair around the barrier.  The .release.cluster form measured ~1,000 cycles per
-// arrival in the softmax warps (profile of run 36: 5,470 instead of 3,400 working cycles per step).
-__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
-    asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
-}
-__device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity) { mbar_wait(bar, parity); }
-// TMA load whose bytes complete on the LEADER's barrier (same offset, peer bit cleared)
-__device__ __forceinline__ void tma_load_3d_pair(uint32_t dst, const CUtensorMap* m, uint32_t bar, int c0, int c1, int c2) {
-    asm volatile(
-        "cp.async.bulk.tensor.3d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
-        ::"r"(dst), "l"(m), "r"(bar & 0xFEFFFFFFu), "r"(c0), "r"(c1), "r"(c2) : "memory");
-}
-__device__ __forceinline__ void tmem_alloc_pair(uint32_t dst_smem, uint32_t ncols) {   // one warp in EACH CTA, same warp index
-    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(dst_smem), "r"(ncols) : "memory");
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
-}
-__device__ __forceinline__ void tmem_dealloc_pair(uint32_t taddr, uint32_t ncols) {
-    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
-}
-// all previously issued MMAs of this thread arrive on the barrier at this offset in BOTH CTAs when complete
-__device__ __forceinline__ void tc_commit_pair(uint32_t bar) {
-    asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
-                 ::"r"(bar), "h"((uint16_t)3) : "memory");
-}
-// -DSVR2_V6_NO_MMA: experiment build that issues no MMA (results are garbage): does the softmax step get cheaper without the
-// tensor pipe's TMEM / shared-memory traffic?
-__device__ __forceinline__ void mma2_ss(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accum) {
-#ifdef SVR2_V6_NO_MMA
-    return;
-#endif
-    asm volatile(
-        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
-        "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}"
-        ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accum) : "memory");
-}
-__device__ __forceinline__ void mma2_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint32_t idesc, uint32_t accum) {
-#ifdef SVR2_V6_NO_MMA
-    return;
-#endif
-    asm volatile(
-        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
-        "tcgen05.mma.cta_group::2.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
-        ::"r"(d_tmem), "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"(accum) : "memory");
-}
 
 #define PROF_WAIT(slot, stmt) do { if constexpr (kProf) { const long long t0_ = clock64(); stmt; prof_acc[slot] += clock64() - t0_; } else { stmt; } } while (0)
 template <bool kProf>

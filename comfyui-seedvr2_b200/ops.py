@@ -218,7 +218,7 @@ def window_attn(plan: WindowPlan, q: torch.Tensor, k: torch.Tensor, v: torch.Ten
     # attention and text pooling are two kernels; they are launched separately so the attention kernel can be timed alone
     _call("svr2_window_attn_fwd", 1, dev, _lib.lib().svr2_window_attn_fwd,
           q.data_ptr(), k.data_ptr(), v.data_ptr(), d["table"].data_ptr(), d["work"].data_ptr(), plan.work.shape[0],
-          plan.n_windows, T, H, W, plan.txt_len, heads, plan.packed_rows, out_vid.data_ptr(), txt_part.data_ptr(),
+          d["work4"].data_ptr(), plan.work4.shape[0], plan.n_windows, T, H, W, plan.txt_len, heads, plan.packed_rows, out_vid.data_ptr(), txt_part.data_ptr(),
           None, _stream(q))
     if plan.txt_len:
         _call("svr2_txt_pool_fwd", 1, dev, _lib.lib().svr2_txt_pool_fwd, txt_part.data_ptr(), out_txt.data_ptr(),

@@ -48,6 +48,11 @@ class WindowPlan:
         _lib.check(L.svr2_window_attn_worklist(tp, n, self.txt_len, work.ctypes.data_as(ctypes.POINTER(ctypes.c_int32)),
                                                work.shape[0], ctypes.byref(n_items)), "svr2_window_attn_worklist")
         self.work = work
+        _lib.check(L.svr2_window_attn_worklist_tiles(tp, n, self.txt_len, 4, None, 0, ctypes.byref(n_items)), "svr2_window_attn_worklist_tiles")
+        work4 = np.zeros((int(n_items.value), 2), dtype=np.int32)
+        _lib.check(L.svr2_window_attn_worklist_tiles(tp, n, self.txt_len, 4, work4.ctypes.data_as(ctypes.POINTER(ctypes.c_int32)),
+                                                     work4.shape[0], ctypes.byref(n_items)), "svr2_window_attn_worklist_tiles")
+        self.work4 = work4          # the same list in units of four query tiles (CTA-pair kernel)
         self._dev: Dict[torch.device, Dict[str, torch.Tensor]] = {}
 
     # ---- host-side views (reference vocabulary) -----------------------------------------------------------------
@@ -84,6 +89,7 @@ class WindowPlan:
             d = {
                 "table": torch.from_numpy(self.table).to(device),
                 "work": torch.from_numpy(self.work).to(device),
+                "work4": torch.from_numpy(self.work4).to(device),
             }
             self._dev[device] = d
         return d

@@ -131,20 +131,26 @@ int svr2_pack_rowmap(const int32_t* win_table, int n_windows, int T, int H, int 
  */
 int svr2_window_attn_worklist(const int32_t* win_table_host, int n_windows, int txt_len, int32_t* work,
                               int max_items, int64_t* n_items);
+/* The same list in units of `tiles_per_item` query tiles (2 = the list above; 4 = the list of the CTA-pair kernel,
+ * window_attn_v7.cu, whose cluster takes four query tiles of a window at a time):  work [max_items][2] = (window, group). */
+int svr2_window_attn_worklist_tiles(const int32_t* win_table_host, int n_windows, int txt_len, int tiles_per_item,
+                                    int32_t* work, int max_items, int64_t* n_items);
 
 /*
  * Variable-length window attention over the packed layout, window reverse and text pooling fused in the epilogue.
  * Replaces FlashAttentionVarlen / pytorch_varlen_attention's per-window SDPA loop (src/models/dit_3b/attention.py:
  * 24-61,138-157), unconcat_win (na.py:396-417) and window_reverse (na.py:638, mmattn.py:264).
  * softmax(QK^T / sqrt(128)) V per sequence, non-causal, fp32 softmax, bf16 P.  TMA + tcgen05 + TMEM (sm_100a).
- *   q,k,v_pack [P, heads, 128] bf16;  win_table / work: DEVICE copies of the plan's tables;
+ *   q,k,v_pack [P, heads, 128] bf16;  win_table / work / work4: DEVICE copies of the plan's tables (work4 = the
+ *   4-tile work list, or NULL with n_work4 = 0: the kernels that need it are then not dispatched);
  *   out_vid [L, heads*128] bf16 in ORIGINAL token order;
  *   txt_part [n_windows, Lt, heads*128] bf16 workspace (per-window text rows);  out_txt [Lt, heads*128] bf16 = mean
  *   over windows (na.py:414), or NULL to leave the pooling to svr2_txt_pool_fwd.
  */
 int svr2_window_attn_fwd(const void* q_pack, const void* k_pack, const void* v_pack, const int32_t* win_table,
-                         const int32_t* work, int n_work, int n_windows, int T, int H, int W, int txt_len, int heads,
-                         int64_t P, void* out_vid, void* txt_part, void* out_txt, void* stream);
+                         const int32_t* work, int n_work, const int32_t* work4, int n_work4, int n_windows, int T, int H,
+                         int W, int txt_len, int heads, int64_t P, void* out_vid, void* txt_part, void* out_txt,
+                         void* stream);
 
 /*
  * Debug hook (no reference counterpart): point the attention kernel at a device buffer of n_ctas * 64 int64 slots and

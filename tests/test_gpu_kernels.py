@@ -232,7 +232,7 @@ def test_window_attn_generations_bit_identical(svr2, cuda, monkeypatch, grid, sh
         return ov.clone(), ot.clone()
 
     base = run("v2", q)
-    for other in ("v4", "v5", "v5", "v5", "v6", "v6"):    # repeated launches of generations 7 / 8 must also agree with each other
+    for other in ("v4", "v5", "v5", "v5", "v6", "v6", "v7", "v7"):    # repeated launches of generations 7 / 8 must also agree with each other
         ov, ot = run(other, q)
         assert torch.equal(base[0], ov), f"video rows differ between generation 4 (v2) and {other}"
         assert torch.equal(base[1], ot), f"pooled text rows differ between generation 4 (v2) and {other}"
@@ -242,12 +242,12 @@ def test_window_attn_generations_bit_identical(svr2, cuda, monkeypatch, grid, sh
     q2 = q.clone()
     q2[: plan.packed_rows // 2] *= 6.0
     base = run("v2", q2)
-    for other in ("v5", "v6"):
+    for other in ("v5", "v6", "v7"):
         ov, ot = run(other, q2)
         assert torch.equal(base[0], ov) and torch.equal(base[1], ot), f"{other} differs from generation 4 under lazy rescales"
 
 
-@pytest.mark.parametrize("impl", ["tcgen05", "v6", "v5", "v2", "v4", "v3", "v1", "mma"])
+@pytest.mark.parametrize("impl", ["tcgen05", "v7", "v6", "v5", "v2", "v4", "v3", "v1", "mma"])
 @pytest.mark.parametrize("grid,shifted,heads", ATTN_CASES)
 def test_window_attn_vs_fp32(svr2, cuda, monkeypatch, impl, grid, shifted, heads):
     monkeypatch.setenv("SVR2_ATTN_IMPL", impl)
