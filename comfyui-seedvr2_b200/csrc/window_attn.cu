@@ -482,7 +482,7 @@ extern "C" int svr2_window_attn_fwd(const void* q_pack, const void* k_pack, cons
     //    pipeline runs across item boundaries.  In the power-capped C1 step: 151.5 us against 163.7 us per launch (run 42);
     //  * longer sequences: generation 4 (window_attn_v2.cu) — two query tiles per CTA share every K/V tile; 2 % ahead at C2,
     //    equal at the C3 per-rank size.
-    // v3 / v4 / v5 (generations 5-7), v1 (one CTA per item) and mma (the legacy mma.sync comparator) are A/B aids; "v2" /
+    // v3 / v4 / v5 (generations 5-7), v7 (generation 9: pairs with two query tiles per CTA), v1 (one CTA per item) and mma (the legacy mma.sync comparator) are A/B aids; "v2" /
     // "v6" force one of the two product kernels.  Every one is a CUDA kernel of this library.
     const char* e = getenv("SVR2_ATTN_IMPL");
     int rc;
