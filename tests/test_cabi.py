@@ -61,3 +61,25 @@ def test_product_has_no_oracle_or_fallback():
             src = open(os.path.join(pkg, fn)).read()
             assert "import oracle" not in src and "from oracle" not in src, fn
             assert "scaled_dot_product_attention" not in src and "flash_attn" not in src, fn
+
+
+@pytest.mark.parametrize("grid,shifted", [((1, 128, 128), False), ((1, 128, 128), True), ((9, 90, 160), True), ((31, 68, 120), False),
+                                          ((1, 3, 5), True)])
+def test_attention_work_lists_cover_every_query_tile_once(svr2, grid, shifted):
+    """Host-side work lists of the attention kernels (pure integer, no GPU): the 2-tile list (generations 4 / 8) and the
+    4-tile list (generation 9) must each cover every 128-row query tile of every window exactly once, longest sequences
+    first — the per-window Python loop of pytorch_varlen_attention (attention.py:24-61) restated as a static schedule."""
+    import numpy as np
+    plan = svr2.get_plan(grid, (4, 3, 3), shifted, 58)
+    seq = plan.table[:, 7].astype(np.int64) + plan.txt_len
+    for work, tiles in ((plan.work, 2), (plan.work4, 4)):
+        seen = {}
+        for wi, grp in work.tolist():
+            for t in range(grp * tiles, (grp + 1) * tiles):
+                if t * 128 < seq[wi]:
+                    assert (wi, t) not in seen
+                    seen[(wi, t)] = True
+            assert grp * tiles * 128 < seq[wi], "an entry without a single valid tile"
+        assert len(seen) == int(sum((s + 127) // 128 for s in seq))
+        lens = [int(seq[wi]) for wi, _ in work.tolist()]
+        assert lens == sorted(lens, reverse=True)
