@@ -1,0 +1,5 @@
+#!/bin/bash
+# Run 56 (2 GPUs): the driver's N=2 bench launch, own arm and reference arm
+mkdir -p gpurun_out
+timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29533 bench.py --gpus 2 --steps 5 --warmup 3 > gpurun_out/bench_n2.json 2> gpurun_out/bench_n2.err; echo "own arm rc=$?"; tail -1 gpurun_out/bench_n2.json | cut -c1-400
+timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29534 bench.py --impl reference --gpus 2 --steps 1 --warmup 1 > gpurun_out/bench_ref_n2.json 2> gpurun_out/bench_ref_n2.err; echo "reference arm rc=$?"; tail -1 gpurun_out/bench_ref_n2.json | cut -c1-300
