@@ -68,6 +68,11 @@ try:
     for total2, overlap2, hw in ((41, 4, (36, 64)), (23, 2, (20, 20)), (16, 0, (8, 8))):
         r2 = segments.segment_ranges(total2, world, overlap2)
         l2 = [e - s for s, e in r2]
+        if any(l < max(2 * overlap2, 1) for l in l2):
+            if rank == 0:
+                print(f"peer stitch total {total2} overlap {overlap2} world {world}: a segment is shorter than 2 x overlap "
+                      f"(order-dependent stitch) -> this split stays on the NCCL gather path")
+            continue
         def chunk2(r):
             g = torch.Generator().manual_seed(200 + r)
             return torch.rand(l2[r], hw[0], hw[1], 3, generator=g)
