@@ -129,6 +129,9 @@ __device__ __forceinline__ void cur_next_item(const Params& p, const Walk& w, Cu
 template <int N> __device__ __forceinline__ void reg_alloc() { asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(N)); }
 template <int N> __device__ __forceinline__ void reg_dealloc() { asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(N)); }
 
+#ifndef SVR2_V6_FLAT_WALK
+#define SVR2_V6_FLAT_WALK 0       // 1: the softmax warpgroups walk the generic (item, key tile) cursor like the other roles (A/B)
+#endif
 #define PROF_WAIT(slot, stmt) do { if constexpr (kProf) { const long long t0_ = clock64(); stmt; prof_acc[slot] += clock64() - t0_; } else { stmt; } } while (0)
 template <bool kProf>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1)
@@ -394,15 +397,34 @@ window_attn_tc6_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
         long long x_acc[6] = {0, 0, 0, 0, 0, 0};     // kProf: glue between the phases (see scripts/attn_v5_prof.py)
         long long x_t = 0;
         const long long prof_t0 = kProf ? clock64() : 0;
+#if SVR2_V6_FLAT_WALK
         Cursor c;
         cur_init(p, walk, c);
         for (uint32_t g = 0; c.valid; ++g, cur_next(p, walk, c)) {
             if ((g & 1u) != (uint32_t)wg) continue;
-            const Item& it = c.it;
-            const int j = c.j;
-            const bool last = j == it.n_kv - 1;
-            const int nch = (last ? it.last_cols : BN) >> 5;
-            const int valid = it.seq - j * BN;
+            const int j = c.j, cn = c.n, it_n_kv = c.it.n_kv, it_last_cols = c.it.last_cols, it_seq = c.it.seq;
+#else
+        // The softmax warpgroups need only the packed length of an item.  They walk items in an outer loop and their own key
+        // tiles (every other one) in an inner loop; the next item's length is loaded two items ahead (window index) and one item
+        // ahead (length), so an item boundary exposes no global-load latency.  (The generic cursor below costs ~170 more
+        // instructions per step at IPC 0.25: profiles/r01_run54_attn_ncu_stall_sampling.txt.)
+        auto item_wi = [&](int item) { return item < p.n_items ? __ldg(p.work + 2 * (item / p.heads)) : -1; };
+        auto wi_seq = [&](int wi) { return wi >= 0 ? __ldg(p.tab + SVR2_WIN_FIELDS * wi + 7) + p.txt_len : 0; };
+        int next_seq = wi_seq(item_wi(walk.first));
+        int next_wi = item_wi(walk.first + walk.stride);
+        uint32_t g0 = 0;
+        for (int item = walk.first, cn = 0; item < p.n_items; item += walk.stride, ++cn) {
+            const int it_seq = next_seq;
+            next_seq = wi_seq(next_wi);
+            next_wi = item_wi(item + 2 * walk.stride);
+            const int it_n_kv = (it_seq + BN - 1) / BN;
+            const int it_last_cols = (it_seq - (it_n_kv - 1) * BN + 31) & ~31;
+          for (int j = (int)((g0 ^ (uint32_t)wg) & 1u); j < it_n_kv; j += 2) {
+            const uint32_t g = g0 + (uint32_t)j;
+#endif
+            const bool last = j == it_n_kv - 1;
+            const int nch = (last ? it_last_cols : BN) >> 5;
+            const int valid = it_seq - j * BN;
             const uint32_t par = (g >> 1) & 1u;
             const uint32_t ppar = ((g - 1) >> 1) & 1u;
             if constexpr (kProf) { if (x_t != 0) x_acc[5] += clock64() - x_t; }
@@ -502,13 +524,17 @@ window_attn_tc6_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
             l *= alpha;
             l += rs;
             if (last) {
-                if (c.n > 0) PROF_WAIT(6, mbar_wait(bar(BAR_OEMPTY_L), (c.n - 1) & 1));
-                l_fin[(c.n & 1) * 128 + row] = l;
+                if (cn > 0) PROF_WAIT(6, mbar_wait(bar(BAR_OEMPTY_L), (cn - 1) & 1));
+                l_fin[(cn & 1) * 128 + row] = l;
                 mbar_arrive(bar(BAR_LFINAL));
             }
             l_sh[row] = l;
             mbar_arrive(bar(BAR_LPUB + b));
             if constexpr (kProf) { const long long t = clock64(); x_acc[4] += t - x_t; x_t = t; }
+#if !SVR2_V6_FLAT_WALK
+          }
+          g0 += (uint32_t)it_n_kv;
+#endif
         }
         if constexpr (kProf) {
             if (blockIdx.x < 2 && (threadIdx.x & 127) == 0 && p.prof != nullptr) {
