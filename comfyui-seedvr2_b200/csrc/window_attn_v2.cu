@@ -15,7 +15,7 @@
 //         * a softmax warp is latency bound, not pipe bound (issue slots 32 % used): every TMEM round trip, barrier and
 //           fence costs 100-250 cycles and nothing else runs in that warp meanwhile.  Half tiles (64 columns) doubled
 //           those fixed costs per column and were slower; the fix is the opposite — ONE round trip per 128 columns
-//           with the whole S row in registers (setmaxnreg gives the softmax warps 192 registers).
+//           with the whole S row in registers (setmaxnreg gives the softmax warps 200 registers).
 //
 // Work item = (window, pair of 128-row query tiles, head); items are sorted longest sequence first and CTA b takes
 // items b, b+G, b+2G, ...   Roles (16 warps, 512 threads, registers re-balanced with setmaxnreg):
@@ -23,10 +23,10 @@
 //   warps 1,2    tcgen05.mma issuers, one per query tile: S_i = Q_i K^T (SS), O_i += P_i V (A = P from TMEM, B = V
 //                MN-major); warp 3 idle                                                           (56 registers)
 //   warps 4-7    epilogue: O/l -> bf16 -> swizzled staging tile -> coalesced 256-B row stores to the token's ORIGINAL
-//                position (window reverse) or the per-window text buffer                           (88 registers)
+//                position (window reverse) or the per-window text buffer                           (56 registers)
 //   warps 8-11   softmax group 0 (query tile 0): one thread per query row, whole 128-column S row in registers, exact
 //                row max, lazy rescale of O (only when the max moved by more than 2^8), bf16 P written back over S
-//   warps 12-15  softmax group 1 (query tile 1)                                                   (184 registers)
+//   warps 12-15  softmax group 1 (query tile 1)                                                   (200 registers)
 // The two query tiles ping-pong: while one group runs its exp2 burst the tensor core works for the other tile.
 // The last key tile of a sequence is trimmed to a multiple of 32 columns (MMA N / K steps and the softmax shrink with it).
 //
@@ -51,11 +51,13 @@ constexpr int TILE_BYTES = BM * D * 2;    // 32768
 constexpr int BOX_BYTES = TILE_BYTES / 2; // 128 rows x 64 cols bf16
 constexpr int STAGES = 4;
 constexpr int NTHREADS = 512;
-#ifndef SVR2_REGS
-#define SVR2_REGS 72, 72, 184
+#ifndef SVR2_REGS_C      // experiment builds: -DSVR2_REGS_C=.. -DSVR2_REGS_E=.. -DSVR2_REGS_S=..  (nvcc splits -D values at commas)
+#define SVR2_REGS_C 56     // run 60/61: 56/56/200 (no spills) is 2.6 % faster at C2 than 72/72/184; 48/64/200 and 40/72/200 spill and lose
+#define SVR2_REGS_E 56
+#define SVR2_REGS_S 200
 #endif
-constexpr int kRegs[3] = {SVR2_REGS};
-constexpr int REGS_CTRL = kRegs[0], REGS_EPI = kRegs[1], REGS_SOFTMAX = kRegs[2];   // per sub-partition: 32 * (56 + 88 + 2 * 184) = 16384
+constexpr int kRegs[3] = {SVR2_REGS_C, SVR2_REGS_E, SVR2_REGS_S};
+constexpr int REGS_CTRL = kRegs[0], REGS_EPI = kRegs[1], REGS_SOFTMAX = kRegs[2];   // per sub-partition: 32 * (C + E + 2 S) = 16384
 constexpr int OFF_RING = 2 * TILE_BYTES;
 constexpr int OFF_STAGE = OFF_RING + STAGES * TILE_BYTES;
 constexpr int OFF_L = OFF_STAGE + TILE_BYTES;          // float l[2 parities][2 tiles][128 rows]

@@ -41,7 +41,12 @@ constexpr int HALF_BYTES = TILE_BYTES / 2;   // this CTA's half of a K tile (64 
 constexpr int KBOX_BYTES = HALF_BYTES / 2;   // 64 keys x 64 d
 constexpr int STAGES = 8;
 constexpr int NTHREADS = 512;
-constexpr int REGS_CTRL = 72, REGS_EPI = 72, REGS_SOFTMAX = 184;
+#ifndef SVR2_REGS_C      // experiment builds: -DSVR2_REGS_C=.. -DSVR2_REGS_E=.. -DSVR2_REGS_S=..
+#define SVR2_REGS_C 48     // run 61: 48/64/200 removes the softmax role's spills: +3.7 % at C1 over 72/72/184
+#define SVR2_REGS_E 64
+#define SVR2_REGS_S 200
+#endif
+constexpr int REGS_CTRL = SVR2_REGS_C, REGS_EPI = SVR2_REGS_E, REGS_SOFTMAX = SVR2_REGS_S;   // 4 x (C + E + 2 S) x 32 = 65,536
 constexpr int OFF_RING = 2 * TILE_BYTES;
 constexpr int OFF_STAGE = OFF_RING + STAGES * HALF_BYTES;
 constexpr int OFF_M = OFF_STAGE + TILE_BYTES;          // float m[128]
