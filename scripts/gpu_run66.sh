@@ -1,0 +1,6 @@
+#!/bin/bash
+# Run 66: ncu launch list of the bench command with the round's final code
+mkdir -p gpurun_out
+timeout 300 python bench.py --steps 2 --warmup 3 --no-cpu-baseline > gpurun_out/bench_plain.json 2> gpurun_out/bench_plain.err || { echo "plain bench failed"; exit 1; }
+timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none --launch-skip 1000 --launch-count 1200 --csv --log-file gpurun_out/launches.csv python bench.py --steps 2 --warmup 3 --no-cpu-baseline > gpurun_out/ncu_launches.log 2>&1; echo "ncu launch list rc=$?"
+wc -l gpurun_out/launches.csv
