@@ -82,7 +82,13 @@ constexpr float kRescaleThreshold = 8.0f;   // lazy rescale: tolerate P up to 2^
 
 // barrier slots (8 bytes each), per query tile i: slot + i
 enum { BAR_QFULL = 0, BAR_QEMPTY = 2, BAR_SFULL = 4, BAR_PREADY = 6, BAR_OFINAL = 8, BAR_OEMPTY = 10, BAR_LREADY = 12,
-       BAR_KVFULL = 14, BAR_KVEMPTY = 14 + STAGES, BAR_COUNT = 14 + 2 * STAGES };
+       BAR_SLOADED = 14, BAR_KVFULL = 16, BAR_KVEMPTY = 16 + STAGES, BAR_COUNT = 16 + 2 * STAGES };
+// SVR2_V2_SPLIT_QK=1: Q K^T(j+1) is issued in two halves.  Key columns 64..127 of S_i do not alias P_i(j) (columns 0..63), so
+// their MMAs go out as soon as softmax(j) has the S row in registers (BAR_SLOADED) and run under its exp phase; only the lower
+// half has to follow P_i V(j).  The chain between "P is ready" and "S is full" shrinks from 16 to 12 MMAs.
+#ifndef SVR2_V2_SPLIT_QK
+#define SVR2_V2_SPLIT_QK 0
+#endif
 #ifndef SVR2_TURNS
 #define SVR2_TURNS 0      // measured: the bounded counter version gains nothing (see the comment in the softmax role); kept for experiments
 #endif
@@ -197,6 +203,7 @@ window_attn_tc2_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
             mbar_init(bar(BAR_OFINAL + i), 1);
             mbar_init(bar(BAR_OEMPTY + i), 128);
             mbar_init(bar(BAR_LREADY + i), 128);
+            mbar_init(bar(BAR_SLOADED + i), 128);
         }
         for (int s = 0; s < STAGES; ++s) {
             mbar_init(bar(BAR_KVFULL + s), 1);
@@ -265,16 +272,18 @@ window_attn_tc2_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
             constexpr uint32_t hi_sw = smem_desc_hi_sw128(1024);   // 8-row (K-major Q, K) / 8-key (MN-major V) groups 1024 B apart
             const int i = warp - 1;
             // S_i = Q_i K^T : 8 x (128 x ncols x 16)
-            auto issue_qk = [&](uint32_t kbase, int ncols) {
+            // key columns [c0, c0 + ncols) of the tile at kbase (key row r of a K-major SW128 box sits 128 r bytes in)
+            auto issue_qk_cols = [&](uint32_t kbase, int c0, int ncols) {
                 const uint32_t idesc_qk = idesc_bf16(BM, ncols, 0);
                 const uint32_t qlo = smem_desc_lo(base + i * TILE_BYTES, 16);
-                const uint32_t klo = smem_desc_lo(kbase, 16);
+                const uint32_t klo = smem_desc_lo(kbase + (uint32_t)c0 * 128u, 16);
 #pragma unroll
                 for (int kk = 0; kk < 8; ++kk) {
                     const uint32_t off = ((uint32_t)(kk >> 2) * BOX_BYTES + (uint32_t)(kk & 3) * 32u) >> 4;
-                    mma_ss(tmem + i * 128, make_desc(qlo + off, hi_sw), make_desc(klo + off, hi_sw), idesc_qk, kk > 0);
+                    mma_ss(tmem + i * 128 + c0, make_desc(qlo + off, hi_sw), make_desc(klo + off, hi_sw), idesc_qk, kk > 0);
                 }
             };
+            auto issue_qk = [&](uint32_t kbase, int ncols) { issue_qk_cols(kbase, 0, ncols); };
             // O_i += P_i V : A = P from TMEM (16 keys = 8 columns per step), B = V MN-major (16 keys = 2048 B; LBO = next 64 d)
             auto issue_pv = [&](uint32_t vbase, int ksteps, bool first) {
                 const uint32_t vlo = smem_desc_lo(vbase, BOX_BYTES);
@@ -286,7 +295,7 @@ window_attn_tc2_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
             };
             uint32_t kv0 = 0;            // ring index of the current item's K tile 0 (K_t at 2t, V_t at 2t+1)
             uint32_t cq = 0;             // items in which this query tile took part
-            uint32_t pr = 0;             // PREADY_i phases consumed
+            uint32_t pr = 0;             // PREADY_i phases consumed (= softmax steps of this tile: also the SLOADED_i phase)
             int n_done = 0;
             auto ring_slot = [&](uint32_t idx) { return (kv0 + idx) % STAGES; };
             auto ring_par = [&](uint32_t idx) { return ((kv0 + idx) / STAGES) & 1u; };
@@ -321,6 +330,16 @@ window_attn_tc2_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
                 for (int j = 0; j < it.n_kv; ++j) {
                     const bool more = j + 1 < it.n_kv;
                     DBG_PROGRESS(1 + i, (n_done << 12) | (it.nq << 8) | j);
+#if SVR2_V2_SPLIT_QK
+                    const int hi_cols = more ? cols(j + 1) - 64 : 0;       // > 0: the next S tile has an upper half
+                    if (hi_cols > 0) {
+                        OTHER_WAIT(bar(BAR_KVFULL + ring_slot(2 * j + 2)), ring_par(2 * j + 2));          // K_{j+1}
+                        OTHER_WAIT(bar(BAR_SLOADED + i), pr & 1u);                                        // S_i(j) is in registers
+                        tc_fence_after();
+                        if (elect_one()) issue_qk_cols(sRing + ring_slot(2 * j + 2) * TILE_BYTES, 64, hi_cols);
+                        __syncwarp();
+                    }
+#endif
                     OTHER_WAIT(bar(BAR_KVFULL + ring_slot(2 * j + 1)), ring_par(2 * j + 1));              // V_j
                     if (more) OTHER_WAIT(bar(BAR_KVFULL + ring_slot(2 * j + 2)), ring_par(2 * j + 2));    // K_{j+1}
                     OTHER_WAIT(bar(BAR_PREADY + i), pr & 1u);
@@ -332,7 +351,11 @@ window_attn_tc2_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
                         if (more) {
                             // the tensor core runs MMAs in issue order: S_i (and the P_i aliased on it) is overwritten
                             // only after P_i V has read it
+#if SVR2_V2_SPLIT_QK
+                            issue_qk_cols(sRing + ring_slot(2 * j + 2) * TILE_BYTES, 0, cols(j + 1) < 64 ? cols(j + 1) : 64);
+#else
                             issue_qk(sRing + ring_slot(2 * j + 2) * TILE_BYTES, cols(j + 1));
+#endif
                             tc_commit(bar(BAR_SFULL + i));
                             if (j + 2 == it.n_kv) tc_commit(bar(BAR_QEMPTY + i));
                         } else {
@@ -475,6 +498,10 @@ window_attn_tc2_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
                 if (nch > 1) tmem_ld32(tS3 - 32, s + 64);
                 tmem_ld32(tS3, s + 96);
                 tc_wait_ld();
+#if SVR2_V2_SPLIT_QK
+                tc_fence_before();
+                mbar_arrive(bar(BAR_SLOADED + i));                                     // the upper half of S_i may be overwritten
+#endif
                 if (valid < nch * 32) mask_chunk(s + 96, valid - 32 * (nch - 1));      // only in the last key tile of a sequence
                 float m8[8];
 #pragma unroll
