@@ -34,6 +34,20 @@ def test_errors_are_reported_not_swallowed(svr2):
         svr2._lib.check(-1, "svr2_window_plan")
 
 
+def test_new_entry_points_validate_their_arguments_before_launching(svr2):
+    """Argument errors of the round's later entry points come back as codes + text, without touching a device."""
+    L = svr2._lib.lib()
+    assert L.svr2_sr_input_fwd(None, None, None, 1.0, 0.0, 0, None, 4, 16, None) == -1
+    assert b"svr2_sr_input_fwd" in L.svr2_last_error()
+    assert L.svr2_v_lerp_endpoint_fwd(None, None, 0.0, 1.0, None, 8, None) == -1
+    assert b"svr2_v_lerp_endpoint_fwd" in L.svr2_last_error()
+    assert L.svr2_segment_stitch_peer(None, None, None, 0, 0, 1, 16, None) == -1
+    assert b"svr2_segment_stitch_peer" in L.svr2_last_error()
+    n = ctypes.c_int64(0)
+    assert L.svr2_window_attn_worklist_tiles(None, 1, 58, 4, None, 0, ctypes.byref(n)) == -1
+    assert b"worklist" in L.svr2_last_error()
+
+
 @pytest.mark.parametrize("key", sorted(GEO))
 def test_host_plan_matches_reference(svr2, key):
     rec = GEO[key]
