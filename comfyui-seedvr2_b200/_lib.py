@@ -37,6 +37,7 @@ SIGNATURES = {
     "svr2_v_lerp_endpoint_fwd": (c_int, [c_void_p, c_void_p, c_float, c_float, c_void_p, c_int64, c_void_p]),
 }
 
+ABI_VERSION = 2      # svr2_abi_version() of the library these SIGNATURES describe
 _lib = None
 
 
@@ -62,6 +63,10 @@ def lib() -> ctypes.CDLL:
             fn = getattr(handle, name)      # AttributeError if the library does not export a declared symbol
             fn.restype = res
             fn.argtypes = args
+        got = handle.svr2_abi_version()
+        if got != ABI_VERSION:      # a stale in-tree .so would be called with the wrong argument lists
+            raise RuntimeError(f"{LIB_PATH} has ABI version {got}, this package binds version {ABI_VERSION}: rebuild it "
+                               f"(`make -C {CSRC}`)")
         _lib = handle
     return _lib
 

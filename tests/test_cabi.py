@@ -22,7 +22,7 @@ def test_exports_every_declared_symbol(svr2):
     handle = ctypes.CDLL(svr2._lib.LIB_PATH)
     for name in declared:
         assert hasattr(handle, name), f"{name} is declared but not exported"
-    assert svr2._lib.lib().svr2_abi_version() == 1
+    assert svr2._lib.lib().svr2_abi_version() == svr2._lib.ABI_VERSION == 2
 
 
 def test_errors_are_reported_not_swallowed(svr2):
