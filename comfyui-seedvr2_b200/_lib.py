@@ -23,6 +23,7 @@ SIGNATURES = {
     "svr2_modnorm_affine_fwd": (c_int, [c_void_p] * 6 + [c_int64, c_int, c_int, c_float, c_void_p]),
     "svr2_gate_residual_modnorm_fwd": (c_int, [c_void_p] * 8 + [c_int64, c_int, c_int, c_float, c_void_p]),
     "svr2_swiglu_fwd": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_void_p]),
+    "svr2_swiglu_rows_fwd": (c_int, [c_void_p, c_void_p, c_int64, c_int, c_void_p]),
     "svr2_qkv_pack_fwd": (c_int, [c_void_p] * 7 + [c_int, c_int, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int,
                                   c_float, c_void_p, c_void_p, c_void_p, c_int64, c_void_p]),
     "svr2_pack_rowmap": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p, c_int64, c_void_p]),

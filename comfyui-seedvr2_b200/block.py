@@ -25,6 +25,7 @@ from . import ops
 from .plan import WindowPlan, get_plan
 
 _SHIFTED = {"720pwin_by_size_bysize": False, "720pswin_by_size_bysize": True}
+_SWIGLU_STACKED = os.environ.get("SVR2_SWIGLU_STACKED", "0") == "1"      # experiment flag, off: see _SwiGLU.forward
 _GELU_EPILOGUE = os.environ.get("SVR2_GELU_EPILOGUE", "1") != "0"     # 7B MLP: library GEMM with fused bias + GELU epilogue
 
 
@@ -108,7 +109,15 @@ class _SwiGLU(nn.Module):      # reference mlp.py:46-62
         self.proj_in = nn.Linear(dim, hidden, bias=False)
 
     def forward(self, x):
-        h = ops.swiglu(F.linear(x, _bf16(self.proj_in_gate.weight)), F.linear(x, _bf16(self.proj_in.weight)))
+        if _SWIGLU_STACKED and x.is_cuda and x.dim() == 2:
+            # experiment (run 72): the two in-projections as ONE GEMM over the stacked weights [W_gate ; W_in]
+            w = self.__dict__.get("_w_stacked")
+            if w is None or w.device != x.device:
+                w = torch.cat([_bf16(self.proj_in_gate.weight), _bf16(self.proj_in.weight)], 0).contiguous()
+                self.__dict__["_w_stacked"] = w
+            h = ops.swiglu_rows(F.linear(x, w))
+        else:
+            h = ops.swiglu(F.linear(x, _bf16(self.proj_in_gate.weight)), F.linear(x, _bf16(self.proj_in.weight)))
         return F.linear(h, _bf16(self.proj_out.weight))
 
 

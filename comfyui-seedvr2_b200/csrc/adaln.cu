@@ -209,6 +209,24 @@ swiglu_kernel(const __nv_bfloat16* __restrict__ gate, const __nv_bfloat16* __res
     }
 }
 
+// The same on the output of ONE GEMM with the weights [W_gate ; W_up] stacked: row r holds gate at [0, hidden) and up at
+// [hidden, 2 hidden).  (Experiment of run 72: does cuBLAS run the MLP in-projection better as one N = 2 hidden GEMM?)
+__global__ void __launch_bounds__(256)
+swiglu_rows_kernel(const __nv_bfloat16* __restrict__ gate_up, __nv_bfloat16* __restrict__ out, int64_t rows, int h8) {
+    const int64_t n8 = rows * h8;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t r = i / h8;
+        const int c = (int)(i - r * h8);
+        const __nv_bfloat16* g = gate_up + (r * 2 * h8 + c) * 8;
+        float f[8];
+        unpack8(ldg8_stream(g), f);
+        const bf16x8 u = ldg8_stream(g + (int64_t)h8 * 8);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) f[e] = __fdividef(f[e], 1.0f + __expf(-f[e]));
+        stg8(out + i * 8, mul8(pack8(f), u));
+    }
+}
+
 template <bool FUSE>
 static int launch_modnorm(const void* x, const void* resid, const void* emb, const void* gateB, const void* shiftB,
                           const void* scaleB, void* out, void* y, int64_t L, int D, int gate_layer, int mod_layer,
@@ -307,5 +325,18 @@ extern "C" int svr2_swiglu_fwd(const void* gate, const void* up, void* out, int6
     svr2::swiglu_kernel<<<(unsigned)grid, 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)gate, (const __nv_bfloat16*)up,
                                                                            (__nv_bfloat16*)out, n8);
     SVR2_CHECK_LAUNCH("svr2_swiglu_fwd");
+    return SVR2_OK;
+}
+
+extern "C" int svr2_swiglu_rows_fwd(const void* gate_up, void* out, int64_t rows, int hidden, void* stream) {
+    SVR2_CHECK_ARG(gate_up && out, "svr2_swiglu_rows_fwd: null pointer");
+    SVR2_CHECK_ARG(rows >= 0 && hidden > 0 && hidden % 8 == 0, "svr2_swiglu_rows_fwd: hidden %d must be a positive multiple of 8", hidden);
+    if (rows == 0) return SVR2_OK;
+    const int64_t n8 = rows * (hidden / 8);
+    int64_t grid = (n8 + 255) / 256;
+    const int64_t cap = (int64_t)svr2::sm_count() * 8;
+    if (grid > cap) grid = cap;
+    svr2::swiglu_rows_kernel<<<(unsigned)grid, 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)gate_up, (__nv_bfloat16*)out, rows, hidden / 8);
+    SVR2_CHECK_LAUNCH("svr2_swiglu_rows_fwd");
     return SVR2_OK;
 }

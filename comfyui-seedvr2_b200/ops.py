@@ -174,6 +174,18 @@ def swiglu(gate: torch.Tensor, up: torch.Tensor) -> torch.Tensor:
 
 
 @torch._dynamo.disable
+def swiglu_rows(gate_up: torch.Tensor) -> torch.Tensor:
+    """silu(gate) * up on a [rows, 2*hidden] buffer holding gate | up side by side (one stacked-weight GEMM's output)."""
+    _need(gate_up, "gate_up")
+    rows, h2 = gate_up.shape
+    out = torch.empty(rows, h2 // 2, dtype=torch.bfloat16, device=gate_up.device)
+    if rows:
+        _call("svr2_swiglu_rows_fwd", 1, gate_up.device, _lib.lib().svr2_swiglu_rows_fwd, gate_up.data_ptr(), out.data_ptr(),
+              rows, h2 // 2, _stream(gate_up))
+    return out
+
+
+@torch._dynamo.disable
 def qkv_pack(plan: WindowPlan, qkv_vid: torch.Tensor, qkv_txt: torch.Tensor, wq_vid, wk_vid, wq_txt, wk_txt,
              freqs: Optional[torch.Tensor], rope_kind: int, heads: int, eps: float):
     """-> (q, k, v) packed [P, heads, 128] bf16: q/k RMSNorm + RoPE + window partition + text interleave."""

@@ -99,6 +99,9 @@ int svr2_gate_residual_modnorm_fwd(const void* h, const void* resid, const void*
  * gate/up/out bf16, n elements (multiple of 8), out may alias gate or up.
  */
 int svr2_swiglu_fwd(const void* gate, const void* up, void* out, int64_t n, void* stream);
+/* The same on a [rows, 2*hidden] buffer whose rows hold gate | up side by side: the output of ONE GEMM with the two
+ * in-projection weights of SwiGLUMLP (mlp.py:56-58) stacked.  out [rows, hidden]. */
+int svr2_swiglu_rows_fwd(const void* gate_up, void* out, int64_t rows, int hidden, void* stream);
 
 /*
  * q/k RMSNorm (affine, per head) + 3D RoPE + window partition + text interleave, one pass over qkv.
