@@ -299,10 +299,8 @@ def run_ours(args):
     attn_ms_per_launch = attn_ms / max(attn_n, 1)
     achieved_tf = (attn_flops / layers) / (attn_ms_per_launch * 1e-3) / 1e12 if attn_n else 0.0
     plans = [svr2.get_plan(tok_grid, (4, 3, 3), sh, TXT_LEN) for sh in (False, True)]
-    forced = os.environ.get("SVR2_ATTN_IMPL")
     short = all(pl.packed_rows <= 576 * pl.n_windows for pl in plans)          # the library's dispatch rule (window_attn.cu)
-    attn_kernel = (f"forced SVR2_ATTN_IMPL={forced}" if forced else
-                   "generation 8, window_attn_tc6_kernel: CTA pairs, tcgen05.mma.cta_group::2 + TMA + TMEM" if short else
+    attn_kernel = ("generation 8, window_attn_tc6_kernel: CTA pairs, tcgen05.mma.cta_group::2 + TMA + TMEM" if short else
                    "generation 4, window_attn_tc2_kernel: TMA + tcgen05 + TMEM")
     traffic = None
     try:

@@ -234,7 +234,8 @@ static int launch_modnorm(const void* x, const void* resid, const void* emb, con
     if (L == 0) return SVR2_OK;
     const int threads = ((D / 8) + 31) / 32 * 32;
     constexpr int kRows = FUSE ? 2 : 4;          // same bytes in flight per thread either way (the fused kernel loads h and resid)
-    static int occ[kMaxWarps + 1] = {0};          // resident CTAs per SM for this block size (queried once)
+    static int occ_dev[kMaxDevices][kMaxWarps + 1] = {};   // resident CTAs per SM for this block size (queried once per device)
+    int* occ = occ_dev[cur_device()];
     const int wi = threads / 32;
     if (occ[wi] == 0) {
         int n = 0;
@@ -244,7 +245,7 @@ static int launch_modnorm(const void* x, const void* resid, const void* emb, con
     const int64_t want = (L + kRows - 1) / kRows;
     const int64_t cap = (int64_t)sm_count() * occ[wi];
     const int grid = (int)(want < cap ? want : cap);
-    static const bool prefetch = [] { const char* e = getenv("SVR2_MODNORM_PREFETCH"); return !(e && e[0] == '0'); }();
+    constexpr bool prefetch = true;      // next row group's loads issued before this group's reduction
     auto kern = prefetch ? modnorm_kernel<FUSE, kRows, false, true> : modnorm_kernel<FUSE, kRows, false, false>;
     kern<<<grid, threads, 0, st>>>((const __nv_bfloat16*)x, (const __nv_bfloat16*)resid, (const __nv_bfloat16*)emb,
                                    (const __nv_bfloat16*)gateB, (const __nv_bfloat16*)shiftB, (const __nv_bfloat16*)scaleB,
@@ -258,7 +259,7 @@ static int launch_modnorm(const void* x, const void* resid, const void* emb, con
 extern "C" int svr2_modnorm_fwd(const void* x, const void* emb, const void* shiftB, const void* scaleB, void* y,
                                 int64_t L, int D, int layer, float eps, void* stream) {
     SVR2_CHECK_ARG(x && y, "svr2_modnorm_fwd: null x/y");
-    SVR2_CHECK_ARG(L >= 0 && D > 0 && D % 8 == 0 && D <= 4096, "svr2_modnorm_fwd: D=%d must be a multiple of 8, <= 8192", D);
+    SVR2_CHECK_ARG(L >= 0 && D > 0 && D % 8 == 0 && D <= 4096, "svr2_modnorm_fwd: D=%d must be a multiple of 8, <= 4096", D);
     SVR2_CHECK_ARG(layer == 0 || layer == 1, "svr2_modnorm_fwd: layer must be 0 (attn) or 1 (mlp)");
     const int has_mod = (shiftB != nullptr || scaleB != nullptr || emb != nullptr) ? 1 : 0;
     SVR2_CHECK_ARG(!has_mod || (shiftB && scaleB && emb), "svr2_modnorm_fwd: emb, shiftB and scaleB go together");

@@ -165,15 +165,37 @@ __device__ __forceinline__ int64_t win_token(const Win& w, int j, int H, int W, 
     return ((int64_t)(w.t0 + t) * H + (w.h0 + h)) * W + (w.w0 + x);
 }
 
+// ---- per-device host-side caches (one process may drive several GPUs: ops._call switches the current device per call)
+constexpr int kMaxDevices = 64;
+inline int cur_device() {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    return (dev < 0 || dev >= kMaxDevices) ? 0 : dev;
+}
 inline int sm_count() {
-    static int n = 0;
-    if (n == 0) {
-        int dev = 0;
-        cudaGetDevice(&dev);
-        cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
-        if (n <= 0) n = 148;
+    static int n[kMaxDevices] = {0};
+    const int dev = cur_device();
+    if (n[dev] == 0) {
+        cudaDeviceGetAttribute(&n[dev], cudaDevAttrMultiProcessorCount, dev);
+        if (n[dev] <= 0) n[dev] = 148;
     }
-    return n;
+    return n[dev];
+}
+// Opt a kernel in to `bytes` of dynamic shared memory on the CURRENT device, once per device (the attribute is per device).
+struct PerDeviceFlag {
+    bool set[kMaxDevices] = {};
+};
+template <class Kernel>
+inline int ensure_dyn_smem(Kernel kernel, int bytes, PerDeviceFlag& done, const char* what) {
+    const int dev = cur_device();
+    if (done.set[dev]) return SVR2_OK;
+    const cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+    if (e != cudaSuccess) {
+        set_error("%s: cannot reserve %d B shared memory: %s", what, bytes, cudaGetErrorString(e));
+        return SVR2_E_CUDA;
+    }
+    done.set[dev] = true;
+    return SVR2_OK;
 }
 
 }  // namespace svr2

@@ -29,9 +29,10 @@
 // SMEM map: Q0 | Q1 | ring[4] (32 KB each) | staging (16 KB) | row sums l[2][2][2][128] | row max exchange [2][2][128] | mbarriers.
 #include <cuda.h>
 
-#include "common.cuh"
-#include "sm100_ptx.cuh"
-#include "softmax_row.cuh"
+#include "../common.cuh"
+#include "../attn_launch.cuh"
+#include "../sm100_ptx.cuh"
+#include "../softmax_row.cuh"
 
 namespace svr2 {
 namespace tc3 {
@@ -500,9 +501,6 @@ window_attn_tc3_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
 
 // ------------------------------------------------------------------------------------------------ host side
 namespace svr2 {
-extern long long* g_trace;
-extern int g_trace_ctas;
-int make_tmap(CUtensorMap* m, const void* ptr, int64_t P, int heads);
 
 int launch_window_attn_tc3(const void* q, const void* k, const void* v, const int32_t* tab, const int32_t* work,
                            int n_work, int H, int W, int txt_len, int heads, int64_t P, void* out_vid, void* txt_part,
@@ -512,19 +510,9 @@ int launch_window_attn_tc3(const void* q, const void* k, const void* v, const in
     if ((rc = make_tmap(&tq, q, P, heads)) != SVR2_OK) return rc;
     if ((rc = make_tmap(&tk, k, P, heads)) != SVR2_OK) return rc;
     if ((rc = make_tmap(&tv, v, P, heads)) != SVR2_OK) return rc;
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(tc3::window_attn_tc3_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                             tc3::SMEM_BYTES);
-        if (e == cudaSuccess)
-            e = cudaFuncSetAttribute(tc3::window_attn_tc3_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                     tc3::SMEM_BYTES);
-        if (e != cudaSuccess) {
-            set_error("svr2_window_attn_fwd: cannot reserve %d B shared memory: %s", tc3::SMEM_BYTES, cudaGetErrorString(e));
-            return SVR2_E_CUDA;
-        }
-        attr_set = true;
-    }
+    static PerDeviceFlag smem_ok[2];
+    if ((rc = ensure_dyn_smem(tc3::window_attn_tc3_kernel<false>, tc3::SMEM_BYTES, smem_ok[0], "svr2_window_attn_fwd")) != SVR2_OK) return rc;
+    if ((rc = ensure_dyn_smem(tc3::window_attn_tc3_kernel<true>, tc3::SMEM_BYTES, smem_ok[1], "svr2_window_attn_fwd")) != SVR2_OK) return rc;
     tc3::Params p;
     p.tab = tab; p.work = work; p.n_items = n_work * heads;
     p.H = H; p.W = W; p.txt_len = txt_len; p.heads = heads;

@@ -16,10 +16,11 @@
 #include <cuda.h>
 #include <cstdlib>
 
-#include "common.cuh"
-#include "sm100_pair.cuh"
-#include "sm100_ptx.cuh"
-#include "softmax_row.cuh"
+#include "../common.cuh"
+#include "../attn_launch.cuh"
+#include "../sm100_pair.cuh"
+#include "../sm100_ptx.cuh"
+#include "../softmax_row.cuh"
 
 namespace svr2 {
 namespace tc7 {
@@ -428,7 +429,6 @@ window_attn_tc7_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
 
 }  // namespace tc7
 
-int make_tmap_box(CUtensorMap* m, const void* ptr, int64_t P, int heads, int box_rows);
 
 int launch_window_attn_tc7(const void* q, const void* k, const void* v, const int32_t* tab, const int32_t* work4,
                            int n_work4, int H, int W, int txt_len, int heads, int64_t P, void* out_vid,
@@ -438,15 +438,8 @@ int launch_window_attn_tc7(const void* q, const void* k, const void* v, const in
     if ((rc = make_tmap_box(&tq, q, P, heads, 128)) != SVR2_OK) return rc;
     if ((rc = make_tmap_box(&tk, k, P, heads, 64)) != SVR2_OK) return rc;      // half key tiles
     if ((rc = make_tmap_box(&tv, v, P, heads, 128)) != SVR2_OK) return rc;     // one 64-column box = half of the d columns
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(tc7::window_attn_tc7_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, tc7::SMEM_BYTES);
-        if (e != cudaSuccess) {
-            set_error("svr2_window_attn_fwd: cannot reserve %d B shared memory: %s", tc7::SMEM_BYTES, cudaGetErrorString(e));
-            return SVR2_E_CUDA;
-        }
-        attr_set = true;
-    }
+    static PerDeviceFlag smem_ok[1];
+    if ((rc = ensure_dyn_smem(tc7::window_attn_tc7_kernel, tc7::SMEM_BYTES, smem_ok[0], "svr2_window_attn_fwd")) != SVR2_OK) return rc;
     tc7::Params p;
     p.tab = tab; p.work = work4; p.n_items = n_work4 * heads;
     p.H = H; p.W = W; p.txt_len = txt_len; p.heads = heads;

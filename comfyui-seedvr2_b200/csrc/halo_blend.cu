@@ -24,7 +24,11 @@ __device__ __forceinline__ float prev_weight(int f, int overlap) {
 // one expression for every kernel that blends, so that they round identically
 __device__ __forceinline__ float4 blend4(const float4 a, const float4 b, float wp, float wc) {
     float4 r;
-    r.x = a.x * wp + b.x * wc; r.y = a.y * wp + b.y * wc; r.z = a.z * wp + b.z * wc; r.w = a.w * wp + b.w * wc;
+    // separately rounded mul, mul, add like the reference's three fp32 tensor ops (no FMA contraction)
+    r.x = __fadd_rn(__fmul_rn(a.x, wp), __fmul_rn(b.x, wc));
+    r.y = __fadd_rn(__fmul_rn(a.y, wp), __fmul_rn(b.y, wc));
+    r.z = __fadd_rn(__fmul_rn(a.z, wp), __fmul_rn(b.z, wc));
+    r.w = __fadd_rn(__fmul_rn(a.w, wp), __fmul_rn(b.w, wc));
     return r;
 }
 

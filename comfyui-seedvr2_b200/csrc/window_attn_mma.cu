@@ -4,6 +4,7 @@
 //
 // CTA = 128 query rows of one (window, head); 8 warps x 16 rows; K/V tiles of 64 rows double-buffered with cp.async.
 #include "common.cuh"
+#include "attn_launch.cuh"
 
 namespace svr2 {
 namespace mma_attn {
@@ -202,11 +203,9 @@ int launch_txt_pool(const void* txt_part, void* out_txt, int n_windows, int txt_
 int launch_window_attn_mma(const void* q, const void* k, const void* v, const int32_t* tab, const int32_t* work,
                            int n_work, int H, int W, int txt_len, int heads, void* out_vid, void* txt_part,
                            cudaStream_t st) {
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaFuncSetAttribute(mma_attn::window_attn_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, mma_attn::SMEM_BYTES);
-        attr_set = true;
-    }
+    int rc;
+    static PerDeviceFlag smem_ok[1];
+    if ((rc = ensure_dyn_smem(mma_attn::window_attn_mma_kernel, mma_attn::SMEM_BYTES, smem_ok[0], "svr2_window_attn_fwd")) != SVR2_OK) return rc;
     dim3 grid(n_work, heads, 2);
     mma_attn::window_attn_mma_kernel<<<grid, mma_attn::NTHREADS, mma_attn::SMEM_BYTES, st>>>(
         (const __nv_bfloat16*)q, (const __nv_bfloat16*)k, (const __nv_bfloat16*)v, tab, work, H, W, txt_len, heads,

@@ -36,6 +36,7 @@
 #include <cstdlib>
 
 #include "common.cuh"
+#include "attn_launch.cuh"
 #include "sm100_ptx.cuh"
 #include "softmax_row.cuh"
 
@@ -590,9 +591,6 @@ window_attn_tc2_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
 
 // ------------------------------------------------------------------------------------------------ host side
 namespace svr2 {
-extern long long* g_trace;
-extern int g_trace_ctas;
-int make_tmap(CUtensorMap* m, const void* ptr, int64_t P, int heads);
 
 int launch_window_attn_tc2(const void* q, const void* k, const void* v, const int32_t* tab, const int32_t* work,
                            int n_work, int n_windows, int H, int W, int txt_len, int heads, int64_t P, void* out_vid,
@@ -602,31 +600,17 @@ int launch_window_attn_tc2(const void* q, const void* k, const void* v, const in
     if ((rc = make_tmap(&tq, q, P, heads)) != SVR2_OK) return rc;
     if ((rc = make_tmap(&tk, k, P, heads)) != SVR2_OK) return rc;
     if ((rc = make_tmap(&tv, v, P, heads)) != SVR2_OK) return rc;
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(tc2::window_attn_tc2_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                             tc2::SMEM_BYTES);
-        if (e == cudaSuccess)
-            e = cudaFuncSetAttribute(tc2::window_attn_tc2_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                     tc2::SMEM_BYTES);
-        if (e != cudaSuccess) {
-            set_error("svr2_window_attn_fwd: cannot reserve %d B shared memory: %s", tc2::SMEM_BYTES, cudaGetErrorString(e));
-            return SVR2_E_CUDA;
-        }
-        attr_set = true;
-    }
+    static PerDeviceFlag smem_ok[2];
+    if ((rc = ensure_dyn_smem(tc2::window_attn_tc2_kernel<false>, tc2::SMEM_BYTES, smem_ok[0], "svr2_window_attn_fwd")) != SVR2_OK) return rc;
+    if ((rc = ensure_dyn_smem(tc2::window_attn_tc2_kernel<true>, tc2::SMEM_BYTES, smem_ok[1], "svr2_window_attn_fwd")) != SVR2_OK) return rc;
     tc2::Params p;
     p.tab = tab; p.work = work; p.n_items = n_work * heads;
     p.H = H; p.W = W; p.txt_len = txt_len; p.heads = heads;
     p.out_vid = (__nv_bfloat16*)out_vid; p.txt_part = (__nv_bfloat16*)txt_part;
     p.trace = g_trace; p.trace_ctas = g_trace_ctas;
-    // Turn-taking staggers the two query tiles from the first key tile on: +7 % at 4 key tiles per sequence (2048^2 stills),
-    // but -5 % at 39 (720p, 33 frames), where the groups find their own rhythm and the enforced order only adds waits.
-    // SVR2_ATTN_TURNS=0/1 overrides the choice (A/B runs).
-    {
-        const char* e = getenv("SVR2_ATTN_TURNS");
-        p.turns = e ? (e[0] != '0') : (P / n_windows <= 8 * tc2::BN);      // mean sequence length
-    }
+    // Turn-taking between the two softmax groups is compiled out (SVR2_TURNS 0: the bounded-counter version measured no
+    // gain in round 1); builds with -DSVR2_TURNS=1 enable it for short sequences only.
+    p.turns = SVR2_TURNS && (P / n_windows <= 8 * tc2::BN);
     const int sms = sm_count();
     const int grid = p.n_items < sms ? p.n_items : sms;       // one persistent CTA per SM
     if (p.trace != nullptr) tc2::window_attn_tc2_kernel<true><<<grid, tc2::NTHREADS, tc2::SMEM_BYTES, st>>>(tq, tk, tv, p);

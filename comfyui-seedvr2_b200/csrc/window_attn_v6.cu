@@ -22,6 +22,7 @@
 #include <cstdlib>
 
 #include "common.cuh"
+#include "attn_launch.cuh"
 #include "sm100_pair.cuh"
 #include "sm100_ptx.cuh"
 #include "softmax_row.cuh"
@@ -561,8 +562,6 @@ window_attn_tc6_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
 
 }  // namespace tc6
 
-extern long long* g_trace;
-int make_tmap_box(CUtensorMap* m, const void* ptr, int64_t P, int heads, int box_rows);
 
 int launch_window_attn_tc6(const void* q, const void* k, const void* v, const int32_t* tab, const int32_t* work,
                            int n_work, int n_windows, int H, int W, int txt_len, int heads, int64_t P, void* out_vid,
@@ -573,18 +572,9 @@ int launch_window_attn_tc6(const void* q, const void* k, const void* v, const in
     if ((rc = make_tmap_box(&tq, q, P, heads, 128)) != SVR2_OK) return rc;
     if ((rc = make_tmap_box(&tk, k, P, heads, 64)) != SVR2_OK) return rc;      // half key tiles
     if ((rc = make_tmap_box(&tv, v, P, heads, 128)) != SVR2_OK) return rc;     // one 64-column box = half of the d columns
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(tc6::window_attn_tc6_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                             tc6::SMEM_BYTES);
-        if (e == cudaSuccess)
-            e = cudaFuncSetAttribute(tc6::window_attn_tc6_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, tc6::SMEM_BYTES);
-        if (e != cudaSuccess) {
-            set_error("svr2_window_attn_fwd: cannot reserve %d B shared memory: %s", tc6::SMEM_BYTES, cudaGetErrorString(e));
-            return SVR2_E_CUDA;
-        }
-        attr_set = true;
-    }
+    static PerDeviceFlag smem_ok[2];
+    if ((rc = ensure_dyn_smem(tc6::window_attn_tc6_kernel<false>, tc6::SMEM_BYTES, smem_ok[0], "svr2_window_attn_fwd")) != SVR2_OK) return rc;
+    if ((rc = ensure_dyn_smem(tc6::window_attn_tc6_kernel<true>, tc6::SMEM_BYTES, smem_ok[1], "svr2_window_attn_fwd")) != SVR2_OK) return rc;
     tc6::Params p;
     p.tab = tab; p.work = work; p.n_items = n_work * heads;
     p.H = H; p.W = W; p.txt_len = txt_len; p.heads = heads;

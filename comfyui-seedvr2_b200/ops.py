@@ -13,6 +13,7 @@ from . import _lib
 from .plan import WindowPlan
 
 ROPE_NONE, ROPE_3B_MM, ROPE_7B_PIX = 0, 1, 2
+ATTN_AUTO, ATTN_GEN4, ATTN_GEN8, ATTN_MMA = 0, 4, 8, 100      # include/seedvr2_b200.h SVR2_ATTN_*
 
 
 class KernelTimer:
@@ -214,8 +215,9 @@ def qkv_pack(plan: WindowPlan, qkv_vid: torch.Tensor, qkv_txt: torch.Tensor, wq_
 
 
 @torch._dynamo.disable
-def window_attn(plan: WindowPlan, q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, heads: int):
-    """-> (out_vid [L, heads*128] in original token order, out_txt [Lt, heads*128] mean over windows)."""
+def window_attn(plan: WindowPlan, q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, heads: int, impl: int = ATTN_AUTO):
+    """-> (out_vid [L, heads*128] in original token order, out_txt [Lt, heads*128] mean over windows).
+    ``impl`` names a kernel explicitly (tests / A-B runs); the product path leaves it at ATTN_AUTO."""
     for n, t in (("q", q), ("k", k), ("v", v)):
         _need(t, n)
         if t.shape != (plan.packed_rows, heads, 128):
@@ -228,10 +230,16 @@ def window_attn(plan: WindowPlan, q: torch.Tensor, k: torch.Tensor, v: torch.Ten
     txt_part = torch.empty(plan.n_windows, plan.txt_len, heads * 128, dtype=torch.bfloat16, device=dev)
     d = plan.on(dev)
     # attention and text pooling are two kernels; they are launched separately so the attention kernel can be timed alone
-    _call("svr2_window_attn_fwd", 1, dev, _lib.lib().svr2_window_attn_fwd,
-          q.data_ptr(), k.data_ptr(), v.data_ptr(), d["table"].data_ptr(), d["work"].data_ptr(), plan.work.shape[0],
-          d["work4"].data_ptr(), plan.work4.shape[0], plan.n_windows, T, H, W, plan.txt_len, heads, plan.packed_rows, out_vid.data_ptr(), txt_part.data_ptr(),
-          None, _stream(q))
+    if impl == ATTN_AUTO:
+        _call("svr2_window_attn_fwd", 1, dev, _lib.lib().svr2_window_attn_fwd,
+              q.data_ptr(), k.data_ptr(), v.data_ptr(), d["table"].data_ptr(), d["work"].data_ptr(), plan.work.shape[0],
+              d["work4"].data_ptr(), plan.work4.shape[0], plan.n_windows, T, H, W, plan.txt_len, heads, plan.packed_rows,
+              out_vid.data_ptr(), txt_part.data_ptr(), None, _stream(q))
+    else:
+        _call("svr2_window_attn_fwd", 1, dev, _lib.lib().svr2_window_attn_fwd_impl,
+              q.data_ptr(), k.data_ptr(), v.data_ptr(), d["table"].data_ptr(), d["work"].data_ptr(), plan.work.shape[0],
+              d["work4"].data_ptr(), plan.work4.shape[0], plan.n_windows, T, H, W, plan.txt_len, heads, plan.packed_rows,
+              out_vid.data_ptr(), txt_part.data_ptr(), None, int(impl), _stream(q))
     if plan.txt_len:
         _call("svr2_txt_pool_fwd", 1, dev, _lib.lib().svr2_txt_pool_fwd, txt_part.data_ptr(), out_txt.data_ptr(),
               plan.n_windows, plan.txt_len, heads, _stream(q))

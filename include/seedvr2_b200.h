@@ -156,6 +156,25 @@ int svr2_window_attn_fwd(const void* q_pack, const void* k_pack, const void* v_p
                          void* stream);
 
 /*
+ * The same call with the kernel named explicitly (tests and A/B runs; the product path calls svr2_window_attn_fwd):
+ *   SVR2_ATTN_AUTO  what svr2_window_attn_fwd picks from the packed lengths
+ *   SVR2_ATTN_GEN8  CTA pairs, tcgen05.mma.cta_group::2 (window_attn_v6.cu);  SVR2_ATTN_GEN4  persistent CTA per SM
+ *   (window_attn_v2.cu) — the two product kernels, bit-identical outputs
+ *   SVR2_ATTN_MMA   legacy mma.sync kernel (window_attn_mma.cu): an independent CUDA implementation kept as a test
+ *   comparator, never selected by SVR2_ATTN_AUTO
+ * Other codes name the earlier generations under csrc/experiments/ and return SVR2_E_UNSUPPORTED unless the library was
+ * built with `make EXPERIMENTS=1`.
+ */
+#define SVR2_ATTN_AUTO 0
+#define SVR2_ATTN_GEN4 4
+#define SVR2_ATTN_GEN8 8
+#define SVR2_ATTN_MMA  100
+int svr2_window_attn_fwd_impl(const void* q_pack, const void* k_pack, const void* v_pack, const int32_t* win_table,
+                              const int32_t* work, int n_work, const int32_t* work4, int n_work4, int n_windows, int T,
+                              int H, int W, int txt_len, int heads, int64_t P, void* out_vid, void* txt_part,
+                              void* out_txt, int impl, void* stream);
+
+/*
  * Debug hook (no reference counterpart): point the attention kernel at a device buffer of n_ctas * 64 int64 slots and
  * every CTA records clock64 stamps of its pipeline phases (slot map in csrc/window_attn.cu).  NULL switches it off.
  * Returns the number of slots per CTA.  Used by scripts/attn_trace.py to read the per-CTA timeline.

@@ -22,7 +22,19 @@ def test_exports_every_declared_symbol(svr2):
     handle = ctypes.CDLL(svr2._lib.LIB_PATH)
     for name in declared:
         assert hasattr(handle, name), f"{name} is declared but not exported"
-    assert svr2._lib.lib().svr2_abi_version() == svr2._lib.ABI_VERSION == 2
+    assert svr2._lib.lib().svr2_abi_version() == svr2._lib.ABI_VERSION
+
+
+def test_shipped_library_holds_only_dispatched_attention_kernels(svr2):
+    """The product library carries the two dispatched attention kernels and the mma.sync test comparator; the earlier
+    generations (csrc/experiments/) are compiled only with `make EXPERIMENTS=1`, and no entry point reads an environment
+    variable to pick a kernel."""
+    blob = open(svr2._lib.LIB_PATH, "rb").read()
+    for name in (b"window_attn_tc2_kernel", b"window_attn_tc6_kernel", b"window_attn_mma_kernel"):
+        assert name in blob, name
+    for name in (b"window_attn_tc3_kernel", b"window_attn_tc4_kernel", b"window_attn_tc5_kernel", b"window_attn_tc7_kernel",
+                 b"window_attn_tc_kernel", b"SVR2_ATTN_IMPL", b"SVR2_ATTN_TURNS", b"SVR2_MODNORM_PREFETCH"):
+        assert name not in blob, name
 
 
 def test_errors_are_reported_not_swallowed(svr2):

@@ -217,72 +217,103 @@ ATTN_CASES = [((2, 20, 36), False, 2), ((1, 32, 32), True, 3), ((5, 17, 30), Tru
 
 
 @pytest.mark.parametrize("grid,shifted,heads", ATTN_CASES)
-def test_window_attn_generations_bit_identical(svr2, cuda, monkeypatch, grid, shifted, heads):
-    """Generation 7 (one query tile per item, S and P double-buffered, two warpgroups on alternate key tiles), generation 4
-    (two query tiles, whole key tiles) and generation 6 (double-buffered half tiles) use the same exponent reference, lazy
-    rescale rule and summation order: their outputs must be identical bit for bit."""
+def test_window_attn_generations_bit_identical(svr2, cuda, grid, shifted, heads):
+    """The two product kernels — generation 4 (two query tiles per CTA, whole key tiles) and generation 8 (CTA pairs, one query
+    tile per CTA, two softmax warpgroups on alternate key tiles) — use the same exponent reference, lazy-rescale rule and
+    summation order: their outputs must be identical bit for bit, so the length-based dispatch cannot move a result."""
+    ops = svr2.ops
     plan = svr2.get_plan(grid, (4, 3, 3), shifted, cases.TXT_LEN)
     g = torch.Generator().manual_seed(11)
     q, k, v = (torch.randn(plan.packed_rows, heads, 128, generator=g).bfloat16().to(cuda) for _ in range(3))
 
     def run(impl, q):
-        monkeypatch.setenv("SVR2_ATTN_IMPL", impl)
-        ov, ot = svr2.ops.window_attn(plan, q, k, v, heads)
+        ov, ot = ops.window_attn(plan, q, k, v, heads, impl=impl)
         torch.cuda.synchronize()
         return ov.clone(), ot.clone()
 
-    base = run("v2", q)
-    for other in ("v4", "v5", "v5", "v5", "v6", "v6", "v7", "v7"):    # repeated launches of generations 7 / 8 must also agree with each other
+    base = run(ops.ATTN_GEN4, q)
+    for other in (ops.ATTN_GEN8, ops.ATTN_GEN8, ops.ATTN_AUTO):      # repeated launches must also agree with each other
         ov, ot = run(other, q)
-        assert torch.equal(base[0], ov), f"video rows differ between generation 4 (v2) and {other}"
-        assert torch.equal(base[1], ot), f"pooled text rows differ between generation 4 (v2) and {other}"
-    # rows whose maximum jumps from key tile to key tile exercise the lazy rescale of O, where generation 7 hands the
-    # reference exponent and the row sum from warpgroup to warpgroup (generation 6 takes row maxima per half tile and is
-    # only bit-compatible while no rescale fires)
+        assert torch.equal(base[0], ov), f"video rows differ between generation 4 and kernel {other}"
+        assert torch.equal(base[1], ot), f"pooled text rows differ between generation 4 and kernel {other}"
+    # rows whose maximum jumps from key tile to key tile exercise the lazy rescale of O, where generation 8 hands the
+    # reference exponent and the row sum from warpgroup to warpgroup
     q2 = q.clone()
     q2[: plan.packed_rows // 2] *= 6.0
-    base = run("v2", q2)
-    for other in ("v5", "v6", "v7"):
-        ov, ot = run(other, q2)
-        assert torch.equal(base[0], ov) and torch.equal(base[1], ot), f"{other} differs from generation 4 under lazy rescales"
+    base = run(ops.ATTN_GEN4, q2)
+    ov, ot = run(ops.ATTN_GEN8, q2)
+    assert torch.equal(base[0], ov) and torch.equal(base[1], ot), "generation 8 differs from generation 4 under lazy rescales"
 
 
-@pytest.mark.parametrize("impl", ["tcgen05", "v7", "v6", "v5", "v2", "v4", "v3", "v1", "mma"])
+def test_window_attn_experiments_not_in_product_build(svr2, cuda):
+    """Earlier generations live under csrc/experiments/ and are NOT part of the shipped library: naming one is an error."""
+    plan = svr2.get_plan((1, 8, 8), (4, 3, 3), False, cases.TXT_LEN)
+    q = torch.zeros(plan.packed_rows, 1, 128, dtype=torch.bfloat16, device=cuda)
+    with pytest.raises(NotImplementedError):
+        svr2.ops.window_attn(plan, q, q, q, 1, impl=7)
+
+
+@pytest.mark.parametrize("impl", ["auto", "gen8", "gen4", "mma"])
 @pytest.mark.parametrize("grid,shifted,heads", ATTN_CASES)
-def test_window_attn_vs_fp32(svr2, cuda, monkeypatch, impl, grid, shifted, heads):
-    monkeypatch.setenv("SVR2_ATTN_IMPL", impl)
+def test_window_attn_vs_fp32(svr2, cuda, impl, grid, shifted, heads):
+    code = {"auto": svr2.ops.ATTN_AUTO, "gen8": svr2.ops.ATTN_GEN8, "gen4": svr2.ops.ATTN_GEN4, "mma": svr2.ops.ATTN_MMA}[impl]
     plan = svr2.get_plan(grid, (4, 3, 3), shifted, cases.TXT_LEN)
     g = torch.Generator().manual_seed(3)
     q, k, v = (torch.randn(plan.packed_rows, heads, 128, generator=g).bfloat16() for _ in range(3))
     q = q * 1.5      # sharper softmax
-    ov, ot = svr2.ops.window_attn(plan, q.to(cuda), k.to(cuda), v.to(cuda), heads)
+    ov, ot = svr2.ops.window_attn(plan, q.to(cuda), k.to(cuda), v.to(cuda), heads, impl=code)
     torch.cuda.synchronize()
     ev, et = _sdpa_reference(plan, q, k, v, heads)
     dv, dt = (ov.cpu().float() - ev).abs().max(), (ot.cpu().float() - et).abs().max()
     assert float(dv) <= 2e-2 and float(dt) <= 2e-2, f"{impl}: vid {float(dv)} txt {float(dt)}"   # north-star tolerance
 
 
-@pytest.mark.parametrize("grid,shifted,heads", [((1, 128, 128), False, 20), ((1, 128, 128), True, 20), ((9, 90, 160), True, 4),
-                                                ((31, 68, 120), False, 2), ((6, 68, 120), True, 3), ((10, 135, 240), True, 1)])
-def test_window_attn_full_size_properties(svr2, cuda, monkeypatch, grid, shifted, heads):
-    """BASELINE-size runs checked through size-independent properties:
-    (1) V = ones -> every output row is exactly softmax-normalised (1.0): masking + all tiles + scatter coverage;
-    (2) linearity in V; (3) tcgen05 and the mma.sync comparator agree."""
+def _sdpa_reference_gpu(plan, q, k, v, heads):
+    """The oracle's per-window attention (oracle/block.py:window_attention, i.e. the reference's pytorch_varlen_attention
+    loop, attention.py:24-61 + the text mean na.py:414) in fp32 ON THE GPU, so that BASELINE-size grids finish in seconds.
+    Plain torch ops on the packed layout — an independent restatement, none of the library's kernels."""
+    dev = q.device
+    cu = plan.cu_seqlens
+    tgt = torch.from_numpy(geometry.window_index(*plan.grid, plan.window, plan.shifted, plan.txt_len)[0]).to(dev)
+    out_v = torch.zeros(plan.n_tokens, heads * 128, device=dev)
+    tacc = torch.zeros(plan.txt_len, heads * 128, device=dev)
+    voff = 0
+    for i in range(plan.n_windows):
+        a, b = int(cu[i]), int(cu[i + 1])
+        qi, ki, vi = (t[a:b].float().permute(1, 0, 2) for t in (q, k, v))          # [heads, n, 128]
+        s = torch.baddbmm(torch.zeros((), device=dev), qi, ki.transpose(1, 2), beta=0, alpha=128 ** -0.5)
+        o = torch.bmm(torch.softmax(s, dim=-1), vi).permute(1, 0, 2).reshape(b - a, heads * 128)
+        n = b - a - plan.txt_len
+        out_v[tgt[voff:voff + n]] = o[:n]
+        tacc += o[n:].bfloat16().float()       # per-window text rows are bf16 before the mean (na.py:414)
+        voff += n
+    return out_v, tacc / plan.n_windows
+
+
+# BASELINE grids at the real head counts (3B: 20 heads, 7B: 24 heads): C1 win/swin, C2 win/swin, C3 per-rank, C3, C4
+FULL_ATTN_CASES = [((1, 128, 128), False, 20), ((1, 128, 128), True, 20), ((9, 90, 160), False, 20), ((9, 90, 160), True, 20),
+                   ((6, 68, 120), True, 24), ((31, 68, 120), False, 24), ((10, 135, 240), True, 24)]
+
+
+@pytest.mark.parametrize("grid,shifted,heads", FULL_ATTN_CASES)
+def test_window_attn_full_size_vs_fp32(svr2, cuda, grid, shifted, heads):
+    """svr2_window_attn_fwd at the BASELINE token grids with the architectures' head counts against the fp32 restatement of
+    the reference's per-window SDPA loop (run on the GPU): max-abs <= 2e-2 (north-star tolerance) on every video row and
+    on the pooled text rows.  Also: V = ones gives exactly-normalised rows (masking + tile coverage + scatter coverage)."""
+    torch.backends.cuda.matmul.allow_tf32 = False
     plan = svr2.get_plan(grid, (4, 3, 3), shifted, cases.TXT_LEN)
     g = torch.Generator(device="cuda").manual_seed(11)
     P = plan.packed_rows
-    q, k, v1, v2 = (torch.randn(P, heads, 128, generator=g, device=cuda, dtype=torch.float32).bfloat16() for _ in range(4))
-    monkeypatch.setenv("SVR2_ATTN_IMPL", "tcgen05")
-    ones = torch.ones_like(v1)
-    ov, ot = svr2.ops.window_attn(plan, q, k, ones, heads)
-    assert float((ov.float() - 1).abs().max()) <= 2 ** -7 and float((ot.float() - 1).abs().max()) <= 2 ** -7
-    o1, t1 = svr2.ops.window_attn(plan, q, k, v1, heads)
-    o2, t2 = svr2.ops.window_attn(plan, q, k, v2, heads)
-    o3, t3 = svr2.ops.window_attn(plan, q, k, (v1.float() * 0.5 + v2.float() * 0.25).bfloat16(), heads)
-    assert float((o3.float() - (0.5 * o1.float() + 0.25 * o2.float())).abs().max()) <= 2e-2
-    monkeypatch.setenv("SVR2_ATTN_IMPL", "mma")
-    m1, mt1 = svr2.ops.window_attn(plan, q, k, v1, heads)
-    assert float((m1.float() - o1.float()).abs().max()) <= 2e-2 and float((mt1.float() - t1.float()).abs().max()) <= 2e-2
+    q, k, v = (torch.randn(P, heads, 128, generator=g, device=cuda, dtype=torch.float32).bfloat16() for _ in range(3))
+    ov, ot = svr2.ops.window_attn(plan, q, k, v, heads)
+    ev, et = _sdpa_reference_gpu(plan, q, k, v, heads)
+    dv, dt = float((ov.float() - ev).abs().max()), float((ot.float() - et).abs().max())
+    print(f"window_attn {grid} {'swin' if shifted else 'win'} heads {heads}: max|d| vid {dv:.5f} txt {dt:.5f} (<= 2e-2)")
+    assert dv <= 2e-2 and dt <= 2e-2
+    del ev, et
+    ones = torch.ones_like(v)
+    o1, t1 = svr2.ops.window_attn(plan, q, k, ones, heads)
+    assert float((o1.float() - 1).abs().max()) <= 2 ** -7 and float((t1.float() - 1).abs().max()) <= 2 ** -7
 
 
 # ----------------------------------------------------------------------------------------------- halo blend
@@ -292,4 +323,8 @@ def test_halo_blend(svr2, cuda, overlap):
     a, b = torch.rand(overlap, 18, 20, 3, generator=g), torch.rand(overlap, 18, 20, 3, generator=g)
     out = svr2.ops.halo_blend(a.to(cuda), b.to(cuda), overlap)
     ref = partition.blend(a, b, overlap)
+    # the blend itself is separately rounded mul, mul, add like the reference's tensor ops; the Hann weight comes from the
+    # device cosf, which may differ from torch's CPU cos by an ulp
     assert float((out.cpu() - ref).abs().max()) <= 1e-6
+    if overlap < 3:      # linear weights are exact on both sides: bit-equal to blend_overlapping_frames
+        assert torch.equal(out.cpu(), ref)
