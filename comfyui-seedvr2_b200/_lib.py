@@ -31,6 +31,9 @@ SIGNATURES = {
     "svr2_window_attn_worklist_tiles": (c_int, [POINTER(c_int32), c_int, c_int, c_int, POINTER(c_int32), c_int, POINTER(c_int64)]),
     "svr2_window_attn_fwd": (c_int, [c_void_p] * 5 + [c_int, c_void_p] + [c_int] * 7 + [c_int64, c_void_p, c_void_p, c_void_p, c_void_p]),
     "svr2_window_attn_fwd_impl": (c_int, [c_void_p] * 5 + [c_int, c_void_p] + [c_int] * 7 + [c_int64, c_void_p, c_void_p, c_void_p, c_int, c_void_p]),
+    "svr2_linear_fwd": (c_int, [c_void_p] * 4 + [c_int64, c_int, c_int, c_int, c_void_p]),
+    "svr2_linear_swiglu_fwd": (c_int, [c_void_p] * 4 + [c_int64, c_int, c_int, c_void_p]),
+    "svr2_linear_gate_residual_fwd": (c_int, [c_void_p] * 5 + [c_int, c_void_p, c_void_p, c_int64, c_int, c_int, c_void_p]),
     "svr2_debug_attn_trace": (c_int, [c_void_p, c_int]),
     "svr2_txt_pool_fwd": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
     "svr2_halo_blend": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int64, c_void_p]),
@@ -39,7 +42,7 @@ SIGNATURES = {
     "svr2_v_lerp_endpoint_fwd": (c_int, [c_void_p, c_void_p, c_float, c_float, c_void_p, c_int64, c_void_p]),
 }
 
-ABI_VERSION = 3      # svr2_abi_version() of the library these SIGNATURES describe
+ABI_VERSION = 4      # svr2_abi_version() of the library these SIGNATURES describe
 _lib = None
 
 

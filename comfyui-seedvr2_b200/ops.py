@@ -295,3 +295,68 @@ def v_lerp_endpoint(x_t: torch.Tensor, pred: torch.Tensor, A: float = 0.0, B: fl
     _call("svr2_v_lerp_endpoint_fwd", 1, x_t.device, _lib.lib().svr2_v_lerp_endpoint_fwd, x_t.data_ptr(), pred.data_ptr(),
           float(A), float(B), out.data_ptr(), x_t.numel(), _stream(x_t))
     return out
+
+
+# ----------------------------------------------------------------------------------------------- linear layers (csrc/gemm.cu)
+ACT_NONE, ACT_GELU_TANH = 0, 1
+
+
+def _need_weight(w: torch.Tensor, name: str, K: int) -> torch.Tensor:
+    _need(w, name)
+    if w.dim() != 2 or w.shape[1] != K:
+        raise RuntimeError(f"seedvr2_b200: `{name}` must be [N, {K}] (nn.Linear layout), got {tuple(w.shape)}")
+    return w
+
+
+@torch._dynamo.disable
+def linear(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor] = None, activation: int = ACT_NONE,
+           out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """y = x @ weight.T (+ bias), optionally GELU-tanh in the epilogue: the tcgen05 GEMM of csrc/gemm.cu."""
+    _need(x, "x")
+    M, K = x.shape
+    _need_weight(weight, "weight", K)
+    N = weight.shape[0]
+    if bias is not None:
+        _need(bias, "bias")
+    y = torch.empty(M, N, dtype=torch.bfloat16, device=x.device) if out is None else _need(out, "out")
+    if M:
+        _call("svr2_linear_fwd", 1, x.device, _lib.lib().svr2_linear_fwd, x.data_ptr(), weight.data_ptr(), _ptr(bias),
+              y.data_ptr(), M, N, K, int(activation), _stream(x))
+    return y
+
+
+@torch._dynamo.disable
+def linear_swiglu(x: torch.Tensor, w_gate: torch.Tensor, w_up: torch.Tensor) -> torch.Tensor:
+    """silu(x @ w_gate.T) * (x @ w_up.T) in one GEMM (reference mlp.py:60-62)."""
+    _need(x, "x")
+    M, K = x.shape
+    _need_weight(w_gate, "w_gate", K)
+    _need_weight(w_up, "w_up", K)
+    if w_gate.shape != w_up.shape:
+        raise RuntimeError("linear_swiglu: w_gate and w_up differ in shape")
+    N = w_gate.shape[0]
+    y = torch.empty(M, N, dtype=torch.bfloat16, device=x.device)
+    if M:
+        _call("svr2_linear_swiglu_fwd", 1, x.device, _lib.lib().svr2_linear_swiglu_fwd, x.data_ptr(), w_gate.data_ptr(),
+              w_up.data_ptr(), y.data_ptr(), M, N, K, _stream(x))
+    return y
+
+
+@torch._dynamo.disable
+def linear_gate_residual(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor], emb: torch.Tensor,
+                         gate_b: torch.Tensor, layer: int, resid: torch.Tensor) -> torch.Tensor:
+    """(x @ weight.T + bias) * (gateA[layer] + gateB) + resid in one GEMM (proj_out + AdaSingle "out" + residual)."""
+    _need(x, "x"); _need(emb, "emb"); _need(gate_b, "gate_b"); _need(resid, "resid")
+    M, K = x.shape
+    _need_weight(weight, "weight", K)
+    N = weight.shape[0]
+    if bias is not None:
+        _need(bias, "bias")
+    if resid.shape != (M, N):
+        raise RuntimeError(f"linear_gate_residual: resid must be [{M}, {N}]")
+    out = torch.empty(M, N, dtype=torch.bfloat16, device=x.device)
+    if M:
+        _call("svr2_linear_gate_residual_fwd", 1, x.device, _lib.lib().svr2_linear_gate_residual_fwd, x.data_ptr(),
+              weight.data_ptr(), _ptr(bias), emb.data_ptr(), gate_b.data_ptr(), int(layer), resid.data_ptr(), out.data_ptr(),
+              M, N, K, _stream(x))
+    return out

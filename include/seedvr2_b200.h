@@ -104,6 +104,36 @@ int svr2_swiglu_fwd(const void* gate, const void* up, void* out, int64_t n, void
 int svr2_swiglu_rows_fwd(const void* gate_up, void* out, int64_t rows, int hidden, void* stream);
 
 /*
+ * The block's linear layers: ONE persistent tcgen05 GEMM kernel (CTA pairs, TMA-staged operands, TMEM
+ * accumulators, csrc/gemm.cu) whose epilogue applies the row-wise work that follows the linear in the reference.
+ * x [M, K] bf16 row-major; weights in nn.Linear layout [N, K] bf16 row-major; bias [N] bf16 or NULL; y / out [M, N] bf16.
+ * N % 64 == 0, K % 8 == 0.  The accumulator (+ bias) is rounded to bf16 first — the linear's output tensor in the
+ * reference — and every following op rounds again like the reference's bf16 path.
+ *
+ * svr2_linear_fwd: y = x W^T + bias, optionally followed by GELU-tanh.
+ *   Replaces proj_qkv (src/models/dit_3b/nablocks/attention/mmattn.py:56-59,173; no bias) and, with
+ *   SVR2_ACT_GELU_TANH, the 7B MLP's proj_in + F.gelu(approximate="tanh") (src/models/dit_3b/mlp.py:28-43).
+ */
+#define SVR2_ACT_NONE      0
+#define SVR2_ACT_GELU_TANH 1
+int svr2_linear_fwd(const void* x, const void* weight, const void* bias, void* y, int64_t M, int N, int K, int activation,
+                    void* stream);
+/*
+ * svr2_linear_swiglu_fwd: y = silu(x Wg^T) * (x Wu^T) — both in-projections of SwiGLUMLP in one tile (two B operands), the
+ * activation in the epilogue; the two [M, hidden] projections never reach HBM.
+ *   Replaces `F.silu(self.proj_in_gate(x)) * self.proj_in(x)` (src/models/dit_3b/mlp.py:46-62).  N = hidden, N % 128 == 0.
+ */
+int svr2_linear_swiglu_fwd(const void* x, const void* w_gate, const void* w_up, void* y, int64_t M, int N, int K, void* stream);
+/*
+ * svr2_linear_gate_residual_fwd: out = (x W^T + bias) * (gateA[layer] + gateB) + resid.
+ *   Replaces attn.proj_out / mlp.proj_out (mmattn.py:269, mlp.py:43,62) + AdaSingle mode="out" (modulation.py:111-116) +
+ *   the residual add (mmsr_block.py:114,126).  emb [6 N] bf16 (d, layer, {shift, scale, gate}); gateB [N]; resid [M, N];
+ *   out must not alias x; N <= 4096.
+ */
+int svr2_linear_gate_residual_fwd(const void* x, const void* weight, const void* bias, const void* emb, const void* gateB,
+                                  int layer, const void* resid, void* out, int64_t M, int N, int K, void* stream);
+
+/*
  * q/k RMSNorm (affine, per head) + 3D RoPE + window partition + text interleave, one pass over qkv.
  * Replaces window_partition index_select (na.py:637, mmattn.py:199), norm_q/norm_k (mmattn.py:207-208,
  * normalization.py:88-109), the text repeat (mmattn.py:223-236), RoPE (dit_3b/rope.py:92-127, dit_7b/rope.py:73-91 +
