@@ -19,6 +19,11 @@ def _mk(M, N, K, seed, dev, scale=1.0):
     return x, w, b
 
 
+def _ulp(t):
+    """One bf16 ulp at the magnitude of each element (8 significant bits)."""
+    return torch.exp2(torch.floor(torch.log2(t.abs().clamp_min(2.0 ** -120))) - 7)
+
+
 def _lin32(x, w, b=None):
     torch.backends.cuda.matmul.allow_tf32 = False
     y = x.float() @ w.float().t()
@@ -50,13 +55,21 @@ def test_linear_swiglu(svr2, cuda, M, N, K):
     _, wu, _ = _mk(M, N, K, 3, cuda)
     y = svr2.ops.linear_swiglu(x, wg, wu)
     g, u = _lin32(x, wg).bfloat16(), _lin32(x, wu).bfloat16()          # the two linears' bf16 outputs (mlp.py:60-62)
-    ref = (F.silu(g.float()).bfloat16().float() * u.float()).bfloat16()
-    d = float((y.float() - ref.float()).abs().max())
-    assert d <= 2e-2, d
-    # vs the unfused library path of round 1 (two GEMMs + svr2_swiglu_fwd)
-    old = svr2.ops.swiglu(F.linear(x, wg), F.linear(x, wu))
-    frac = float((y != old).float().mean())
-    assert float((y.float() - old.float()).abs().max()) <= 2e-2 and frac < 0.02, frac
+    sg = F.silu(g.float()).bfloat16().float()
+    ref = (sg * u.float()).bfloat16().float()
+    # Derived bound: fp32 accumulation order may flip the last bf16 bit of each GEMM output (g and u), and the product is
+    # rounded once more: |d| <= (silu'(g) ulp(g) + ulp(silu)) |u| + ulp(u) |silu(g)| + ulp(out), silu' <= 1.1 — silu(g) is a
+    # bf16 tensor too (mlp.py:60), so a moved g can move its rounding by one more ulp.  Where |out| <= 1 this is
+    # below the north-star 2e-2; the large products (|out| ~ 10, one ulp = 0.0625) are why an absolute bound cannot hold.
+    tol = (1.1 * _ulp(g.float()) + _ulp(sg)) * u.float().abs() + _ulp(u.float()) * sg.abs() + _ulp(ref) + 1e-3
+    err = (y.float() - ref).abs()
+    assert bool((err <= tol).all()), float((err / tol).max())
+    small = ref.abs() <= 1.0
+    assert float(err[small].max()) <= 2e-2
+    # vs the unfused library path of round 1 (two GEMMs + svr2_swiglu_fwd): same rounding points, different accumulation order
+    old = svr2.ops.swiglu(F.linear(x, wg), F.linear(x, wu)).float()
+    frac = float((y.float() != old).float().mean())
+    assert bool(((y.float() - old).abs() <= 2 * tol).all()) and frac < 0.02, frac       # either side may carry the flips
 
 
 @pytest.mark.parametrize("M,N,K", [(58, 256, 128), (2050, 12288, 3072), (700, 512, 64)])
@@ -64,10 +77,13 @@ def test_linear_gelu(svr2, cuda, M, N, K):
     x, w, b = _mk(M, N, K, 4, cuda)
     y = svr2.ops.linear(x, w, b, activation=svr2.ops.ACT_GELU_TANH)
     h = _lin32(x, w, b).bfloat16()                                      # proj_in's bf16 output (mlp.py:40-42)
-    ref = F.gelu(h.float(), approximate="tanh").bfloat16()
-    d = float((y.float() - ref.float()).abs().max())
-    assert d <= 2e-2, d
-    assert float((y != ref).float().mean()) < 0.02
+    ref = F.gelu(h.float(), approximate="tanh").bfloat16().float()
+    # one last-bit flip of h (accumulation order) times gelu' (<= 1.13), plus the output rounding
+    tol = 1.13 * _ulp(h.float()) + _ulp(ref) + 1e-3
+    err = (y.float() - ref).abs()
+    assert bool((err <= tol).all()), float((err / tol).max())
+    assert float(err[ref.abs() <= 1.0].max()) <= 2e-2
+    assert float((y.float() != ref).float().mean()) < 0.02
 
 
 @pytest.mark.parametrize("M,N,K,layer", [(58, 256, 128, 0), (16442, 2560, 2560, 0), (16442, 2560, 6912, 1), (2050, 3072, 12288, 1),
@@ -83,13 +99,18 @@ def test_linear_gate_residual(svr2, cuda, M, N, K, layer, with_bias):
     out = svr2.ops.linear_gate_residual(x, w, bias, emb, gate_b, layer, resid)
     h = _lin32(x, w, bias).bfloat16()
     gate = (emb.view(N, 2, 3)[:, layer, 2].float() + gate_b.float()).bfloat16()       # modulation.py:75-76,111-116
-    ref = ((h.float() * gate.float()).bfloat16().float() + resid.float()).bfloat16()
-    d = float((out.float() - ref.float()).abs().max())
-    assert d <= 2e-2, d
+    hg = (h.float() * gate.float()).bfloat16().float()
+    ref = (hg + resid.float()).bfloat16().float()
+    # one last-bit flip of h times |gate|, the product's own rounding, the sum's rounding
+    tol = _ulp(h.float()) * gate.float().abs() + _ulp(hg) + _ulp(ref) + 1e-3
+    err = (out.float() - ref).abs()
+    assert bool((err <= tol).all()), float((err / tol).max())
+    calm = (ref.abs() <= 1.0) & (hg.abs() <= 1.0) & (h.float().abs() <= 2.0)      # no cancellation of large intermediates
+    assert float(err[calm].max()) <= 2e-2
     # vs the unfused path of round 1: library GEMM + svr2_gate_residual_fwd
-    old = svr2.ops.gate_residual(F.linear(x, w, bias), resid, emb, gate_b, layer)
-    assert float((out.float() - old.float()).abs().max()) <= 3e-2
-    assert float((out != old).float().mean()) < 0.03
+    old = svr2.ops.gate_residual(F.linear(x, w, bias), resid, emb, gate_b, layer).float()
+    assert bool(((out.float() - old).abs() <= 2 * tol).all())
+    assert float((out.float() != old).float().mean()) < 0.03
 
 
 def test_linear_rejects_bad_shapes(svr2, cuda):
