@@ -34,6 +34,7 @@ SIGNATURES = {
     "svr2_linear_fwd": (c_int, [c_void_p] * 4 + [c_int64, c_int, c_int, c_int, c_void_p]),
     "svr2_linear_swiglu_fwd": (c_int, [c_void_p] * 4 + [c_int64, c_int, c_int, c_void_p]),
     "svr2_linear_gate_residual_fwd": (c_int, [c_void_p] * 5 + [c_int, c_void_p, c_void_p, c_int64, c_int, c_int, c_void_p]),
+    "svr2_window_attn_fwd_noalloc": (c_int, [c_void_p] * 5 + [c_int] * 7 + [c_int64, c_void_p, c_void_p, c_void_p]),
     "svr2_debug_attn_trace": (c_int, [c_void_p, c_int]),
     "svr2_txt_pool_fwd": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
     "svr2_halo_blend": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int64, c_void_p]),

@@ -113,3 +113,51 @@ extern "C" int svr2_txt_pool_fwd(const void* txt_part, void* out_txt, int n_wind
     SVR2_CHECK_ARG(txt_part && out_txt && n_windows > 0 && txt_len >= 0 && heads > 0, "svr2_txt_pool_fwd: bad arguments");
     return svr2::launch_txt_pool(txt_part, out_txt, n_windows, txt_len, heads, (cudaStream_t)stream);
 }
+
+// ------------------------------------------------------------------------------------------------------------------------
+// svr2_window_attn_fwd_noalloc — svr2_window_attn_fwd for callers that cannot allocate (CUDA graph capture, serving loops,
+// harnesses that forbid cudaMalloc).  No counterpart in the reference.
+// The per-window text rows (the `txt_part` workspace of svr2_window_attn_fwd) live in this file-scope device array instead of
+// caller memory.  Every GPU that loads the library holds the array until the process exits.  All calls on a device share it:
+// calls that overlap on the GPU (different streams) race.  Nothing in it has to start at zero — the attention kernel writes
+// every (window, text row, head) slot it later pools — so the previous call's contents are simply overwritten.
+static __device__ __align__(256) unsigned char g_noalloc_txt_part[SVR2_NOALLOC_SCRATCH_BYTES];
+
+namespace svr2 {
+namespace {
+// The array's name is only a host-side stand-in in host code; the device address is looked up once per device, with that
+// device current, and cached.
+int noalloc_scratch(void** out) {
+    static void* ptr[kMaxDevices] = {};
+    const int dev = cur_device();
+    if (ptr[dev] == nullptr) {
+        void* p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_txt_part);
+        if (e != cudaSuccess || p == nullptr) {
+            set_error("svr2_window_attn_fwd_noalloc: cudaGetSymbolAddress failed on device %d: %s", dev, cudaGetErrorString(e));
+            return SVR2_E_CUDA;
+        }
+        ptr[dev] = p;
+    }
+    *out = ptr[dev];
+    return SVR2_OK;
+}
+}  // namespace
+}  // namespace svr2
+
+extern "C" int svr2_window_attn_fwd_noalloc(const void* q_pack, const void* k_pack, const void* v_pack, const int32_t* win_table,
+                                            const int32_t* work, int n_work, int n_windows, int T, int H, int W, int txt_len,
+                                            int heads, int64_t P, void* out_vid, void* out_txt, void* stream) {
+    SVR2_CHECK_ARG(n_windows > 0 && heads > 0 && txt_len >= 0, "svr2_window_attn_fwd_noalloc: bad sizes");
+    SVR2_CHECK_ARG(txt_len == 0 || out_txt, "svr2_window_attn_fwd_noalloc: out_txt is required (the pooling runs inside the call)");
+    const int64_t need = (int64_t)n_windows * txt_len * heads * SVR2_HEAD_DIM * 2;
+    SVR2_CHECK_ARG(need <= (int64_t)SVR2_NOALLOC_SCRATCH_BYTES,
+                   "svr2_window_attn_fwd_noalloc: %d windows x %d text rows x %d heads need %lld B of scratch, the static array "
+                   "holds %lld B; use svr2_window_attn_fwd with a caller workspace", n_windows, txt_len, heads, (long long)need,
+                   (long long)SVR2_NOALLOC_SCRATCH_BYTES);
+    void* scratch = nullptr;
+    const int rc = svr2::noalloc_scratch(&scratch);
+    if (rc != SVR2_OK) return rc;
+    return svr2_window_attn_fwd_impl(q_pack, k_pack, v_pack, win_table, work, n_work, nullptr, 0, n_windows, T, H, W, txt_len, heads,
+                                     P, out_vid, scratch, txt_len ? out_txt : nullptr, SVR2_ATTN_AUTO, stream);
+}

@@ -205,6 +205,22 @@ int svr2_window_attn_fwd_impl(const void* q_pack, const void* k_pack, const void
                               void* out_txt, int impl, void* stream);
 
 /*
+ * svr2_window_attn_fwd without caller scratch, for callers that cannot allocate (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * Same inputs, outputs and kernels as svr2_window_attn_fwd; the per-window text rows (`txt_part`) live in a file-scope
+ * static device array of SVR2_NOALLOC_SCRATCH_BYTES (32 MiB) that every GPU loading the library holds until exit, and the
+ * text pooling always runs inside the call (out_txt is required when txt_len > 0).  The call allocates nothing (no
+ * cudaMalloc / cudaFree / allocating library routine).  Limit: n_windows * txt_len * heads * 128 * 2 bytes must fit the
+ * array (58 text rows: up to 112 windows at 20 heads, 94 at 24 heads) — larger problems return SVR2_E_INVALID with a message.
+ * All calls on one device share the array: calls that overlap on the GPU race; stream-ordered calls are safe (nothing in
+ * the array needs to start at zero, every slot that is pooled is written first).
+ */
+#define SVR2_NOALLOC_SCRATCH_BYTES (32u << 20)
+int svr2_window_attn_fwd_noalloc(const void* q_pack, const void* k_pack, const void* v_pack, const int32_t* win_table,
+                                 const int32_t* work, int n_work, int n_windows, int T, int H, int W, int txt_len, int heads,
+                                 int64_t P, void* out_vid, void* out_txt, void* stream);
+
+/*
  * Debug hook (no reference counterpart): point the attention kernel at a device buffer of n_ctas * 64 int64 slots and
  * every CTA records clock64 stamps of its pipeline phases (slot map in csrc/window_attn.cu).  NULL switches it off.
  * Returns the number of slots per CTA.  Used by scripts/attn_trace.py to read the per-CTA timeline.
