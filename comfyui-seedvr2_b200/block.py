@@ -25,8 +25,16 @@ from . import ops
 from .plan import WindowPlan, get_plan
 
 _SHIFTED = {"720pwin_by_size_bysize": False, "720pswin_by_size_bysize": True}
-_SWIGLU_STACKED = os.environ.get("SVR2_SWIGLU_STACKED", "0") == "1"      # experiment flag, off: see _SwiGLU.forward
-_GELU_EPILOGUE = os.environ.get("SVR2_GELU_EPILOGUE", "1") != "0"     # 7B MLP: library GEMM with fused bias + GELU epilogue
+# The block's linear layers run on the library's own tcgen05 GEMM (csrc/gemm.cu) with the following row-wise op fused into the
+# epilogue.  USE_TC_GEMM = False restores round 1's library GEMMs (cuBLAS through torch) + separate elementwise kernels — kept
+# ONLY so bench.py can time both arms in one process; it is still all-CUDA and never the default.
+USE_TC_GEMM = os.environ.get("SVR2_LIBRARY_GEMM", "0") != "1"
+
+
+def _linear(x, w, b=None):
+    if USE_TC_GEMM and x.is_cuda and x.dim() == 2 and w.shape[0] % 64 == 0 and w.shape[1] % 8 == 0:
+        return ops.linear(x.contiguous(), _bf16(w), None if b is None else _bf16(b))
+    return F.linear(x, _bf16(w), None if b is None else _bf16(b))
 
 
 def _factory_kind(f) -> Optional[str]:
@@ -108,17 +116,14 @@ class _SwiGLU(nn.Module):      # reference mlp.py:46-62
         self.proj_out = nn.Linear(hidden, dim, bias=False)
         self.proj_in = nn.Linear(dim, hidden, bias=False)
 
+    def hidden(self, x):
+        """silu(proj_in_gate(x)) * proj_in(x): ONE GEMM with two B operands and the activation in its epilogue."""
+        if USE_TC_GEMM and x.is_cuda and x.dim() == 2:
+            return ops.linear_swiglu(x.contiguous(), _bf16(self.proj_in_gate.weight), _bf16(self.proj_in.weight))
+        return ops.swiglu(F.linear(x, _bf16(self.proj_in_gate.weight)), F.linear(x, _bf16(self.proj_in.weight)))
+
     def forward(self, x):
-        if _SWIGLU_STACKED and x.is_cuda and x.dim() == 2:
-            # experiment (run 72): the two in-projections as ONE GEMM over the stacked weights [W_gate ; W_in]
-            w = self.__dict__.get("_w_stacked")
-            if w is None or w.device != x.device:
-                w = torch.cat([_bf16(self.proj_in_gate.weight), _bf16(self.proj_in.weight)], 0).contiguous()
-                self.__dict__["_w_stacked"] = w
-            h = ops.swiglu_rows(F.linear(x, w))
-        else:
-            h = ops.swiglu(F.linear(x, _bf16(self.proj_in_gate.weight)), F.linear(x, _bf16(self.proj_in.weight)))
-        return F.linear(h, _bf16(self.proj_out.weight))
+        return _linear(self.hidden(x), self.proj_out.weight)
 
 
 class _GeluMLP(nn.Module):     # reference mlp.py:28-43
@@ -127,15 +132,26 @@ class _GeluMLP(nn.Module):     # reference mlp.py:28-43
         self.proj_in = nn.Linear(dim, dim * expand_ratio)
         self.proj_out = nn.Linear(dim * expand_ratio, dim)
 
+    def hidden(self, x):
+        """gelu_tanh(proj_in(x)): bias + activation in the GEMM epilogue; the [L, 4D] pre-activation never reaches HBM."""
+        if USE_TC_GEMM and x.is_cuda and x.dim() == 2:
+            return ops.linear(x.contiguous(), _bf16(self.proj_in.weight), _bf16(self.proj_in.bias), ops.ACT_GELU_TANH)
+        if x.is_cuda and x.dim() == 2:      # round 1: cuBLASLt epilogue
+            return torch._addmm_activation(_bf16(self.proj_in.bias), x, _bf16(self.proj_in.weight).t(), use_gelu=True)
+        return F.gelu(F.linear(x, _bf16(self.proj_in.weight), _bf16(self.proj_in.bias)), approximate="tanh")
+
     def forward(self, x):
-        if _GELU_EPILOGUE and x.is_cuda and x.dim() == 2:
-            # bias + tanh-GELU applied in the cuBLASLt epilogue of proj_in: the [L, 4D] pre-activation never makes a
-            # round trip through HBM (it is 4x the block's row width — the largest elementwise pass of a 7B block).
-            # GELU then sees the fp32 accumulator instead of its bf16 rounding; the block golden tests hold the bound.
-            h = torch._addmm_activation(_bf16(self.proj_in.bias), x, _bf16(self.proj_in.weight).t(), use_gelu=True)
-        else:
-            h = F.gelu(F.linear(x, _bf16(self.proj_in.weight), _bf16(self.proj_in.bias)), approximate="tanh")
-        return F.linear(h, _bf16(self.proj_out.weight), _bf16(self.proj_out.bias))
+        return _linear(self.hidden(x), self.proj_out.weight, self.proj_out.bias)
+
+
+def _proj_gate_residual(x, lin: nn.Linear, e, gate_b, layer: int, resid):
+    """lin(x) * (gateA[layer] + gateB) + resid — proj_out + AdaSingle "out" + residual (mmattn.py:269 / mlp.py:43,62,
+    modulation.py:111-116, mmsr_block.py:114,126) as ONE GEMM; gate_b None = plain residual (3B last layer's text rows)."""
+    bias = None if lin.bias is None else _bf16(lin.bias)
+    if USE_TC_GEMM and gate_b is not None:
+        return ops.linear_gate_residual(x.contiguous(), _bf16(lin.weight), bias, e, _bf16(gate_b), layer, resid.contiguous())
+    h = _linear(x, lin.weight, lin.bias)
+    return ops.gate_residual(h, resid.contiguous(), e if gate_b is not None else None, None if gate_b is None else _bf16(gate_b), layer)
 
 
 _cast_cache = {}      # id(tensor) -> (weakref, version, data_ptr, device, bf16 copy)
@@ -222,11 +238,11 @@ class NaSwinAttentionB200(nn.Module):
         """proj_qkv -> pack (norm+rope+partition) -> window attention; returns attention outputs BEFORE proj_out."""
         both = _joined(vid, txt) if self.proj_qkv.shared_weights else None
         if both is not None:
-            qkv = F.linear(both, _bf16(self.proj_qkv.all.weight))
+            qkv = _linear(both, self.proj_qkv.all.weight)
             vqkv, tqkv = qkv[:vid.shape[0]], qkv[vid.shape[0]:]
         else:
-            vqkv = F.linear(vid, _bf16(self.proj_qkv.pick("vid").weight))
-            tqkv = F.linear(txt, _bf16(self.proj_qkv.pick("txt").weight))
+            vqkv = _linear(vid, self.proj_qkv.pick("vid").weight)
+            tqkv = _linear(txt, self.proj_qkv.pick("txt").weight)
         if self.rope is not None:
             freqs = self.rope.rope.freqs
             if freqs.dtype != torch.float32:
@@ -243,12 +259,14 @@ class NaSwinAttentionB200(nn.Module):
         grid, txt_len = _GridMemo.read(vid_shape, txt_shape)
         plan = get_plan(grid, self.window, self.shifted, txt_len)
         ov, ot = self.core(vid, txt, plan)
+        # Unfused tail, kept for callers of the attention module on its own (the product's attention wrappers,
+        # compatibility.py:437-522).  The block itself calls core() and fuses proj_out with the gate + residual.
         both = _joined(ov, ot) if self.proj_out.shared_weights else None
         if both is not None:
-            o = F.linear(both, _bf16(self.proj_out.all.weight), _bf16(self.proj_out.all.bias))
+            o = _linear(both, self.proj_out.all.weight, self.proj_out.all.bias)
             return o[:ov.shape[0]], o[ov.shape[0]:]
         po_v, po_t = self.proj_out.pick("vid"), self.proj_out.pick("txt")
-        return (F.linear(ov, _bf16(po_v.weight), _bf16(po_v.bias)), F.linear(ot, _bf16(po_t.weight), _bf16(po_t.bias)))
+        return _linear(ov, po_v.weight, po_v.bias), _linear(ot, po_t.weight, po_t.bias)
 
 
 class _BlockBase(nn.Module):
@@ -278,38 +296,42 @@ class _BlockBase(nn.Module):
         av, at = self._ada("vid"), (None if self.txt_tail_skipped else self._ada("txt"))
         L = vid.shape[0]
 
+        attn = self.attn
         if av is at and self.mlp.shared_weights:
-            # Shared-weight layer: ada / mlp (and attn) hold ONE module for both branches, so every row-wise step runs once
-            # on the joined rows [vid; txt].  The joined tensor is free when the previous layer produced it; the first
-            # shared layer pays one copy.
+            # Shared-weight layer: ada / mlp (and attn) hold ONE module for both branches, so every row-wise step and every
+            # GEMM runs once on the joined rows [vid; txt].  The joined tensor is free when the previous layer produced it;
+            # the first shared layer pays one copy.
             x = _joined(vid, txt)
             if x is None:
                 x = torch.cat([vid, txt])
             a = ops.modnorm(x, e, _bf16(av.attn_shift), _bf16(av.attn_scale), 0, eps)
-            o_v, o_t = self.attn(a[:L], a[L:], vid_shape, txt_shape, cache)
+            o_v, o_t = attn.core(a[:L], a[L:], plan)
             o = _joined(o_v, o_t)
-            if o is None:       # a wrapper around attn.forward returned copies (compatibility.py:437-522)
+            if o is None:
                 o = torch.cat([o_v, o_t])
-            x1, m = ops.gate_residual_modnorm(o, x, e, _bf16(av.attn_gate), _bf16(av.mlp_shift), _bf16(av.mlp_scale), eps)
-            x2 = ops.gate_residual(self.mlp.all(m), x1, e, _bf16(av.mlp_gate), 1)
+            x1 = _proj_gate_residual(o, attn.proj_out.all, e, av.attn_gate, 0, x)            # GEMM + gate + residual
+            m = ops.modnorm(x1, e, _bf16(av.mlp_shift), _bf16(av.mlp_scale), 1, eps)
+            x2 = _proj_gate_residual(self.mlp.all.hidden(m), self.mlp.all.proj_out, e, av.mlp_gate, 1, x1)
             return x2[:L], x2[L:], vid_shape, txt_shape
 
         # --- attention half
         a_v = ops.modnorm(vid, e, _bf16(av.attn_shift), _bf16(av.attn_scale), 0, eps)
         a_t = (ops.modnorm(txt, e, _bf16(at.attn_shift), _bf16(at.attn_scale), 0, eps) if at is not None
                else ops.modnorm(txt, None, None, None, 0, eps))
-        o_v, o_t = self.attn(a_v, a_t, vid_shape, txt_shape, cache)
-        # --- gate + residual, fused with the MLP half's norm + modulation
-        vid1, m_v = ops.gate_residual_modnorm(o_v, vid, e, _bf16(av.attn_gate), _bf16(av.mlp_shift), _bf16(av.mlp_scale), eps)
-        m_v = self.mlp.pick("vid")(m_v)
-        vid2 = ops.gate_residual(m_v, vid1, e, _bf16(av.mlp_gate), 1)
+        o_v, o_t = attn.core(a_v, a_t, plan)
+        # --- proj_out + gate + residual in one GEMM, then the MLP half's norm + modulation
+        vid1 = _proj_gate_residual(o_v, attn.proj_out.pick("vid"), e, av.attn_gate, 0, vid)
+        m_v = ops.modnorm(vid1, e, _bf16(av.mlp_shift), _bf16(av.mlp_scale), 1, eps)
+        mlp_v = self.mlp.pick("vid")
+        vid2 = _proj_gate_residual(mlp_v.hidden(m_v), mlp_v.proj_out, e, av.mlp_gate, 1, vid1)
         if at is not None:
-            txt1, m_t = ops.gate_residual_modnorm(o_t, txt, e, _bf16(at.attn_gate), _bf16(at.mlp_shift), _bf16(at.mlp_scale), eps)
-            m_t = self.mlp.pick("txt")(m_t)
-            txt2 = ops.gate_residual(m_t, txt1, e, _bf16(at.mlp_gate), 1)
+            txt1 = _proj_gate_residual(o_t, attn.proj_out.pick("txt"), e, at.attn_gate, 0, txt)
+            m_t = ops.modnorm(txt1, e, _bf16(at.mlp_shift), _bf16(at.mlp_scale), 1, eps)
+            mlp_t = self.mlp.pick("txt")
+            txt2 = _proj_gate_residual(mlp_t.hidden(m_t), mlp_t.proj_out, e, at.mlp_gate, 1, txt1)
         else:
             # vid_only MMModules pass txt through untouched (mm.py:69-73): txt1 = attn(txt) + txt ; txt2 = txt1 + txt1
-            txt1 = ops.gate_residual(o_t, txt, None, None, 0)
+            txt1 = _proj_gate_residual(o_t, attn.proj_out.pick("txt"), None, None, 0, txt)
             txt2 = ops.gate_residual(txt1, txt1, None, None, 1)
         return vid2, txt2, vid_shape, txt_shape
 
