@@ -66,6 +66,31 @@ def padded_batch_frames(n_frames: int) -> int:
     return n_frames if n_frames % 4 == 1 else ((n_frames - 1 + 3) // 4) * 4 + 1
 
 
+def batch_ranges(total_frames: int, batch_size: int, overlap: int) -> List[Tuple[int, int]]:
+    """[start, end) frames of every latent batch INSIDE one rank's segment (generation_phases.py:267-282): batches of
+    ``batch_size`` frames advance by ``batch_size - overlap``; a trailing batch that would hold nothing but overlap frames is
+    dropped; ``overlap >= batch_size`` resets the overlap to 0 as the reference does.  Each batch is then padded to 4n+1
+    frames (``padded_batch_frames``) and is one DiT forward."""
+    if total_frames < 0 or batch_size <= 0 or overlap < 0:
+        raise ValueError("batch_ranges: bad arguments")
+    step = batch_size - overlap if overlap > 0 else batch_size
+    if step <= 0:
+        step, overlap = batch_size, 0
+    out = []
+    for idx in range(0, total_frames, step):
+        end = min(idx + batch_size, total_frames)
+        if idx > 0 and end - idx <= overlap:
+            break
+        out.append((idx, end))
+    return out
+
+
+def latent_frames(n_frames: int) -> int:
+    """Latent frames of a batch of ``n_frames`` pixel frames: padded to 4n+1, then the VAE's 4x temporal compression with the
+    first frame kept (T = (F - 1) / 4 + 1)."""
+    return (padded_batch_frames(n_frames) - 1) // 4 + 1 if n_frames > 0 else 0
+
+
 def _default_blend(prev_tail: torch.Tensor, cur_head: torch.Tensor, overlap: int) -> torch.Tensor:
     from . import ops
     return ops.halo_blend(prev_tail.contiguous(), cur_head.contiguous(), overlap)

@@ -6,7 +6,10 @@ adaLN src/models/dit_3b/modulation.py:65-118, RMSNorm normalization.py:88-109, M
 varlen attention attention.py:24-61 (per-window SDPA), text pooling na.py:396-417.
 
 Written with plain torch ops in the reference's op ORDER so that running it in bf16 reproduces the reference's
-rounding points and running it in fp32 gives the ground truth.  ``params`` uses the reference's
+rounding points and running it in fp32 gives the ground truth.  Device-agnostic: every tensor follows
+``vid.device``, so the same restatement is the checker on the CPU (golden-pinned, tests/test_oracle_golden.py) and — with
+``vid`` on ``cuda`` — the reference's own bf16 PyTorch path on a GPU (per-window ``F.scaled_dot_product_attention``,
+attention.py:24-61) for the full-width parity tests and bench.py's GPU-vs-GPU baseline leg.  ``params`` uses the reference's
 state-dict key names relative to the block (e.g. ``attn.proj_qkv.vid.weight``).
 """
 from dataclasses import dataclass
@@ -79,7 +82,8 @@ def window_attention(cfg: BlockCfg, p: Dict[str, torch.Tensor], vid: torch.Tenso
     vqkv = F.linear(vid, p[f"attn.proj_qkv.{bv}.weight"])
     tqkv = F.linear(txt, p[f"attn.proj_qkv.{bt}.weight"])
     tgt, src, wshape, cu = geometry.window_index(T, H, W, cfg.window, cfg.shifted, Lt)
-    tgt_t, src_t = torch.from_numpy(tgt), torch.from_numpy(src)
+    dev = vid.device
+    tgt_t, src_t = torch.from_numpy(tgt).to(dev), torch.from_numpy(src).to(dev)
     vqkv = vqkv.index_select(0, tgt_t).reshape(-1, 3, Hh, d)
     tqkv = tqkv.reshape(-1, 3, Hh, d)
     vq, vk, vv = vqkv.unbind(1)
@@ -94,12 +98,13 @@ def window_attention(cfg: BlockCfg, p: Dict[str, torch.Tensor], vid: torch.Tenso
     freqs = p["attn.rope.rope.freqs"]
     if cfg.model == "3b":
         va, ta = rope.angles_3b(ws, Lt, freqs)
+        va, ta = va.to(dev), ta.to(dev)
         vq, vk = rope.rotate(vq, va), rope.rotate(vk, va)
         tq, tk = rope.rotate(tq, ta), rope.rotate(tk, ta)
     else:
-        va = rope.angles_7b(ws, freqs).to(vq.dtype)      # dit_7b/rope.py:85
+        va = rope.angles_7b(ws, freqs).to(dev).to(vq.dtype)      # dit_7b/rope.py:85
         vq, vk = rope.rotate(vq, va), rope.rotate(vk, va)
-    vout = torch.empty(vq.shape[0], Hh, d, dtype=vq.dtype)
+    vout = torch.empty(vq.shape[0], Hh, d, dtype=vq.dtype, device=dev)
     tacc = []
     off = 0
     for k, (f, h, w) in enumerate(ws):

@@ -22,6 +22,23 @@ def segment_ranges(total_frames: int, num_devices: int, overlap: int, start_fram
     return out
 
 
+def batch_ranges(total_frames: int, batch_size: int, overlap: int) -> List[Tuple[int, int]]:
+    """Latent batches inside one segment, generation_phases.py:259-282 line by line (step, reset, early break)."""
+    step = batch_size - overlap if overlap > 0 else batch_size
+    if step <= 0:
+        step = batch_size
+        overlap = 0
+    num = 0
+    out = []
+    for idx in range(0, total_frames, step):
+        end_idx = min(idx + batch_size, total_frames)
+        if idx > 0 and end_idx - idx <= overlap:
+            break
+        num += 1
+        out.append((idx, end_idx))
+    return out
+
+
 def blend_weights(overlap: int, dtype=torch.float32) -> torch.Tensor:
     """Weight of the PREVIOUS segment's tail per overlapping frame."""
     if overlap >= 3:

@@ -18,8 +18,9 @@ def _axis_angles(pos: torch.Tensor, freqs: torch.Tensor) -> torch.Tensor:
 
 
 def angles_3b(window_shape: Sequence[Tuple[int, int, int]], txt_len: int, freqs: torch.Tensor):
-    """-> (vid_angles [sum Lw, 6*len(freqs)], txt_angles [txt_len, 6*len(freqs)]) fp32."""
-    freqs = freqs.float()
+    """-> (vid_angles [sum Lw, 6*len(freqs)], txt_angles [txt_len, 6*len(freqs)]) fp32, built on the CPU (the caller moves
+    them): the tables are then bit-identical whatever device the activations live on."""
+    freqs = freqs.float().cpu()
     out = []
     for (f, h, w) in window_shape:
         at = _axis_angles(torch.arange(txt_len, txt_len + f), freqs)[:, None, None, :].expand(f, h, w, -1)
@@ -31,8 +32,9 @@ def angles_3b(window_shape: Sequence[Tuple[int, int, int]], txt_len: int, freqs:
 
 
 def angles_7b(window_shape: Sequence[Tuple[int, int, int]], freqs: torch.Tensor) -> torch.Tensor:
-    """-> vid_angles [sum Lw, 6*len(freqs)] fp32 (caller casts to the activation dtype as the reference does)."""
-    freqs = freqs.float()
+    """-> vid_angles [sum Lw, 6*len(freqs)] fp32 on the CPU (caller moves it and casts to the activation dtype as the
+    reference does)."""
+    freqs = freqs.float().cpu()
     out = []
     for (f, h, w) in window_shape:
         at = _axis_angles(torch.linspace(-1, 1, steps=f), freqs)[:, None, None, :].expand(f, h, w, -1)

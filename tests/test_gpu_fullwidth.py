@@ -1,0 +1,128 @@
+"""GPU parity at the REAL architectures (configs_3b: D = 2560, 20 heads, SwiGLU 6912; configs_7b: D = 3072, 24 heads, GELU
+12288) on the BASELINE token grids, against the reference's own PyTorch path run on the same GPU.
+
+The checker is ``oracle.block.block_forward`` with every tensor on ``cuda``: plain torch ops in the reference's op order with
+one ``F.scaled_dot_product_attention`` call per window (src/models/dit_3b/attention.py:24-61), i.e. what the reference executes
+on a GPU with ``attention_mode='sdpa'`` — in bf16 (the reference's compute dtype, compatibility.py:221) and in fp32 (ground
+truth).  The oracle is pinned to the real reference blocks by tests/golden (CPU, narrow width); this file carries that chain to
+full width, where round 1 only checked the row-wise kernels (VERDICT r01 "weak" #1).
+
+Two input scales per case:
+  * 0.25 (the scale of the golden fixtures): |out| < 2, one bf16 ulp <= 0.0078 — the north star's max-abs <= 2e-2 against the
+    reference's bf16 output is asserted;
+  * 1.0 (unit normal, SURVEY §8d's synthetic inputs): |out| reaches 4-8 where ONE bf16 ulp is 0.03-0.06, so 2e-2 is below the
+    resolution of the output format; there the assertion is that the product is as close to the fp32 truth as the reference's
+    bf16 path is (max-abs and RMS within 1.25x), and the max-abs against the reference bf16 output is printed for the record.
+"""
+import pytest
+import torch
+
+from oracle import block as oblock
+from oracle import workload as owork
+
+pytestmark = pytest.mark.gpu
+TXT_LEN = 58
+TOL = 2e-2
+
+# (name, model, token grid, shared, is_last, shifted)
+CASES = [
+    ("3b_c1_sep_win", "3b", (1, 128, 128), False, False, False),
+    ("3b_c1_shared_swin", "3b", (1, 128, 128), True, False, True),
+    ("3b_c1_last_swin", "3b", (1, 128, 128), True, True, True),
+    ("3b_1080p33f_sep_swin", "3b", (9, 68, 120), False, False, True),
+    ("3b_c2_shared_win", "3b", (9, 90, 160), True, False, False),
+    ("7b_c3r_win", "7b", (6, 68, 120), False, False, False),
+    ("7b_c3r_swin", "7b", (6, 68, 120), False, False, True),
+    ("7b_c4_win", "7b", (10, 135, 240), False, False, False),
+]
+
+
+def _product_block(svr2, cfg, params, dev):
+    method = "720pswin_by_size_bysize" if cfg.shifted else "720pwin_by_size_bysize"
+    common = dict(vid_dim=cfg.dim, txt_dim=cfg.dim, emb_dim=6 * cfg.dim, heads=cfg.heads, head_dim=128, expand_ratio=4,
+                  norm=None, norm_eps=1e-5, ada=None, qk_bias=False, qk_norm=None, window=(4, 3, 3), window_method=method)
+    with torch.device("meta"):
+        if cfg.model == "3b":
+            blk = svr2.NaMMSRTransformerBlockB200(**common, mlp_type="swiglu", shared_weights=cfg.shared, rope_type="mmrope3d",
+                                                  rope_dim=128, is_last_layer=cfg.is_last)
+        else:
+            blk = svr2.NaMMSRTransformerBlockB200_7B(**common, qk_rope=True, shared_qkv=False, shared_mlp=False, mlp_type="normal")
+    sd = {k: (v.float() if k.endswith("freqs") else v.bfloat16()).to(dev) for k, v in params.items()}
+    blk.load_state_dict(sd, strict=True, assign=True)       # the loader's path: meta construction + assign (model_loader.py:809)
+    return blk
+
+
+def _stats(a, b):
+    d = (a.float() - b.float())
+    return float(d.abs().max()), float(d.pow(2).mean().sqrt())
+
+
+@pytest.mark.parametrize("case", CASES, ids=lambda c: c[0])
+def test_fullwidth_block_vs_reference_path_on_gpu(svr2, cuda, case):
+    name, model, grid, shared, is_last, shifted = case
+    cfg = owork.block_cfg(model, shared=shared, shifted=shifted)
+    cfg.is_last = is_last
+    params = owork.block_params(cfg, seed=3)
+    if is_last:       # vid_only MMModules of the last 3B layer hold no text parameters; shared layers use ".all" anyway
+        assert cfg.shared
+    blk = _product_block(svr2, cfg, params, cuda)
+    p16 = {k: (v.float() if k.endswith("freqs") else v.bfloat16()).to(cuda) for k, v in params.items()}
+    p32 = {k: v.float() for k, v in p16.items()}            # the SAME (bf16-representable) weights in fp32
+    vid_shape = torch.tensor([list(grid)])
+    txt_shape = torch.tensor([[TXT_LEN]])
+    for scale in (0.25, 1.0):
+        vid, txt, emb = owork.block_inputs(cfg, grid, TXT_LEN, seed=5)
+        vid, txt, emb = (vid * scale).bfloat16().to(cuda), (txt * scale).bfloat16().to(cuda), (emb * scale * 2).bfloat16().to(cuda)
+        with torch.no_grad():
+            v, t, _, _ = blk(vid=vid, txt=txt, vid_shape=vid_shape, txt_shape=txt_shape, emb=emb, cache=None)
+            rv16, rt16 = oblock.block_forward(cfg, p16, vid, txt, grid, emb)
+            rv32, rt32 = oblock.block_forward(cfg, p32, vid.float(), txt.float(), grid, emb.float())
+        torch.cuda.synchronize()
+        d_v, _ = _stats(v, rv16)
+        d_t, _ = _stats(t, rt16)
+        e_v, e_v_rms = _stats(v, rv32)
+        r_v, r_v_rms = _stats(rv16, rv32)
+        e_t, e_t_rms = _stats(t, rt32)
+        r_t, r_t_rms = _stats(rt16, rt32)
+        amax = float(rv32.abs().max())
+        print(f"\n{name} scale {scale}: |out|max {amax:.2f} | vs reference-bf16: vid {d_v:.4f} txt {d_t:.4f} | vs fp32: ours vid {e_v:.4f} "
+              f"(rms {e_v_rms:.5f}) txt {e_t:.4f} ; reference-bf16 vid {r_v:.4f} (rms {r_v_rms:.5f}) txt {r_t:.4f}")
+        if scale == 0.25:
+            assert d_v <= TOL and d_t <= TOL, f"{name}: block output exceeds 2e-2 against the reference's bf16 path"
+        # at both scales: no further from the truth than the reference's own bf16 path (25 % slack for rounding luck)
+        assert e_v <= 1.25 * r_v + 1e-3 and e_v_rms <= 1.25 * r_v_rms + 1e-5, f"{name}: video rows further from fp32 than the reference"
+        assert e_t <= 1.25 * r_t + 1e-3 and e_t_rms <= 1.25 * r_t_rms + 1e-5, f"{name}: text rows further from fp32 than the reference"
+        del v, t, rv16, rt16, rv32, rt32
+        torch.cuda.empty_cache()
+
+
+@pytest.mark.parametrize("model,grid,shifted", [("3b", (1, 128, 128), False), ("3b", (9, 90, 160), True), ("3b", (9, 68, 120), False),
+                                                ("7b", (31, 68, 120), False), ("7b", (10, 135, 240), True)],
+                         ids=["3b_c1_win", "3b_c2_swin", "3b_1080p33f_win", "7b_c3_win", "7b_c4_swin"])
+def test_fullwidth_attention_core_vs_fp32_sdpa(svr2, cuda, model, grid, shifted):
+    """proj_qkv -> q/k RMSNorm + RoPE + window gather -> varlen attention -> window reverse + text mean at 20 / 24 heads on the
+    BASELINE grids, against the oracle's per-window SDPA in fp32 AND in bf16 on the GPU (replaces round 1's property-only
+    check of the full-size attention against the repo's own mma.sync comparator)."""
+    cfg = owork.block_cfg(model, shared=False, shifted=shifted)
+    params = owork.block_params(cfg, seed=7)
+    blk = _product_block(svr2, cfg, params, cuda)
+    p16 = {k: (v.float() if k.endswith("freqs") else v.bfloat16()).to(cuda) for k, v in params.items()}
+    p32 = {k: v.float() for k, v in p16.items()}
+    vid, txt, _ = owork.block_inputs(cfg, grid, TXT_LEN, seed=9)
+    vid, txt = vid.bfloat16().to(cuda), txt.bfloat16().to(cuda)
+    plan = svr2.get_plan(grid, (4, 3, 3), shifted, TXT_LEN)
+    with torch.no_grad():
+        ov, ot = blk.attn.core(vid, txt, plan)
+        rv16, rt16 = oblock.window_attention(cfg, p16, vid, txt, grid)
+        rv32, rt32 = oblock.window_attention(cfg, p32, vid.float(), txt.float(), grid)
+    torch.cuda.synchronize()
+    d_v, _ = _stats(ov, rv16)
+    d_t, _ = _stats(ot, rt16)
+    e_v, e_rms = _stats(ov, rv32)
+    r_v, r_rms = _stats(rv16, rv32)
+    e_t, _ = _stats(ot, rt32)
+    print(f"\n{model} {grid} shifted={shifted}: attention core vs reference-bf16 vid {d_v:.4f} txt {d_t:.4f} | vs fp32 ours {e_v:.4f} "
+          f"(rms {e_rms:.5f}) txt {e_t:.4f}; reference-bf16 {r_v:.4f} (rms {r_rms:.5f}); |out|max {float(rv32.abs().max()):.2f}")
+    assert e_v <= TOL and e_t <= TOL, "attention core exceeds 2e-2 against fp32 per-window SDPA"
+    assert d_v <= TOL and d_t <= TOL, "attention core exceeds 2e-2 against the reference's bf16 per-window SDPA"
+    assert e_rms <= 1.25 * r_rms + 1e-5

@@ -38,6 +38,31 @@ def test_preloaded_chunks(svr2):
     assert [segments.padded_batch_frames(n) for n in (1, 2, 5, 19, 20, 21, 33)] == [1, 5, 5, 21, 21, 21, 33]
 
 
+@pytest.mark.parametrize("total,bs,ov", [(232, 33, 4), (120, 33, 4), (116, 33, 4), (62, 33, 4), (33, 33, 4), (29, 33, 4), (121, 33, 4),
+                                         (121, 121, 4), (37, 33, 4), (38, 33, 4), (10, 5, 0), (10, 4, 4), (10, 4, 7), (0, 33, 4), (1, 33, 4)])
+def test_batch_ranges_match_oracle(svr2, total, bs, ov):
+    from seedvr2_b200 import segments
+    got = segments.batch_ranges(total, bs, ov)
+    assert got == partition.batch_ranges(total, bs, ov)
+    if total:
+        assert got[0][0] == 0 and got[-1][1] == total
+        assert all(b - a <= bs for a, b in got)
+
+
+def test_stream_workload_is_balanced(svr2):
+    """bench.py's default job: 232 frames at 1080p, batch_size 33, overlap 4 — the reference's own split arithmetic gives every
+    rank the same number of 33-frame forwards at 1, 2, 4 and 8 ranks (the last batch of the last rank holds 29 frames)."""
+    from seedvr2_b200 import segments
+    for n in (1, 2, 4, 8):
+        per_rank = []
+        for (a, b) in segments.segment_ranges(232, n, 4):
+            bt = segments.batch_ranges(b - a, 33, 4)
+            per_rank.append([segments.latent_frames(e - s) for s, e in bt])
+        assert all(len(x) == 8 // n for x in per_rank), per_rank
+        assert sorted(set(sum(per_rank, []))) == [8, 9]
+    assert [segments.latent_frames(f) for f in (1, 5, 21, 29, 33, 121)] == [1, 2, 6, 8, 9, 31]
+
+
 def _worker(rank, world, port, lens, overlap, out_path):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     dist.init_process_group("gloo", rank=rank, world_size=world)
