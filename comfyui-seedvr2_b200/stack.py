@@ -198,6 +198,15 @@ class GraphedForward:
         with torch.cuda.graph(self.graph), torch.no_grad():
             self.out = stack.forward(self.vid, self.txt, None, self.txt_shape, self.timestep, grid=self.grid)
         self.launches_per_replay = ops.launch_count() - n0      # kernels of libseedvr2_b200.so inside the graph
+        # The graph holds RAW device pointers of everything the forward resolved at capture time.  The window plans sit in an
+        # LRU (plan._PLANS) and the bf16 copies of non-bf16 parameters in block._cast_cache; either can drop its entry while
+        # this graph is still replayed, so the graph keeps its own strong references (a replay after ~32 other
+        # grids read recycled memory).
+        from .block import _cast_cache
+        from .plan import get_plan
+        tok = (T2, H2 // stack.patch[1], W2 // stack.patch[2])
+        self._plans = [get_plan(tok, c["window"], shifted, txt_len) for shifted in (False, True)]
+        self._casts = [entry[4] for entry in _cast_cache.values()]
 
     def replay(self) -> torch.Tensor:
         from . import ops

@@ -123,6 +123,8 @@ def test_fullwidth_attention_core_vs_fp32_sdpa(svr2, cuda, model, grid, shifted)
     e_t, _ = _stats(ot, rt32)
     print(f"\n{model} {grid} shifted={shifted}: attention core vs reference-bf16 vid {d_v:.4f} txt {d_t:.4f} | vs fp32 ours {e_v:.4f} "
           f"(rms {e_rms:.5f}) txt {e_t:.4f}; reference-bf16 {r_v:.4f} (rms {r_rms:.5f}); |out|max {float(rv32.abs().max()):.2f}")
-    assert e_v <= TOL and e_t <= TOL, "attention core exceeds 2e-2 against fp32 per-window SDPA"
+    # 3B: within 2e-2 of the fp32 truth.  7B rounds its RoPE angles to bf16 (dit_7b/rope.py:85), which moves the reference's OWN
+    # bf16 result 0.1-0.3 away from fp32 at these grids; there the bound is the reference's own distance.
+    assert e_v <= max(TOL, 1.05 * r_v) and e_t <= TOL, "attention core further from fp32 per-window SDPA than the reference's bf16 path"
     assert d_v <= TOL and d_t <= TOL, "attention core exceeds 2e-2 against the reference's bf16 per-window SDPA"
     assert e_rms <= 1.25 * r_rms + 1e-5

@@ -43,6 +43,34 @@ def test_graph_replay_equals_eager(svr2, cuda, model, kw, grid):
         assert torch.equal(out, eager), f"trial {trial}: graph replay differs from the kernel-by-kernel forward"
 
 
+def test_graph_survives_plan_eviction(svr2, cuda):
+    """A captured forward holds raw pointers into its window plans' device tensors; the plan LRU (plan._PLANS, 64 entries) must
+    not be able to free them under a live graph.  Create > 64 other plans with device tensors, churn the allocator,
+    replay the first graph."""
+    import gc
+    from seedvr2_b200 import plan as planmod
+    st = _stack(svr2, cuda, "3b", num_layers=2, vid_dim=256, heads=2, mm_layers=1, txt_in_dim=64)
+    grid, txt_len = (2, 24, 40), 58
+    g = torch.Generator(device="cpu").manual_seed(11)
+    gf = st.graph_for(grid, txt_len, cuda)
+    gf.vid.copy_(torch.randn(grid[0] * grid[1] * grid[2], 33, generator=g).bfloat16().to(cuda))
+    gf.txt.copy_(torch.randn(txt_len, 64, generator=g).bfloat16().to(cuda))
+    gf.timestep.fill_(1000.0)
+    want = gf.replay().clone()
+    torch.cuda.synchronize()
+    for i in range(planmod._PLAN_CAP + 8):
+        p = planmod.get_plan((1, 10 + i, 12), (4, 3, 3), bool(i & 1), txt_len)
+        p.row_map(cuda)
+    assert (grid[0], grid[1] // 2, grid[2] // 2) not in [k[0] for k in planmod._PLANS], "the test did not evict the graph's plans"
+    gc.collect()
+    torch.cuda.empty_cache()
+    junk = [torch.full((1 << 18,), 7, dtype=torch.int32, device=cuda) for _ in range(64)]      # recycle freed blocks
+    got = gf.replay().clone()
+    torch.cuda.synchronize()
+    del junk
+    assert torch.equal(got, want)
+
+
 def test_forward_host_round_trip(svr2, cuda):
     """forward_host: pinned host buffers in, pinned host buffer out, graphed and not, same bits."""
     st = _stack(svr2, cuda, "3b", num_layers=2, vid_dim=256, heads=2, mm_layers=1, txt_in_dim=64)
