@@ -563,13 +563,13 @@ def run_ours(args):
     # ---- tcgen05 GEMMs (csrc/gemm.cu): algorithmic FLOPs of the block linears of one step / their summed launch time
     mlp = 3 * D * 6912 if model == "3b" else 2 * D * 4 * D
     lin_flops = sum(layers * (tokens_of(g) + TXT_LEN) * 2 * (4 * D * D + mlp) for g in job.grids)
-    gemm_names = ("svr2_linear_fwd", "svr2_linear_swiglu_fwd", "svr2_linear_gate_residual_fwd")
+    gemm_names = ("svr2_linear_fwd", "svr2_linear_swiglu_fwd", "svr2_linear_gate_residual_fwd", "svr2_linear_qkv_pack_fwd")
     gemm_ms = sum(per_kernel.get(n, (0, 0.0))[1] for n in gemm_names)
     gemm_n = sum(per_kernel.get(n, (0, 0.0))[0] for n in gemm_names)
     gemm = None
     if gemm_n:
         gtf = lin_flops / (gemm_ms * 1e-3) / 1e12
-        gemm = {"kernel": "svr2_linear_fwd / _swiglu_fwd / _gate_residual_fwd (linear_tc_kernel: CTA pairs, tcgen05.mma.cta_group::2, "
+        gemm = {"kernel": "svr2_linear_qkv_pack_fwd / _swiglu_fwd / _gate_residual_fwd / svr2_linear_fwd (linear_tc_kernel: CTA pairs, tcgen05.mma.cta_group::2, "
                           "TMA ring, double-buffered TMEM accumulator, fused epilogues)", "bound": "tensor", "achieved": gtf,
                 "peak": pk["bf16_tflops_sustained"], "unit": "TFLOP/s", "frac": gtf / pk["bf16_tflops_sustained"],
                 "frac_of_burst_peak": gtf / pk["bf16_tflops"], "algorithmic_flops_per_step": lin_flops, "ms_per_step": gemm_ms,

@@ -34,6 +34,11 @@ SIGNATURES = {
     "svr2_linear_fwd": (c_int, [c_void_p] * 4 + [c_int64, c_int, c_int, c_int, c_void_p]),
     "svr2_linear_swiglu_fwd": (c_int, [c_void_p] * 4 + [c_int64, c_int, c_int, c_void_p]),
     "svr2_linear_gate_residual_fwd": (c_int, [c_void_p] * 5 + [c_int, c_void_p, c_void_p, c_int64, c_int, c_int, c_void_p]),
+    "svr2_linear_qkv_pack_fwd": (c_int, [c_void_p, c_void_p, c_int64, c_int, c_int, c_void_p, c_void_p, c_int, c_int] + [c_void_p] * 4 +
+                                 [c_float] + [c_void_p] * 5),
+    "svr2_rope_plan": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int64, c_int, c_void_p, c_int, c_void_p, c_int,
+                               c_void_p, c_void_p, c_void_p]),
+    "svr2_txt_replicate_fwd": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p]),
     "svr2_window_attn_fwd_noalloc": (c_int, [c_void_p] * 5 + [c_int] * 7 + [c_int64, c_void_p, c_void_p, c_void_p]),
     "svr2_debug_attn_trace": (c_int, [c_void_p, c_int]),
     "svr2_txt_pool_fwd": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
@@ -43,7 +48,7 @@ SIGNATURES = {
     "svr2_v_lerp_endpoint_fwd": (c_int, [c_void_p, c_void_p, c_float, c_float, c_void_p, c_int64, c_void_p]),
 }
 
-ABI_VERSION = 4      # svr2_abi_version() of the library these SIGNATURES describe
+ABI_VERSION = 5      # svr2_abi_version() of the library these SIGNATURES describe
 _lib = None
 
 

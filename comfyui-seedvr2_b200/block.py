@@ -29,6 +29,9 @@ _SHIFTED = {"720pwin_by_size_bysize": False, "720pswin_by_size_bysize": True}
 # epilogue.  USE_TC_GEMM = False restores round 1's library GEMMs (cuBLAS through torch) + separate elementwise kernels — kept
 # ONLY so bench.py can time both arms in one process; it is still all-CUDA and never the default.
 USE_TC_GEMM = os.environ.get("SVR2_LIBRARY_GEMM", "0") != "1"
+# proj_qkv + q/k RMSNorm + RoPE + window partition as ONE kernel (svr2_linear_qkv_pack_fwd).  SVR2_UNFUSED_QKV=1 restores
+# svr2_linear_fwd + svr2_qkv_pack_fwd (same results; kept for A/B timing and for configurations the fused epilogue does not cover).
+USE_FUSED_QKV = os.environ.get("SVR2_UNFUSED_QKV", "0") != "1"
 
 
 def _linear(x, w, b=None):
@@ -234,8 +237,38 @@ class NaSwinAttentionB200(nn.Module):
         self.norm_k = _Slot(lambda: _Weight(head_dim), shared_qknorm)
         self.rope = _Rope(rope_kind, head_dim) if rope_kind != ops.ROPE_NONE else None
 
+    def _freqs(self):
+        """(fp32 frequencies on the device, their values as a tuple — read ONCE per buffer: the only host sync of the fused path)."""
+        f = self.rope.rope.freqs
+        memo = self.__dict__.get("_freqs_memo")
+        if memo is None or memo[0] is not f or memo[1] != f._version or memo[2] != f.data_ptr():
+            f32 = f if f.dtype == torch.float32 else f.float()
+            memo = (f, f._version, f.data_ptr(), f32, tuple(float(v) for v in f32.tolist()))
+            self.__dict__["_freqs_memo"] = memo
+        return memo[3], memo[4]
+
     def core(self, vid: torch.Tensor, txt: torch.Tensor, plan: WindowPlan):
         """proj_qkv -> pack (norm+rope+partition) -> window attention; returns attention outputs BEFORE proj_out."""
+        if USE_TC_GEMM and USE_FUSED_QKV and vid.is_cuda:
+            if self.rope is not None:
+                (freqs, fkey), kind = self._freqs(), self.rope.kind
+            else:
+                freqs, fkey, kind = None, (), ops.ROPE_NONE
+            if ops.qkv_fused_supported(plan, kind, len(fkey), self.heads):
+                # ONE GEMM per weight set whose epilogue normalises, rotates and scatters q, k, v into the packed window layout
+                nw = (_bf16(self.norm_q.pick("vid").weight), _bf16(self.norm_k.pick("vid").weight),
+                      _bf16(self.norm_q.pick("txt").weight), _bf16(self.norm_k.pick("txt").weight))
+                both = _joined(vid, txt) if self.proj_qkv.shared_weights else None
+                if both is not None:
+                    bufs = ops.linear_qkv_pack(plan, both, _bf16(self.proj_qkv.all.weight), 0, *nw, freqs, fkey, kind, self.heads, self.eps)
+                else:
+                    bufs = ops.linear_qkv_pack(plan, vid.contiguous(), _bf16(self.proj_qkv.pick("vid").weight), 0, *nw, freqs, fkey,
+                                               kind, self.heads, self.eps)
+                    bufs = ops.linear_qkv_pack(plan, txt.contiguous(), _bf16(self.proj_qkv.pick("txt").weight), plan.n_tokens, *nw,
+                                               freqs, fkey, kind, self.heads, self.eps, out=bufs)
+                q, k, v, tq = bufs
+                ops.replicate_text(plan, tq, q, k, v, self.heads)
+                return ops.window_attn(plan, q, k, v, self.heads)
         both = _joined(vid, txt) if self.proj_qkv.shared_weights else None
         if both is not None:
             qkv = _linear(both, self.proj_qkv.all.weight)

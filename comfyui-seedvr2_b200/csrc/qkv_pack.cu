@@ -231,7 +231,109 @@ __global__ void pack_rowmap_kernel(const int32_t* __restrict__ tab, int n_window
     row_map[row] = m;
 }
 
+// ---- per-plan tables of the fused projection (svr2_linear_qkv_pack_fwd, gemm.cu) ---------------------------------------------
+// Rope table: one row of n_freqs (cos, sin) pairs per distinct POSITION VALUE of the plan, computed by the very code path of
+// rope_pair() above so both qkv paths rotate by identical bits.  3B: row r = position r (video: Lt + t, h, w; text row j: j for
+// all three axes).  7B: row base_of_n[n] + idx = linspace(-1, 1, n)[idx] for every window extent n that occurs in the plan.
+__global__ void rope_table_kernel(int rope_kind, const float* __restrict__ freqs, int n_freqs, int rows,
+                                  const int32_t* __restrict__ base_of_n, float2* __restrict__ out) {
+    const int e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= rows * n_freqs) return;
+    const int r = e / n_freqs, fi = e - r * n_freqs;
+    const float f = __ldg(freqs + fi);
+    float c, sn;
+    if (rope_kind == SVR2_ROPE_3B_MM) {
+        const float ang = __fmul_rn((float)r, f);
+        c = cosf(ang);
+        sn = sinf(ang);
+    } else {
+        int n = 1, idx = 0;
+        for (int k = 1; k <= 64; ++k) {
+            const int b = __ldg(base_of_n + k);
+            if (b >= 0 && r >= b && r < b + k) { n = k; idx = r - b; }
+        }
+        const float ang = bf16r(__fmul_rn(torch_linspace_m1_p1(idx, n), f));
+        c = bf16r(cosf(ang));
+        sn = bf16r(sinf(ang));
+    }
+    out[e] = make_float2(c, sn);
+}
+
+// Token map: the inverse of the packed-row map.  tok_map[token] = (packed row, table row of axis t, h, w); the text rows follow
+// the L video tokens: tok_map[L + j] = (-(1 + j), j, j, j) (3B) or (-(1 + j), -1, -1, -1) (7B / no rope: text is not rotated).
+__global__ void tok_map_kernel(const int32_t* __restrict__ tab, const int4* __restrict__ row_map, int64_t P, int64_t L,
+                               int txt_len, int rope_kind, const int32_t* __restrict__ base_of_n, int4* __restrict__ tok_map) {
+    const int64_t row = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (row >= P) return;
+    const int4 m = __ldg(row_map + row);
+    if (m.x < 0) {
+        if (m.w != 0) return;           // every window repeats the text rows; window 0 writes their entries
+        const int j = -(m.x + 1);
+        const int r = rope_kind == SVR2_ROPE_3B_MM ? j : -1;
+        tok_map[L + j] = make_int4(-(1 + j), r, r, r);
+        return;
+    }
+    const int lt = m.y & 0xffff, lh = (m.y >> 16) & 0xffff, lw = m.z;
+    int4 o = make_int4((int)row, -1, -1, -1);
+    if (rope_kind == SVR2_ROPE_3B_MM) {
+        o.y = txt_len + lt; o.z = lh; o.w = lw;
+    } else if (rope_kind == SVR2_ROPE_7B_PIX) {
+        const int32_t* t = tab + m.w * SVR2_WIN_FIELDS;
+        o.y = __ldg(base_of_n + __ldg(t + 3)) + lt;
+        o.z = __ldg(base_of_n + __ldg(t + 4)) + lh;
+        o.w = __ldg(base_of_n + __ldg(t + 5)) + lw;
+    }
+    tok_map[m.x] = o;
+}
+
+// Text rows of q, k, v (normalised + rotated once by the projection's epilogue) copied into every window's sequence
+// (mmattn.py:223-236 repeats them per window; concat_win puts them after the window's video rows).
+__global__ void txt_replicate_kernel(const uint4* __restrict__ txt_qkv, const int32_t* __restrict__ tab, int txt_len, int heads,
+                                     uint4* __restrict__ qp, uint4* __restrict__ kp, uint4* __restrict__ vp) {
+    const int w = blockIdx.x / txt_len, j = blockIdx.x - w * txt_len;
+    const int32_t* t = tab + w * SVR2_WIN_FIELDS;
+    const int64_t drow = (int64_t)__ldg(t + 6) + __ldg(t + 7) + j;       // row_start + n_vid + j
+    const int per_kind = heads * (SVR2_HEAD_DIM * 2 / 16);                  // uint4 per (row, kind)
+    for (int i = threadIdx.x; i < 3 * per_kind; i += blockDim.x) {
+        const int kind = i / per_kind, c = i - kind * per_kind;
+        uint4* dst = kind == 0 ? qp : (kind == 1 ? kp : vp);
+        dst[drow * per_kind + c] = __ldg(txt_qkv + ((int64_t)j * 3 + kind) * per_kind + c);
+    }
+}
+
 }  // namespace svr2
+
+extern "C" int svr2_rope_plan(const int32_t* win_table, const int32_t* row_map, int n_windows, int T, int H, int W, int txt_len,
+                              int64_t P, int rope_kind, const float* freqs, int n_freqs, const int32_t* base_of_n, int rope_rows,
+                              int32_t* tok_map, float* rope_cs, void* stream) {
+    SVR2_CHECK_ARG(win_table && row_map && tok_map && n_windows > 0 && P > 0 && P < ((int64_t)1 << 31), "svr2_rope_plan: bad arguments");
+    SVR2_CHECK_ARG(rope_kind == SVR2_ROPE_NONE || rope_kind == SVR2_ROPE_3B_MM || rope_kind == SVR2_ROPE_7B_PIX,
+                   "svr2_rope_plan: unknown rope_kind %d", rope_kind);
+    SVR2_CHECK_ARG(rope_kind == SVR2_ROPE_NONE || (freqs && rope_cs && n_freqs > 0 && rope_rows > 0), "svr2_rope_plan: rope inputs missing");
+    SVR2_CHECK_ARG(rope_kind != SVR2_ROPE_7B_PIX || base_of_n, "svr2_rope_plan: the 7B table needs base_of_n[65]");
+    const int64_t L = (int64_t)T * H * W;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (rope_kind != SVR2_ROPE_NONE) {
+        const int n = rope_rows * n_freqs;
+        svr2::rope_table_kernel<<<(n + 255) / 256, 256, 0, st>>>(rope_kind, freqs, n_freqs, rope_rows, base_of_n, (float2*)rope_cs);
+        SVR2_CHECK_LAUNCH("svr2_rope_plan(table)");
+    }
+    svr2::tok_map_kernel<<<(unsigned)((P + 255) / 256), 256, 0, st>>>(win_table, (const int4*)row_map, P, L, txt_len, rope_kind,
+                                                                      base_of_n, (int4*)tok_map);
+    SVR2_CHECK_LAUNCH("svr2_rope_plan(token map)");
+    return SVR2_OK;
+}
+
+extern "C" int svr2_txt_replicate_fwd(const void* txt_qkv, const int32_t* win_table, int n_windows, int txt_len, int heads,
+                                      void* q_pack, void* k_pack, void* v_pack, void* stream) {
+    SVR2_CHECK_ARG(win_table && q_pack && k_pack && v_pack && n_windows > 0 && heads > 0 && txt_len >= 0, "svr2_txt_replicate_fwd: bad arguments");
+    if (txt_len == 0) return SVR2_OK;
+    SVR2_CHECK_ARG(txt_qkv, "svr2_txt_replicate_fwd: null pointer");
+    svr2::txt_replicate_kernel<<<(unsigned)(n_windows * txt_len), 256, 0, (cudaStream_t)stream>>>(
+        (const uint4*)txt_qkv, win_table, txt_len, heads, (uint4*)q_pack, (uint4*)k_pack, (uint4*)v_pack);
+    SVR2_CHECK_LAUNCH("svr2_txt_replicate_fwd");
+    return SVR2_OK;
+}
 
 extern "C" int svr2_pack_rowmap(const int32_t* win_table, int n_windows, int T, int H, int W, int txt_len, int32_t* row_map,
                                 int64_t P, void* stream) {

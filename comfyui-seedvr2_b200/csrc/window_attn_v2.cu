@@ -30,6 +30,14 @@
 // The two query tiles ping-pong: while one group runs its exp2 burst the tensor core works for the other tile.
 // The last key tile of a sequence is trimmed to a multiple of 32 columns (MMA N / K steps and the softmax shrink with it).
 //
+// Generation 10 = the same kernel instantiated with HALVES = 2 (24 warps): TWO threads per query row, each owning 64 of the key
+// tile's 128 columns (softmax warps 8-15 take columns [0,64), warps 16-23 columns [64,128) of the same rows).  Every generation
+// up to 9 ran two softmax warps per scheduler, each a long dependent chain (~770 warp-instructions per step at IPC 0.25 —
+// latency bound, run 54), and a third warp could not fit in registers next to two 128-column rows.  A half row needs ~100
+// registers, so four softmax warps share a scheduler and hide each other's latencies.  The two halves of a row exchange their
+// partial row max through shared memory (one 64-thread named barrier per step); their partial row sums are only added by the
+// epilogue.  P(j) written by the upper half aliases S columns the lower half has already loaded (the exchange barrier orders it).
+//
 // TMEM map (columns): S0 [0,128)  S1 [128,256)  O0 [256,384)  O1 [384,512);  P_i aliases the first 64 columns of S_i.
 // SMEM map: Q0 | Q1 | ring[4] | staging (32 KB each) | row sums l[2][2][128] | mbarriers.
 #include <cuda.h>
@@ -51,19 +59,22 @@ constexpr int BM = 128, BN = 128;
 constexpr int TILE_BYTES = BM * D * 2;    // 32768
 constexpr int BOX_BYTES = TILE_BYTES / 2; // 128 rows x 64 cols bf16
 constexpr int STAGES = 4;
-constexpr int NTHREADS = 512;
+constexpr int NTHREADS = 512;             // generation 4; generation 10 adds 8 softmax warps (768)
 #ifndef SVR2_REGS_C      // experiment builds: -DSVR2_REGS_C=.. -DSVR2_REGS_E=.. -DSVR2_REGS_S=..  (nvcc splits -D values at commas)
 #define SVR2_REGS_C 56     // run 60/61: 56/56/200 (no spills) is 2.6 % faster at C2 than 72/72/184; 48/64/200 and 40/72/200 spill and lose
 #define SVR2_REGS_E 56
 #define SVR2_REGS_S 200
 #endif
 constexpr int kRegs[3] = {SVR2_REGS_C, SVR2_REGS_E, SVR2_REGS_S};
-constexpr int REGS_CTRL = kRegs[0], REGS_EPI = kRegs[1], REGS_SOFTMAX = kRegs[2];   // per sub-partition: 32 * (C + E + 2 S) = 16384
+// per sub-partition: 32 * (C + E + 2 S) = 16384
+constexpr int kRegs10[3] = {48, 48, 104};                // generation 10: per sub-partition 32 * (C + E + 4 S) = 16384
 constexpr int OFF_RING = 2 * TILE_BYTES;
 constexpr int OFF_STAGE = OFF_RING + STAGES * TILE_BYTES;
-constexpr int OFF_L = OFF_STAGE + TILE_BYTES;          // float l[2 parities][2 tiles][128 rows]
-constexpr int OFF_BAR = OFF_L + 2 * 2 * 128 * 4;
-constexpr int SMEM_BYTES = OFF_BAR + 256;              // 231,680 B of the 232,448 B a CTA may opt in to
+constexpr int STAGE_BYTES = BM * 128;                  // epilogue staging: 128 rows x 64 columns, two passes per tile
+constexpr int OFF_L = OFF_STAGE + STAGE_BYTES;         // float l[2 parities][2 tiles][2 halves][128 rows]
+constexpr int OFF_XCH = OFF_L + 2 * 2 * 2 * 128 * 4;   // float partial row max [2 tiles][2 halves][128 rows] (generation 10)
+constexpr int OFF_BAR = OFF_XCH + 2 * 2 * 128 * 4;
+constexpr int SMEM_BYTES = OFF_BAR + 256;              // 219,392 B of the 232,448 B a CTA may opt in to
 constexpr uint32_t TMEM_COLS = 512;
 #ifndef SVR2_FMA8
 #define SVR2_FMA8 3
@@ -175,15 +186,18 @@ __device__ __forceinline__ void trace_item(const Params& p, int n, int what) {
     }
 }
 
-template <bool kTrace>
-__global__ void __launch_bounds__(NTHREADS, 1)
+template <bool kTrace, int HALVES>
+__global__ void __launch_bounds__(NTHREADS + 256 * (HALVES - 1), 1)
 window_attn_tc2_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_k,
                        const __grid_constant__ CUtensorMap tm_v, const Params p) {
     extern __shared__ __align__(1024) unsigned char smem[];
     const uint32_t base = smem_u32(smem);                          // SWIZZLE_128B tiles need 1024-B alignment
     const uint32_t sRing = base + OFF_RING;
     const uint32_t sBar = base + OFF_BAR;
+    constexpr int REGS_CTRL = HALVES == 2 ? kRegs10[0] : kRegs[0], REGS_EPI = HALVES == 2 ? kRegs10[1] : kRegs[1],
+                  REGS_SOFTMAX = HALVES == 2 ? kRegs10[2] : kRegs[2];
     float* l_buf = reinterpret_cast<float*>(smem + OFF_L);
+    float* xch = reinterpret_cast<float*>(smem + OFF_XCH);
     volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(smem + OFF_BAR + BAR_COUNT * 8);
     volatile uint32_t* turn_cnt = reinterpret_cast<volatile uint32_t*>(smem + OFF_BAR + 248);   // softmax steps finished, x4 warps, per group
     auto bar = [&](int slot) { return sBar + 8u * (uint32_t)slot; };
@@ -200,11 +214,11 @@ window_attn_tc2_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
             mbar_init(bar(BAR_QFULL + i), 1);
             mbar_init(bar(BAR_QEMPTY + i), 1);
             mbar_init(bar(BAR_SFULL + i), 1);
-            mbar_init(bar(BAR_PREADY + i), 128);
+            mbar_init(bar(BAR_PREADY + i), 128 * HALVES);
             mbar_init(bar(BAR_OFINAL + i), 1);
             mbar_init(bar(BAR_OEMPTY + i), 128);
-            mbar_init(bar(BAR_LREADY + i), 128);
-            mbar_init(bar(BAR_SLOADED + i), 128);
+            mbar_init(bar(BAR_LREADY + i), 128 * HALVES);
+            mbar_init(bar(BAR_SLOADED + i), 128 * HALVES);
         }
         for (int s = 0; s < STAGES; ++s) {
             mbar_init(bar(BAR_KVFULL + s), 1);
@@ -392,27 +406,8 @@ window_attn_tc2_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
                 OTHER_WAIT(bar(BAR_OFINAL + i), cc & 1);
                 tc_fence_after();
                 if (threadIdx.x == 128 && i == 0) trace_item<kTrace>(p, n_it, 5);
-                const float inv = 1.0f / l_buf[((cc & 1) * 2 + i) * 128 + row];
-#pragma unroll 1
-                for (int c4 = 0; c4 < 4; ++c4) {
-                    uint32_t ov[32];
-                    tmem_ld32(tO + c4 * 32, ov);
-                    tc_wait_ld();
-                    if (c4 == 3) {                                   // O_i is in registers: the next item may overwrite it
-                        tc_fence_before();
-                        mbar_arrive(bar(BAR_OEMPTY + i));
-                    }
-#pragma unroll
-                    for (int q = 0; q < 4; ++q) {
-                        uint4 u;
-                        u.x = pack2(__uint_as_float(ov[8 * q + 0]) * inv, __uint_as_float(ov[8 * q + 1]) * inv);
-                        u.y = pack2(__uint_as_float(ov[8 * q + 2]) * inv, __uint_as_float(ov[8 * q + 3]) * inv);
-                        u.z = pack2(__uint_as_float(ov[8 * q + 4]) * inv, __uint_as_float(ov[8 * q + 5]) * inv);
-                        u.w = pack2(__uint_as_float(ov[8 * q + 6]) * inv, __uint_as_float(ov[8 * q + 7]) * inv);
-                        const int ch = c4 * 4 + q;
-                        *reinterpret_cast<uint4*>(stage + row * 256 + (((ch & 8) | ((ch ^ row) & 7)) << 4)) = u;
-                    }
-                }
+                const float* lrow = l_buf + (((cc & 1) * 2 + i) * 2) * 128 + row;
+                const float inv = 1.0f / (HALVES == 2 ? lrow[0] + lrow[128] : lrow[0]);
                 // destination of my row: video rows go back to their original token (window reverse), text rows to the
                 // per-window text buffer that svr2_txt_pool_fwd averages
                 const int jrow = it.q0 + i * BM + row;
@@ -423,17 +418,41 @@ window_attn_tc2_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
                 } else if (jrow < it.seq) {
                     dst = (unsigned long long)(p.txt_part + ((int64_t)it.wi * p.txt_len + (jrow - it.w.n_vid)) * row_stride + it.head * D);
                 }
-                __syncwarp();
-                const int ch = lane & 15;
+                // two passes of 64 columns: registers -> swizzled 128-byte staging rows -> 128-byte row segments in HBM
+#pragma unroll 1
+                for (int hf = 0; hf < 2; ++hf) {
+#pragma unroll 1
+                    for (int c2 = 0; c2 < 2; ++c2) {
+                        uint32_t ov[32];
+                        tmem_ld32(tO + (hf * 2 + c2) * 32, ov);
+                        tc_wait_ld();
+                        if (hf == 1 && c2 == 1) {                        // O_i is in registers: the next item may overwrite it
+                            tc_fence_before();
+                            mbar_arrive(bar(BAR_OEMPTY + i));
+                        }
+#pragma unroll
+                        for (int q = 0; q < 4; ++q) {
+                            uint4 u;
+                            u.x = pack2(__uint_as_float(ov[8 * q + 0]) * inv, __uint_as_float(ov[8 * q + 1]) * inv);
+                            u.y = pack2(__uint_as_float(ov[8 * q + 2]) * inv, __uint_as_float(ov[8 * q + 3]) * inv);
+                            u.z = pack2(__uint_as_float(ov[8 * q + 4]) * inv, __uint_as_float(ov[8 * q + 5]) * inv);
+                            u.w = pack2(__uint_as_float(ov[8 * q + 6]) * inv, __uint_as_float(ov[8 * q + 7]) * inv);
+                            const int ch = c2 * 4 + q;
+                            *reinterpret_cast<uint4*>(stage + row * 128 + (((ch ^ row) & 7) << 4)) = u;
+                        }
+                    }
+                    __syncwarp();
+                    const int ch = lane & 7;
 #pragma unroll 4
-                for (int t = 0; t < 16; ++t) {
-                    const int rl = 2 * t + (lane >> 4);                // row (inside this warp's 32) served by my half-warp
-                    const unsigned long long d = __shfl_sync(0xffffffffu, dst, rl);
-                    const int r = quad * 32 + rl;
-                    const uint4 u = *reinterpret_cast<const uint4*>(stage + r * 256 + (((ch & 8) | ((ch ^ r) & 7)) << 4));
-                    if (d != 0ull) *reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(d) + ch * 8) = u;
+                    for (int t = 0; t < 8; ++t) {
+                        const int rl = 4 * t + (lane >> 3);              // row (inside this warp's 32) served by my quarter-warp
+                        const unsigned long long d = __shfl_sync(0xffffffffu, dst, rl);
+                        const int r = quad * 32 + rl;
+                        const uint4 u = *reinterpret_cast<const uint4*>(stage + r * 128 + (((ch ^ r) & 7) << 4));
+                        if (d != 0ull) *reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(d) + hf * 64 + ch * 8) = u;
+                    }
+                    __syncwarp();                                       // staging rows of this warp are free again
                 }
-                __syncwarp();                                           // staging rows of this warp are free again
                 if (threadIdx.x == 128) trace_item<kTrace>(p, n_it, 6 + i);
                 if (i) ++c1; else ++c0;
             }

@@ -214,6 +214,69 @@ def qkv_pack(plan: WindowPlan, qkv_vid: torch.Tensor, qkv_txt: torch.Tensor, wq_
     return q, k, v
 
 
+QKV_FUSED_MAX_ROPE_ENTRIES = 2048      # csrc/gemm.cu kMaxRopeEntries: (cos, sin) pairs of the rope table held in shared memory
+
+
+def qkv_fused_supported(plan: WindowPlan, rope_kind: int, n_freqs: int, heads: int) -> bool:
+    """Whether svr2_linear_qkv_pack_fwd covers this configuration (else: svr2_linear_fwd + svr2_qkv_pack_fwd, same results)."""
+    if heads % 2 or (rope_kind != ROPE_NONE and n_freqs not in (21, 10)):
+        return False
+    if rope_kind == ROPE_3B_MM:
+        t = plan.table
+        rows = max(plan.txt_len + int(t[:, 3].max()), int(t[:, 4].max()), int(t[:, 5].max()), plan.txt_len, 1)
+    elif rope_kind == ROPE_7B_PIX:
+        ns = set(int(v) for v in plan.table[:, 3:6].reshape(-1))
+        if max(ns) > 64:
+            return False
+        rows = sum(ns)
+    else:
+        rows = 0
+    return rows * max(n_freqs, 1) <= QKV_FUSED_MAX_ROPE_ENTRIES
+
+
+@torch._dynamo.disable
+def linear_qkv_pack(plan: WindowPlan, x: torch.Tensor, weight: torch.Tensor, row_offset: int, wq_vid, wk_vid, wq_txt, wk_txt,
+                    freqs: Optional[torch.Tensor], freqs_key: Tuple[float, ...], rope_kind: int, heads: int, eps: float,
+                    out: Optional[Tuple[torch.Tensor, ...]] = None):
+    """x [M, K] = rows [row_offset, row_offset + M) of the order (video tokens, then text tokens)  ->  (q, k, v, txt_qkv):
+    q, k, v packed [P, heads, 128] with the video rows of this call written, txt_qkv [Lt, 3, heads, 128] with its text rows
+    written.  Pass ``out`` to add a second call's rows (separate-weight layers: one call per branch) to the same buffers.
+    ``replicate_text`` must follow once all text rows are in."""
+    _need(x, "x")
+    M, K = x.shape
+    _need_weight(weight, "weight", K)
+    if weight.shape[0] != 3 * heads * 128:
+        raise RuntimeError(f"linear_qkv_pack: weight must be [{3 * heads * 128}, {K}]")
+    for n, t in (("wq_vid", wq_vid), ("wk_vid", wk_vid), ("wq_txt", wq_txt), ("wk_txt", wk_txt)):
+        _need(t, n)
+    if row_offset < 0 or row_offset + M > plan.n_tokens + plan.txt_len:
+        raise RuntimeError("linear_qkv_pack: rows out of range for the plan")
+    dev = x.device
+    if rope_kind != ROPE_NONE:
+        _need(freqs, "freqs", torch.float32)
+    tok_map, cs, rows = plan.rope_plan(dev, rope_kind, freqs_key if rope_kind != ROPE_NONE else (), freqs)
+    if out is None:
+        P = plan.packed_rows
+        q = torch.empty(P, heads, 128, dtype=torch.bfloat16, device=dev)
+        out = (q, torch.empty_like(q), torch.empty_like(q), torch.empty(plan.txt_len, 3, heads, 128, dtype=torch.bfloat16, device=dev))
+    q, k, v, tq = out
+    if M:
+        _call("svr2_linear_qkv_pack_fwd", 1, dev, _lib.lib().svr2_linear_qkv_pack_fwd, x.data_ptr(), weight.data_ptr(), M, K, heads,
+              tok_map.data_ptr() + 16 * row_offset, None if cs is None else cs.data_ptr(), rows,
+              len(freqs_key) if rope_kind != ROPE_NONE else 0, wq_vid.data_ptr(), wk_vid.data_ptr(), wq_txt.data_ptr(),
+              wk_txt.data_ptr(), float(eps), q.data_ptr(), k.data_ptr(), v.data_ptr(), tq.data_ptr(), _stream(x))
+    return out
+
+
+@torch._dynamo.disable
+def replicate_text(plan: WindowPlan, txt_qkv: torch.Tensor, q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, heads: int) -> None:
+    """Copies the text rows of q, k, v into every window's sequence (mmattn.py:223-236)."""
+    if plan.txt_len:
+        d = plan.on(q.device)
+        _call("svr2_txt_replicate_fwd", 1, q.device, _lib.lib().svr2_txt_replicate_fwd, txt_qkv.data_ptr(), d["table"].data_ptr(),
+              plan.n_windows, plan.txt_len, heads, q.data_ptr(), k.data_ptr(), v.data_ptr(), _stream(q))
+
+
 @torch._dynamo.disable
 def window_attn(plan: WindowPlan, q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, heads: int, impl: int = ATTN_AUTO):
     """-> (out_vid [L, heads*128] in original token order, out_txt [Lt, heads*128] mean over windows).

@@ -110,6 +110,44 @@ class WindowPlan:
             d["row_map"] = rm
         return d["row_map"]
 
+    def rope_plan(self, device: torch.device, rope_kind: int, freqs_key: Tuple[float, ...], freqs: Optional[torch.Tensor]):
+        """Tables of the fused qkv projection (svr2_rope_plan), once per (device, rope kind, frequency values):
+        (tok_map [L + Lt, 4] int32, rope_cs [rows, n_freqs, 2] fp32 or None, rows).  ``freqs_key`` = the frequency VALUES (the
+        blocks of a model hold equal copies of the checkpoint buffer, so they share one table)."""
+        d = self.on(device)
+        key = ("rope_plan", int(rope_kind), tuple(freqs_key))
+        if key not in d:
+            if torch.device(device).type != "cuda":
+                raise RuntimeError("svr2_rope_plan runs on a CUDA device only (no CPU fallback)")
+            T, H, W = self.grid
+            n_freqs = len(freqs_key)
+            base_of_n = None
+            rows = 0
+            if rope_kind == 1:        # 3B: table row = position value
+                rows = max(self.txt_len + int(self.table[:, 3].max()), int(self.table[:, 4].max()), int(self.table[:, 5].max()),
+                           self.txt_len, 1)
+            elif rope_kind == 2:      # 7B: rows for linspace(-1, 1, n) of every window extent n in the plan
+                ns = sorted(set(int(v) for v in self.table[:, 3:6].reshape(-1)))
+                if ns[-1] > 64:
+                    raise NotImplementedError(f"svr2_rope_plan: window extent {ns[-1]} > 64")
+                b = np.full(65, -1, dtype=np.int32)
+                for n in ns:
+                    b[n] = rows
+                    rows += n
+                base_of_n = torch.from_numpy(b).to(device)
+            tok_map = torch.empty(self.n_tokens + self.txt_len, 4, dtype=torch.int32, device=device)
+            cs = torch.empty(rows, n_freqs, 2, dtype=torch.float32, device=device) if rope_kind else None
+            with torch.cuda.device(device):
+                stream = torch.cuda.current_stream(device).cuda_stream
+                _lib.check(_lib.lib().svr2_rope_plan(
+                    d["table"].data_ptr(), self.row_map(device).data_ptr(), self.n_windows, T, H, W, self.txt_len, self.packed_rows,
+                    int(rope_kind), None if freqs is None else freqs.data_ptr(), n_freqs,
+                    None if base_of_n is None else base_of_n.data_ptr(), rows, tok_map.data_ptr(),
+                    None if cs is None else cs.data_ptr(), stream), "svr2_rope_plan")
+                torch.cuda.current_stream(device).synchronize()       # freqs / base_of_n may be temporaries of the caller
+            d[key] = (tok_map, cs, rows)
+        return d[key]
+
     def index_tensors(self, device: torch.device):
         """(tgt_idx, src_idx, window_shape, cu_seqlens) on `device`, computed by svr2_window_index (bit-exact)."""
         d = self.on(device)

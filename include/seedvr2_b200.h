@@ -158,6 +158,45 @@ int svr2_pack_rowmap(const int32_t* win_table, int n_windows, int T, int H, int 
                      int64_t P, void* stream);
 
 /*
+ * The block's qkv projection with everything that follows it up to the attention kernel fused into the GEMM epilogue:
+ *   q,k,v_pack = window_partition(rope(rmsnorm(x Wqkv^T)))
+ * Replaces proj_qkv (mmattn.py:56-59,173 / dit_7b mmsr_block.py:85-90) + everything svr2_qkv_pack_fwd replaces (norm_q / norm_k,
+ * RoPE, window_partition, concat_win; mmattn.py:199-248) — the [rows, 3*heads*128] qkv tensor never reaches HBM (SURVEY §8f N1c,
+ * §8d: 0 algorithmic bytes for partition / interleave).  tcgen05 GEMM of csrc/gemm.cu; a 256-column tile is two whole heads.
+ *   x [M, K] bf16 rows in this order: video tokens (original order), then text tokens — any contiguous range of that order:
+ *   tok_map points at the entry of row 0 (video GEMM: tok_map, M = L; text GEMM: tok_map + 4*L, M = Lt; joined rows: M = L + Lt);
+ *   weight [3*heads*128, K] bf16 (nn.Linear layout, rows ordered q heads | k heads | v heads);
+ *   tok_map / rope_cs / rope_rows from svr2_rope_plan;  n_freqs 21 (3B), 10 (7B) or 0 (no rope);
+ *   wq_*, wk_* [128] bf16 norm weights (the _txt pair may be NULL when no row is a text row);
+ *   q,k,v_pack [P, heads, 128] bf16: video rows land at their packed position;
+ *   txt_qkv [Lt, 3, heads, 128] bf16: text rows, copied into every window's sequence by svr2_txt_replicate_fwd afterwards.
+ */
+int svr2_linear_qkv_pack_fwd(const void* x, const void* weight, int64_t M, int K, int heads, const int32_t* tok_map,
+                             const float* rope_cs, int rope_rows, int n_freqs, const void* wq_vid, const void* wk_vid,
+                             const void* wq_txt, const void* wk_txt, float eps, void* q_pack, void* k_pack, void* v_pack,
+                             void* txt_qkv, void* stream);
+
+/*
+ * Per-plan tables of svr2_linear_qkv_pack_fwd, computed once per (plan, rope kind, frequencies) on the device:
+ *   tok_map [L + Lt][4] int32: the inverse of the packed-row map — for video token i (original order) its packed row and the
+ *   rope-table row of each axis; for text row j (entry L + j): -(1 + j) and, 3B, row j for all axes (rope.py:173), else -1.
+ *   rope_cs [rope_rows][n_freqs][2] fp32 (cos, sin): one row per distinct position value.  3B (dit_3b/rope.py:154-176): row r =
+ *   position r, rope_rows > max(Lt + window nt, nh, nw, Lt) - 1.  7B (dit_7b/rope.py:73-111): row base_of_n[n] + i =
+ *   linspace(-1, 1, n)[i] for every window extent n of the plan; base_of_n [65] int32 on the device, -1 where n is absent.
+ * Same cos / sin bits as svr2_qkv_pack_fwd computes per row.  row_map from svr2_pack_rowmap.
+ */
+int svr2_rope_plan(const int32_t* win_table, const int32_t* row_map, int n_windows, int T, int H, int W, int txt_len, int64_t P,
+                   int rope_kind, const float* freqs, int n_freqs, const int32_t* base_of_n, int rope_rows, int32_t* tok_map,
+                   float* rope_cs, void* stream);
+
+/*
+ * Text rows of q, k, v into every window's sequence: q_pack[row_start(w) + n_vid(w) + j] = txt_qkv[j, 0] (k: [j, 1], v: [j, 2]).
+ * Replaces the per-window repeat of the text q/k/v (mmattn.py:223-236) for the fused projection above.
+ */
+int svr2_txt_replicate_fwd(const void* txt_qkv, const int32_t* win_table, int n_windows, int txt_len, int heads, void* q_pack,
+                           void* k_pack, void* v_pack, void* stream);
+
+/*
  * Work list for svr2_window_attn_fwd, host side, pure integer: one item = (window, pair of 128-row query tiles), items
  * sorted longest sequence first so the ragged shifted-window remnants fill the tail of the last wave.
  *   work [max_items][2] int32 (window, q_pair) or NULL to only count;  *n_items receives the item count.

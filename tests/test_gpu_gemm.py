@@ -121,3 +121,75 @@ def test_linear_rejects_bad_shapes(svr2, cuda):
         svr2.ops.linear(x, torch.zeros(64, 32, dtype=torch.bfloat16, device=cuda))           # K mismatch
     with pytest.raises(NotImplementedError):
         svr2.ops.linear(x.float(), torch.zeros(64, 64, device=cuda))                         # fp32: no other path
+
+
+# ---------------------------------------------------------------------------------------- fused qkv projection (svr2_linear_qkv_pack_fwd)
+def _freqs(kind, svr2):
+    import math
+    if kind == svr2.ops.ROPE_3B_MM:
+        dim = 128 // 3
+        return 1.0 / (10000 ** (torch.arange(0, dim, 2)[: dim // 2].float() / dim))
+    if kind == svr2.ops.ROPE_7B_PIX:
+        return torch.linspace(1.0, 128.0, 10) * math.pi
+    return None
+
+
+@pytest.mark.parametrize("grid,shifted,heads,K,kind,joined", [
+    ((2, 20, 36), False, 2, 256, 1, True), ((2, 20, 36), True, 2, 256, 1, False), ((3, 20, 36), True, 4, 128, 2, False),
+    ((5, 17, 30), False, 2, 192, 2, False), ((1, 32, 32), True, 2, 256, 0, True), ((1, 128, 128), False, 20, 2560, 1, True),
+    ((9, 68, 120), True, 20, 2560, 1, False), ((6, 68, 120), True, 24, 3072, 2, False), ((10, 135, 240), False, 24, 3072, 2, False)],
+    ids=["3b_small_joined", "3b_small_swin_separate", "7b_small_swin", "7b_small_win", "norope_joined", "3b_c1_joined", "3b_1080p33f_swin",
+         "7b_c3r_swin", "7b_c4_win"])
+def test_linear_qkv_pack_equals_linear_then_qkv_pack(svr2, cuda, grid, shifted, heads, K, kind, joined):
+    """The fused projection (GEMM epilogue: q/k RMSNorm + RoPE + window scatter, text rows replicated afterwards) against the
+    two-kernel path it replaces (svr2_linear_fwd + svr2_qkv_pack_fwd, itself checked against the oracle in test_gpu_kernels.py):
+    v rows bit-equal; q / k rows equal except where the fp32 order of the row's sum of squares moves one bf16 rounding."""
+    ops = svr2.ops
+    txt_len = 58
+    plan = svr2.get_plan(grid, (4, 3, 3), shifted, txt_len)
+    L, N = plan.n_tokens, 3 * heads * 128
+    g = torch.Generator(device="cuda").manual_seed(11)
+    x = torch.randn(L + txt_len, K, generator=g, device=cuda).bfloat16()
+    w_vid = (torch.randn(N, K, generator=g, device=cuda) / K ** 0.5).bfloat16()
+    w_txt = w_vid if joined else (torch.randn(N, K, generator=g, device=cuda) / K ** 0.5).bfloat16()
+    nw = [(1.0 + 0.1 * torch.randn(128, generator=g, device=cuda)).bfloat16() for _ in range(4)]
+    f = _freqs(kind, svr2)
+    fdev = None if f is None else f.to(cuda)
+    fkey = () if f is None else tuple(float(v) for v in f.tolist())
+    assert ops.qkv_fused_supported(plan, kind, len(fkey), heads)
+    # reference path of the repo: dense projection, then the pack kernel
+    qkv_v = ops.linear(x[:L].contiguous(), w_vid)
+    qkv_t = ops.linear(x[L:].contiguous(), w_txt)
+    q0, k0, v0 = ops.qkv_pack(plan, qkv_v, qkv_t, nw[0], nw[1], nw[2], nw[3], fdev, kind, heads, 1e-5)
+    if joined:
+        bufs = ops.linear_qkv_pack(plan, x, w_vid, 0, *nw, fdev, fkey, kind, heads, 1e-5)
+    else:
+        bufs = ops.linear_qkv_pack(plan, x[:L].contiguous(), w_vid, 0, *nw, fdev, fkey, kind, heads, 1e-5)
+        bufs = ops.linear_qkv_pack(plan, x[L:].contiguous(), w_txt, L, *nw, fdev, fkey, kind, heads, 1e-5, out=bufs)
+    q1, k1, v1, tq = bufs
+    ops.replicate_text(plan, tq, q1, k1, v1, heads)
+    torch.cuda.synchronize()
+    assert torch.equal(v1, v0), "v rows must be bit-equal (a gather of the projection's bf16 output)"
+    for name, a, b in (("q", q1, q0), ("k", k1, k0)):
+        d = (a.float() - b.float()).abs()
+        frac = float((a != b).float().mean())
+        # a rotated element is a difference of two products and can cancel to ~0: ulps are taken at the head row's magnitude
+        ulps = float((d / _ulp(b.float().abs().amax(dim=-1, keepdim=True))).max())
+        print(f"{name}: {frac * 100:.4f} % of elements differ, max {ulps:.1f} bf16 ulp")
+        assert frac < 5e-3 and ulps <= 2.0, (name, frac, ulps)
+    # second call into the same buffers: nothing stale, same bits
+    q2, k2, v2, tq2 = ops.linear_qkv_pack(plan, x if joined else x[:L].contiguous(), w_vid, 0, *nw, fdev, fkey, kind, heads, 1e-5)
+    torch.cuda.synchronize()
+    vid_rows = torch.from_numpy(__import__("numpy").concatenate(
+        [__import__("numpy").arange(r, r + n) for r, n in zip(plan.table[:, 6], plan.table[:, 7])])).to(cuda)
+    assert torch.equal(q2[vid_rows], q1[vid_rows]) and torch.equal(v2[vid_rows], v1[vid_rows])
+
+
+def test_linear_qkv_pack_rejects(svr2, cuda):
+    plan = svr2.get_plan((1, 8, 8), (4, 3, 3), False, 58)
+    x = torch.zeros(64 + 58, 64, dtype=torch.bfloat16, device=cuda)
+    w3 = torch.zeros(3 * 3 * 128, 64, dtype=torch.bfloat16, device=cuda)
+    nw = [torch.ones(128, dtype=torch.bfloat16, device=cuda)] * 4
+    with pytest.raises(RuntimeError):       # odd head count: a 256-column tile would straddle q | k
+        svr2.ops.linear_qkv_pack(plan, x, w3, 0, *nw, None, (), 0, 3, 1e-5)
+    assert not svr2.ops.qkv_fused_supported(plan, 1, 7, 2)        # a frequency count the epilogue is not built for
