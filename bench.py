@@ -2,7 +2,7 @@
 """bench.py — DiT frames/sec of the SeedVR2 one-step NaDiT hot path on B200 (BASELINE.json `metric`: "DiT frames/sec,
 SeedVR2-3B 1080p, 1/2/4/8 B200; window-attn TFLOP/s vs peak").
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload v1080|v1080_121|c0|c1|c2|c3|c3r|c4] [--impl ours|reference]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload v1080|v1080_121|v1080_b|c0|c1|c2|c3|c3r|c4] [--impl ours|reference]
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P bench.py --gpus N ...
 
 Default workload `v1080`: a 232-frame 1920x1080 stream through SeedVR2-3B with the reference's streaming settings
@@ -45,6 +45,8 @@ WORKLOADS = {
                   desc="SeedVR2-3B 1080p stream, 232 frames, batch_size 33, temporal_overlap 4"),
     "v1080_121": dict(model="3b", hw=(136, 240), frames=121, batch=121, overlap=4, px=(1080, 1920), split="temporal",
                       desc="SeedVR2-3B 121 frames 1920x1080, one batch per rank"),
+    "v1080_b": dict(model="3b", hw=(136, 240), frames=33, batch=33, overlap=0, px=(1080, 1920), split="replica",
+                    desc="SeedVR2-3B ONE 33-frame 1920x1080 batch (one forward of the v1080 stream; profiling size)"),
     "c0": dict(model="3b", hw=(64, 64), frames=1, batch=1, overlap=0, px=(512, 512), split="replica", desc="SeedVR2-3B 1 frame 512x512"),
     "c1": dict(model="3b", hw=(256, 256), frames=1, batch=1, overlap=0, px=(2048, 2048), split="replica",
                desc="SeedVR2-3B 1 frame 2048x2048 image upscale"),

@@ -14,10 +14,11 @@ extern int g_trace_ctas;
 int launch_txt_pool(const void* txt_part, void* out_txt, int n_windows, int txt_len, int heads, cudaStream_t st);
 
 // ---- product kernels (bit-identical outputs)
-// generation 4 (window_attn_v2.cu): persistent, two query tiles per CTA share every K/V tile — long sequences
+// generation 4 (window_attn_v2.cu): persistent, two query tiles per CTA share every K/V tile — long sequences.
+// halves = 2: generation 10, the same kernel with two threads per query row (64 key columns each), 24 warps
 int launch_window_attn_tc2(const void* q, const void* k, const void* v, const int32_t* tab, const int32_t* work,
                            int n_work, int n_windows, int H, int W, int txt_len, int heads, int64_t P, void* out_vid,
-                           void* txt_part, cudaStream_t st);
+                           void* txt_part, int halves, cudaStream_t st);
 // generation 8 (window_attn_v6.cu): CTA pairs, tcgen05.mma.cta_group::2 — short sequences
 int launch_window_attn_tc6(const void* q, const void* k, const void* v, const int32_t* tab, const int32_t* work,
                            int n_work, int n_windows, int H, int W, int txt_len, int heads, int64_t P, void* out_vid,

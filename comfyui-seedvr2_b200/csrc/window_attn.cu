@@ -77,7 +77,10 @@ extern "C" int svr2_window_attn_fwd_impl(const void* q_pack, const void* k_pack,
         rc = svr2::launch_window_attn_tc6(q_pack, k_pack, v_pack, win_table, work, n_work, n_windows, H, W, txt_len, heads, P, out_vid, txt_part, st);
         break;
     case SVR2_ATTN_GEN4:
-        rc = svr2::launch_window_attn_tc2(q_pack, k_pack, v_pack, win_table, work, n_work, n_windows, H, W, txt_len, heads, P, out_vid, txt_part, st);
+        rc = svr2::launch_window_attn_tc2(q_pack, k_pack, v_pack, win_table, work, n_work, n_windows, H, W, txt_len, heads, P, out_vid, txt_part, 1, st);
+        break;
+    case SVR2_ATTN_GEN10:
+        rc = svr2::launch_window_attn_tc2(q_pack, k_pack, v_pack, win_table, work, n_work, n_windows, H, W, txt_len, heads, P, out_vid, txt_part, 2, st);
         break;
     case SVR2_ATTN_MMA:
         rc = svr2::launch_window_attn_mma(q_pack, k_pack, v_pack, win_table, work, n_work, H, W, txt_len, heads, out_vid, txt_part, st);

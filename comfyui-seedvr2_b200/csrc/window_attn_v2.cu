@@ -67,7 +67,7 @@ constexpr int NTHREADS = 512;             // generation 4; generation 10 adds 8 
 #endif
 constexpr int kRegs[3] = {SVR2_REGS_C, SVR2_REGS_E, SVR2_REGS_S};
 // per sub-partition: 32 * (C + E + 2 S) = 16384
-constexpr int kRegs10[3] = {48, 48, 104};                // generation 10: per sub-partition 32 * (C + E + 4 S) = 16384
+constexpr int kRegs10[3] = {48, 48, 96};     // generation 10: the CTA is launched with 80 x 768 registers; 128 (C + E) + 512 S must fit in them
 constexpr int OFF_RING = 2 * TILE_BYTES;
 constexpr int OFF_STAGE = OFF_RING + STAGES * TILE_BYTES;
 constexpr int STAGE_BYTES = BM * 128;                  // epilogue staging: 128 rows x 64 columns, two passes per tile
@@ -457,6 +457,139 @@ window_attn_tc2_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
                 if (i) ++c1; else ++c0;
             }
         }
+    } else if constexpr (HALVES == 2) {
+        reg_alloc<REGS_SOFTMAX>();
+        // ------------------------------------------------------------------ softmax group i, column half h: TWO threads per query row
+        // warps 8-15: columns [0, 64) of the key tile (tiles 0, 1); warps 16-23: columns [64, 128).  The arithmetic per element
+        // is generation 4's; what changes is who holds which columns, the exchange of the partial row max and the split row sum.
+        const int half = (warp - 8) >> 3, i = ((warp - 8) >> 2) & 1, quad = warp & 3, row = quad * 32 + lane;
+        const uint32_t lane_off = (uint32_t)(quad * 32) << 16;
+        const uint32_t tS = tmem + lane_off + i * 128;
+        const uint32_t tO = tmem + lane_off + 256 + i * 128 + half * 64;
+        float* x_mine = xch + (i * 2 + half) * 128 + row;
+        const float* x_other = xch + (i * 2 + (half ^ 1)) * 128 + row;
+        const int bar_id = 1 + i * 4 + quad;        // named barrier of the two warps that hold the same 32 rows
+        uint32_t sf = 0, c_cnt = 0;
+        for (int item = blockIdx.x; item < p.n_items; item += gridDim.x) {
+            const Item it = decode_item(p, item);
+            if (i >= it.nq) continue;
+            float m = -INFINITY, l = 0.f;
+            for (int j = 0; j < it.n_kv; ++j, ++sf) {
+                const bool last = j == it.n_kv - 1;
+                const int nch = (last ? it.last_cols : BN) >> 5;            // 32-column chunks in this key tile (warp-uniform)
+                const int my_n = min(max(nch - 2 * half, 0), 2);            // ... of which this half owns chunks 2h, 2h + 1
+                const int v0 = it.seq - j * BN - 64 * half;                 // my columns >= v0 are beyond the sequence
+                SOFTMAX_WAIT(bar(BAR_SFULL + i), sf & 1u);
+                tc_fence_after();
+                // Pass 1: this half's partial row max straight from TMEM, 32 columns at a time.  The S row is NOT kept in registers:
+                // a half row next to the exp temporaries needs ~110 registers, the role has 96, and a spill here is an L2 round trip
+                // (this kernel leaves ~8 KB of L1) — run 13: 20 % slower than generation 4 with a dozen spilled scalars per step.
+                float m8[8];
+#pragma unroll
+                for (int q = 0; q < 8; ++q) m8[q] = -INFINITY;
+                if (my_n > 0) {
+                    uint32_t s[32];
+                    tmem_ld32(tS + 64 * half, s);
+                    tc_wait_ld();
+                    if (v0 < 32) mask_chunk(s, v0);
+                    chunk_max8(m8, s);
+                }
+                if (my_n > 1) {
+                    uint32_t s[32];
+                    tmem_ld32(tS + 64 * half + 32, s);
+                    tc_wait_ld();
+                    if (v0 < 64) mask_chunk(s, v0 - 32);
+                    chunk_max8(m8, s);
+                }
+                float mx = fmaxf(max3(m8[0], m8[1], m8[2]), max3(max3(m8[3], m8[4], m8[5]), m8[6], m8[7]));
+                // the row max over both halves (every later write of x_mine follows the partner's read: its P-ready arrival, which
+                // the next S depends on, comes after it)
+                *x_mine = mx;
+                named_bar_sync(bar_id, 64);
+                mx = fmaxf(mx, *x_other);
+                if (j == 0) {
+                    m = ref_of(mx);
+                } else {
+                    // lazy rescale, decided identically by both halves (same rows, same values): each rescales its 64 columns of O_i
+                    const bool need = mx * kScaleLog2 - m > kRescaleThreshold;
+                    if (__any_sync(0xffffffffu, need)) {
+                        const float m_new = need ? ref_of(mx) : m;
+                        const float alpha = ex2(m - m_new);
+                        l *= alpha;
+                        m = m_new;
+#pragma unroll 1
+                        for (int c8 = 0; c8 < 4; ++c8) {
+                            uint32_t ov[16];
+                            tmem_ld16(tO + c8 * 16, ov);
+                            tc_wait_ld();
+#pragma unroll
+                            for (int c = 0; c < 16; ++c) ov[c] = __float_as_uint(__uint_as_float(ov[c]) * alpha);
+                            tmem_st16(tO + c8 * 16, ov);
+                        }
+                    }
+                }
+                const float mb = m;
+                // Pass 2: S again from TMEM, chunk by chunk, P written over the front of S_i.  P chunk c (32 keys = 16 packed
+                // columns) sits at tS + 16 c: chunks 0, 1 (lower half) land on S columns [0, 32), which the lower half itself has
+                // consumed by then; chunks 2, 3 (upper half) land on S columns [32, 64) = the lower half's SECOND chunk, so the upper
+                // half stores only after the lower half has that chunk in registers (arrive / sync on the pair's named barrier).
+                const uint32_t tP = tS + 32 * half;
+                float rs = 0.f;
+                if (half == 0) {
+                    if (my_n > 0) {
+                        uint32_t s[32], pk[16];
+                        tmem_ld32(tS, s);
+                        tc_wait_ld();
+                        if (v0 < 32) mask_chunk(s, v0);
+                        rs = chunk_exp_mix<kFmaEighths>(s, pk, mb);
+                        tmem_st16(tP, pk);
+                    }
+                    if (my_n > 1) {
+                        uint32_t s[32], pk[16];
+                        tmem_ld32(tS + 32, s);
+                        tc_wait_ld();
+                        named_bar_arrive(bar_id, 64);
+                        if (v0 < 64) mask_chunk(s, v0 - 32);
+                        rs += chunk_exp_mix<kFmaEighths>(s, pk, mb);
+                        tmem_st16(tP + 16, pk);
+                    } else {
+                        named_bar_arrive(bar_id, 64);
+                    }
+                } else {
+                    if (my_n > 0) {
+                        uint32_t s[32], pk[16];
+                        tmem_ld32(tS + 64, s);
+                        tc_wait_ld();
+                        if (v0 < 32) mask_chunk(s, v0);
+                        rs = chunk_exp_mix<kFmaEighths>(s, pk, mb);
+                        named_bar_sync(bar_id, 64);
+                        tmem_st16(tP, pk);
+                    } else {
+                        named_bar_sync(bar_id, 64);
+                    }
+                    if (my_n > 1) {
+                        uint32_t s[32], pk[16];
+                        tmem_ld32(tS + 96, s);
+                        tc_wait_ld();
+                        if (v0 < 64) mask_chunk(s, v0 - 32);
+                        rs += chunk_exp_mix<kFmaEighths>(s, pk, mb);
+                        tmem_st16(tP + 16, pk);
+                    }
+                }
+                l += rs;
+                tc_wait_st();
+                tc_fence_before();
+                mbar_arrive(bar(BAR_PREADY + i));
+            }
+            // publish this half's partial row sum for the epilogue warps (double-buffered by item parity).  A one-key-tile item
+            // can finish before the epilogue has picked up the PREVIOUS item's row sums (it may still be storing the item before
+            // that): LREADY would then complete two phases and its parity alias.  The epilogue's "O is drained" arrival of the
+            // previous item follows its LREADY wait, so waiting for it here keeps LREADY at most one phase ahead.
+            if (c_cnt > 0) SOFTMAX_WAIT(bar(BAR_OEMPTY + i), (c_cnt - 1) & 1u);
+            l_buf[(((c_cnt & 1) * 2 + i) * 2 + half) * 128 + row] = l;
+            mbar_arrive(bar(BAR_LREADY + i));
+            ++c_cnt;
+        }
     } else {
         reg_alloc<REGS_SOFTMAX>();
         // ------------------------------------------------------------------ softmax group i: one thread per query row
@@ -591,7 +724,8 @@ window_attn_tc2_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
             }
             other_steps += (i == 1 || it.nq == 2) ? it.n_kv : 0;
             // publish the row sum for the epilogue warps (double-buffered by item parity)
-            l_buf[((c_cnt & 1) * 2 + i) * 128 + row] = l;
+            if (c_cnt > 0) SOFTMAX_WAIT(bar(BAR_OEMPTY + i), (c_cnt - 1) & 1u);      // see generation 10 above: LREADY stays one phase ahead at most
+            l_buf[(((c_cnt & 1) * 2 + i) * 2) * 128 + row] = l;
             mbar_arrive(bar(BAR_LREADY + i));
             ++c_cnt;
         }
@@ -613,15 +747,24 @@ namespace svr2 {
 
 int launch_window_attn_tc2(const void* q, const void* k, const void* v, const int32_t* tab, const int32_t* work,
                            int n_work, int n_windows, int H, int W, int txt_len, int heads, int64_t P, void* out_vid,
-                           void* txt_part, cudaStream_t st) {
+                           void* txt_part, int halves, cudaStream_t st) {
     CUtensorMap tq, tk, tv;
     int rc;
     if ((rc = make_tmap(&tq, q, P, heads)) != SVR2_OK) return rc;
     if ((rc = make_tmap(&tk, k, P, heads)) != SVR2_OK) return rc;
     if ((rc = make_tmap(&tv, v, P, heads)) != SVR2_OK) return rc;
-    static PerDeviceFlag smem_ok[2];
-    if ((rc = ensure_dyn_smem(tc2::window_attn_tc2_kernel<false>, tc2::SMEM_BYTES, smem_ok[0], "svr2_window_attn_fwd")) != SVR2_OK) return rc;
-    if ((rc = ensure_dyn_smem(tc2::window_attn_tc2_kernel<true>, tc2::SMEM_BYTES, smem_ok[1], "svr2_window_attn_fwd")) != SVR2_OK) return rc;
+    static PerDeviceFlag smem_ok[3];
+    if ((rc = ensure_dyn_smem(tc2::window_attn_tc2_kernel<false, 1>, tc2::SMEM_BYTES, smem_ok[0], "svr2_window_attn_fwd")) != SVR2_OK) return rc;
+    if ((rc = ensure_dyn_smem(tc2::window_attn_tc2_kernel<true, 1>, tc2::SMEM_BYTES, smem_ok[1], "svr2_window_attn_fwd")) != SVR2_OK) return rc;
+#ifdef SVR2_EXPERIMENTS
+    if ((rc = ensure_dyn_smem(tc2::window_attn_tc2_kernel<false, 2>, tc2::SMEM_BYTES, smem_ok[2], "svr2_window_attn_fwd")) != SVR2_OK) return rc;
+#else
+    if (halves != 1) {
+        set_error("svr2_window_attn_fwd_impl: generation 10 (two threads per query row) is an experiment — measured 4-8 %% slower than "
+                  "generation 4 (run 14) — and is only compiled with `make EXPERIMENTS=1`");
+        return SVR2_E_UNSUPPORTED;
+    }
+#endif
     tc2::Params p;
     p.tab = tab; p.work = work; p.n_items = n_work * heads;
     p.H = H; p.W = W; p.txt_len = txt_len; p.heads = heads;
@@ -632,8 +775,12 @@ int launch_window_attn_tc2(const void* q, const void* k, const void* v, const in
     p.turns = SVR2_TURNS && (P / n_windows <= 8 * tc2::BN);
     const int sms = sm_count();
     const int grid = p.n_items < sms ? p.n_items : sms;       // one persistent CTA per SM
-    if (p.trace != nullptr) tc2::window_attn_tc2_kernel<true><<<grid, tc2::NTHREADS, tc2::SMEM_BYTES, st>>>(tq, tk, tv, p);
-    else tc2::window_attn_tc2_kernel<false><<<grid, tc2::NTHREADS, tc2::SMEM_BYTES, st>>>(tq, tk, tv, p);
+#ifdef SVR2_EXPERIMENTS
+    if (halves == 2) tc2::window_attn_tc2_kernel<false, 2><<<grid, tc2::NTHREADS + 256, tc2::SMEM_BYTES, st>>>(tq, tk, tv, p);
+    else
+#endif
+    if (p.trace != nullptr) tc2::window_attn_tc2_kernel<true, 1><<<grid, tc2::NTHREADS, tc2::SMEM_BYTES, st>>>(tq, tk, tv, p);
+    else tc2::window_attn_tc2_kernel<false, 1><<<grid, tc2::NTHREADS, tc2::SMEM_BYTES, st>>>(tq, tk, tv, p);
     SVR2_CHECK_LAUNCH("svr2_window_attn_fwd(tcgen05, persistent)");
     return SVR2_OK;
 }

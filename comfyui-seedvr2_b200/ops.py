@@ -13,7 +13,7 @@ from . import _lib
 from .plan import WindowPlan
 
 ROPE_NONE, ROPE_3B_MM, ROPE_7B_PIX = 0, 1, 2
-ATTN_AUTO, ATTN_GEN4, ATTN_GEN8, ATTN_MMA = 0, 4, 8, 100      # include/seedvr2_b200.h SVR2_ATTN_*
+ATTN_AUTO, ATTN_GEN4, ATTN_GEN8, ATTN_GEN10, ATTN_MMA = 0, 4, 8, 10, 100      # include/seedvr2_b200.h SVR2_ATTN_*
 
 
 class KernelTimer:

@@ -237,6 +237,7 @@ int svr2_window_attn_fwd(const void* q_pack, const void* k_pack, const void* v_p
 #define SVR2_ATTN_AUTO 0
 #define SVR2_ATTN_GEN4 4
 #define SVR2_ATTN_GEN8 8
+#define SVR2_ATTN_GEN10 10   /* generation 4's kernel with two threads per query row (window_attn_v2.cu, HALVES = 2) */
 #define SVR2_ATTN_MMA  100
 int svr2_window_attn_fwd_impl(const void* q_pack, const void* k_pack, const void* v_pack, const int32_t* win_table,
                               const int32_t* work, int n_work, const int32_t* work4, int n_work4, int n_windows, int T,
@@ -313,6 +314,30 @@ int svr2_sr_input_fwd(const void* noise, const void* latent, const void* aug_noi
  * out may alias x_t or pred.
  */
 int svr2_v_lerp_endpoint_fwd(const void* x_t, const void* pred, float A, float B, void* out, int64_t n, void* stream);
+
+/*
+ * GPU post-processing of a decoded batch: the pipeline's default colour correction and the output conversion.
+ *
+ * svr2_wavelet_level_fwd: one level of wavelet_decomposition (src/utils/color_fix.py:122-184) —
+ *   low = wavelet_blur(src, radius): 3x3 kernel [1 2 1]^T [1 2 1] / 16 with dilation `radius`, replicate padding (a grouped
+ *   conv2d in the reference; same tap order and fp32 accumulation as ATen's depthwise kernel);
+ *   high = (high + src) - low, two separately rounded ops (`high_freq.add_(image).sub_(low_freq)`); `first` != 0: high starts at 0.
+ *   src is indexed [T, C, H, W] through four ELEMENT strides (the pipeline hands a permuted view of its [T, H, W, C] video);
+ *   low / high are planar contiguous [T, C, H, W]; high may be NULL (the style image only needs its low band).
+ *   The caller passes radius = min(2^level, max(1, min(H, W) / 8)) (color_fix.py:136-139).
+ * svr2_colorfix_finish_fwd: wavelet_reconstruction's combine + the batch normalisation + the writer's conversion —
+ *   v = clamp(high + low_style, -1, 1) * 0.5 + 0.5  (color_fix.py:240-246, generation_phases.py:1337) -> out [T, H, W, C] (same
+ *   dtype, may be NULL) and / or out_u8 [T, H, W, C] = (uint8)(v * 255) truncated like numpy's astype (inference_cli.py:691,734),
+ *   with R and B swapped when bgr != 0 (cv2 order, inference_cli.py:693-695).
+ * dtype: SVR2_DTYPE_F32 or SVR2_DTYPE_BF16 (the pipeline post-processes in its compute dtype, generation_phases.py:1229-1237);
+ * bf16 rounds where the reference's bf16 tensors round.
+ */
+#define SVR2_DTYPE_F32  0
+#define SVR2_DTYPE_BF16 1
+int svr2_wavelet_level_fwd(const void* src, int64_t stride_t, int64_t stride_c, int64_t stride_y, int64_t stride_x, void* low,
+                           void* high, int first, int T, int C, int H, int W, int radius, int dtype, void* stream);
+int svr2_colorfix_finish_fwd(const void* high, const void* low_style, void* out, void* out_u8, int bgr, int T, int C, int H, int W,
+                             int dtype, void* stream);
 
 #ifdef __cplusplus
 }

@@ -41,6 +41,28 @@ x = r(M, D)
 wqkv, wo, bo = r(3 * D, D) / D ** 0.5, r(D, D) / D ** 0.5, r(D)
 emb, gb, resid = r(6 * D), r(D), r(M, D)
 report(f"proj_qkv [{M},{D}]x[{3 * D},{D}]", 2 * M * D * 3 * D, timeit(lambda: ops.linear(x, wqkv)), timeit(lambda: F.linear(x, wqkv)))
+if which in ("v1080", "c1", "c3r"):
+    # the fused projection (GEMM + q/k RMSNorm + RoPE + window scatter) against GEMM + svr2_qkv_pack_fwd
+    import math
+    grid = {"v1080": (9, 68, 120), "c1": (1, 128, 128), "c3r": (6, 68, 120)}[which]
+    heads, kind = D // 128, (2 if which == "c3r" else 1)
+    plan = svr2.get_plan(grid, (4, 3, 3), False, 58)
+    Mx = plan.n_tokens + 58
+    xq = r(Mx, D)
+    nw = [(1.0 + 0.1 * torch.randn(128, generator=g, device=dev)).bfloat16() for _ in range(4)]
+    f = (1.0 / (10000 ** (torch.arange(0, 42, 2)[:21].float() / 42)) if kind == 1 else torch.linspace(1.0, 128.0, 10) * math.pi).to(dev)
+    fkey = tuple(float(v) for v in f.tolist())
+    bufs = ops.linear_qkv_pack(plan, xq, wqkv, 0, *nw, f, fkey, kind, heads, 1e-5)
+
+    def fused():
+        ops.linear_qkv_pack(plan, xq, wqkv, 0, *nw, f, fkey, kind, heads, 1e-5, out=bufs)
+        ops.replicate_text(plan, bufs[3], bufs[0], bufs[1], bufs[2], heads)
+
+    def unfused():
+        y = ops.linear(xq, wqkv)
+        ops.qkv_pack(plan, y[:plan.n_tokens], y[plan.n_tokens:], *nw, f, kind, heads, 1e-5)
+
+    report("proj_qkv + norm + rope + partition (fused)", 2 * Mx * D * 3 * D, timeit(fused), timeit(unfused))
 report("proj_out + gate + residual", 2 * M * D * D, timeit(lambda: ops.linear_gate_residual(x, wo, bo, emb, gb, 0, resid)),
        timeit(lambda: ops.gate_residual(F.linear(x, wo, bo), resid, emb, gb, 0)))
 if which == "c3r":

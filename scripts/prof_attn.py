@@ -3,7 +3,7 @@ import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 import seedvr2_b200 as svr2
-grids = {"c1": ((1, 128, 128), 20), "c2": ((9, 90, 160), 20), "c3": ((31, 68, 120), 24)}
+grids = {"v1080": ((9, 68, 120), 20), "c1": ((1, 128, 128), 20), "c2": ((9, 90, 160), 20), "c3": ((31, 68, 120), 24)}
 name = sys.argv[1] if len(sys.argv) > 1 else "c1"
 shifted = len(sys.argv) > 2 and sys.argv[2] == "swin"
 grid, heads = grids[name]

@@ -253,11 +253,48 @@ def test_window_attn_experiments_not_in_product_build(svr2, cuda):
         svr2.ops.window_attn(plan, q, q, q, 1, impl=7)
 
 
-@pytest.mark.parametrize("impl", ["auto", "gen8", "gen4", "mma"])
+@pytest.mark.parametrize("grid,shifted,heads", ATTN_CASES + [((9, 68, 120), True, 4), ((1, 128, 128), False, 4)])
+def test_window_attn_generation10_matches_generation4(svr2, cuda, grid, shifted, heads):
+    """Generation 10 (two threads per query row, 64 key columns each) computes every exponential with generation 4's arithmetic
+    and the exact same row max; only the row sum is added in a different order (two partial sums per row), so outputs may differ
+    by one bf16 rounding of O / l — never more — and repeated launches are bit-identical."""
+    ops = svr2.ops
+    plan = svr2.get_plan(grid, (4, 3, 3), shifted, cases.TXT_LEN)
+    try:
+        z = torch.zeros(plan.packed_rows, heads, 128, dtype=torch.bfloat16, device=cuda)
+        ops.window_attn(plan, z, z, z, heads, impl=ops.ATTN_GEN10)
+    except NotImplementedError:
+        pytest.skip("generation 10 is an experiment kernel: built only with `make -C comfyui-seedvr2_b200/csrc EXPERIMENTS=1`")
+    g = torch.Generator().manual_seed(13)
+    q, k, v = (torch.randn(plan.packed_rows, heads, 128, generator=g).bfloat16().to(cuda) for _ in range(3))
+    for scale in (1.0, 6.0):                     # 6.0: row maxima that jump between key tiles exercise the lazy rescale
+        qq = q.clone()
+        qq[: plan.packed_rows // 2] *= scale
+        a_v, a_t = ops.window_attn(plan, qq, k, v, heads, impl=ops.ATTN_GEN4)
+        b_v, b_t = ops.window_attn(plan, qq, k, v, heads, impl=ops.ATTN_GEN10)
+        c_v, c_t = ops.window_attn(plan, qq, k, v, heads, impl=ops.ATTN_GEN10)
+        torch.cuda.synchronize()
+        assert torch.equal(b_v, c_v) and torch.equal(b_t, c_t), "generation 10 is not deterministic"
+        d = (a_v.float() - b_v.float()).abs()
+        ulp = torch.exp2(torch.floor(torch.log2(a_v.float().abs().clamp_min(2.0 ** -100))) - 7)
+        assert bool((d <= ulp).all()), float((d / ulp).max())
+        assert float((a_v != b_v).float().mean()) < 0.02
+        # pooled text rows: a mean over windows of per-window bf16 rows, each of which may carry one such rounding
+        assert float((a_t.float() - b_t.float()).abs().max()) <= 2.0 ** -8 * float(a_v.float().abs().max())
+
+
+@pytest.mark.parametrize("impl", ["auto", "gen8", "gen4", "gen10", "mma"])
 @pytest.mark.parametrize("grid,shifted,heads", ATTN_CASES)
 def test_window_attn_vs_fp32(svr2, cuda, impl, grid, shifted, heads):
-    code = {"auto": svr2.ops.ATTN_AUTO, "gen8": svr2.ops.ATTN_GEN8, "gen4": svr2.ops.ATTN_GEN4, "mma": svr2.ops.ATTN_MMA}[impl]
+    code = {"auto": svr2.ops.ATTN_AUTO, "gen8": svr2.ops.ATTN_GEN8, "gen4": svr2.ops.ATTN_GEN4, "gen10": svr2.ops.ATTN_GEN10,
+            "mma": svr2.ops.ATTN_MMA}[impl]
     plan = svr2.get_plan(grid, (4, 3, 3), shifted, cases.TXT_LEN)
+    if impl == "gen10":
+        try:
+            z = torch.zeros(plan.packed_rows, heads, 128, dtype=torch.bfloat16, device=cuda)
+            svr2.ops.window_attn(plan, z, z, z, heads, impl=code)
+        except NotImplementedError:
+            pytest.skip("generation 10 is an experiment kernel (make EXPERIMENTS=1)")
     g = torch.Generator().manual_seed(3)
     q, k, v = (torch.randn(plan.packed_rows, heads, 128, generator=g).bfloat16() for _ in range(3))
     q = q * 1.5      # sharper softmax

@@ -1,0 +1,63 @@
+"""GPU post-processing (comfyui-seedvr2_b200/postprocess.py -> svr2_wavelet_level_fwd, svr2_colorfix_finish_fwd) against the
+reference's own ``wavelet_reconstruction`` + batch normalisation run on the same GPU (staged copy under baseline/_ref; the oracle
+restatement where it is not staged) and the writer's uint8 conversion (inference_cli.py:691-695)."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import postprocess as opost
+from oracle import refstage
+
+pytestmark = pytest.mark.gpu
+
+
+def _reference(sample, style):
+    """[T, H, W, C] in [0, 1] by the reference's code path (generation_phases.py:1296-1337)."""
+    if refstage.available():
+        refstage.activate()
+        from src.utils.color_fix import wavelet_reconstruction
+        out = wavelet_reconstruction(sample.clone(), style.clone(), None)
+        out = out.permute(0, 2, 3, 1).contiguous()
+        return out.clamp_(-1, 1).mul_(0.5).add_(0.5), "reference"
+    return opost.wavelet_color_fix(sample.clone(), style.clone()), "oracle"
+
+
+@pytest.mark.parametrize("shape", [(2, 3, 90, 160), (1, 3, 20, 37), (3, 3, 272, 480), (1, 4, 64, 64), (2, 3, 1080, 1920)],
+                         ids=["2x90x160", "radius_cap_20x37", "3x272x480", "four_channels", "1080p"])
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16], ids=["fp32", "bf16"])
+def test_wavelet_color_fix_matches_reference(svr2, cuda, shape, dtype):
+    T, C, H, W = shape
+    g = torch.Generator(device="cuda").manual_seed(5)
+    # the pipeline hands a permuted view of its [T, H, W, C] video (generation_phases.py:1222-1225)
+    video = (torch.rand(T, H, W, C, generator=g, device=cuda) * 2.6 - 1.3).to(dtype)
+    sample = video.permute(0, 3, 1, 2)
+    style = (torch.rand(T, C, H, W, generator=g, device=cuda) * 2.2 - 1.1).to(dtype)
+    want, who = _reference(sample, style)
+    got, got_u8 = svr2.postprocess.wavelet_color_fix(sample, style, want_float=True, want_uint8=True, bgr=False)
+    _, got_bgr = svr2.postprocess.wavelet_color_fix(sample, style, want_float=False, want_uint8=True, bgr=True)
+    torch.cuda.synchronize()
+    assert got.shape == want.shape and got.dtype == want.dtype
+    d = float((got.float() - want.float()).abs().max())
+    frac = float((got != want).float().mean())
+    print(f"\n{shape} {dtype} vs {who}: max|d| {d:.3e}, {frac * 100:.4f} % of elements differ")
+    if dtype == torch.float32:
+        assert d <= 4e-7          # at most a couple of fp32 ulps at |x| <= 1 (tap order of the library convolution)
+    else:
+        assert d <= 2.0 ** -8 and frac < 1e-3      # one bf16 ulp below 1.0, on a rounding tie of the fp32 accumulator
+    # uint8: exactly the writer's conversion of OUR float frames; against the reference's frames at most one level apart, rarely
+    u8 = opost.to_uint8(got)
+    assert np.array_equal(got_u8.cpu().numpy(), u8)
+    assert np.array_equal(got_bgr.cpu().numpy(), opost.to_uint8(got, bgr=True))
+    ref_u8 = opost.to_uint8(want)
+    dd = np.abs(got_u8.cpu().numpy().astype(np.int16) - ref_u8.astype(np.int16))
+    assert dd.max() <= 1 and float((dd != 0).mean()) < (1e-4 if dtype == torch.float32 else 2e-3)
+
+
+def test_wavelet_color_fix_rejects(svr2, cuda):
+    a = torch.zeros(1, 3, 16, 16, device=cuda)
+    with pytest.raises(NotImplementedError):
+        svr2.postprocess.wavelet_color_fix(a, torch.zeros(1, 3, 8, 8, device=cuda))
+    with pytest.raises(NotImplementedError):
+        svr2.postprocess.wavelet_color_fix(a.half(), a.half())
+    with pytest.raises(RuntimeError):
+        svr2.postprocess.wavelet_color_fix(a.cpu(), a.cpu())

@@ -148,3 +148,20 @@ def test_sampler_oracle_matches_reference(case):
     assert torch.equal(vid, gold["dit_input"])
     assert x0.dtype == gold["x0"].dtype and torch.equal(x0, gold["x0"])
     assert gold["timestep"].tolist() == [1000.0] and gold["vid_shape"].tolist() == [list(case.grid)]
+
+
+def test_postprocess_oracle_matches_reference_module():
+    """oracle/postprocess.py against the real src/utils/color_fix.py:wavelet_reconstruction (staged copy or /root/reference), CPU."""
+    import torch
+    from oracle import postprocess as opost
+    from oracle import refstage
+    if not refstage.available():
+        pytest.skip("reference not staged")
+    refstage.activate()
+    from src.utils.color_fix import wavelet_reconstruction
+    g = torch.Generator().manual_seed(3)
+    for shape, dt in (((2, 3, 40, 56), torch.float32), ((1, 3, 20, 37), torch.float32), ((2, 3, 40, 56), torch.bfloat16)):
+        a = (torch.rand(*shape, generator=g) * 2.6 - 1.3).to(dt)
+        b = (torch.rand(*shape, generator=g) * 2.2 - 1.1).to(dt)
+        ref = wavelet_reconstruction(a.clone(), b.clone(), None).permute(0, 2, 3, 1).contiguous().clamp_(-1, 1).mul_(0.5).add_(0.5)
+        assert torch.equal(opost.wavelet_color_fix(a, b), ref)

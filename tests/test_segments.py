@@ -116,3 +116,42 @@ def test_stitch_layout_places_frames_like_the_sequential_loop(svr2, lens, overla
         assert torch.equal(ref[off + head: off + head + n_body], chunks[r][first_body:first_body + n_body])
     with pytest.raises(ValueError):
         segments.stitch_layout((6, 3, 6), 2)           # a segment shorter than 2 * overlap: order-dependent, not offered
+
+
+# ---- the launcher (comfyui-seedvr2_b200/launch.py): frame ranges per rank, per-rank pipeline, stitch, prepend handling -------------
+def _launch_worker(rank, world, port, total, overlap, prepend, preloaded, out_path):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world), LOCAL_RANK=str(rank))
+    import seedvr2_b200  # noqa: F401
+    from seedvr2_b200 import launch
+    r, w, dev = launch.init_distributed("gloo")
+    assert (r, w) == (rank, world) and dev.type == "cpu"
+    seen = {}
+
+    def pipeline(a, b, pre):       # a deterministic stand-in for the per-rank upscaling pipeline: frame f -> value f (+ rank tint)
+        seen["range"], seen["prepend"] = (a, b), pre
+        f = torch.arange(a, b, dtype=torch.float32).view(-1, 1, 1, 1).expand(-1, 4, 6, 3).clone()
+        return f + 0.001 * rank
+
+    out = launch.run_segments(total, pipeline, overlap=overlap, prepend_frames=prepend, preloaded=preloaded, batch_size=5,
+                              blend=partition.blend)
+    torch.save({"out": out, "range": seen["range"], "prepend": seen["prepend"]}, f"{out_path}.{rank}")
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("total,overlap,prepend,preloaded", [(41, 4, 0, False), (41, 4, 3, False), (30, 2, 0, True), (17, 0, 0, False)])
+def test_launcher_runs_segments_and_stitches(svr2, tmp_path, total, overlap, prepend, preloaded):
+    from seedvr2_b200 import segments
+    world = 2
+    out_path = str(tmp_path / "launch")
+    mp.spawn(_launch_worker, args=(world, _free_port(), total, overlap, prepend, preloaded, out_path), nprocs=world, join=True)
+    res = [torch.load(f"{out_path}.{r}") for r in range(world)]
+    ranges = (segments.chunk_ranges_preloaded(total, world, overlap, 5) if preloaded else segments.segment_ranges(total, world, overlap))
+    assert [tuple(r["range"]) for r in res] == [tuple(x) for x in ranges]
+    assert [r["prepend"] for r in res] == [prepend, 0]                      # only the first segment starts the video
+    assert res[1]["out"] is None
+    chunks = [torch.arange(a, b, dtype=torch.float32).view(-1, 1, 1, 1).expand(-1, 4, 6, 3) + 0.001 * r for r, (a, b) in enumerate(ranges)]
+    want = partition.stitch(chunks, overlap)
+    if prepend:
+        want = want[prepend:]
+    assert torch.equal(res[0]["out"], want)
