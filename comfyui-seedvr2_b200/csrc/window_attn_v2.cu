@@ -101,6 +101,10 @@ enum { BAR_QFULL = 0, BAR_QEMPTY = 2, BAR_SFULL = 4, BAR_PREADY = 6, BAR_OFINAL 
 #ifndef SVR2_V2_SPLIT_QK
 #define SVR2_V2_SPLIT_QK 0
 #endif
+#ifndef SVR2_SPEC_EXP
+#define SVR2_SPEC_EXP 0     // 1: exponentials against the current reference WHILE the row max is reduced.  Bit-identical, and 12-14 % slower
+                            // (run 18: C2 920 against 1,046 TFLOP/s, v1080 836 against 986) — the max phase is not what the step waits for
+#endif
 #ifndef SVR2_TURNS
 #define SVR2_TURNS 0      // measured: the bounded counter version gains nothing (see the comment in the softmax role); kept for experiments
 #endif
@@ -659,10 +663,49 @@ window_attn_tc2_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
                 float m8[8];
 #pragma unroll
                 for (int q = 0; q < 8; ++q) m8[q] = -INFINITY;
-                if (nch > 3) chunk_max8(m8, s);
-                if (nch > 2) chunk_max8(m8, s + 32);
-                if (nch > 1) chunk_max8(m8, s + 64);
-                chunk_max8(m8, s + 96);
+                const uint32_t tP3 = tS + 16 * (nch - 1);
+                float rs = 0.f;
+                bool redo = true;           // (re)compute P against the reference exponent m after the block below
+#if SVR2_SPEC_EXP
+                if (j > 0) {
+                    // Speculative exponentials.  With the lazy rescale the reference exponent of a row changes only when its max
+                    // moves by more than 2^8, so in the common case P(j) depends on the OLD m and not on this tile's row max: the
+                    // exponentials are formed against m while the max is being reduced (two independent instruction streams in
+                    // every chunk instead of a max phase followed by an exp phase), and only a warp in which some row does need a
+                    // new reference rescales O and forms P again.  Same values either way: bit-identical to the two-phase order.
+                    if (nch > 3) {
+                        uint32_t pk[16];
+                        chunk_max8(m8, s);
+                        rs = chunk_exp_mix<kFmaEighths>(s, pk, m);
+                        tmem_st16(tP3 - 48, pk);
+                    }
+                    if (nch > 2) {
+                        uint32_t pk[16];
+                        chunk_max8(m8, s + 32);
+                        rs += chunk_exp_mix<kFmaEighths>(s + 32, pk, m);
+                        tmem_st16(tP3 - 32, pk);
+                    }
+                    if (nch > 1) {
+                        uint32_t pk[16];
+                        chunk_max8(m8, s + 64);
+                        rs += chunk_exp_mix<kFmaEighths>(s + 64, pk, m);
+                        tmem_st16(tP3 - 16, pk);
+                    }
+                    {
+                        uint32_t pk[16];
+                        chunk_max8(m8, s + 96);
+                        rs += chunk_exp_mix<kFmaEighths>(s + 96, pk, m);
+                        tmem_st16(tP3, pk);
+                    }
+                    redo = false;
+                } else
+#endif
+                {
+                    if (nch > 3) chunk_max8(m8, s);
+                    if (nch > 2) chunk_max8(m8, s + 32);
+                    if (nch > 1) chunk_max8(m8, s + 64);
+                    chunk_max8(m8, s + 96);
+                }
                 const float mx = fmaxf(max3(m8[0], m8[1], m8[2]), max3(max3(m8[3], m8[4], m8[5]), m8[6], m8[7]));
                 if (j == 0) {
                     m = ref_of(mx);
@@ -684,32 +727,34 @@ window_attn_tc2_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
                             for (int c = 0; c < 16; ++c) ov[c] = __float_as_uint(__uint_as_float(ov[c]) * alpha);
                             tmem_st16(tO + c8 * 16, ov);
                         }
+                        redo = true;
                     }
                 }
-                const float mb = m;
-                // bf16 P overwrites the front of S_i chunk by chunk (the whole row is already in registers); kFmaEighths/8 of the
-                // exponentials run on the FMA pipe, the rest on MUFU
-                const uint32_t tP3 = tS + 16 * (nch - 1);
-                float rs = 0.f;
-                if (nch > 3) {
-                    uint32_t pk[16];
-                    rs = chunk_exp_mix<kFmaEighths>(s, pk, mb);
-                    tmem_st16(tP3 - 48, pk);
-                }
-                if (nch > 2) {
-                    uint32_t pk[16];
-                    rs += chunk_exp_mix<kFmaEighths>(s + 32, pk, mb);
-                    tmem_st16(tP3 - 32, pk);
-                }
-                if (nch > 1) {
-                    uint32_t pk[16];
-                    rs += chunk_exp_mix<kFmaEighths>(s + 64, pk, mb);
-                    tmem_st16(tP3 - 16, pk);
-                }
-                {
-                    uint32_t pk[16];
-                    rs += chunk_exp_mix<kFmaEighths>(s + 96, pk, mb);
-                    tmem_st16(tP3, pk);
+                if (redo) {
+                    const float mb = m;
+                    // bf16 P overwrites the front of S_i chunk by chunk (the whole row is already in registers); kFmaEighths/8 of
+                    // the exponentials run on the FMA pipe, the rest on MUFU
+                    rs = 0.f;
+                    if (nch > 3) {
+                        uint32_t pk[16];
+                        rs = chunk_exp_mix<kFmaEighths>(s, pk, mb);
+                        tmem_st16(tP3 - 48, pk);
+                    }
+                    if (nch > 2) {
+                        uint32_t pk[16];
+                        rs += chunk_exp_mix<kFmaEighths>(s + 32, pk, mb);
+                        tmem_st16(tP3 - 32, pk);
+                    }
+                    if (nch > 1) {
+                        uint32_t pk[16];
+                        rs += chunk_exp_mix<kFmaEighths>(s + 64, pk, mb);
+                        tmem_st16(tP3 - 16, pk);
+                    }
+                    {
+                        uint32_t pk[16];
+                        rs += chunk_exp_mix<kFmaEighths>(s + 96, pk, mb);
+                        tmem_st16(tP3, pk);
+                    }
                 }
                 l += rs;
                 if (SVR2_TURNS && p.turns && lane == 0) atomicAdd(const_cast<uint32_t*>(&turn_cnt[i]), 1u);
