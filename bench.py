@@ -183,11 +183,12 @@ class RefBlockRunner:
     """One transformer block of the reference path at full width: the stock NaMMSRTransformerBlock from baseline/_ref when it
     is staged (`kind` "reference"), else oracle.block.block_forward (`kind` "port")."""
 
-    def __init__(self, model, device, dtype):
+    def __init__(self, model, device, dtype, attention_mode="sdpa"):
         import torch
         from oracle import refstage
         from oracle import workload as owork
         self.torch, self.model, self.device, self.dtype = torch, model, device, dtype
+        self.attention_mode = attention_mode
         self.owork = owork
         self.kind = "reference" if refstage.available() else "port"
         self.refstage = refstage
@@ -206,7 +207,8 @@ class RefBlockRunner:
         sd = self.cache[wkey]
         if self.kind == "reference":
             with torch.device("meta"):
-                blk = self.refstage.build_block(self.model, cfg.dim, cfg.heads, shared=cfg.shared, shifted=shifted)
+                blk = self.refstage.build_block(self.model, cfg.dim, cfg.heads, shared=cfg.shared, shifted=shifted,
+                                                attention_mode=self.attention_mode)
             blk.load_state_dict(sd, strict=True, assign=True)
             blk.eval()
         else:
@@ -642,33 +644,48 @@ def run_ours(args):
 
 def ref_torch_gpu(name, dev, our_value):
     """The reference's own PyTorch path on THIS GPU (SURVEY §8d "the number to beat"): the stock block from baseline/_ref (or the
-    oracle port) in bf16, attention_mode='sdpa' (one F.scaled_dot_product_attention per window), CUDA-event timed per layer kind
-    at the first batch's token grid and extrapolated over layers and batches like the CPU arm."""
+    oracle port) in bf16, CUDA-event timed per layer kind at the first batch's token grid and extrapolated over layers and batches
+    like the CPU arm — with attention_mode='sdpa' (one F.scaled_dot_product_attention per window, the reference's default) and,
+    where the flash-attn package runs on this GPU, attention_mode='flash_attn' (flash_attn_varlen_func, attention.py:64-91)."""
     import torch
     w = WORKLOADS[name]
     g0 = tok_grid(job_layout(name, 1)["ranks"][0]["batches"][0][2])
-    runner = RefBlockRunner(w["model"], dev, torch.bfloat16)
-    vid, txt, emb = runner.inputs(g0)
-    by_kind = {}
-    for sh, sf, _ in layer_kinds(w["model"]):
-        runner.run(sh, sf, g0, vid.clone(), txt.clone(), emb)
-        torch.cuda.synchronize()
-        ts = []
-        for _ in range(3):
-            v, t = vid.clone(), txt.clone()
-            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            e0.record()
-            runner.run(sh, sf, g0, v, t, emb)
-            e1.record()
+
+    def one_mode(mode):
+        runner = RefBlockRunner(w["model"], dev, torch.bfloat16, attention_mode=mode)
+        if mode != "sdpa" and runner.kind != "reference":
+            raise RuntimeError("the oracle port restates the sdpa path only")
+        vid, txt, emb = runner.inputs(g0)
+        by_kind = {}
+        for sh, sf, _ in layer_kinds(w["model"]):
+            runner.run(sh, sf, g0, vid.clone(), txt.clone(), emb)
             torch.cuda.synchronize()
-            ts.append(e0.elapsed_time(e1) * 1e-3)
-        by_kind[(sh, sf)] = sorted(ts)[1]
-    fps, per_forward = extrapolate_fps(name, by_kind)
-    return {"value": fps, "unit": "frames/s", "kind": runner.kind, "dtype": "bf16", "attention_mode": "sdpa",
-            "ms_per_block": {f"{'shared' if sh else 'separate'}_{'swin' if sf else 'win'}": 1e3 * t for (sh, sf), t in by_kind.items()},
-            "ms_per_forward": 1e3 * per_forward, "ours_over_reference_gpu": our_value / fps,
-            "sample": f"median of 3 eager runs of one block per layer kind at token grid {g0[0]}x{g0[1]}x{g0[2]} on this GPU, "
-                      "extrapolated over layers and batches (the reference's shell ops outside the blocks are not counted)"}
+            ts = []
+            for _ in range(3):
+                v, t = vid.clone(), txt.clone()
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+                runner.run(sh, sf, g0, v, t, emb)
+                e1.record()
+                torch.cuda.synchronize()
+                ts.append(e0.elapsed_time(e1) * 1e-3)
+            by_kind[(sh, sf)] = sorted(ts)[1]
+        fps, per_forward = extrapolate_fps(name, by_kind)
+        return runner.kind, fps, per_forward, by_kind
+
+    kind, fps, per_forward, by_kind = one_mode("sdpa")
+    out = {"value": fps, "unit": "frames/s", "kind": kind, "dtype": "bf16", "attention_mode": "sdpa",
+           "ms_per_block": {f"{'shared' if sh else 'separate'}_{'swin' if sf else 'win'}": 1e3 * t for (sh, sf), t in by_kind.items()},
+           "ms_per_forward": 1e3 * per_forward, "ours_over_reference_gpu": our_value / fps,
+           "sample": f"median of 3 eager runs of one block per layer kind at token grid {g0[0]}x{g0[1]}x{g0[2]} on this GPU, "
+                     "extrapolated over layers and batches (the reference's shell ops outside the blocks are not counted)"}
+    try:
+        _, fps_fa, per_forward_fa, _ = one_mode("flash_attn")
+        out["flash_attn"] = {"value": fps_fa, "unit": "frames/s", "ms_per_forward": 1e3 * per_forward_fa,
+                             "ours_over_reference_gpu": our_value / fps_fa, "attention_mode": "flash_attn (flash_attn_varlen_func)"}
+    except Exception as e:       # package absent, or its kernels do not run on sm_100
+        out["flash_attn"] = {"unavailable": f"{type(e).__name__}: {e}"[:200]}
+    return out
 
 
 def main():

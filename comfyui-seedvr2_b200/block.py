@@ -192,23 +192,24 @@ def _joined(a: torch.Tensor, b: torch.Tensor) -> Optional[torch.Tensor]:
 class _GridMemo:
     """vid_shape lives on the GPU (na.py:97); reading it is a D2H sync the reference pays several times per layer.
     The same tensor OBJECT flows through all blocks of a forward, so one sync per forward is enough — also for 7B,
-    whose forward disables the reference Cache (quirk Q2)."""
-    tensor = None
-    version = -1
-    value = None
+    whose forward disables the reference Cache (quirk Q2).  Keyed per tensor object (weak reference + version), so several
+    models driven from one process — other threads, other streams — do not evict each other's entry."""
+    _memo = {}      # id(vid_shape) -> (weakref, version, (grid, txt_len))
 
     @classmethod
     def read(cls, vid_shape: torch.Tensor, txt_shape: torch.Tensor):
-        if cls.tensor is vid_shape and cls.version == vid_shape._version:
-            return cls.value
+        key = id(vid_shape)
+        hit = cls._memo.get(key)
+        if hit is not None and hit[0]() is vid_shape and hit[1] == vid_shape._version:
+            return hit[2]
         vs = vid_shape.tolist()
         ts = txt_shape.tolist()
         if len(vs) != 1 or len(ts) != 1:
             # the pipeline always runs b=1 (generation_phases.py:678,701); b>1 hits reference quirk Q7
             raise NotImplementedError("seedvr2_b200 blocks support batch size 1 only")
-        cls.tensor, cls.version = vid_shape, vid_shape._version
-        cls.value = (tuple(int(v) for v in vs[0]), int(math.prod(ts[0])))
-        return cls.value
+        value = (tuple(int(v) for v in vs[0]), int(math.prod(ts[0])))
+        cls._memo[key] = (weakref.ref(vid_shape, lambda _r, k=key: cls._memo.pop(k, None)), vid_shape._version, value)
+        return value
 
 
 class NaSwinAttentionB200(nn.Module):

@@ -135,3 +135,70 @@ def test_fullwidth_block_vs_stock_reference_block_on_gpu(svr2, cuda, model, grid
           f" | oracle vs stock: vid {o_v:.4f} txt {o_t:.4f} | |out|max {float(rv.float().abs().max()):.2f}")
     assert d_v <= 2e-2 and d_t <= 2e-2
     assert o_v <= 2e-2 and o_t <= 2e-2, "the oracle has drifted from the stock reference block at full width"
+
+
+@pytest.mark.parametrize("model", ["3b", "7b"])
+def test_reference_nadit_full_width_installed_vs_stock_on_gpu(svr2, cuda, model):
+    """The drop-in at the REAL widths (configs_3b: D = 2560, 20 heads, SwiGLU 6912, separate + shared + last layer; configs_7b:
+    D = 3072, 24 heads, GELU 12288; 4 layers of each): the reference's NaDiT built twice from the same kwargs and the same random
+    state dict — once with the stock blocks, once after install() — both in bf16 on the same GPU, real Cache, autocast.  The two
+    outputs differ only by what the blocks do: PSNR >= 45 dB (north star) and no further from the fp32 stock model than the stock
+    bf16 model is."""
+    import math
+    NaDiT = refstage.nadit_class(model)
+    mm = 2 if model == "3b" else None
+    kw = refstage.nadit_kwargs(model, num_layers=4, mm_layers=mm, txt_in_dim=512)
+    torch.manual_seed(7)
+    with torch.device("meta"):
+        probe = NaDiT(**kw)
+    g = torch.Generator().manual_seed(17)
+    sd = {}
+    for k, v in probe.state_dict().items():
+        if k.endswith("freqs"):
+            sd[k] = cases.rope_freqs(model)
+        elif k.endswith(("_scale", "norm_q.vid.weight", "norm_k.vid.weight", "norm_q.txt.weight", "norm_k.txt.weight", "norm_q.all.weight",
+                         "norm_k.all.weight", "vid_out_norm.weight")):
+            sd[k] = (1.0 + 0.05 * torch.randn(v.shape, generator=g)).bfloat16()
+        elif v.dim() >= 2:
+            sd[k] = (torch.randn(v.shape, generator=g) / math.sqrt(v.shape[-1])).bfloat16()
+        else:
+            sd[k] = (0.02 * torch.randn(v.shape, generator=g)).bfloat16()
+    grid = (2, 48, 80)                       # latent grid -> 2 x 24 x 40 tokens
+    vid = torch.randn(grid[0] * grid[1] * grid[2], 33, generator=g).bfloat16().to(cuda)
+    txt = (0.25 * torch.randn(58, 512, generator=g)).bfloat16().to(cuda)
+    vs = torch.tensor([list(grid)], device=cuda)
+    ts = torch.tensor([[58]], device=cuda)
+    t = torch.tensor([1000.0], device=cuda)
+    fkw = dict(disable_cache=False) if model == "3b" else {}
+
+    def build(dtype):
+        with torch.device("meta"):
+            m = NaDiT(**kw)
+        state = {k: (v.float() if k.endswith("freqs") else v.to(dtype)).to(cuda) for k, v in sd.items()}
+        missing, unexpected = m.load_state_dict(state, strict=False, assign=True)
+        assert not missing and not unexpected
+        for mod in m.modules():
+            for name, buf in list(mod._buffers.items()):
+                if buf is not None and buf.is_meta:
+                    mod._buffers[name] = torch.zeros(buf.shape, dtype=buf.dtype, device=cuda)
+        return m.eval()
+
+    with torch.no_grad():
+        stock32 = build(torch.float32)(vid.float(), txt.float(), vs, ts, t, **fkw).vid_sample
+        stock16 = build(torch.bfloat16)(vid, txt, vs, ts, t, **fkw).vid_sample
+        svr2.install()
+        try:
+            ours_model = build(torch.bfloat16)
+            ours_cls = svr2.NaMMSRTransformerBlockB200 if model == "3b" else svr2.NaMMSRTransformerBlockB200_7B
+            assert all(type(b) is ours_cls for b in ours_model.blocks)
+            with torch.autocast("cuda", dtype=torch.bfloat16):
+                ours = ours_model(vid, txt, vs, ts, t, **fkw).vid_sample
+        finally:
+            svr2.uninstall()
+    torch.cuda.synchronize()
+    p_vs16 = cases.psnr(ours.float().cpu(), stock16.float().cpu())
+    p_vs32 = cases.psnr(ours.float().cpu(), stock32.cpu())
+    p_ref = cases.psnr(stock16.float().cpu(), stock32.cpu())
+    print(f"\n{model} full width, 4 layers: install()ed vs stock bf16 {p_vs16:.1f} dB | vs stock fp32: ours {p_vs32:.1f} dB, stock bf16 {p_ref:.1f} dB")
+    assert p_vs16 >= 45.0 and p_vs32 >= 45.0
+    assert p_vs32 >= p_ref - 1.0
