@@ -139,8 +139,6 @@ class _GeluMLP(nn.Module):     # reference mlp.py:28-43
         """gelu_tanh(proj_in(x)): bias + activation in the GEMM epilogue; the [L, 4D] pre-activation never reaches HBM."""
         if USE_TC_GEMM and x.is_cuda and x.dim() == 2:
             return ops.linear(x.contiguous(), _bf16(self.proj_in.weight), _bf16(self.proj_in.bias), ops.ACT_GELU_TANH)
-        if x.is_cuda and x.dim() == 2:      # round 1: cuBLASLt epilogue
-            return torch._addmm_activation(_bf16(self.proj_in.bias), x, _bf16(self.proj_in.weight).t(), use_gelu=True)
         return F.gelu(F.linear(x, _bf16(self.proj_in.weight), _bf16(self.proj_in.bias)), approximate="tanh")
 
     def forward(self, x):

@@ -58,6 +58,23 @@ def test_new_entry_points_validate_their_arguments_before_launching(svr2):
     n = ctypes.c_int64(0)
     assert L.svr2_window_attn_worklist_tiles(None, 1, 58, 4, None, 0, ctypes.byref(n)) == -1
     assert b"worklist" in L.svr2_last_error()
+    # round 2: GEMMs, fused qkv projection and its plan tables, post-processing
+    one = ctypes.c_void_p(16)      # a non-null pointer that is never dereferenced: every call below fails validation first
+    assert L.svr2_linear_fwd(one, one, None, one, 8, 60, 64, 0, None) == -1 and b"multiple of 64" in L.svr2_last_error()
+    assert L.svr2_linear_fwd(one, one, None, one, 8, 64, 64, 7, None) == -1 and b"activation" in L.svr2_last_error()
+    assert L.svr2_linear_swiglu_fwd(one, one, None, one, 8, 128, 64, None) == -1
+    assert L.svr2_linear_gate_residual_fwd(one, one, None, one, one, 2, one, one, 8, 64, 64, None) == -1 and b"layer" in L.svr2_last_error()
+    assert L.svr2_linear_qkv_pack_fwd(one, one, 8, 64, 3, one, None, 0, 0, one, one, one, one, 1e-5, one, one, one, one, None) == -1
+    assert b"even" in L.svr2_last_error()
+    assert L.svr2_linear_qkv_pack_fwd(one, one, 8, 64, 2, one, one, 4, 7, one, one, one, one, 1e-5, one, one, one, one, None) == -1
+    assert b"n_freqs" in L.svr2_last_error()
+    assert L.svr2_linear_qkv_pack_fwd(one, one, 8, 64, 2, one, one, 4000, 21, one, one, one, one, 1e-5, one, one, one, one, None) == -1
+    assert b"shared memory" in L.svr2_last_error()
+    assert L.svr2_rope_plan(None, None, 1, 1, 8, 8, 58, 100, 1, None, 21, None, 70, None, None, None) == -1
+    assert L.svr2_txt_replicate_fwd(None, None, 0, 58, 2, None, None, None, None) == -1
+    assert L.svr2_wavelet_level_fwd(one, 1, 1, 1, 1, one, None, 1, 1, 3, 8, 8, 0, 0, None) == -1 and b"radius" in L.svr2_last_error()
+    assert L.svr2_wavelet_level_fwd(one, 1, 1, 1, 1, one, None, 1, 1, 3, 8, 8, 1, 5, None) == -1 and b"dtype" in L.svr2_last_error()
+    assert L.svr2_colorfix_finish_fwd(one, one, None, None, 0, 1, 3, 8, 8, 0, None) == -1
 
 
 @pytest.mark.parametrize("key", sorted(GEO))
