@@ -101,13 +101,6 @@ enum { BAR_QFULL = 0, BAR_QEMPTY = 2, BAR_SFULL = 4, BAR_PREADY = 6, BAR_OFINAL 
 #ifndef SVR2_V2_SPLIT_QK
 #define SVR2_V2_SPLIT_QK 0
 #endif
-#ifndef SVR2_TWO_PASS
-#define SVR2_TWO_PASS 1     // softmax: S is read from TMEM twice (whole row for the max, then chunk by chunk for the exponentials)
-#endif
-#ifndef SVR2_SPEC_EXP
-#define SVR2_SPEC_EXP 0     // 1: exponentials against the current reference WHILE the row max is reduced.  Bit-identical, and 12-14 % slower
-                            // (run 18: C2 920 against 1,046 TFLOP/s, v1080 836 against 986) — the max phase is not what the step waits for
-#endif
 #ifndef SVR2_TURNS
 #define SVR2_TURNS 0      // measured: the bounded counter version gains nothing (see the comment in the softmax role); kept for experiments
 #endif
@@ -118,7 +111,6 @@ enum { BAR_QFULL = 0, BAR_QEMPTY = 2, BAR_SFULL = 4, BAR_PREADY = 6, BAR_OFINAL 
 #define SVR2_TURN_SLEEP 20        // ns between polls of the turn counter
 #endif
 static_assert(BAR_COUNT * 8 + 8 <= 256, "barrier block too small");
-static_assert(!(SVR2_TWO_PASS && (SVR2_SPEC_EXP || SVR2_V2_SPLIT_QK)), "the experiment paths keep the whole S row in registers: build them with -DSVR2_TWO_PASS=0");
 
 struct Params {
     const int32_t* tab;
@@ -652,35 +644,8 @@ window_attn_tc2_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
                 }
                 // The whole S row in registers: ONE TMEM round trip per key tile.  Register block b holds chunk nch - 4 + b,
                 // so the chunk with the end of the sequence is always block 3 and the masking code exists once.
-                const uint32_t tS3 = tS + 32 * (nch - 1);
-                const uint32_t tP3 = tS + 16 * (nch - 1);
-                float m8[8];
-#pragma unroll
-                for (int q = 0; q < 8; ++q) m8[q] = -INFINITY;
-                float rs = 0.f;
-                bool redo = true;           // (re)compute P against the reference exponent m after the block below
-#if SVR2_TWO_PASS
-                // Two passes over S straight from TMEM, 32 columns at a time with the next chunk's load in flight (buffers sa / sb by
-                // block parity): nothing of the row stays in registers between the max pass and the exp pass, so the exp pass has
-                // ~100 free registers to interleave independent pairs instead of the two or three that fit beside a whole row.
-                // Register block b still holds chunk nch - 4 + b, so the chunk with the end of the sequence is always block 3.
-                const bool tail = valid < nch * 32;                                     // only in the last key tile of a sequence
-                uint32_t sa[32], sb[32];
-                if (nch > 3) tmem_ld32(tS3 - 96, sa);
-                else if (nch > 2) tmem_ld32(tS3 - 64, sb);
-                else if (nch > 1) tmem_ld32(tS3 - 32, sa);
-                else tmem_ld32(tS3, sb);
-                if (nch > 3) { tc_wait_ld(); tmem_ld32(tS3 - 64, sb); chunk_max8(m8, sa); }
-                if (nch > 2) { tc_wait_ld(); tmem_ld32(tS3 - 32, sa); chunk_max8(m8, sb); }
-                if (nch > 1) { tc_wait_ld(); tmem_ld32(tS3, sb); chunk_max8(m8, sa); }
-                tc_wait_ld();
-                // the exp pass starts with the same first chunk: for a full tile its load goes out now, under the reduction and
-                // the rescale decision (sa is free; sb holds the last chunk until its max is taken)
-                if (nch > 3) tmem_ld32(tS3 - 96, sa);
-                if (tail) mask_chunk(sb, valid - 32 * (nch - 1));
-                chunk_max8(m8, sb);
-#else
                 uint32_t s[128];
+                const uint32_t tS3 = tS + 32 * (nch - 1);
                 if (nch > 3) tmem_ld32(tS3 - 96, s);
                 if (nch > 2) tmem_ld32(tS3 - 64, s + 32);
                 if (nch > 1) tmem_ld32(tS3 - 32, s + 64);
@@ -691,49 +656,13 @@ window_attn_tc2_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
                 mbar_arrive(bar(BAR_SLOADED + i));                                     // the upper half of S_i may be overwritten
 #endif
                 if (valid < nch * 32) mask_chunk(s + 96, valid - 32 * (nch - 1));      // only in the last key tile of a sequence
-#endif
-#if SVR2_SPEC_EXP
-                if (j > 0) {
-                    // Speculative exponentials.  With the lazy rescale the reference exponent of a row changes only when its max
-                    // moves by more than 2^8, so in the common case P(j) depends on the OLD m and not on this tile's row max: the
-                    // exponentials are formed against m while the max is being reduced (two independent instruction streams in
-                    // every chunk instead of a max phase followed by an exp phase), and only a warp in which some row does need a
-                    // new reference rescales O and forms P again.  Same values either way: bit-identical to the two-phase order.
-                    if (nch > 3) {
-                        uint32_t pk[16];
-                        chunk_max8(m8, s);
-                        rs = chunk_exp_mix<kFmaEighths>(s, pk, m);
-                        tmem_st16(tP3 - 48, pk);
-                    }
-                    if (nch > 2) {
-                        uint32_t pk[16];
-                        chunk_max8(m8, s + 32);
-                        rs += chunk_exp_mix<kFmaEighths>(s + 32, pk, m);
-                        tmem_st16(tP3 - 32, pk);
-                    }
-                    if (nch > 1) {
-                        uint32_t pk[16];
-                        chunk_max8(m8, s + 64);
-                        rs += chunk_exp_mix<kFmaEighths>(s + 64, pk, m);
-                        tmem_st16(tP3 - 16, pk);
-                    }
-                    {
-                        uint32_t pk[16];
-                        chunk_max8(m8, s + 96);
-                        rs += chunk_exp_mix<kFmaEighths>(s + 96, pk, m);
-                        tmem_st16(tP3, pk);
-                    }
-                    redo = false;
-                } else
-#endif
-                {
-#if !SVR2_TWO_PASS
-                    if (nch > 3) chunk_max8(m8, s);
-                    if (nch > 2) chunk_max8(m8, s + 32);
-                    if (nch > 1) chunk_max8(m8, s + 64);
-                    chunk_max8(m8, s + 96);
-#endif
-                }
+                float m8[8];
+#pragma unroll
+                for (int q = 0; q < 8; ++q) m8[q] = -INFINITY;
+                if (nch > 3) chunk_max8(m8, s);
+                if (nch > 2) chunk_max8(m8, s + 32);
+                if (nch > 1) chunk_max8(m8, s + 64);
+                chunk_max8(m8, s + 96);
                 const float mx = fmaxf(max3(m8[0], m8[1], m8[2]), max3(max3(m8[3], m8[4], m8[5]), m8[6], m8[7]));
                 if (j == 0) {
                     m = ref_of(mx);
@@ -755,78 +684,33 @@ window_attn_tc2_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
                             for (int c = 0; c < 16; ++c) ov[c] = __float_as_uint(__uint_as_float(ov[c]) * alpha);
                             tmem_st16(tO + c8 * 16, ov);
                         }
-                        redo = true;
                     }
                 }
-#if SVR2_TWO_PASS
-                if (redo) {
-                    // Second pass over S straight from TMEM, 32 columns at a time with the next chunk's load in flight: the 128
-                    // registers of the row die after the max pass, so the exp phase has ~100 free registers to interleave many
-                    // independent pairs instead of the two or three that fit beside a whole row.  P chunk c (16 packed columns at
-                    // 16 c) only ever lands on S columns of chunks the thread has already consumed.  Same arithmetic, same bits.
-                    const float mb = m;
-                    rs = 0.f;
-                    // (the first chunk of a four-chunk tile is already on its way, see the max pass)
-                    if (nch == 3) tmem_ld32(tS3 - 64, sb);
-                    else if (nch == 2) tmem_ld32(tS3 - 32, sa);
-                    else if (nch == 1) tmem_ld32(tS3, sb);
-                    if (nch > 3) {
-                        uint32_t pk[16];
-                        tc_wait_ld();
-                        tmem_ld32(tS3 - 64, sb);
-                        rs = chunk_exp_mix<kFmaEighths>(sa, pk, mb);
-                        tmem_st16(tP3 - 48, pk);
-                    }
-                    if (nch > 2) {
-                        uint32_t pk[16];
-                        tc_wait_ld();
-                        tmem_ld32(tS3 - 32, sa);
-                        rs += chunk_exp_mix<kFmaEighths>(sb, pk, mb);
-                        tmem_st16(tP3 - 32, pk);
-                    }
-                    if (nch > 1) {
-                        uint32_t pk[16];
-                        tc_wait_ld();
-                        tmem_ld32(tS3, sb);
-                        rs += chunk_exp_mix<kFmaEighths>(sa, pk, mb);
-                        tmem_st16(tP3 - 16, pk);
-                    }
-                    {
-                        uint32_t pk[16];
-                        tc_wait_ld();
-                        if (tail) mask_chunk(sb, valid - 32 * (nch - 1));
-                        rs += chunk_exp_mix<kFmaEighths>(sb, pk, mb);
-                        tmem_st16(tP3, pk);
-                    }
+                const float mb = m;
+                // bf16 P overwrites the front of S_i chunk by chunk (the whole row is already in registers); kFmaEighths/8 of the
+                // exponentials run on the FMA pipe, the rest on MUFU
+                const uint32_t tP3 = tS + 16 * (nch - 1);
+                float rs = 0.f;
+                if (nch > 3) {
+                    uint32_t pk[16];
+                    rs = chunk_exp_mix<kFmaEighths>(s, pk, mb);
+                    tmem_st16(tP3 - 48, pk);
                 }
-#else
-                if (redo) {
-                    const float mb = m;
-                    // bf16 P overwrites the front of S_i chunk by chunk (the whole row is already in registers); kFmaEighths/8 of
-                    // the exponentials run on the FMA pipe, the rest on MUFU
-                    rs = 0.f;
-                    if (nch > 3) {
-                        uint32_t pk[16];
-                        rs = chunk_exp_mix<kFmaEighths>(s, pk, mb);
-                        tmem_st16(tP3 - 48, pk);
-                    }
-                    if (nch > 2) {
-                        uint32_t pk[16];
-                        rs += chunk_exp_mix<kFmaEighths>(s + 32, pk, mb);
-                        tmem_st16(tP3 - 32, pk);
-                    }
-                    if (nch > 1) {
-                        uint32_t pk[16];
-                        rs += chunk_exp_mix<kFmaEighths>(s + 64, pk, mb);
-                        tmem_st16(tP3 - 16, pk);
-                    }
-                    {
-                        uint32_t pk[16];
-                        rs += chunk_exp_mix<kFmaEighths>(s + 96, pk, mb);
-                        tmem_st16(tP3, pk);
-                    }
+                if (nch > 2) {
+                    uint32_t pk[16];
+                    rs += chunk_exp_mix<kFmaEighths>(s + 32, pk, mb);
+                    tmem_st16(tP3 - 32, pk);
                 }
-#endif
+                if (nch > 1) {
+                    uint32_t pk[16];
+                    rs += chunk_exp_mix<kFmaEighths>(s + 64, pk, mb);
+                    tmem_st16(tP3 - 16, pk);
+                }
+                {
+                    uint32_t pk[16];
+                    rs += chunk_exp_mix<kFmaEighths>(s + 96, pk, mb);
+                    tmem_st16(tP3, pk);
+                }
                 l += rs;
                 if (SVR2_TURNS && p.turns && lane == 0) atomicAdd(const_cast<uint32_t*>(&turn_cnt[i]), 1u);
                 tc_wait_st();
