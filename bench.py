@@ -579,6 +579,8 @@ def run_ours(args):
                 "frac_of_burst_peak": gtf / pk["bf16_tflops"], "algorithmic_flops_per_step": lin_flops, "ms_per_step": gemm_ms,
                 "launches_per_step": gemm_n, "share_of_step": gemm_ms / (ms_eager_total / steps_1b) if ms_eager_total else None,
                 "timing": "CUDA events around every GEMM launch, one step launched kernel by kernel (per-kernel pass)"}
+    if gemm is not None:      # the step's dominant kernels by time, summarised beside the attention roofline the metric names
+        roofline["gemm"] = {k: gemm[k] for k in ("bound", "achieved", "peak", "unit", "frac", "share_of_step")}
     # ---- HBM-bound kernels: algorithmic bytes per launch, bf16
     qkvb = 3 * heads * 128 * 2
     n_b = len(job.grids)

@@ -13,7 +13,7 @@ from .block import NaMMSRTransformerBlockB200, NaMMSRTransformerBlockB200_7B, Na
 from .plan import WindowPlan, get_plan
 from .stack import NaDiTStack
 
-__all__ = ["install", "uninstall", "build_extension", "NaMMSRTransformerBlockB200", "NaMMSRTransformerBlockB200_7B",
+__all__ = ["install", "uninstall", "convert_parameters_", "build_extension", "NaMMSRTransformerBlockB200", "NaMMSRTransformerBlockB200_7B",
            "NaSwinAttentionB200", "NaDiTStack", "WindowPlan", "get_plan", "ops", "plan"]
 
 _saved = {}
@@ -35,6 +35,25 @@ def install(models_pkg: str = "src.models") -> None:
         mod = importlib.import_module(f"{models_pkg}.{sub}.nablocks")
         _saved.setdefault((models_pkg, sub), mod.nadit_blocks["mmdit_sr"])
         mod.nadit_blocks["mmdit_sr"] = cls
+
+
+def convert_parameters_(model) -> int:
+    """Optional, after the checkpoint is loaded: rewrite the parameters of every B200 block in ``model`` to bf16 IN PLACE
+    (``param.data``), keeping ``attn.rope.rope.freqs`` in its loaded dtype.  Checkpoints loaded with ``assign=True`` keep the file's
+    dtype (fp16 for the shipped files, model_loader.py:809); the blocks then cast each such parameter once and keep the bf16 copy
+    next to the original (block._bf16), which doubles the weight memory (+7 GB for 3B, +16 GB for 7B) and survives a BlockSwap
+    offload of the original.  After this call there is one copy.  Returns the number of tensors converted."""
+    import torch
+    from .block import _BlockBase, _cast_cache
+    n = 0
+    for mod in model.modules():
+        if isinstance(mod, _BlockBase):
+            for name, p in mod.named_parameters():
+                if p.dtype != torch.bfloat16 and p.dtype.is_floating_point:
+                    p.data = p.data.to(torch.bfloat16)
+                    n += 1
+    _cast_cache.clear()
+    return n
 
 
 def uninstall(models_pkg: str = "src.models") -> None:

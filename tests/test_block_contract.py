@@ -70,3 +70,18 @@ def test_non_bf16_parameters_are_cast_once(svr2):
     assert b is not a and torch.equal(b, p.detach().to(torch.bfloat16))
     q = torch.nn.Parameter(torch.randn(4).bfloat16())
     assert _bf16(q) is q
+
+
+def test_convert_parameters_in_place(svr2):
+    """fp16 checkpoint parameters (assign=True keeps the file's dtype) can be rewritten to bf16 in place: one copy instead of the
+    original + the block's lazily cast bf16 copy; the checkpoint's rope frequencies keep their dtype."""
+    c = cases.BLOCK_CASES[0]
+    with torch.device("meta"):
+        blk = make_block(svr2, c)
+    sd = {k: (v if k.endswith("freqs") else v.half()) for k, v in cases.block_params(c).items()}
+    blk.load_state_dict(sd, strict=True, assign=True)
+    holder = torch.nn.ModuleList([blk])
+    n = svr2.convert_parameters_(holder)
+    assert n == sum(1 for _ in blk.parameters()) and all(p.dtype == torch.bfloat16 for p in blk.parameters())
+    assert blk.attn.rope.rope.freqs.dtype == torch.float32
+    assert svr2.convert_parameters_(holder) == 0
