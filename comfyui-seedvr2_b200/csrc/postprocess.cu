@@ -86,6 +86,89 @@ __global__ void __launch_bounds__(256) colorfix_finish_kernel(const void* __rest
     }
 }
 
+// ---- LAB colour transfer (the CLI's default colour correction, color_fix.py:249-470): the two colour-space conversions.
+// The histogram matching between them (color_fix.py:473-513) is a global sort + scatter per channel and stays on torch's
+// sort (comfyui-seedvr2_b200/postprocess.py).  Arithmetic follows the reference's fp32 tensor ops one by one (separately
+// rounded, powf as ATen's pow kernel calls it, x*x*x for the cube as ATen special-cases exponent 3); the 3x3 colour matrix is a
+// library matmul in the reference, whose summation order is unspecified — the products are summed in index order here.
+__device__ __forceinline__ float srgb_to_linear(float v) {
+    return v > 0.04045f ? powf(__fdiv_rn(__fadd_rn(v, 0.055f), 1.055f), 2.4f) : __fdiv_rn(v, 12.92f);
+}
+__device__ __forceinline__ float dot3(float a0, float a1, float a2, float m0, float m1, float m2) {
+    return fmaf(a2, m2, fmaf(a1, m1, __fmul_rn(a0, m0)));
+}
+__device__ __forceinline__ float lab_f(float v) {
+    const float eps3 = (float)((6.0 / 29.0) * (6.0 / 29.0) * (6.0 / 29.0));
+    const float kappa = (float)((29.0 / 3.0) * (29.0 / 3.0) * (29.0 / 3.0));
+    return v > eps3 ? powf(v, (float)(1.0 / 3.0)) : __fdiv_rn(__fadd_rn(__fmul_rn(v, kappa), 16.0f), 116.0f);
+}
+
+// lab[t, {L,a,b}, y, x] (fp32) from rgb[t, {r,g,b}, y, x] in [-1, 1]; with `add` != NULL the input is clamp(rnd(rgb + add), -1, 1)
+// (wavelet_reconstruction's combine, so that the LAB path does not need the reconstructed image in memory)
+template <bool BF16>
+__global__ void __launch_bounds__(256) rgb_to_lab_kernel(const void* __restrict__ rgb, const void* __restrict__ add,
+                                                         float* __restrict__ lab, int64_t plane, int64_t n_pix) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;       // pixel index over [T, H, W]
+    if (i >= n_pix) return;
+    const int64_t t = i / plane, p = i - t * plane, base = t * 3 * plane + p;
+    float c[3];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        float v = ld<BF16>(rgb, base + k * plane);
+        if (add != nullptr) v = fminf(fmaxf(rnd<BF16>(__fadd_rn(v, ld<BF16>(add, base + k * plane))), -1.f), 1.f);
+        v = fminf(fmaxf(__fmul_rn(__fadd_rn(v, 1.0f), 0.5f), 0.f), 1.f);       // .add_(1).mul_(0.5).clamp_(0, 1) in fp32
+        c[k] = srgb_to_linear(v);
+    }
+    float X = dot3(c[0], c[1], c[2], 0.4124564f, 0.3575761f, 0.1804375f);
+    const float Y = dot3(c[0], c[1], c[2], 0.2126729f, 0.7151522f, 0.0721750f);
+    float Z = dot3(c[0], c[1], c[2], 0.0193339f, 0.1191920f, 0.9503041f);
+    X = __fdiv_rn(X, 0.95047f);
+    Z = __fdiv_rn(Z, 1.08883f);
+    const float fx = lab_f(X), fy = lab_f(Y), fz = lab_f(Z);
+    lab[base] = __fsub_rn(__fmul_rn(fy, 116.0f), 16.0f);
+    lab[base + plane] = __fmul_rn(__fsub_rn(fx, fy), 500.0f);
+    lab[base + 2 * plane] = __fmul_rn(__fsub_rn(fy, fz), 200.0f);
+}
+
+__device__ __forceinline__ float lab_finv(float f) {
+    const float eps = (float)(6.0 / 29.0);
+    const float kappa = (float)((29.0 / 3.0) * (29.0 / 3.0) * (29.0 / 3.0));
+    return f > eps ? __fmul_rn(__fmul_rn(f, f), f) : __fdiv_rn(__fsub_rn(__fmul_rn(f, 116.0f), 16.0f), kappa);
+}
+__device__ __forceinline__ float linear_to_srgb(float v) {
+    return v > 0.0031308f ? __fsub_rn(__fmul_rn(powf(fmaxf(v, 0.f), (float)(1.0 / 2.4)), 1.055f), 0.055f) : __fmul_rn(v, 12.92f);
+}
+
+// lab (fp32, planar) -> rgb in [-1, 1] rounded to the pipeline dtype (`result.to(original_dtype)`), then the batch normalisation
+// clamp(-1, 1) * 0.5 + 0.5 and the writer's conversion, as colorfix_finish_kernel
+template <bool BF16>
+__global__ void __launch_bounds__(256) lab_to_rgb_finish_kernel(const float* __restrict__ lab, void* __restrict__ out,
+                                                                uint8_t* __restrict__ out_u8, int bgr, int64_t plane, int64_t n_pix) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_pix) return;
+    const int64_t t = i / plane, p = i - t * plane, base = t * 3 * plane + p;
+    const float L = lab[base], a = lab[base + plane], b = lab[base + 2 * plane];
+    const float fy = __fdiv_rn(__fadd_rn(L, 16.0f), 116.0f);
+    const float fx = __fadd_rn(__fdiv_rn(a, 500.0f), fy);
+    const float fz = __fsub_rn(fy, __fdiv_rn(b, 200.0f));
+    const float X = __fmul_rn(lab_finv(fx), 0.95047f), Y = lab_finv(fy), Z = __fmul_rn(lab_finv(fz), 1.08883f);
+    float c[3];
+    c[0] = dot3(X, Y, Z, 3.2404542f, -1.5371385f, -0.4985314f);
+    c[1] = dot3(X, Y, Z, -0.9692660f, 1.8760108f, 0.0415560f);
+    c[2] = dot3(X, Y, Z, 0.0556434f, -0.2040259f, 1.0572252f);
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        float v = fminf(fmaxf(linear_to_srgb(c[k]), 0.f), 1.f);
+        v = rnd<BF16>(__fsub_rn(__fmul_rn(v, 2.0f), 1.0f));                  // .mul_(2).sub_(1) in fp32, then back to the pipeline dtype
+        v = fminf(fmaxf(v, -1.f), 1.f);
+        v = rnd<BF16>(__fmul_rn(v, 0.5f));
+        v = rnd<BF16>(__fadd_rn(v, 0.5f));
+        const int64_t o = i * 3 + k;                                          // [T, H, W, C]
+        if (out != nullptr) st<BF16>(out, o, v);
+        if (out_u8 != nullptr) out_u8[i * 3 + (bgr ? 2 - k : k)] = (uint8_t)(int)__fmul_rn(v, 255.0f);
+    }
+}
+
 }  // namespace post
 }  // namespace svr2
 
@@ -118,5 +201,32 @@ extern "C" int svr2_colorfix_finish_fwd(const void* high, const void* low_style,
     else
         svr2::post::colorfix_finish_kernel<false><<<blocks, 256, 0, st>>>(high, low_style, out, (uint8_t*)out_u8, bgr, C, H, W, n);
     SVR2_CHECK_LAUNCH("svr2_colorfix_finish_fwd");
+    return SVR2_OK;
+}
+
+extern "C" int svr2_rgb_to_lab_fwd(const void* rgb, const void* add, float* lab, int T, int H, int W, int dtype, void* stream) {
+    SVR2_CHECK_ARG(rgb && lab && T > 0 && H > 0 && W > 0, "svr2_rgb_to_lab_fwd: bad arguments");
+    SVR2_CHECK_ARG(dtype == SVR2_DTYPE_F32 || dtype == SVR2_DTYPE_BF16, "svr2_rgb_to_lab_fwd: dtype must be SVR2_DTYPE_F32 or SVR2_DTYPE_BF16");
+    const int64_t plane = (int64_t)H * W, n = plane * T;
+    const unsigned blocks = (unsigned)((n + 255) / 256);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (dtype == SVR2_DTYPE_BF16) svr2::post::rgb_to_lab_kernel<true><<<blocks, 256, 0, st>>>(rgb, add, lab, plane, n);
+    else svr2::post::rgb_to_lab_kernel<false><<<blocks, 256, 0, st>>>(rgb, add, lab, plane, n);
+    SVR2_CHECK_LAUNCH("svr2_rgb_to_lab_fwd");
+    return SVR2_OK;
+}
+
+extern "C" int svr2_lab_to_rgb_finish_fwd(const float* lab, void* out, void* out_u8, int bgr, int T, int H, int W, int dtype,
+                                          void* stream) {
+    SVR2_CHECK_ARG(lab && (out || out_u8) && T > 0 && H > 0 && W > 0, "svr2_lab_to_rgb_finish_fwd: bad arguments");
+    SVR2_CHECK_ARG(dtype == SVR2_DTYPE_F32 || dtype == SVR2_DTYPE_BF16, "svr2_lab_to_rgb_finish_fwd: dtype must be SVR2_DTYPE_F32 or SVR2_DTYPE_BF16");
+    const int64_t plane = (int64_t)H * W, n = plane * T;
+    const unsigned blocks = (unsigned)((n + 255) / 256);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (dtype == SVR2_DTYPE_BF16)
+        svr2::post::lab_to_rgb_finish_kernel<true><<<blocks, 256, 0, st>>>(lab, out, (uint8_t*)out_u8, bgr, plane, n);
+    else
+        svr2::post::lab_to_rgb_finish_kernel<false><<<blocks, 256, 0, st>>>(lab, out, (uint8_t*)out_u8, bgr, plane, n);
+    SVR2_CHECK_LAUNCH("svr2_lab_to_rgb_finish_fwd");
     return SVR2_OK;
 }

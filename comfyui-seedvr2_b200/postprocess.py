@@ -68,3 +68,54 @@ def wavelet_color_fix(sample: torch.Tensor, style: torch.Tensor, want_float: boo
               None if out is None else out.data_ptr(), None if out_u8 is None else out_u8.data_ptr(), int(bgr), T, C, H, W,
               _dtype_code(sample), ops._stream(sample))
     return out, out_u8
+
+
+def _histogram_match(source: torch.Tensor, reference: torch.Tensor) -> torch.Tensor:
+    """_histogram_matching_channel (color_fix.py:473-513) for equal element counts: rank-wise replacement of the source values by
+    the reference values.  A global sort + scatter — torch's radix sort, as in the reference."""
+    flat = source.reshape(-1)
+    _, idx = torch.sort(flat)
+    ref_sorted, _ = torch.sort(reference.reshape(-1))
+    out = torch.empty_like(flat)
+    out.scatter_(0, idx, ref_sorted)
+    return out.reshape(source.shape)
+
+
+@torch._dynamo.disable
+def lab_color_fix(sample: torch.Tensor, style: torch.Tensor, luminance_weight: float = 0.8, want_float: bool = True,
+                  want_uint8: bool = False, bgr: bool = False) -> Tuple[Optional[torch.Tensor], Optional[torch.Tensor]]:
+    """``lab_color_transfer(sample, style, luminance_weight)`` (color_fix.py:249-367, the CLI's default ``--color_correction lab``)
+    followed by the batch normalisation and, on request, the writer's uint8 conversion — same return convention as
+    ``wavelet_color_fix``.  RGB only (the pipeline strips and re-attaches alpha around the colour correction)."""
+    if not sample.is_cuda or not style.is_cuda:
+        raise RuntimeError("seedvr2_b200.postprocess: frames must live on a CUDA device; there is no CPU path")
+    if sample.dim() != 4 or sample.shape != style.shape or sample.shape[1] != 3:
+        raise NotImplementedError(f"lab_color_fix: sample {tuple(sample.shape)} and style {tuple(style.shape)} must be equal [T, 3, H, W]")
+    if style.dtype != sample.dtype:
+        style = style.to(sample.dtype)
+    code = _dtype_code(sample)
+    T, C, H, W = sample.shape
+    dev = sample.device
+    high, _ = _decompose(sample, True)                    # step 1: wavelet reconstruction (content details + style colours)
+    _, low_style = _decompose(style, False)
+    lab_c = torch.empty(T, 3, H, W, dtype=torch.float32, device=dev)
+    lab_s = torch.empty_like(lab_c)
+    L = _lib.lib()
+    ops._call("svr2_rgb_to_lab_fwd", 1, dev, L.svr2_rgb_to_lab_fwd, high.data_ptr(), low_style.data_ptr(), lab_c.data_ptr(), T, H, W, code,
+              ops._stream(sample))
+    sc = style.contiguous()
+    ops._call("svr2_rgb_to_lab_fwd", 1, dev, L.svr2_rgb_to_lab_fwd, sc.data_ptr(), None, lab_s.data_ptr(), T, H, W, code, ops._stream(sample))
+    del high, low_style
+    a = _histogram_match(lab_c[:, 1], lab_s[:, 1])
+    b = _histogram_match(lab_c[:, 2], lab_s[:, 2])
+    if luminance_weight < 1.0:
+        mL = _histogram_match(lab_c[:, 0], lab_s[:, 0])
+        rL = lab_c[:, 0].mul(luminance_weight).add_(mL.mul(1.0 - luminance_weight))
+    else:
+        rL = lab_c[:, 0]
+    lab = torch.stack([rL, a, b], dim=1)
+    out = torch.empty(T, H, W, 3, dtype=sample.dtype, device=dev) if want_float else None
+    out_u8 = torch.empty(T, H, W, 3, dtype=torch.uint8, device=dev) if want_uint8 else None
+    ops._call("svr2_lab_to_rgb_finish_fwd", 1, dev, L.svr2_lab_to_rgb_finish_fwd, lab.data_ptr(), None if out is None else out.data_ptr(),
+              None if out_u8 is None else out_u8.data_ptr(), int(bgr), T, H, W, code, ops._stream(sample))
+    return out, out_u8

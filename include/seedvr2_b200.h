@@ -339,6 +339,20 @@ int svr2_wavelet_level_fwd(const void* src, int64_t stride_t, int64_t stride_c, 
 int svr2_colorfix_finish_fwd(const void* high, const void* low_style, void* out, void* out_u8, int bgr, int T, int C, int H, int W,
                              int dtype, void* stream);
 
+/*
+ * The two colour-space conversions of lab_color_transfer (src/utils/color_fix.py:249-470, the CLI's default colour correction);
+ * the histogram matching between them (color_fix.py:473-513: global sort + scatter per channel) stays on the host library's sort.
+ * svr2_rgb_to_lab_fwd: rgb [T, 3, H, W] planar in [-1, 1] -> lab [T, 3, H, W] fp32 (_rgb_to_lab_batch after `.add_(1).mul_(0.5)
+ *   .clamp_(0, 1)`); with `add` != NULL the input is clamp(rgb + add, -1, 1) — wavelet_reconstruction's combine, the first step of
+ *   lab_color_transfer, fed with the high / low bands of svr2_wavelet_level_fwd.
+ * svr2_lab_to_rgb_finish_fwd: lab -> rgb (_lab_to_rgb_batch) `.mul_(2).sub_(1)`, cast to the pipeline dtype, then the batch
+ *   normalisation and writer conversion of svr2_colorfix_finish_fwd -> out [T, H, W, 3] / out_u8.
+ * fp32 ops rounded one by one like the reference's tensor ops; the 3x3 colour matrices are summed in index order (the
+ * reference's matmul order is the library's), so parity is within a few fp32 ulps, not bit-exact.
+ */
+int svr2_rgb_to_lab_fwd(const void* rgb, const void* add, float* lab, int T, int H, int W, int dtype, void* stream);
+int svr2_lab_to_rgb_finish_fwd(const float* lab, void* out, void* out_u8, int bgr, int T, int H, int W, int dtype, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

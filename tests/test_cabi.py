@@ -75,6 +75,8 @@ def test_new_entry_points_validate_their_arguments_before_launching(svr2):
     assert L.svr2_wavelet_level_fwd(one, 1, 1, 1, 1, one, None, 1, 1, 3, 8, 8, 0, 0, None) == -1 and b"radius" in L.svr2_last_error()
     assert L.svr2_wavelet_level_fwd(one, 1, 1, 1, 1, one, None, 1, 1, 3, 8, 8, 1, 5, None) == -1 and b"dtype" in L.svr2_last_error()
     assert L.svr2_colorfix_finish_fwd(one, one, None, None, 0, 1, 3, 8, 8, 0, None) == -1
+    assert L.svr2_rgb_to_lab_fwd(one, None, one, 1, 8, 8, 9, None) == -1 and b"dtype" in L.svr2_last_error()
+    assert L.svr2_lab_to_rgb_finish_fwd(one, None, None, 0, 1, 8, 8, 0, None) == -1
 
 
 @pytest.mark.parametrize("key", sorted(GEO))

@@ -165,3 +165,14 @@ def test_postprocess_oracle_matches_reference_module():
         b = (torch.rand(*shape, generator=g) * 2.2 - 1.1).to(dt)
         ref = wavelet_reconstruction(a.clone(), b.clone(), None).permute(0, 2, 3, 1).contiguous().clamp_(-1, 1).mul_(0.5).add_(0.5)
         assert torch.equal(opost.wavelet_color_fix(a, b), ref)
+    # the CLI's default, lab_color_transfer (color_fix.py:249-367)
+    from src.utils.color_fix import lab_color_transfer
+
+    class _D:
+        def log(self, *a, **k):
+            pass
+    for dt in (torch.float32, torch.bfloat16):
+        a = (torch.rand(2, 3, 40, 56, generator=g) * 2.4 - 1.2).to(dt)
+        b = (torch.rand(2, 3, 40, 56, generator=g) * 2.0 - 1.0).to(dt)
+        ref = lab_color_transfer(a.clone(), b.clone(), _D(), luminance_weight=0.8).permute(0, 2, 3, 1).contiguous().clamp_(-1, 1).mul_(0.5).add_(0.5)
+        assert torch.equal(opost.lab_color_fix(a, b), ref)
