@@ -1,0 +1,382 @@
+// svr2_causal_conv3d_fwd — the video VAE's causal 3-D convolution as an implicit GEMM on tcgen05 (first
+// slice: the stride-1 convolutions of the residual blocks, which carry >95 % of the VAE's FLOPs).
+//
+// Reference: InflatedCausalConv3d (src/models/video_vae_v3/modules/causal_inflation_lib.py:61-262).  The temporal padding is
+// removed from the module's padding (:74) and replaced by a causal head: 2 * temporal_padding copies of the first frame
+// (extend_head, :422-437, basic_forward :228), or the last kernel_t - 1 frames of the previous temporal slice kept in
+// `self.memory` (:226-227, slicing_forward :254-272).  Spatially the convolution zero-pads (Conv3d padding (0, 1, 1)).
+//
+//   out[t, h, w, co] = bias[co] + sum_{dt, dh, dw, ci} W[co, dt, dh, dw, ci] * X[t + dt - (kt - 1), h + dh - ks/2, w + dw - ks/2, ci]
+//   X[t' < 0] = head[t' + (kt - 1)]   (memory of the previous slice)   or   X[0]   (first slice: replicated first frame)
+//   (+ resid[t, h, w, co], rounded after the convolution's own rounding: ResnetBlock3D's input_tensor + hidden_states)
+//
+// Layout: activations channels-last [T, H, W, C] (torch.channels_last_3d of the reference's [1, C, T, H, W] — same bytes), weights
+// pre-packed once to [C_out, kt, ks, ks, C_in] (svr2_conv3d_pack_weight), so that the GEMM's K axis is (tap, channel) and every
+// 64-channel K step of an output tile is ONE 4-D TMA box of the input: 64 channels x 16 w x 8 h x 1 frame at the tap's offset.
+// The TMA unit zero-fills the out-of-range rows and columns (the spatial zero padding), and lands the box in exactly the
+// 128-byte-swizzled K-major layout tcgen05.mma reads — no im2col buffer, no halo exchange, no padding copy.
+//
+// Kernel shape: the GEMM of gemm.cu.  CTA pair, tcgen05.mma.cta_group::2 with M = 256 output positions (a 16 x 16 patch of one
+// frame; each CTA stages its 8 rows), N = 256 or 128 output channels, fp32 accumulators double-buffered in TMEM, persistent over
+// (frame, patch, channel tile), warp 0 = TMA producer, warp 1 = MMA issuer, warps 4-7 = epilogue (bias, residual, rounding,
+// swizzled slab, 4-D TMA store that clips the patch at the frame's edge).  fp16 (the VAE's dtype) or bf16, fp32 accumulation.
+#include <cuda.h>
+#include <cuda_fp16.h>
+
+#include "common.cuh"
+#include "sm100_pair.cuh"
+#include "sm100_ptx.cuh"
+#include "tmap.cuh"
+
+namespace svr2 {
+namespace conv {
+
+using namespace ptx;
+using namespace pairx;
+
+constexpr int BM = 128;                  // output positions per CTA: 8 rows x 16 columns of one frame
+constexpr int PATCH_W = 16, PATCH_H = 8; // per CTA; the pair covers 16 x 16
+constexpr int BK = 64;                   // channels per K step (one 128-byte swizzle atom)
+constexpr int A_BYTES = BM * BK * 2;
+constexpr int SLAB_BYTES = 32 * 128;     // 2 patch rows x 16 columns x 64 channels: one TMA store box
+constexpr uint32_t TMEM_COLS = 512;
+
+template <int BN>
+struct Cfg {
+    static constexpr int B_BYTES = (BN / 2) * BK * 2;
+    static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+    static constexpr int STAGES = BN == 256 ? 5 : 7;
+    static constexpr int NTHREADS = 256;
+    static constexpr int OFF_SLAB = STAGES * STAGE_BYTES;
+    static constexpr int OFF_BAR = OFF_SLAB + 4 * 2 * SLAB_BYTES;
+    static constexpr int SMEM_BYTES = OFF_BAR + 256;
+    static constexpr int BAR_FULL = 0, BAR_EMPTY = STAGES, BAR_TFULL = 2 * STAGES, BAR_TEMPTY = 2 * STAGES + 2,
+                         BAR_COUNT = 2 * STAGES + 4;
+    static_assert(BAR_COUNT * 8 + 8 <= 256, "barrier block too small");
+    static_assert(SMEM_BYTES <= 232448, "shared memory");
+    static_assert(OFF_SLAB % 1024 == 0 && STAGE_BYTES % 1024 == 0, "swizzled tiles need 1024-byte alignment");
+};
+
+struct Params {
+    int T, H, W, Cin, Cout;
+    int kt, ks;                 // temporal taps (1 | 3), spatial taps per axis (1 | 3)
+    int h_tiles, w_tiles, n_tiles;
+    int has_head;               // frames t' < 0 come from the head tensor (kt - 1 frames); otherwise frame 0 is replicated
+    const void* bias;           // [Cout] or nullptr
+    const void* resid;          // [T, H, W, Cout] or nullptr
+};
+
+__device__ __forceinline__ void tma_load_4d_pair(uint32_t dst, const CUtensorMap* m, uint32_t bar, int c0, int c1, int c2, int c3) {
+    asm volatile(
+        "cp.async.bulk.tensor.4d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
+        ::"r"(dst), "l"(m), "r"(bar & 0xFEFFFFFFu), "r"(c0), "r"(c1), "r"(c2), "r"(c3) : "memory");
+}
+__device__ __forceinline__ void tma_store_4d(const CUtensorMap* m, uint32_t src, int c0, int c1, int c2, int c3) {
+    asm volatile("cp.async.bulk.tensor.4d.global.shared::cta.bulk_group [%0, {%2, %3, %4, %5}], [%1];"
+                 ::"l"(m), "r"(src), "r"(c0), "r"(c1), "r"(c2), "r"(c3) : "memory");
+}
+// kind::f16 instruction descriptor, fp16 or bf16 operands (both K-major), fp32 accumulator
+__host__ __device__ constexpr uint32_t idesc_16(bool f16, int M, int N) {
+    return (1u << 4) | ((f16 ? 0u : 1u) << 7) | ((f16 ? 0u : 1u) << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+
+template <bool F16> struct Num;
+template <> struct Num<true> {
+    using T2 = __half2;
+    static __device__ __forceinline__ uint32_t pack(float a, float b) { const __half2 v = __floats2half2_rn(a, b); return *reinterpret_cast<const uint32_t*>(&v); }
+    static __device__ __forceinline__ float2 unpack(uint32_t u) { return __half22float2(*reinterpret_cast<const __half2*>(&u)); }
+    static __device__ __forceinline__ uint32_t add(uint32_t a, uint32_t b) {
+        const __half2 v = __hadd2_rn(*reinterpret_cast<const __half2*>(&a), *reinterpret_cast<const __half2*>(&b));
+        return *reinterpret_cast<const uint32_t*>(&v);
+    }
+};
+template <> struct Num<false> {
+    static __device__ __forceinline__ uint32_t pack(float a, float b) { const __nv_bfloat162 v = __floats2bfloat162_rn(a, b); return *reinterpret_cast<const uint32_t*>(&v); }
+    static __device__ __forceinline__ float2 unpack(uint32_t u) { return __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&u)); }
+    static __device__ __forceinline__ uint32_t add(uint32_t a, uint32_t b) {
+        const __nv_bfloat162 v = __hadd2_rn(*reinterpret_cast<const __nv_bfloat162*>(&a), *reinterpret_cast<const __nv_bfloat162*>(&b));
+        return *reinterpret_cast<const uint32_t*>(&v);
+    }
+};
+
+struct Tile {
+    int t, h0, w0, nt;
+};
+__device__ __forceinline__ Tile decode_tile(const Params& p, int id) {
+    Tile r;
+    r.nt = id % p.n_tiles;
+    int sp = id / p.n_tiles;
+    r.w0 = (sp % p.w_tiles) * PATCH_W;
+    sp /= p.w_tiles;
+    r.h0 = (sp % p.h_tiles) * (2 * PATCH_H);
+    r.t = sp / p.h_tiles;
+    return r;
+}
+
+template <int BN, bool F16>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(Cfg<BN>::NTHREADS, 1)
+conv3d_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ CUtensorMap tm_head,
+                 const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ CUtensorMap tm_y, const Params p) {
+    using C = Cfg<BN>;
+    using N = Num<F16>;
+    constexpr int STAGES = C::STAGES, STAGE_BYTES = C::STAGE_BYTES;
+    constexpr int BAR_FULL = C::BAR_FULL, BAR_EMPTY = C::BAR_EMPTY, BAR_TFULL = C::BAR_TFULL, BAR_TEMPTY = C::BAR_TEMPTY;
+    extern __shared__ __align__(1024) unsigned char smem[];
+    const uint32_t base = smem_u32(smem);
+    const uint32_t sBar = base + C::OFF_BAR;
+    volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(smem + C::OFF_BAR + C::BAR_COUNT * 8);
+    auto bar = [&](int slot) { return sBar + 8u * (uint32_t)slot; };
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t rank = cluster_rank();
+    const bool leader = rank == 0;
+    const int first = (int)(blockIdx.x >> 1), stride = (int)(gridDim.x >> 1);
+    const int n_tiles_total = p.T * p.h_tiles * p.w_tiles * p.n_tiles;
+    const int c_chunks = p.Cin / BK;
+    const int taps = p.kt * p.ks * p.ks;
+    const int kb_count = taps * c_chunks;
+
+    if (threadIdx.x == 0) {
+        if (base & 1023u) __trap();
+        for (int s = 0; s < STAGES; ++s) {
+            mbar_init(bar(BAR_FULL + s), 1);
+            mbar_init(bar(BAR_EMPTY + s), 1);
+        }
+        for (int b = 0; b < 2; ++b) {
+            mbar_init(bar(BAR_TFULL + b), 1);
+            mbar_init(bar(BAR_TEMPTY + b), 8);          // one arrival per epilogue warp of the pair
+        }
+        fence_mbar_init();
+    }
+    if (warp == 2) tmem_alloc_pair(smem_u32(const_cast<uint32_t*>(tmem_slot)), TMEM_COLS);
+    if (warp == 0 && lane == 0) {
+        prefetch_tmap(&tm_x);
+        prefetch_tmap(&tm_head);
+        prefetch_tmap(&tm_w);
+        prefetch_tmap(&tm_y);
+    }
+    tc_fence_before();
+    __syncthreads();
+    cluster_sync_all();
+    tc_fence_after();
+    const uint32_t tmem = *tmem_slot;
+
+    if (warp == 0) {
+        // ------------------------------------------------------------------ TMA producer: one input box + one weight box per K step
+        if (lane == 0) {
+            const int half = p.ks >> 1;
+            uint32_t it = 0;
+            for (int id = first; id < n_tiles_total; id += stride) {
+                const Tile tl = decode_tile(p, id);
+                const int hh = tl.h0 + (int)rank * PATCH_H;
+                const int b_row = tl.nt * BN + (int)rank * (BN / 2);
+                int kcol = 0;
+                for (int dt = 0; dt < p.kt; ++dt) {
+                    // the causal head: frames before the slice come from the previous slice's memory, or repeat frame 0
+                    int ts = tl.t + dt - (p.kt - 1);
+                    const CUtensorMap* ta = &tm_x;
+                    if (ts < 0) {
+                        if (p.has_head) { ta = &tm_head; ts += p.kt - 1; }
+                        else ts = 0;
+                    }
+                    for (int dh = 0; dh < p.ks; ++dh)
+                        for (int dw = 0; dw < p.ks; ++dw)
+                            for (int cc = 0; cc < c_chunks; ++cc, ++it, kcol += BK) {
+                                const uint32_t s = it % STAGES, use = it / STAGES;
+                                mbar_wait(bar(BAR_EMPTY + s), (use & 1) ^ 1);
+                                if (leader) mbar_expect_tx(bar(BAR_FULL + s), 2 * STAGE_BYTES);
+                                const uint32_t dst = base + s * STAGE_BYTES;
+                                tma_load_4d_pair(dst, ta, bar(BAR_FULL + s), cc * BK, tl.w0 + dw - half, hh + dh - half, ts);
+                                tma_load_2d_pair(dst + A_BYTES, &tm_w, bar(BAR_FULL + s), kcol, b_row);
+                            }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ------------------------------------------------------------------ tcgen05.mma issuer of the pair (leader CTA)
+        if (leader) {
+            constexpr uint32_t idesc = idesc_16(F16, 2 * BM, BN);
+            constexpr uint32_t hi_sw = smem_desc_hi_sw128(1024);
+            uint32_t it = 0, tc = 0;
+            for (int id = first; id < n_tiles_total; id += stride, ++tc) {
+                const uint32_t b = tc & 1;
+                mbar_wait(bar(BAR_TEMPTY + b), ((tc >> 1) & 1) ^ 1);
+                tc_fence_after();
+                const uint32_t d_tmem = tmem + b * BN;
+                for (int kb = 0; kb < kb_count; ++kb, ++it) {
+                    const uint32_t s = it % STAGES, use = it / STAGES;
+                    mbar_wait(bar(BAR_FULL + s), use & 1);
+                    tc_fence_after();
+                    if (elect_one()) {
+                        const uint32_t alo = smem_desc_lo(base + s * STAGE_BYTES, 16);
+                        const uint32_t blo = smem_desc_lo(base + s * STAGE_BYTES + A_BYTES, 16);
+#pragma unroll
+                        for (int kk = 0; kk < BK / 16; ++kk)
+                            mma2_ss(d_tmem, make_desc(alo + kk * 2, hi_sw), make_desc(blo + kk * 2, hi_sw), idesc,
+                                    (uint32_t)((kb | kk) != 0));
+                        tc_commit_pair(bar(BAR_EMPTY + s));
+                        if (kb == kb_count - 1) tc_commit_pair(bar(BAR_TFULL + b));
+                    }
+                    __syncwarp();
+                }
+            }
+        }
+    } else if (warp >= 4) {
+        // ------------------------------------------------------------------ epilogue: one thread per output position
+        const int q = warp & 3;
+        const uint32_t lane_off = (uint32_t)(q * 32) << 16;
+        unsigned char* slab0 = smem + C::OFF_SLAB + q * 2 * SLAB_BYTES;
+        const uint32_t tempty_g0 = mapa(bar(BAR_TEMPTY + 0), 0), tempty_g1 = mapa(bar(BAR_TEMPTY + 1), 0);
+        const __half* bias = reinterpret_cast<const __half*>(p.bias);          // 2-byte elements either way
+        const __half* resid = reinterpret_cast<const __half*>(p.resid);
+        uint32_t tc = 0, n_store = 0;
+        for (int id = first; id < n_tiles_total; id += stride, ++tc) {
+            const Tile tl = decode_tile(p, id);
+            const uint32_t b = tc & 1;
+            const int hs = tl.h0 + (int)rank * PATCH_H + q * 2;               // first of this warp's two patch rows
+            const int h = hs + (lane >> 4), w = tl.w0 + (lane & 15);
+            const bool valid = h < p.H && w < p.W;
+            const int64_t pos = ((int64_t)tl.t * p.H + h) * p.W + w;
+            const int col_tile = tl.nt * BN;
+            mbar_wait(bar(BAR_TFULL + b), (tc >> 1) & 1);
+            tc_fence_after();
+            const uint32_t tacc = tmem + lane_off + b * BN;
+#pragma unroll 1
+            for (int sl = 0; sl < BN / 64; ++sl) {
+                const int col0 = col_tile + sl * 64;
+                uint32_t o[32];
+#pragma unroll
+                for (int hf = 0; hf < 2; ++hf) {
+                    const int c = col0 + hf * 32;
+                    uint32_t v[32];
+                    tmem_ld32(tacc + sl * 64 + hf * 32, v);
+                    uint4 bq[4], rq[4];
+                    if (bias != nullptr) {
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) bq[j] = __ldg(reinterpret_cast<const uint4*>(bias + c) + j);
+                    }
+                    if (resid != nullptr) {
+#pragma unroll
+                        for (int j = 0; j < 4; ++j)
+                            rq[j] = valid ? __ldg(reinterpret_cast<const uint4*>(resid + pos * p.Cout + c) + j) : make_uint4(0u, 0u, 0u, 0u);
+                    }
+                    tc_wait_ld();
+                    const uint32_t* bw = reinterpret_cast<const uint32_t*>(bq);
+                    const uint32_t* rw = reinterpret_cast<const uint32_t*>(rq);
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) {
+                        float a0 = __uint_as_float(v[2 * i]), a1 = __uint_as_float(v[2 * i + 1]);
+                        if (bias != nullptr) {
+                            const float2 bf = N::unpack(bw[i]);
+                            a0 += bf.x; a1 += bf.y;
+                        }
+                        uint32_t h2 = N::pack(a0, a1);                        // the convolution's output in the tensor dtype
+                        if (resid != nullptr) h2 = N::add(h2, rw[i]);         // + input_tensor, rounded again
+                        o[hf * 16 + i] = h2;
+                    }
+                }
+                if (sl == BN / 64 - 1) {
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive_cluster(b ? tempty_g1 : tempty_g0);
+                }
+                unsigned char* slab = slab0 + (n_store & 1) * SLAB_BYTES;
+                if (lane == 0) bulk_wait_read<1>();
+                __syncwarp();
+#pragma unroll
+                for (int j = 0; j < 8; ++j)
+                    *reinterpret_cast<uint4*>(slab + lane * 128 + ((j ^ (lane & 7)) << 4)) =
+                        make_uint4(o[4 * j], o[4 * j + 1], o[4 * j + 2], o[4 * j + 3]);
+                fence_proxy_async_smem();
+                __syncwarp();
+                if (lane == 0 && hs < p.H) {
+                    tma_store_4d(&tm_y, smem_u32(slab), col0, tl.w0, hs, tl.t);      // box 64 c x 16 w x 2 h x 1 t, clipped at the edges
+                    bulk_commit();
+                }
+                ++n_store;
+            }
+        }
+        if (lane == 0) bulk_wait<0>();
+    }
+    tc_fence_before();
+    __syncthreads();
+    cluster_sync_all();
+    if (warp == 2) {
+        __syncwarp();
+        tmem_dealloc_pair(tmem, TMEM_COLS);
+    }
+}
+
+template <int BN, bool F16>
+int launch(const void* x, const void* head, const void* w, void* y, Params p, cudaStream_t st) {
+    const char* name = "svr2_causal_conv3d_fwd";
+    p.h_tiles = (p.H + 2 * PATCH_H - 1) / (2 * PATCH_H);
+    p.w_tiles = (p.W + PATCH_W - 1) / PATCH_W;
+    p.n_tiles = p.Cout / BN;
+    CUtensorMap tx, th, tw, ty;
+    int rc;
+    if ((rc = make_tmap_thwc(&tx, x, p.T, p.H, p.W, p.Cin, PATCH_W, PATCH_H)) != SVR2_OK) return rc;
+    if (p.has_head) {
+        if ((rc = make_tmap_thwc(&th, head, p.kt - 1, p.H, p.W, p.Cin, PATCH_W, PATCH_H)) != SVR2_OK) return rc;
+    } else {
+        th = tx;
+    }
+    const int64_t ktot = (int64_t)p.kt * p.ks * p.ks * p.Cin;
+    if ((rc = make_tmap_2d(&tw, w, p.Cout, ktot, ktot, BN / 2)) != SVR2_OK) return rc;
+    if ((rc = make_tmap_thwc(&ty, y, p.T, p.H, p.W, p.Cout, PATCH_W, 2)) != SVR2_OK) return rc;
+    static PerDeviceFlag smem_ok;
+    if ((rc = ensure_dyn_smem(conv3d_tc_kernel<BN, F16>, Cfg<BN>::SMEM_BYTES, smem_ok, name)) != SVR2_OK) return rc;
+    const int pairs = sm_count() / 2;
+    const int64_t tiles = (int64_t)p.T * p.h_tiles * p.w_tiles * p.n_tiles;
+    const int grid = 2 * (int)(tiles < pairs ? tiles : pairs);
+    conv3d_tc_kernel<BN, F16><<<grid, Cfg<BN>::NTHREADS, Cfg<BN>::SMEM_BYTES, st>>>(tx, th, tw, ty, p);
+    SVR2_CHECK_LAUNCH(name);
+    return SVR2_OK;
+}
+
+// [Cout, Cin, kt, kh, kw] (nn.Conv3d) -> [Cout, kt, kh, kw, Cin]: the implicit GEMM's K axis is (tap, channel)
+__global__ void pack_weight_kernel(const uint16_t* __restrict__ w, uint16_t* __restrict__ out, int Cout, int Cin, int taps) {
+    const int64_t n = (int64_t)Cout * Cin * taps;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        const int ci = (int)(i % Cin);
+        const int tap = (int)((i / Cin) % taps);
+        const int64_t co = i / ((int64_t)Cin * taps);
+        out[i] = w[(co * Cin + ci) * taps + tap];
+    }
+}
+
+}  // namespace conv
+}  // namespace svr2
+
+extern "C" int svr2_conv3d_pack_weight(const void* weight, void* packed, int c_out, int c_in, int kt, int kh, int kw, void* stream) {
+    SVR2_CHECK_ARG(weight && packed, "svr2_conv3d_pack_weight: null pointer");
+    SVR2_CHECK_ARG(c_out > 0 && c_in > 0 && kt > 0 && kh > 0 && kw > 0, "svr2_conv3d_pack_weight: bad shape");
+    const int64_t n = (int64_t)c_out * c_in * kt * kh * kw;
+    const int blocks = (int)((n + 255) / 256 < 148 * 8 ? (n + 255) / 256 : 148 * 8);
+    svr2::conv::pack_weight_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>((const uint16_t*)weight, (uint16_t*)packed, c_out, c_in,
+                                                                            kt * kh * kw);
+    SVR2_CHECK_LAUNCH("svr2_conv3d_pack_weight");
+    return SVR2_OK;
+}
+
+extern "C" int svr2_causal_conv3d_fwd(const void* x, const void* head, const void* weight_packed, const void* bias, const void* resid,
+                                      void* y, int T, int H, int W, int c_in, int c_out, int kt, int ks, int dtype, void* stream) {
+    const char* name = "svr2_causal_conv3d_fwd";
+    SVR2_CHECK_ARG(x && weight_packed && y, "%s: null pointer", name);
+    SVR2_CHECK_ARG(dtype == SVR2_DTYPE_F16 || dtype == SVR2_DTYPE_BF16, "%s: dtype %d (fp16 or bf16)", name, dtype);
+    SVR2_CHECK_ARG(T >= 0 && H > 0 && W > 0, "%s: bad extent T=%d H=%d W=%d", name, T, H, W);
+    SVR2_CHECK_ARG((kt == 1 || kt == 3) && (ks == 1 || ks == 3), "%s: kernel %dx%dx%d (temporal 1|3, spatial 1|3, stride 1)", name, kt, ks, ks);
+    SVR2_CHECK_ARG(c_in > 0 && c_in % 64 == 0, "%s: c_in=%d must be a positive multiple of 64", name, c_in);
+    SVR2_CHECK_ARG(c_out > 0 && c_out % 128 == 0, "%s: c_out=%d must be a positive multiple of 128", name, c_out);
+    SVR2_CHECK_ARG((int64_t)T * H * W < ((int64_t)1 << 31), "%s: too many positions", name);
+    if (T == 0) return SVR2_OK;
+    svr2::conv::Params p{};
+    p.T = T; p.H = H; p.W = W; p.Cin = c_in; p.Cout = c_out; p.kt = kt; p.ks = ks;
+    p.has_head = (head != nullptr && kt > 1) ? 1 : 0;
+    p.bias = bias; p.resid = resid;
+    const bool f16 = dtype == SVR2_DTYPE_F16;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (c_out % 256 == 0)
+        return f16 ? svr2::conv::launch<256, true>(x, head, weight_packed, y, p, st) : svr2::conv::launch<256, false>(x, head, weight_packed, y, p, st);
+    return f16 ? svr2::conv::launch<128, true>(x, head, weight_packed, y, p, st) : svr2::conv::launch<128, false>(x, head, weight_packed, y, p, st);
+}

@@ -27,7 +27,7 @@ int encode(CUtensorMap* m, const void* ptr, int rank, const cuuint64_t* gdim, co
         set_error("cuTensorMapEncodeTiled not available from the driver");
         return SVR2_E_CUDA;
     }
-    const cuuint32_t estr[3] = {1, 1, 1};
+    const cuuint32_t estr[4] = {1, 1, 1, 1};
     const CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank, const_cast<void*>(ptr), gdim, gstr, box, estr,
                            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
@@ -53,6 +53,13 @@ int make_tmap_2d(CUtensorMap* m, const void* ptr, int64_t rows, int64_t cols, in
     const cuuint64_t gstr[1] = {(cuuint64_t)ld * 2};
     const cuuint32_t box[2] = {64, (cuuint32_t)box_rows};
     return encode(m, ptr, 2, gdim, gstr, box);
+}
+
+int make_tmap_thwc(CUtensorMap* m, const void* ptr, int64_t T, int64_t H, int64_t W, int64_t C, int box_w, int box_h) {
+    const cuuint64_t gdim[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)T};
+    const cuuint64_t gstr[3] = {(cuuint64_t)C * 2, (cuuint64_t)W * C * 2, (cuuint64_t)H * W * C * 2};
+    const cuuint32_t box[4] = {64, (cuuint32_t)box_w, (cuuint32_t)box_h, 1};
+    return encode(m, ptr, 4, gdim, gstr, box);
 }
 
 }  // namespace svr2

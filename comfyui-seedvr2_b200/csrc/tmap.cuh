@@ -12,5 +12,9 @@ inline int make_tmap(CUtensorMap* m, const void* ptr, int64_t P, int heads) { re
 // Row-major [rows, cols] bf16 matrix with a row pitch of ld elements; box = 64 cols x box_rows rows, 128-byte swizzle (the
 // canonical K-major UMMA operand layout).  Out-of-range rows / cols are zero-filled by the TMA unit.
 int make_tmap_2d(CUtensorMap* m, const void* ptr, int64_t rows, int64_t cols, int64_t ld, int box_rows);
+// Channels-last [T, H, W, C] tensor of 2-byte elements viewed as (c, w, h, t); box = 64 c x box_w x box_h x 1 frame, 128-byte
+// swizzle: rows of the box (w fastest) land as consecutive 128-byte rows — a K-major UMMA operand of box_w * box_h positions.
+// Coordinates may be negative / past the edge: the TMA unit zero-fills on load (the convolution's zero padding), clips on store.
+int make_tmap_thwc(CUtensorMap* m, const void* ptr, int64_t T, int64_t H, int64_t W, int64_t C, int box_w, int box_h);
 
 }  // namespace svr2

@@ -334,6 +334,7 @@ int svr2_v_lerp_endpoint_fwd(const void* x_t, const void* pred, float A, float B
  */
 #define SVR2_DTYPE_F32  0
 #define SVR2_DTYPE_BF16 1
+#define SVR2_DTYPE_F16  2
 int svr2_wavelet_level_fwd(const void* src, int64_t stride_t, int64_t stride_c, int64_t stride_y, int64_t stride_x, void* low,
                            void* high, int first, int T, int C, int H, int W, int radius, int dtype, void* stream);
 int svr2_colorfix_finish_fwd(const void* high, const void* low_style, void* out, void* out_u8, int bgr, int T, int C, int H, int W,
@@ -352,6 +353,22 @@ int svr2_colorfix_finish_fwd(const void* high, const void* low_style, void* out,
  */
 int svr2_rgb_to_lab_fwd(const void* rgb, const void* add, float* lab, int T, int H, int W, int dtype, void* stream);
 int svr2_lab_to_rgb_finish_fwd(const float* lab, void* out, void* out_u8, int bgr, int T, int H, int W, int dtype, void* stream);
+
+/*
+ * SURVEY §8f row N3 (first slice): the video VAE's causal 3-D convolution, stride 1 — InflatedCausalConv3d
+ * (src/models/video_vae_v3/modules/causal_inflation_lib.py:61-262) as it is used by ResnetBlock3D.conv1 / conv2
+ * (src/models/video_vae_v3/modules/attn_video_vae.py:263-280) and the up-sampler's convolutions.  Implicit GEMM on tcgen05:
+ * no im2col buffer, the input is read by 4-D TMA boxes at the tap's offset (zero fill = the spatial zero padding).
+ *   x [T, H, W, c_in], y / resid [T, H, W, c_out]: channels-last (torch.channels_last_3d of the reference's [1, C, T, H, W]);
+ *   weight_packed [c_out, kt, ks, ks, c_in] from svr2_conv3d_pack_weight (nn.Conv3d's [c_out, c_in, kt, kh, kw], packed once);
+ *   head: NULL = first temporal slice, the first frame is repeated kt - 1 times in front (extend_head, :422-437, basic_forward
+ *     :228); else [kt - 1, H, W, c_in] = the last kt - 1 input frames of the previous slice (`self.memory`, :226-227, :254-272);
+ *   bias [c_out] or NULL; resid or NULL: y = round(round(conv + bias) + resid) — ResnetBlock3D's `input_tensor + hidden_states`.
+ *   kt in {1, 3}, ks in {1, 3}, c_in % 64 == 0, c_out % 128 == 0, dtype SVR2_DTYPE_F16 (the VAE's) or SVR2_DTYPE_BF16.
+ */
+int svr2_conv3d_pack_weight(const void* weight, void* packed, int c_out, int c_in, int kt, int kh, int kw, void* stream);
+int svr2_causal_conv3d_fwd(const void* x, const void* head, const void* weight_packed, const void* bias, const void* resid,
+                           void* y, int T, int H, int W, int c_in, int c_out, int kt, int ks, int dtype, void* stream);
 
 #ifdef __cplusplus
 }

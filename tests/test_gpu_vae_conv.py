@@ -1,0 +1,155 @@
+"""svr2_causal_conv3d_fwd (csrc/conv3d.cu) through comfyui-seedvr2_b200/vae_conv.py: the VAE's causal 3-D convolution.
+
+Checked against (1) the oracle (oracle/vae_conv.py) evaluated in fp32 on the same fp16 / bf16 inputs, with a bound derived from
+the two rounding sources — the output's own rounding (half an ulp of the result) and the fp32 accumulation over K = 27 C_in terms (the tensor
+pipe aligns and truncates partial sums: measured up to 1e-6 of sum |w||x| at K = 13,824; bound 3e-6); (2) the reference's own InflatedCausalConv3d run on the same GPU through cuDNN, over the temporal slices and
+memory states of the VAE's slicing (staged copy, baseline/_ref); (3) at 1080p, a crop of the result against the oracle on the
+crop's receptive field."""
+import pytest
+import torch
+import torch.nn.functional as F
+
+from oracle import refstage
+from oracle import vae_conv as ovc
+
+pytestmark = pytest.mark.gpu
+
+ULP = {torch.float16: 2.0 ** -11, torch.bfloat16: 2.0 ** -8}      # half an ulp, relative
+
+
+def _bound(x, w, b, dtype):
+    """|ours - fp32 oracle| <= half an ulp of the rounded result (+ the bias add's) + accumulation-order noise."""
+    mag, _ = ovc.causal_conv3d(x.float().abs(), w.float().abs(), None if b is None else b.float().abs())
+    return lambda ref: ULP[dtype] * 1.01 * ref.abs() + 3e-6 * mag + 1e-7
+
+
+def _make(ci, co, kt, ks, T, H, W, dtype, seed=0, bias=True):
+    g = torch.Generator(device="cuda").manual_seed(seed)
+    x = torch.randn(1, ci, T, H, W, generator=g, device="cuda").to(dtype).contiguous(memory_format=torch.channels_last_3d)
+    w = (torch.randn(co, ci, kt, ks, ks, generator=g, device="cuda") * (ci * kt * ks * ks) ** -0.5).to(dtype)
+    b = (torch.randn(co, generator=g, device="cuda") * 0.5).to(dtype) if bias else None
+    return x, w, b
+
+
+CASES = [
+    # ci, co, kt, ks, T, H, W
+    (128, 128, 3, 3, 3, 24, 40),        # ragged: H, W not multiples of the 16 x 16 patch; N tile 128
+    (128, 128, 3, 3, 1, 16, 16),        # one frame: the whole causal head is the replicated first frame
+    (256, 256, 3, 3, 2, 33, 17),        # N tile 256, odd extents
+    (128, 256, 3, 3, 2, 20, 36),        # widening conv1 of a block
+    (512, 512, 3, 3, 2, 9, 50),         # deepest level, fewer rows than one patch
+    (256, 128, 1, 3, 4, 18, 30),        # time_receptive_field "half": (1, 3, 3)
+    (128, 256, 1, 1, 3, 21, 19),        # conv_shortcut: 1 x 1 x 1
+    (64, 128, 3, 3, 2, 16, 32),         # one 64-channel K chunk per tap
+]
+
+
+@pytest.mark.parametrize("case", CASES, ids=lambda c: "x".join(map(str, c)))
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16], ids=["fp16", "bf16"])
+def test_conv_matches_oracle(svr2, cuda, case, dtype):
+    ci, co, kt, ks, T, H, W = case
+    x, w, b = _make(ci, co, kt, ks, T, H, W, dtype, seed=sum(case))
+    ref, _ = ovc.causal_conv3d(x.float(), w.float(), b.float())
+    conv = svr2.vae_conv.CausalConv3dB200(w, b)
+    got = conv(x, "DISABLED")
+    torch.cuda.synchronize()
+    assert got.shape == ref.shape and got.dtype == dtype
+    assert got.is_contiguous(memory_format=torch.channels_last_3d)
+    d = (got.float() - ref).abs()
+    lim = _bound(x, w, b, dtype)(ref)
+    assert bool((d <= lim).all()), f"max excess {float((d - lim).max()):.3e} at |ref| {float(ref.abs().max()):.2f}"
+
+
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16], ids=["fp16", "bf16"])
+def test_head_bias_and_residual(svr2, cuda, dtype):
+    ci, co, T, H, W = 128, 128, 3, 20, 24
+    x, w, b = _make(ci, co, 3, 3, T, H, W, dtype, seed=11)
+    g = torch.Generator(device="cuda").manual_seed(12)
+    head = torch.randn(2, H, W, ci, generator=g, device="cuda").to(dtype)
+    resid = torch.randn(T, H, W, co, generator=g, device="cuda").to(dtype)
+    wp = svr2.vae_conv.pack_conv_weight(w)
+    assert torch.equal(wp, w.permute(0, 2, 3, 4, 1).contiguous())
+    xt = x[0].permute(1, 2, 3, 0)
+    assert xt.is_contiguous()
+    mem = head.permute(3, 0, 1, 2)[None]
+    ref, _ = ovc.causal_conv3d(x.float(), w.float(), None, mem.float())
+    plain = svr2.vae_conv.causal_conv3d(xt, wp, None, head)                     # no bias
+    d = (plain.permute(3, 0, 1, 2)[None].float() - ref).abs()
+    assert bool((d <= _bound(torch.cat((mem, x), 2), w, None, dtype)(ref)).all())
+    with_b = svr2.vae_conv.causal_conv3d(xt, wp, b, head)
+    fused = svr2.vae_conv.causal_conv3d(xt, wp, b, head, resid)
+    # the residual is added to the ROUNDED convolution output, like the reference's separate tensor add: bit-exact
+    assert torch.equal(fused, with_b + resid)
+    # bias enters before the rounding (cuDNN / ATen add it in fp32)
+    ref_b = ref + b.float().view(1, -1, 1, 1, 1)
+    d = (with_b.permute(3, 0, 1, 2)[None].float() - ref_b).abs()
+    assert bool((d <= _bound(torch.cat((mem, x), 2), w, b, dtype)(ref_b)).all())
+
+
+def test_module_streams_like_reference(svr2, cuda):
+    """The reference's InflatedCausalConv3d (fp16, cuDNN) and the mirror over the VAE's temporal slices: outputs within fp16
+    rounding of each other, memories bit-equal, and the streamed result equal to the one-shot one."""
+    if not refstage.available():
+        pytest.skip("reference not staged")
+    refstage.activate()
+    from src.models.video_vae_v3.modules.causal_inflation_lib import init_causal_conv3d
+    from src.models.video_vae_v3.modules.types import MemoryState
+    torch.manual_seed(3)
+    for kernel, pad, ci, co in ((3, 1, 128, 128), ((1, 3, 3), (0, 1, 1), 128, 256), (3, 1, 256, 256)):
+        ref = init_causal_conv3d(ci, co, kernel_size=kernel, stride=1, padding=pad, inflation_mode="tail").eval().cuda().half()
+        mine = svr2.vae_conv.CausalConv3dB200.from_reference(ref)
+        x = torch.randn(1, ci, 9, 40, 56, device="cuda").half().contiguous(memory_format=torch.channels_last_3d)
+        with torch.no_grad():
+            outs_r, outs_m = [], []
+            for i, (a, b) in enumerate(((0, 4), (4, 5), (5, 9))):
+                st = MemoryState.INITIALIZING if i == 0 else MemoryState.ACTIVE
+                outs_r.append(ref(x[:, :, a:b].contiguous(), memory_state=st))
+                outs_m.append(mine(x[:, :, a:b], st))
+                if ref.kernel_size[0] > 1:
+                    assert torch.equal(mine.memory.permute(0, 4, 1, 2, 3), ref.memory)
+            r, m = torch.cat(outs_r, 2).float(), torch.cat(outs_m, 2).float()
+            one_shot = mine(x, MemoryState.DISABLED)
+            assert mine.memory is None
+            assert torch.equal(torch.cat(outs_m, 2), one_shot)               # slicing changes nothing, bit for bit
+            exact, _ = ovc.causal_conv3d(x.float(), ref.weight.float(), ref.bias.float())
+            e_ref, e_mine = float((r - exact).abs().max()), float((m - exact).abs().max())
+            assert e_mine <= max(1.05 * e_ref, 2.0 ** -11 * float(exact.abs().max()) * 1.01), (kernel, e_mine, e_ref)
+            assert float((r - m).abs().max()) <= 2.0 ** -9 * float(exact.abs().max())
+
+
+def test_1080p_crop_against_oracle(svr2, cuda):
+    """Full-size frame (the decoder's top level: 128 channels at 1080 x 1920): crops at the corners, the edges and the centre
+    against the oracle on the crop's receptive field."""
+    ci = co = 128
+    T, H, W = 3, 1080, 1920
+    x, w, b = _make(ci, co, 3, 3, T, H, W, torch.float16, seed=21)
+    conv = svr2.vae_conv.CausalConv3dB200(w, b)
+    got = conv(x, "DISABLED")
+    torch.cuda.synchronize()
+    for (h0, w0) in ((0, 0), (0, W - 40), (H - 24, 0), (H - 24, W - 40), (530, 950), (1064, 1000)):
+        h1, w1 = min(h0 + 24, H), min(w0 + 40, W)
+        ha, wa = max(h0 - 1, 0), max(w0 - 1, 0)
+        hb, wb = min(h1 + 1, H), min(w1 + 1, W)
+        xc = x[:, :, :, ha:hb, wa:wb].float()
+        # zero padding only where the crop touches the frame's edge; elsewhere the halo row / column is real data
+        ref, _ = ovc.causal_conv3d(xc, w.float(), b.float())
+        ref = ref[:, :, :, h0 - ha:h0 - ha + (h1 - h0), w0 - wa:w0 - wa + (w1 - w0)]
+        mag, _ = ovc.causal_conv3d(xc.abs(), w.float().abs(), b.float().abs())
+        mag = mag[:, :, :, h0 - ha:h0 - ha + (h1 - h0), w0 - wa:w0 - wa + (w1 - w0)]
+        d = (got[:, :, :, h0:h1, w0:w1].float() - ref).abs()
+        assert bool((d <= 2.0 ** -11 * 1.01 * ref.abs() + 3e-6 * mag + 1e-7).all()), (h0, w0, float(d.max()))
+
+
+def test_argument_validation(svr2, cuda):
+    x = torch.zeros(2, 8, 8, 48, dtype=torch.float16, device="cuda")
+    w = torch.zeros(128, 3, 3, 3, 48, dtype=torch.float16, device="cuda")
+    with pytest.raises(RuntimeError, match="c_in"):
+        svr2.vae_conv.causal_conv3d(x, w)
+    x = torch.zeros(2, 8, 8, 64, dtype=torch.float16, device="cuda")
+    w = torch.zeros(96, 3, 3, 3, 64, dtype=torch.float16, device="cuda")
+    with pytest.raises(RuntimeError, match="c_out"):
+        svr2.vae_conv.causal_conv3d(x, w)
+    with pytest.raises(NotImplementedError):
+        svr2.vae_conv.causal_conv3d(x.float(), w.float())
+    with pytest.raises(RuntimeError, match="CPU"):
+        svr2.vae_conv.pack_conv_weight(torch.zeros(128, 64, 3, 3, 3, dtype=torch.float16))

@@ -176,3 +176,38 @@ def test_postprocess_oracle_matches_reference_module():
         b = (torch.rand(2, 3, 40, 56, generator=g) * 2.0 - 1.0).to(dt)
         ref = lab_color_transfer(a.clone(), b.clone(), _D(), luminance_weight=0.8).permute(0, 2, 3, 1).contiguous().clamp_(-1, 1).mul_(0.5).add_(0.5)
         assert torch.equal(opost.lab_color_fix(a, b), ref)
+
+
+def test_vae_conv_oracle_matches_reference_module():
+    """oracle/vae_conv.py against the real InflatedCausalConv3d (staged copy) on the CPU: the three memory states, temporal slices of
+    several lengths (one frame included), kernels (3,3,3) / (1,3,3) / (1,1,1), and the memory-limited spatially split path."""
+    import torch
+    from oracle import refstage, vae_conv as ovc
+    if not refstage.available():
+        pytest.skip("reference not staged")
+    refstage.activate()
+    from src.models.video_vae_v3.modules.causal_inflation_lib import init_causal_conv3d
+    from src.models.video_vae_v3.modules.types import MemoryState
+    torch.manual_seed(5)
+    for kernel, pad in ((3, 1), ((1, 3, 3), (0, 1, 1)), (1, 0)):
+        for limit in (float("inf"), 1.2e-5):      # GiB: two to three spatial splits of these tensors
+            conv = init_causal_conv3d(8, 12, kernel_size=kernel, stride=1, padding=pad, inflation_mode="tail").eval()
+            conv.set_memory_limit(limit)
+            x = torch.randn(1, 8, 9, 10, 12)
+            with torch.no_grad():
+                ref = conv(x.clone(), memory_state=MemoryState.DISABLED)
+                got, _ = ovc.causal_conv3d(x, conv.weight, conv.bias)
+                assert ref.shape == got.shape and torch.allclose(ref, got, atol=2e-6, rtol=0), (kernel, limit)
+                # streaming: the slices of the VAE's temporal slicing, memory carried between them
+                mem = None
+                outs_ref, outs_got = [], []
+                for i, (a, b) in enumerate(((0, 4), (4, 5), (5, 9))):
+                    st = MemoryState.INITIALIZING if i == 0 else MemoryState.ACTIVE
+                    outs_ref.append(conv(x[:, :, a:b].clone(), memory_state=st))
+                    y, mem = ovc.causal_conv3d(x[:, :, a:b], conv.weight, conv.bias, mem)
+                    outs_got.append(y)
+                    if conv.kernel_size[0] > 1:
+                        assert torch.equal(conv.memory, mem), (kernel, limit, i)
+                assert torch.allclose(torch.cat(outs_ref, 2), torch.cat(outs_got, 2), atol=2e-6, rtol=0)
+                # and slicing changes nothing: the streamed result is the one-shot result
+                assert torch.allclose(torch.cat(outs_got, 2), got, atol=2e-6, rtol=0)
