@@ -11,15 +11,24 @@
 //   (+ resid[t, h, w, co], rounded after the convolution's own rounding: ResnetBlock3D's input_tensor + hidden_states)
 //
 // Layout: activations channels-last [T, H, W, C] (torch.channels_last_3d of the reference's [1, C, T, H, W] — same bytes), weights
-// pre-packed once to [C_out, kt, ks, ks, C_in] (svr2_conv3d_pack_weight), so that the GEMM's K axis is (tap, channel) and every
-// 64-channel K step of an output tile is ONE 4-D TMA box of the input: 64 channels x 16 w x 8 h x 1 frame at the tap's offset.
-// The TMA unit zero-fills the out-of-range rows and columns (the spatial zero padding), and lands the box in exactly the
-// 128-byte-swizzled K-major layout tcgen05.mma reads — no im2col buffer, no halo exchange, no padding copy.
+// pre-packed once to [C_out, kt, ks, ks, C_in] (svr2_conv3d_pack_weight), so that the GEMM's K axis is (tap, channel).
 //
-// Kernel shape: the GEMM of gemm.cu.  CTA pair, tcgen05.mma.cta_group::2 with M = 256 output positions (a 16 x 16 patch of one
-// frame; each CTA stages its 8 rows), N = 256 or 128 output channels, fp32 accumulators double-buffered in TMEM, persistent over
-// (frame, patch, channel tile), warp 0 = TMA producer, warp 1 = MMA issuer, warps 4-7 = epilogue (bias, residual, rounding,
-// swizzled slab, 4-D TMA store that clips the patch at the frame's edge).  fp16 (the VAE's dtype) or bf16, fp32 accumulation.
+// The A operand is never materialised.  An output tile of one CTA is 16 rows x 8 columns of one frame.  For each (temporal tap,
+// 64-channel chunk) ONE 4-D TMA box brings the tile's receptive field — 18 rows x 16 column slots x 64 channels (36 KB; the
+// box starts one column left of the tile and the TMA unit zero-fills whatever lies outside the frame: the spatial zero padding)
+// — into shared memory as consecutive 128-byte rows, 128-byte swizzled.  That is already a K-major UMMA operand for EVERY one
+// of the 9 spatial taps: tap (dh, dw) is the same patch read from row slot (dh * 16 + dw) on, eight consecutive slots (the
+// tile's 8 columns) per 8-row core group and a group stride of one patch row (2048 B).  The descriptor's start address is then
+// only 128-byte aligned; that is fine because tcgen05.mma, like the TMA unit that wrote the patch, derives the 128-byte-swizzle
+// XOR from the absolute shared-memory address (bits 7-9 into bits 4-6), not from the row's index in the tile — verified on the
+// B200 (run 26: base-offset field left 0 gives exact results, setting it to the phase dw does not).  The nine taps therefore re-read
+// shared memory, not L2: 36 KB of input per 9 K steps instead of 9 x 16 KB.  1 x 1 kernels use a 16 x 8 box (the tile itself).
+//
+// Kernel shape: the GEMM of gemm.cu.  CTA pair, tcgen05.mma.cta_group::2 with M = 256 output positions (16 x 16 of one frame;
+// each CTA stages the patch of its 8 columns and half of the weight tile), N = 256 or 128 output channels, fp32 accumulators
+// double-buffered in TMEM, persistent over (frame, tile, channel tile); warp 0 = TMA producer (a patch ring and a weight ring),
+// warp 1 = MMA issuer, warps 4-7 = epilogue (bias, residual, rounding, swizzled slab, 4-D TMA store clipped at the frame's
+// edge).  fp16 (the VAE's dtype) or bf16, fp32 accumulation.
 #include <cuda.h>
 #include <cuda_fp16.h>
 
@@ -34,27 +43,29 @@ namespace conv {
 using namespace ptx;
 using namespace pairx;
 
-constexpr int BM = 128;                  // output positions per CTA: 8 rows x 16 columns of one frame
-constexpr int PATCH_W = 16, PATCH_H = 8; // per CTA; the pair covers 16 x 16
+constexpr int BM = 128;                  // output positions per CTA: 16 rows x 8 columns of one frame
+constexpr int TILE_H = 16, TILE_W = 8;   // per CTA; the pair covers 16 x 16 (CTA r: columns 8r .. 8r + 7)
 constexpr int BK = 64;                   // channels per K step (one 128-byte swizzle atom)
-constexpr int A_BYTES = BM * BK * 2;
-constexpr int SLAB_BYTES = 32 * 128;     // 2 patch rows x 16 columns x 64 channels: one TMA store box
+constexpr int PATCH_BYTES = 18 * 16 * 128;   // 3 x 3 taps: 18 rows x 16 column slots (10 used) x 64 channels; 1 x 1: 16 x 8 of it
+constexpr int SLAB_BYTES = 32 * 128;     // 4 tile rows x 8 columns x 64 channels: one TMA store box
 constexpr uint32_t TMEM_COLS = 512;
 
 template <int BN>
 struct Cfg {
     static constexpr int B_BYTES = (BN / 2) * BK * 2;
-    static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-    static constexpr int STAGES = BN == 256 ? 5 : 7;
+    static constexpr int PSTAGES = BN == 256 ? 2 : 3;     // patch ring: one stage feeds ks * ks K steps
+    static constexpr int BSTAGES = BN == 256 ? 7 : 8;     // weight ring: one stage per K step
     static constexpr int NTHREADS = 256;
-    static constexpr int OFF_SLAB = STAGES * STAGE_BYTES;
+    static constexpr int OFF_B = PSTAGES * PATCH_BYTES;
+    static constexpr int OFF_SLAB = OFF_B + BSTAGES * B_BYTES;
     static constexpr int OFF_BAR = OFF_SLAB + 4 * 2 * SLAB_BYTES;
     static constexpr int SMEM_BYTES = OFF_BAR + 256;
-    static constexpr int BAR_FULL = 0, BAR_EMPTY = STAGES, BAR_TFULL = 2 * STAGES, BAR_TEMPTY = 2 * STAGES + 2,
-                         BAR_COUNT = 2 * STAGES + 4;
+    static constexpr int BAR_PFULL = 0, BAR_PEMPTY = PSTAGES, BAR_BFULL = 2 * PSTAGES, BAR_BEMPTY = 2 * PSTAGES + BSTAGES,
+                         BAR_TFULL = 2 * (PSTAGES + BSTAGES), BAR_TEMPTY = BAR_TFULL + 2, BAR_COUNT = BAR_TFULL + 4;
     static_assert(BAR_COUNT * 8 + 8 <= 256, "barrier block too small");
     static_assert(SMEM_BYTES <= 232448, "shared memory");
-    static_assert(OFF_SLAB % 1024 == 0 && STAGE_BYTES % 1024 == 0, "swizzled tiles need 1024-byte alignment");
+    static_assert(OFF_B % 1024 == 0 && OFF_SLAB % 1024 == 0 && PATCH_BYTES % 1024 == 0 && B_BYTES % 1024 == 0,
+                  "swizzled tiles need 1024-byte alignment");
 };
 
 struct Params {
@@ -106,9 +117,9 @@ __device__ __forceinline__ Tile decode_tile(const Params& p, int id) {
     Tile r;
     r.nt = id % p.n_tiles;
     int sp = id / p.n_tiles;
-    r.w0 = (sp % p.w_tiles) * PATCH_W;
+    r.w0 = (sp % p.w_tiles) * (2 * TILE_W);
     sp /= p.w_tiles;
-    r.h0 = (sp % p.h_tiles) * (2 * PATCH_H);
+    r.h0 = (sp % p.h_tiles) * TILE_H;
     r.t = sp / p.h_tiles;
     return r;
 }
@@ -119,8 +130,9 @@ conv3d_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant
                  const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ CUtensorMap tm_y, const Params p) {
     using C = Cfg<BN>;
     using N = Num<F16>;
-    constexpr int STAGES = C::STAGES, STAGE_BYTES = C::STAGE_BYTES;
-    constexpr int BAR_FULL = C::BAR_FULL, BAR_EMPTY = C::BAR_EMPTY, BAR_TFULL = C::BAR_TFULL, BAR_TEMPTY = C::BAR_TEMPTY;
+    constexpr int PSTAGES = C::PSTAGES, BSTAGES = C::BSTAGES, B_BYTES = C::B_BYTES;
+    constexpr int BAR_PFULL = C::BAR_PFULL, BAR_PEMPTY = C::BAR_PEMPTY, BAR_BFULL = C::BAR_BFULL, BAR_BEMPTY = C::BAR_BEMPTY,
+                  BAR_TFULL = C::BAR_TFULL, BAR_TEMPTY = C::BAR_TEMPTY;
     extern __shared__ __align__(1024) unsigned char smem[];
     const uint32_t base = smem_u32(smem);
     const uint32_t sBar = base + C::OFF_BAR;
@@ -133,14 +145,21 @@ conv3d_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant
     const int first = (int)(blockIdx.x >> 1), stride = (int)(gridDim.x >> 1);
     const int n_tiles_total = p.T * p.h_tiles * p.w_tiles * p.n_tiles;
     const int c_chunks = p.Cin / BK;
-    const int taps = p.kt * p.ks * p.ks;
-    const int kb_count = taps * c_chunks;
+    const int half = p.ks >> 1;
+    const int taps_sp = p.ks * p.ks;                           // K steps fed by one patch
+    const int slot_w = p.ks == 3 ? 16 : 8;                     // column slots per patch row
+    const uint32_t patch_bytes = (uint32_t)((TILE_H + 2 * half) * slot_w * 128);
+    const int n_patches = p.kt * c_chunks;                     // per tile
 
     if (threadIdx.x == 0) {
         if (base & 1023u) __trap();
-        for (int s = 0; s < STAGES; ++s) {
-            mbar_init(bar(BAR_FULL + s), 1);
-            mbar_init(bar(BAR_EMPTY + s), 1);
+        for (int s = 0; s < PSTAGES; ++s) {
+            mbar_init(bar(BAR_PFULL + s), 1);
+            mbar_init(bar(BAR_PEMPTY + s), 1);
+        }
+        for (int s = 0; s < BSTAGES; ++s) {
+            mbar_init(bar(BAR_BFULL + s), 1);
+            mbar_init(bar(BAR_BEMPTY + s), 1);
         }
         for (int b = 0; b < 2; ++b) {
             mbar_init(bar(BAR_TFULL + b), 1);
@@ -162,15 +181,13 @@ conv3d_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant
     const uint32_t tmem = *tmem_slot;
 
     if (warp == 0) {
-        // ------------------------------------------------------------------ TMA producer: one input box + one weight box per K step
+        // ------------------------------------------------------------------ TMA producer: one patch per (dt, chunk), one weight box per tap
         if (lane == 0) {
-            const int half = p.ks >> 1;
-            uint32_t it = 0;
+            uint32_t pit = 0, bit = 0;
             for (int id = first; id < n_tiles_total; id += stride) {
                 const Tile tl = decode_tile(p, id);
-                const int hh = tl.h0 + (int)rank * PATCH_H;
+                const int ww = tl.w0 + (int)rank * TILE_W - half;
                 const int b_row = tl.nt * BN + (int)rank * (BN / 2);
-                int kcol = 0;
                 for (int dt = 0; dt < p.kt; ++dt) {
                     // the causal head: frames before the slice come from the previous slice's memory, or repeat frame 0
                     int ts = tl.t + dt - (p.kt - 1);
@@ -179,16 +196,19 @@ conv3d_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant
                         if (p.has_head) { ta = &tm_head; ts += p.kt - 1; }
                         else ts = 0;
                     }
-                    for (int dh = 0; dh < p.ks; ++dh)
-                        for (int dw = 0; dw < p.ks; ++dw)
-                            for (int cc = 0; cc < c_chunks; ++cc, ++it, kcol += BK) {
-                                const uint32_t s = it % STAGES, use = it / STAGES;
-                                mbar_wait(bar(BAR_EMPTY + s), (use & 1) ^ 1);
-                                if (leader) mbar_expect_tx(bar(BAR_FULL + s), 2 * STAGE_BYTES);
-                                const uint32_t dst = base + s * STAGE_BYTES;
-                                tma_load_4d_pair(dst, ta, bar(BAR_FULL + s), cc * BK, tl.w0 + dw - half, hh + dh - half, ts);
-                                tma_load_2d_pair(dst + A_BYTES, &tm_w, bar(BAR_FULL + s), kcol, b_row);
-                            }
+                    for (int cc = 0; cc < c_chunks; ++cc, ++pit) {
+                        const uint32_t ps = pit % PSTAGES, puse = pit / PSTAGES;
+                        mbar_wait(bar(BAR_PEMPTY + ps), (puse & 1) ^ 1);
+                        if (leader) mbar_expect_tx(bar(BAR_PFULL + ps), 2 * patch_bytes);
+                        tma_load_4d_pair(base + ps * PATCH_BYTES, ta, bar(BAR_PFULL + ps), cc * BK, ww, tl.h0 - half, ts);
+                        const int kcol0 = dt * taps_sp * p.Cin + cc * BK;
+                        for (int tap = 0; tap < taps_sp; ++tap, ++bit) {
+                            const uint32_t bs = bit % BSTAGES, buse = bit / BSTAGES;
+                            mbar_wait(bar(BAR_BEMPTY + bs), (buse & 1) ^ 1);
+                            if (leader) mbar_expect_tx(bar(BAR_BFULL + bs), 2 * B_BYTES);
+                            tma_load_2d_pair(base + C::OFF_B + bs * B_BYTES, &tm_w, bar(BAR_BFULL + bs), kcol0 + tap * p.Cin, b_row);
+                        }
+                    }
                 }
             }
         }
@@ -196,28 +216,42 @@ conv3d_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant
         // ------------------------------------------------------------------ tcgen05.mma issuer of the pair (leader CTA)
         if (leader) {
             constexpr uint32_t idesc = idesc_16(F16, 2 * BM, BN);
-            constexpr uint32_t hi_sw = smem_desc_hi_sw128(1024);
-            uint32_t it = 0, tc = 0;
+            constexpr uint32_t hi_b = smem_desc_hi_sw128(1024);
+            const uint32_t hi_a = smem_desc_hi_sw128((uint32_t)slot_w * 128u);      // 8-row core groups one patch row apart
+            uint32_t pit = 0, bit = 0, tc = 0;
             for (int id = first; id < n_tiles_total; id += stride, ++tc) {
                 const uint32_t b = tc & 1;
                 mbar_wait(bar(BAR_TEMPTY + b), ((tc >> 1) & 1) ^ 1);
                 tc_fence_after();
                 const uint32_t d_tmem = tmem + b * BN;
-                for (int kb = 0; kb < kb_count; ++kb, ++it) {
-                    const uint32_t s = it % STAGES, use = it / STAGES;
-                    mbar_wait(bar(BAR_FULL + s), use & 1);
-                    tc_fence_after();
-                    if (elect_one()) {
-                        const uint32_t alo = smem_desc_lo(base + s * STAGE_BYTES, 16);
-                        const uint32_t blo = smem_desc_lo(base + s * STAGE_BYTES + A_BYTES, 16);
+                for (int pp = 0; pp < n_patches; ++pp, ++pit) {
+                    const uint32_t ps = pit % PSTAGES, puse = pit / PSTAGES;
+                    mbar_wait(bar(BAR_PFULL + ps), puse & 1);
+                    const uint32_t patch = base + ps * PATCH_BYTES;
+                    for (int tap = 0; tap < taps_sp; ++tap, ++bit) {
+                        const uint32_t bs = bit % BSTAGES, buse = bit / BSTAGES;
+                        mbar_wait(bar(BAR_BFULL + bs), buse & 1);
+                        tc_fence_after();
+                        if (elect_one()) {
+                            const int dh = tap / p.ks, dw = tap - dh * p.ks;
+                            // tap (dh, dw): the patch from row slot dh * slot_w + dw on.  The start is 128-byte, not 1024-byte
+                            // aligned; the swizzle XOR is taken from the absolute shared-memory address bits (measured: run 26 —
+                            // base-offset field 0 is right, base offset = dw is wrong), which is also what the TMA write used
+                            const uint32_t alo = smem_desc_lo(patch + (uint32_t)(dh * slot_w + dw) * 128u, 16);
+                            const uint32_t ahi = hi_a;
+                            const uint32_t blo = smem_desc_lo(base + C::OFF_B + bs * B_BYTES, 16);
 #pragma unroll
-                        for (int kk = 0; kk < BK / 16; ++kk)
-                            mma2_ss(d_tmem, make_desc(alo + kk * 2, hi_sw), make_desc(blo + kk * 2, hi_sw), idesc,
-                                    (uint32_t)((kb | kk) != 0));
-                        tc_commit_pair(bar(BAR_EMPTY + s));
-                        if (kb == kb_count - 1) tc_commit_pair(bar(BAR_TFULL + b));
+                            for (int kk = 0; kk < BK / 16; ++kk)
+                                mma2_ss(d_tmem, make_desc(alo + kk * 2, ahi), make_desc(blo + kk * 2, hi_b), idesc,
+                                        (uint32_t)((pp | tap | kk) != 0));
+                            tc_commit_pair(bar(BAR_BEMPTY + bs));
+                            if (tap == taps_sp - 1) {
+                                tc_commit_pair(bar(BAR_PEMPTY + ps));
+                                if (pp == n_patches - 1) tc_commit_pair(bar(BAR_TFULL + b));
+                            }
+                        }
+                        __syncwarp();
                     }
-                    __syncwarp();
                 }
             }
         }
@@ -233,8 +267,8 @@ conv3d_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant
         for (int id = first; id < n_tiles_total; id += stride, ++tc) {
             const Tile tl = decode_tile(p, id);
             const uint32_t b = tc & 1;
-            const int hs = tl.h0 + (int)rank * PATCH_H + q * 2;               // first of this warp's two patch rows
-            const int h = hs + (lane >> 4), w = tl.w0 + (lane & 15);
+            const int hs = tl.h0 + q * 4, ws = tl.w0 + (int)rank * TILE_W;     // this warp's 4 rows x 8 columns of the tile
+            const int h = hs + (lane >> 3), w = ws + (lane & 7);
             const bool valid = h < p.H && w < p.W;
             const int64_t pos = ((int64_t)tl.t * p.H + h) * p.W + w;
             const int col_tile = tl.nt * BN;
@@ -289,8 +323,8 @@ conv3d_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant
                         make_uint4(o[4 * j], o[4 * j + 1], o[4 * j + 2], o[4 * j + 3]);
                 fence_proxy_async_smem();
                 __syncwarp();
-                if (lane == 0 && hs < p.H) {
-                    tma_store_4d(&tm_y, smem_u32(slab), col0, tl.w0, hs, tl.t);      // box 64 c x 16 w x 2 h x 1 t, clipped at the edges
+                if (lane == 0 && hs < p.H && ws < p.W) {
+                    tma_store_4d(&tm_y, smem_u32(slab), col0, ws, hs, tl.t);      // box 64 c x 8 w x 4 h x 1 t, clipped at the edges
                     bulk_commit();
                 }
                 ++n_store;
@@ -310,20 +344,21 @@ conv3d_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant
 template <int BN, bool F16>
 int launch(const void* x, const void* head, const void* w, void* y, Params p, cudaStream_t st) {
     const char* name = "svr2_causal_conv3d_fwd";
-    p.h_tiles = (p.H + 2 * PATCH_H - 1) / (2 * PATCH_H);
-    p.w_tiles = (p.W + PATCH_W - 1) / PATCH_W;
+    p.h_tiles = (p.H + TILE_H - 1) / TILE_H;
+    p.w_tiles = (p.W + 2 * TILE_W - 1) / (2 * TILE_W);
     p.n_tiles = p.Cout / BN;
+    const int slot_w = p.ks == 3 ? 16 : 8, box_h = TILE_H + 2 * (p.ks / 2);
     CUtensorMap tx, th, tw, ty;
     int rc;
-    if ((rc = make_tmap_thwc(&tx, x, p.T, p.H, p.W, p.Cin, PATCH_W, PATCH_H)) != SVR2_OK) return rc;
+    if ((rc = make_tmap_thwc(&tx, x, p.T, p.H, p.W, p.Cin, slot_w, box_h)) != SVR2_OK) return rc;
     if (p.has_head) {
-        if ((rc = make_tmap_thwc(&th, head, p.kt - 1, p.H, p.W, p.Cin, PATCH_W, PATCH_H)) != SVR2_OK) return rc;
+        if ((rc = make_tmap_thwc(&th, head, p.kt - 1, p.H, p.W, p.Cin, slot_w, box_h)) != SVR2_OK) return rc;
     } else {
         th = tx;
     }
     const int64_t ktot = (int64_t)p.kt * p.ks * p.ks * p.Cin;
     if ((rc = make_tmap_2d(&tw, w, p.Cout, ktot, ktot, BN / 2)) != SVR2_OK) return rc;
-    if ((rc = make_tmap_thwc(&ty, y, p.T, p.H, p.W, p.Cout, PATCH_W, 2)) != SVR2_OK) return rc;
+    if ((rc = make_tmap_thwc(&ty, y, p.T, p.H, p.W, p.Cout, TILE_W, 4)) != SVR2_OK) return rc;
     static PerDeviceFlag smem_ok;
     if ((rc = ensure_dyn_smem(conv3d_tc_kernel<BN, F16>, Cfg<BN>::SMEM_BYTES, smem_ok, name)) != SVR2_OK) return rc;
     const int pairs = sm_count() / 2;
