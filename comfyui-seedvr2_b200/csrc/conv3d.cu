@@ -53,16 +53,21 @@ constexpr uint32_t TMEM_COLS = 512;
 template <int BN>
 struct Cfg {
     static constexpr int B_BYTES = (BN / 2) * BK * 2;
-    static constexpr int PSTAGES = BN == 256 ? 2 : 3;     // patch ring: one stage feeds ks * ks K steps
-    static constexpr int BSTAGES = BN == 256 ? 7 : 8;     // weight ring: one stage per K step
+    static constexpr int PSTAGES = 2;                     // patch ring: one stage feeds ks * ks K steps (1 x 1: 4 stages of 16 KB)
+    static constexpr int PSTAGES_MAX = 4;
+    // weight ring: one stage holds the weight boxes of TPB consecutive taps (a row of the 3 x 3 stencil when N = 128, where a K
+    // step is only 256 tensor-pipe cycles: one barrier round trip per row instead of per tap, 1211 -> 1294 TFLOP/s, run 29)
+    static constexpr int TPB = BN == 256 ? 1 : 3;
+    static constexpr int BSTAGE_BYTES = TPB * B_BYTES;
+    static constexpr int BSTAGES = BN == 256 ? 7 : 5;
     static constexpr int NTHREADS = 256;
     static constexpr int OFF_B = PSTAGES * PATCH_BYTES;
-    static constexpr int OFF_SLAB = OFF_B + BSTAGES * B_BYTES;
+    static constexpr int OFF_SLAB = OFF_B + BSTAGES * BSTAGE_BYTES;
     static constexpr int OFF_BAR = OFF_SLAB + 4 * 2 * SLAB_BYTES;
-    static constexpr int SMEM_BYTES = OFF_BAR + 256;
-    static constexpr int BAR_PFULL = 0, BAR_PEMPTY = PSTAGES, BAR_BFULL = 2 * PSTAGES, BAR_BEMPTY = 2 * PSTAGES + BSTAGES,
-                         BAR_TFULL = 2 * (PSTAGES + BSTAGES), BAR_TEMPTY = BAR_TFULL + 2, BAR_COUNT = BAR_TFULL + 4;
-    static_assert(BAR_COUNT * 8 + 8 <= 256, "barrier block too small");
+    static constexpr int SMEM_BYTES = OFF_BAR + 512;
+    static constexpr int BAR_PFULL = 0, BAR_PEMPTY = PSTAGES_MAX, BAR_BFULL = 2 * PSTAGES_MAX, BAR_BEMPTY = 2 * PSTAGES_MAX + BSTAGES,
+                         BAR_TFULL = 2 * (PSTAGES_MAX + BSTAGES), BAR_TEMPTY = BAR_TFULL + 2, BAR_COUNT = BAR_TFULL + 4;
+    static_assert(BAR_COUNT * 8 + 8 <= 512, "barrier block too small");
     static_assert(SMEM_BYTES <= 232448, "shared memory");
     static_assert(OFF_B % 1024 == 0 && OFF_SLAB % 1024 == 0 && PATCH_BYTES % 1024 == 0 && B_BYTES % 1024 == 0,
                   "swizzled tiles need 1024-byte alignment");
@@ -130,7 +135,7 @@ conv3d_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant
                  const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ CUtensorMap tm_y, const Params p) {
     using C = Cfg<BN>;
     using N = Num<F16>;
-    constexpr int PSTAGES = C::PSTAGES, BSTAGES = C::BSTAGES, B_BYTES = C::B_BYTES;
+    constexpr int BSTAGES = C::BSTAGES, B_BYTES = C::B_BYTES, BSTAGE_BYTES = C::BSTAGE_BYTES;
     constexpr int BAR_PFULL = C::BAR_PFULL, BAR_PEMPTY = C::BAR_PEMPTY, BAR_BFULL = C::BAR_BFULL, BAR_BEMPTY = C::BAR_BEMPTY,
                   BAR_TFULL = C::BAR_TFULL, BAR_TEMPTY = C::BAR_TEMPTY;
     extern __shared__ __align__(1024) unsigned char smem[];
@@ -150,10 +155,13 @@ conv3d_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant
     const int slot_w = p.ks == 3 ? 16 : 8;                     // column slots per patch row
     const uint32_t patch_bytes = (uint32_t)((TILE_H + 2 * half) * slot_w * 128);
     const int n_patches = p.kt * c_chunks;                     // per tile
+    const int tpb = p.ks == 3 ? C::TPB : 1;                    // taps per weight stage (divides ks * ks)
+    const uint32_t pstages = p.ks == 3 ? C::PSTAGES : C::PSTAGES_MAX;
+    const uint32_t pslot = p.ks == 3 ? (uint32_t)PATCH_BYTES : 16384u;      // patch ring slot
 
     if (threadIdx.x == 0) {
         if (base & 1023u) __trap();
-        for (int s = 0; s < PSTAGES; ++s) {
+        for (int s = 0; s < C::PSTAGES_MAX; ++s) {
             mbar_init(bar(BAR_PFULL + s), 1);
             mbar_init(bar(BAR_PEMPTY + s), 1);
         }
@@ -197,16 +205,18 @@ conv3d_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant
                         else ts = 0;
                     }
                     for (int cc = 0; cc < c_chunks; ++cc, ++pit) {
-                        const uint32_t ps = pit % PSTAGES, puse = pit / PSTAGES;
+                        const uint32_t ps = pit % pstages, puse = pit / pstages;
                         mbar_wait(bar(BAR_PEMPTY + ps), (puse & 1) ^ 1);
                         if (leader) mbar_expect_tx(bar(BAR_PFULL + ps), 2 * patch_bytes);
-                        tma_load_4d_pair(base + ps * PATCH_BYTES, ta, bar(BAR_PFULL + ps), cc * BK, ww, tl.h0 - half, ts);
+                        tma_load_4d_pair(base + ps * pslot, ta, bar(BAR_PFULL + ps), cc * BK, ww, tl.h0 - half, ts);
                         const int kcol0 = dt * taps_sp * p.Cin + cc * BK;
-                        for (int tap = 0; tap < taps_sp; ++tap, ++bit) {
+                        for (int tap = 0; tap < taps_sp; tap += tpb, ++bit) {
                             const uint32_t bs = bit % BSTAGES, buse = bit / BSTAGES;
                             mbar_wait(bar(BAR_BEMPTY + bs), (buse & 1) ^ 1);
-                            if (leader) mbar_expect_tx(bar(BAR_BFULL + bs), 2 * B_BYTES);
-                            tma_load_2d_pair(base + C::OFF_B + bs * B_BYTES, &tm_w, bar(BAR_BFULL + bs), kcol0 + tap * p.Cin, b_row);
+                            if (leader) mbar_expect_tx(bar(BAR_BFULL + bs), 2 * tpb * B_BYTES);
+                            for (int j = 0; j < tpb; ++j)
+                                tma_load_2d_pair(base + C::OFF_B + bs * BSTAGE_BYTES + j * B_BYTES, &tm_w, bar(BAR_BFULL + bs),
+                                                 kcol0 + (tap + j) * p.Cin, b_row);
                         }
                     }
                 }
@@ -214,6 +224,8 @@ conv3d_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant
         }
     } else if (warp == 1) {
         // ------------------------------------------------------------------ tcgen05.mma issuer of the pair (leader CTA)
+        // The whole warp walks the loop and waits on the barriers; one elected lane issues.  (A single lane looping while the
+        // other 31 sit at the final barrier measured 30 % slower at N = 128, 10 % at N = 256 — run 29.)
         if (leader) {
             constexpr uint32_t idesc = idesc_16(F16, 2 * BM, BN);
             constexpr uint32_t hi_b = smem_desc_hi_sw128(1024);
@@ -225,33 +237,41 @@ conv3d_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant
                 tc_fence_after();
                 const uint32_t d_tmem = tmem + b * BN;
                 for (int pp = 0; pp < n_patches; ++pp, ++pit) {
-                    const uint32_t ps = pit % PSTAGES, puse = pit / PSTAGES;
+                    const uint32_t ps = pit % pstages, puse = pit / pstages;
                     mbar_wait(bar(BAR_PFULL + ps), puse & 1);
-                    const uint32_t patch = base + ps * PATCH_BYTES;
-                    for (int tap = 0; tap < taps_sp; ++tap, ++bit) {
-                        const uint32_t bs = bit % BSTAGES, buse = bit / BSTAGES;
-                        mbar_wait(bar(BAR_BFULL + bs), buse & 1);
-                        tc_fence_after();
-                        if (elect_one()) {
-                            const int dh = tap / p.ks, dw = tap - dh * p.ks;
+                    const uint32_t patch = base + ps * pslot;
+                    int j = 0;
+                    uint32_t bstage = 0;
+                    for (int dh = 0; dh < p.ks; ++dh)
+                        for (int dw = 0; dw < p.ks; ++dw) {
+                            if (j == 0) {
+                                const uint32_t bs = bit % BSTAGES, buse = bit / BSTAGES;
+                                mbar_wait(bar(BAR_BFULL + bs), buse & 1);
+                                tc_fence_after();
+                                bstage = base + C::OFF_B + bs * BSTAGE_BYTES;
+                            }
                             // tap (dh, dw): the patch from row slot dh * slot_w + dw on.  The start is 128-byte, not 1024-byte
                             // aligned; the swizzle XOR is taken from the absolute shared-memory address bits (measured: run 26 —
                             // base-offset field 0 is right, base offset = dw is wrong), which is also what the TMA write used
                             const uint32_t alo = smem_desc_lo(patch + (uint32_t)(dh * slot_w + dw) * 128u, 16);
-                            const uint32_t ahi = hi_a;
-                            const uint32_t blo = smem_desc_lo(base + C::OFF_B + bs * B_BYTES, 16);
+                            const uint32_t blo = smem_desc_lo(bstage + j * B_BYTES, 16);
+                            if (elect_one()) {
 #pragma unroll
-                            for (int kk = 0; kk < BK / 16; ++kk)
-                                mma2_ss(d_tmem, make_desc(alo + kk * 2, ahi), make_desc(blo + kk * 2, hi_b), idesc,
-                                        (uint32_t)((pp | tap | kk) != 0));
-                            tc_commit_pair(bar(BAR_BEMPTY + bs));
-                            if (tap == taps_sp - 1) {
-                                tc_commit_pair(bar(BAR_PEMPTY + ps));
-                                if (pp == n_patches - 1) tc_commit_pair(bar(BAR_TFULL + b));
+                                for (int kk = 0; kk < BK / 16; ++kk)
+                                    mma2_ss(d_tmem, make_desc(alo + kk * 2, hi_a), make_desc(blo + kk * 2, hi_b), idesc,
+                                            (uint32_t)((pp | dh | dw | kk) != 0));
+                                if (j + 1 == tpb) tc_commit_pair(bar(BAR_BEMPTY + bit % BSTAGES));
+                                if (dh == p.ks - 1 && dw == p.ks - 1) {
+                                    tc_commit_pair(bar(BAR_PEMPTY + ps));
+                                    if (pp == n_patches - 1) tc_commit_pair(bar(BAR_TFULL + b));
+                                }
+                            }
+                            __syncwarp();
+                            if (++j == tpb) {
+                                ++bit;
+                                j = 0;
                             }
                         }
-                        __syncwarp();
-                    }
                 }
             }
         }
