@@ -1,0 +1,108 @@
+"""The video VAE's residual block on the B200: per-frame GroupNorm + SiLU as one fused pass, the two causal
+3-D convolutions as tcgen05 implicit GEMMs, the residual add in the second convolution's epilogue.
+
+``ResnetBlock3DB200`` mirrors ``ResnetBlock3D`` (src/models/video_vae_v3/modules/attn_video_vae.py:253-361) as the VAE builds it
+(no time embedding, no sampler inside the block, SiLU, dropout 0): same ``forward(input_tensor, temb, memory_state)`` call, same
+memory bookkeeping through its convolutions.  ``install_vae_blocks(model)`` replaces every such block of a built VAE in place;
+up / down samplers, the mid-block attention and the 3- / 16-channel boundary convolutions stay the reference's.
+CUDA only — there is no other path."""
+from typing import Optional
+
+import torch
+from torch import nn
+
+from . import _lib, ops
+from .vae_conv import _DTYPE_CODE, CausalConv3dB200
+
+
+def groupnorm_silu(x: torch.Tensor, weight: Optional[torch.Tensor], bias: Optional[torch.Tensor], groups: int, eps: float,
+                   silu: bool = True, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """x [T, H, W, C] (or [T, HW, C]) channels-last: GroupNorm over each frame's (C / groups) x H x W values, then SiLU; rounded to
+    the tensor dtype after each of the two, like the reference's two tensor ops (causal_inflation_lib.py:366-409 + nn.SiLU)."""
+    code = _DTYPE_CODE.get(x.dtype)
+    if code is None:
+        raise NotImplementedError(f"seedvr2_b200.vae_block: fp16 or bf16 activations only (got {x.dtype})")
+    ops._need(x, "x", x.dtype)
+    T, C = x.shape[0], x.shape[-1]
+    hw = x.numel() // max(T * C, 1)
+    for name, t in (("weight", weight), ("bias", bias)):
+        if t is not None:
+            ops._need(t, name, x.dtype)
+            if t.numel() != C:
+                raise RuntimeError(f"seedvr2_b200.vae_block: `{name}` must have {C} elements")
+    y = torch.empty_like(x) if out is None else ops._need(out, "out", x.dtype)
+    if T == 0 or hw == 0:
+        return y
+    lib = _lib.lib()
+    ws = torch.empty(int(lib.svr2_groupnorm_workspace_bytes(T, groups)), dtype=torch.uint8, device=x.device)
+    ops._call("svr2_groupnorm_silu_fwd", 2, x.device, lib.svr2_groupnorm_silu_fwd, x.data_ptr(), ops._ptr(weight), ops._ptr(bias),
+              y.data_ptr(), ws.data_ptr(), T, hw, C, int(groups), float(eps), int(silu), code, ops._stream(x))
+    return y
+
+
+class ResnetBlock3DB200(nn.Module):
+    """Drop-in for the VAE's ``ResnetBlock3D``; see the module docstring."""
+
+    def __init__(self, norm1: nn.GroupNorm, conv1: nn.Module, norm2: nn.GroupNorm, conv2: nn.Module,
+                 conv_shortcut: Optional[nn.Module] = None, output_scale_factor: float = 1.0):
+        super().__init__()
+        self.groups1, self.eps1 = norm1.num_groups, norm1.eps
+        self.groups2, self.eps2 = norm2.num_groups, norm2.eps
+        for name, n in (("norm1", norm1), ("norm2", norm2)):
+            self.register_buffer(name + "_weight", None if n.weight is None else n.weight.detach().clone(), persistent=False)
+            self.register_buffer(name + "_bias", None if n.bias is None else n.bias.detach().clone(), persistent=False)
+        self.conv1 = CausalConv3dB200.from_reference(conv1)
+        self.conv2 = CausalConv3dB200.from_reference(conv2)
+        self.conv_shortcut = None if conv_shortcut is None else CausalConv3dB200.from_reference(conv_shortcut)
+        self.in_channels, self.out_channels = self.conv1.in_channels, self.conv2.out_channels
+        self.output_scale_factor = float(output_scale_factor)
+
+    @classmethod
+    def from_reference(cls, block: nn.Module) -> "ResnetBlock3DB200":
+        """From a built ``ResnetBlock3D``.  Raises NotImplementedError for configurations the VAE does not use."""
+        if getattr(block, "time_emb_proj", None) is not None or getattr(block, "upsample", None) is not None or \
+                getattr(block, "downsample", None) is not None:
+            raise NotImplementedError("seedvr2_b200.vae_block: blocks with a time embedding or an internal sampler are not mirrored")
+        if not isinstance(block.nonlinearity, nn.SiLU):
+            raise NotImplementedError("seedvr2_b200.vae_block: SiLU blocks only")
+        if not isinstance(block.norm1, nn.GroupNorm) or not isinstance(block.norm2, nn.GroupNorm):
+            raise NotImplementedError("seedvr2_b200.vae_block: GroupNorm blocks only")
+        drop = getattr(block, "dropout", None)
+        if drop is not None and getattr(drop, "p", 0.0) != 0.0 and block.training:
+            raise NotImplementedError("seedvr2_b200.vae_block: inference only (dropout)")
+        return cls(block.norm1, block.conv1, block.norm2, block.conv2, getattr(block, "conv_shortcut", None),
+                   getattr(block, "output_scale_factor", 1.0))
+
+    def forward(self, input_tensor: torch.Tensor, temb=None, memory_state="DISABLED", **kwargs) -> torch.Tensor:
+        if temb is not None:
+            raise NotImplementedError("seedvr2_b200.vae_block: the VAE calls its residual blocks with temb=None")
+        x = input_tensor.permute(0, 2, 3, 4, 1)                      # [B, T, H, W, C]: no copy for channels_last_3d input
+        if not x.is_contiguous():
+            x = x.contiguous()
+        B = x.shape[0]
+        h = torch.empty_like(x)
+        for b in range(B):
+            groupnorm_silu(x[b], self.norm1_weight, self.norm1_bias, self.groups1, self.eps1, out=h[b])
+        h = self.conv1.forward_cl(h, memory_state)
+        for b in range(B):
+            groupnorm_silu(h[b], self.norm2_weight, self.norm2_bias, self.groups2, self.eps2, out=h[b])      # in place
+        skip = x if self.conv_shortcut is None else self.conv_shortcut.forward_cl(x, memory_state)
+        out = self.conv2.forward_cl(h, memory_state, resid=skip)     # (input_tensor + hidden_states), :361
+        if self.output_scale_factor != 1.0:
+            out = out / self.output_scale_factor
+        return out.permute(0, 4, 1, 2, 3)
+
+
+def install_vae_blocks(model: nn.Module) -> int:
+    """Replace every ``ResnetBlock3D`` of a built (CUDA, fp16 / bf16) VAE that this module mirrors; returns how many were replaced."""
+    n = 0
+    for parent in list(model.modules()):
+        for name, child in list(parent.named_children()):
+            if type(child).__name__ != "ResnetBlock3D":
+                continue
+            try:
+                setattr(parent, name, ResnetBlock3DB200.from_reference(child))
+                n += 1
+            except NotImplementedError:
+                pass          # a configuration outside the mirror keeps the reference's block
+    return n

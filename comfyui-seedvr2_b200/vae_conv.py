@@ -93,11 +93,6 @@ class CausalConv3dB200(nn.Module):
         pass
 
     def forward(self, input: torch.Tensor, memory_state="DISABLED", resid: Optional[torch.Tensor] = None) -> torch.Tensor:
-        state = _state_name(memory_state)
-        if state != "ACTIVE":
-            self.memory = None                                                  # :216-217
-        kt = self.kernel_size[0]
-        B = input.shape[0]
         x = input.permute(0, 2, 3, 4, 1)                                        # [B, T, H, W, C]: contiguous for channels_last_3d
         if not x.is_contiguous():
             x = x.contiguous()
@@ -105,10 +100,19 @@ class CausalConv3dB200(nn.Module):
         if resid is not None:
             r = resid.permute(0, 2, 3, 4, 1)
             r = r if r.is_contiguous() else r.contiguous()
+        return self.forward_cl(x, memory_state, r).permute(0, 4, 1, 2, 3)       # [B, C_out, T, H, W], channels-last strides
+
+    def forward_cl(self, x: torch.Tensor, memory_state="DISABLED", resid: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """The same on channels-last tensors: x [B, T, H, W, C_in] -> [B, T, H, W, C_out]."""
+        state = _state_name(memory_state)
+        if state != "ACTIVE":
+            self.memory = None                                                  # :216-217
+        kt = self.kernel_size[0]
+        B = x.shape[0]
         y = torch.empty(*x.shape[:4], self.out_channels, dtype=x.dtype, device=x.device)
         for b in range(B):
             head = self.memory[b] if (self.memory is not None and kt > 1) else None
-            causal_conv3d(x[b], self.weight_packed, self.bias, head, None if r is None else r[b], out=y[b])
+            causal_conv3d(x[b], self.weight_packed, self.bias, head, None if resid is None else resid[b], out=y[b])
         if kt > 1 and state != "DISABLED":
             # the last kt - 1 frames of (head, input): basic_forward :229-240, slicing_forward :273-283
             if x.shape[1] >= kt - 1:
@@ -116,4 +120,4 @@ class CausalConv3dB200(nn.Module):
             else:
                 prev = self.memory if self.memory is not None else x[:, :1].expand(-1, kt - 1, -1, -1, -1)
                 self.memory = torch.cat((prev, x), dim=1)[:, -(kt - 1):].contiguous()
-        return y.permute(0, 4, 1, 2, 3)                                         # [B, C_out, T, H, W], channels-last strides
+        return y

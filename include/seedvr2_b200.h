@@ -370,6 +370,19 @@ int svr2_conv3d_pack_weight(const void* weight, void* packed, int c_out, int c_i
 int svr2_causal_conv3d_fwd(const void* x, const void* head, const void* weight_packed, const void* bias, const void* resid,
                            void* y, int T, int H, int W, int c_in, int c_out, int kt, int ks, int dtype, void* stream);
 
+/*
+ * The VAE's per-frame GroupNorm (+ SiLU): causal_norm_wrapper folds time into the batch before nn.GroupNorm
+ * (causal_inflation_lib.py:354-409), ResnetBlock3D applies SiLU to the result (attn_video_vae.py:316-322, 348-356).
+ *   x, y [T, HW, C] channels-last (y may alias x), weight / bias [C] or NULL, statistics per (frame, group) in fp32, output rounded
+ *   after the affine and again after the activation like the two ATen ops; silu = 0 skips the activation.
+ *   workspace: svr2_groupnorm_workspace_bytes(T, groups) bytes of device memory (the statistics partials; no allocation inside).
+ *   C / groups in {2, 4, 8, 16}, C = 8 x a power of two; dtype SVR2_DTYPE_F16 or SVR2_DTYPE_BF16.
+ */
+#define SVR2_GN_CHUNKS 128
+int64_t svr2_groupnorm_workspace_bytes(int T, int groups);
+int svr2_groupnorm_silu_fwd(const void* x, const void* weight, const void* bias, void* y, void* workspace, int T, int64_t HW, int C,
+                            int groups, float eps, int silu, int dtype, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

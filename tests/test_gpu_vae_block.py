@@ -1,0 +1,151 @@
+"""svr2_groupnorm_silu_fwd and the VAE residual block (comfyui-seedvr2_b200/vae_block.py) on the GPU.
+
+GroupNorm + SiLU: against ATen's own two ops on the same GPU in the same dtype (the reference's path: causal_norm_wrapper ->
+nn.GroupNorm per frame, then nn.SiLU) — equal except where a statistics difference of a few fp32 ulps flips a rounding, bounded
+at one ulp of the output on a small fraction — and against the fp32 oracle.
+Residual block: against the reference's block composed from its real, importable parts (InflatedCausalConv3d through cuDNN,
+causal_norm_wrapper, nn.SiLU; diffusers' base class is not in the image) in fp16 over the VAE's temporal slices, both measured
+against the fp32 oracle (oracle/vae_block.py)."""
+import pytest
+import torch
+import torch.nn.functional as F
+from torch import nn
+
+from oracle import refstage
+from oracle import vae_block as ovb
+
+pytestmark = pytest.mark.gpu
+
+
+def _ref_gn_silu(x_thwc, w, b, groups, eps, silu=True):
+    """ATen group_norm per frame + silu in the tensor dtype; x [T, H, W, C]."""
+    y = F.group_norm(x_thwc.permute(0, 3, 1, 2).contiguous(), groups, w, b, eps)
+    if silu:
+        y = F.silu(y)
+    return y.permute(0, 2, 3, 1)
+
+
+@pytest.mark.parametrize("C", [64, 128, 256, 512])
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16], ids=["fp16", "bf16"])
+@pytest.mark.parametrize("shape", [(3, 37, 23), (1, 64, 64), (2, 135, 240)], ids=["3x37x23", "1x64x64", "2x135x240"])
+def test_groupnorm_silu_matches_aten(svr2, cuda, C, dtype, shape):
+    T, H, W = shape
+    g = torch.Generator(device="cuda").manual_seed(C + T)
+    x = (torch.randn(T, H, W, C, generator=g, device=cuda) * 1.7 + 0.4 * torch.randn(1, 1, 1, C, generator=g, device=cuda)).to(dtype)
+    w = (1 + 0.3 * torch.randn(C, generator=g, device=cuda)).to(dtype)
+    b = (0.2 * torch.randn(C, generator=g, device=cuda)).to(dtype)
+    ulp = 2.0 ** (-10 if dtype == torch.float16 else -7)
+    # the normalisation alone: ATen's output, except where a statistics difference of a few fp32 ulps flips the rounding
+    got = svr2.vae_block.groupnorm_silu(x, w, b, 32, 1e-6, silu=False)
+    want = _ref_gn_silu(x, w, b, 32, 1e-6, silu=False)
+    exact = _ref_gn_silu(x.float(), w.float(), b.float(), 32, 1e-6, silu=False)
+    torch.cuda.synchronize()
+    assert got.shape == want.shape and got.dtype == dtype
+    d = (got.float() - want.float()).abs()
+    # never more than one flipped rounding; where a * x + b cancels to ~0 the fp32 evaluation error (a few 1e-7 of |a x|) is
+    # what is left, so the bound carries an absolute term on the operand scale
+    assert bool((d <= ulp * 1.01 * want.float().abs() + 1e-6 * (1 + x.float().abs())).all())
+    assert float((d > 0).float().mean()) < 0.05, float((d > 0).float().mean())      # a flipped rounding of one group's rstd at most
+    e_got, e_want = float((got.float() - exact).abs().max()), float((want.float() - exact).abs().max())
+    assert e_got <= 1.05 * e_want + 1e-6, (e_got, e_want)
+    # the fused activation: bit-equal to ATen's silu of the normalised tensor (same fp32 formula, same rounding point)
+    fused = svr2.vae_block.groupnorm_silu(x, w, b, 32, 1e-6, silu=True)
+    assert torch.equal(fused, F.silu(got))
+    # and end to end against the reference's two ops, on the scale of the activation's input (silu is steep in relative terms
+    # for large negative inputs: one flipped rounding of y = -10 moves silu(y) by 0.8 %)
+    want_act = F.silu(want)
+    lim = ulp * 1.01 * (want_act.float().abs() + want.float().abs()) + 1e-6 * (1 + x.float().abs())
+    assert bool(((fused.float() - want_act.float()).abs() <= lim).all())
+
+
+def test_groupnorm_variants(svr2, cuda):
+    g = torch.Generator(device="cuda").manual_seed(9)
+    x = (torch.randn(2, 40, 56, 128, generator=g, device=cuda) * 0.5 + 60.0).half()      # |mean| >> std: shifted sums must hold
+    w = torch.ones(128, device=cuda).half()
+    b = torch.zeros(128, device=cuda).half()
+    got = svr2.vae_block.groupnorm_silu(x, w, b, 32, 1e-6, silu=False)
+    # ATen rounds the mean to fp16 (60 +- 0.03) before subtracting it, so "exact" is not the target here: ATen's own output is
+    want = _ref_gn_silu(x, w, b, 32, 1e-6, silu=False)
+    d = (got.float() - want.float()).abs()
+    assert bool((d <= 2.0 ** -10 * 1.01 * want.float().abs() + 1e-6 * (1 + x.float().abs())).all())
+    assert float((d > 0).float().mean()) < 0.05
+    exact = _ref_gn_silu(x.float(), None, None, 32, 1e-6, silu=False)
+    assert float((got.float() - exact).abs().max()) <= 1.05 * float((want.float() - exact).abs().max())
+    # no affine, no activation; in place
+    plain = svr2.vae_block.groupnorm_silu(x, None, None, 32, 1e-6, silu=False)
+    assert torch.equal(plain, got)
+    y = x.clone()
+    svr2.vae_block.groupnorm_silu(y, w, b, 32, 1e-6, silu=True, out=y)
+    assert torch.equal(y, svr2.vae_block.groupnorm_silu(x, w, b, 32, 1e-6))
+    # deterministic: the partials are merged in a fixed order
+    assert torch.equal(svr2.vae_block.groupnorm_silu(x, w, b, 32, 1e-6), svr2.vae_block.groupnorm_silu(x, w, b, 32, 1e-6))
+    with pytest.raises(RuntimeError, match="channels per group"):
+        svr2.vae_block.groupnorm_silu(torch.zeros(1, 4, 4, 96, dtype=torch.float16, device=cuda), None, None, 32, 1e-6)
+    with pytest.raises(NotImplementedError):
+        svr2.vae_block.groupnorm_silu(x.float(), None, None, 32, 1e-6)
+
+
+class ResnetBlock3D(nn.Module):
+    """The reference's block from its importable parts, in the order of ResnetBlock3D.forward (attn_video_vae.py:311-361)."""
+
+    def __init__(self, ci, co, init_causal_conv3d, causal_norm_wrapper, full=True):
+        super().__init__()
+        self.wrap = causal_norm_wrapper
+        self.norm1 = nn.GroupNorm(32, ci, eps=1e-6)
+        self.norm2 = nn.GroupNorm(32, co, eps=1e-6)
+        k, p = (3, 1) if full else ((1, 3, 3), (0, 1, 1))
+        self.conv1 = init_causal_conv3d(ci, co, kernel_size=k, stride=1, padding=p, inflation_mode="tail")
+        self.conv2 = init_causal_conv3d(co, co, kernel_size=3, stride=1, padding=1, inflation_mode="tail")
+        self.conv_shortcut = init_causal_conv3d(ci, co, kernel_size=1, stride=1, padding=0, inflation_mode="tail") if ci != co else None
+        self.nonlinearity = nn.SiLU()
+        self.time_emb_proj = self.upsample = self.downsample = None
+        self.output_scale_factor = 1.0
+        for n in (self.norm1, self.norm2):
+            nn.init.normal_(n.weight, 1.0, 0.2)
+            nn.init.normal_(n.bias, 0.0, 0.2)
+
+    def forward(self, x, temb=None, memory_state=None):
+        h = self.nonlinearity(self.wrap(self.norm1, x))
+        h = self.conv1(h, memory_state=memory_state)
+        h = self.nonlinearity(self.wrap(self.norm2, h))
+        h = self.conv2(h, memory_state=memory_state)
+        if self.conv_shortcut is not None:
+            x = self.conv_shortcut(x, memory_state=memory_state)
+        return (x + h) / self.output_scale_factor
+
+
+@pytest.mark.parametrize("ci,co,full", [(128, 128, True), (256, 128, True), (128, 256, False)], ids=["128", "256to128", "128to256_half"])
+def test_resnet_block_matches_reference_parts(svr2, cuda, ci, co, full):
+    if not refstage.available():
+        pytest.skip("reference not staged")
+    refstage.activate()
+    from src.models.video_vae_v3.modules.causal_inflation_lib import causal_norm_wrapper, init_causal_conv3d
+    from src.models.video_vae_v3.modules.types import MemoryState
+    torch.manual_seed(ci + co)
+    ref = ResnetBlock3D(ci, co, init_causal_conv3d, causal_norm_wrapper, full).eval().cuda().half()
+    mine = svr2.vae_block.ResnetBlock3DB200.from_reference(ref)
+    params = {k: v.float() for k, v in ref.state_dict().items()}
+    x = (torch.randn(1, ci, 9, 40, 56, device=cuda) * 1.5).half().contiguous(memory_format=torch.channels_last_3d)
+    # the fp32 oracle must not run its convolutions in TF32 (cuDNN's default for fp32 inputs)
+    with torch.no_grad(), torch.backends.cudnn.flags(enabled=True, allow_tf32=False):
+        outs_r, outs_m, outs_o, mem = [], [], [], None
+        for i, (a, b) in enumerate(((0, 4), (4, 5), (5, 9))):
+            st = MemoryState.INITIALIZING if i == 0 else MemoryState.ACTIVE
+            outs_r.append(ref(x[:, :, a:b].contiguous(), memory_state=st))
+            outs_m.append(mine(x[:, :, a:b], None, memory_state=st))
+            o, mem = ovb.resnet_block3d(x[:, :, a:b].float(), params, memory=mem)
+            outs_o.append(o)
+        r, m, o = torch.cat(outs_r, 2).float(), torch.cat(outs_m, 2).float(), torch.cat(outs_o, 2)
+        one_shot, _ = ovb.resnet_block3d(x.float(), params)
+        assert float((o - one_shot).abs().max()) < 1e-4                      # slicing does not change the function
+        e_ref, e_mine = float((r - o).abs().max()), float((m - o).abs().max())
+        rms_ref, rms_mine = float((r - o).pow(2).mean().sqrt()), float((m - o).pow(2).mean().sqrt())
+        assert m.shape == r.shape
+        assert rms_mine <= 1.1 * rms_ref + 1e-6, ("rms", rms_mine, rms_ref, e_mine, e_ref)
+        assert e_mine <= 1.5 * e_ref + 1e-3, ("max", e_mine, e_ref, rms_mine, rms_ref)
+        # one-shot call with the memory off, and its equality with the streamed result
+        whole = mine(x, None, memory_state=MemoryState.DISABLED)
+        assert torch.equal(whole, torch.cat(outs_m, 2))
+    # the installer finds the block by its class name and swaps it in place
+    holder = nn.Sequential(ref)
+    assert svr2.vae_block.install_vae_blocks(holder) == 1 and isinstance(holder[0], svr2.vae_block.ResnetBlock3DB200)
