@@ -129,7 +129,7 @@ __device__ __forceinline__ Tile decode_tile(const Params& p, int id) {
     return r;
 }
 
-template <int BN, bool F16>
+template <int BN, bool F16, int KS>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(Cfg<BN>::NTHREADS, 1)
 conv3d_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ CUtensorMap tm_head,
                  const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ CUtensorMap tm_y, const Params p) {
@@ -150,14 +150,14 @@ conv3d_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant
     const int first = (int)(blockIdx.x >> 1), stride = (int)(gridDim.x >> 1);
     const int n_tiles_total = p.T * p.h_tiles * p.w_tiles * p.n_tiles;
     const int c_chunks = p.Cin / BK;
-    const int half = p.ks >> 1;
-    const int taps_sp = p.ks * p.ks;                           // K steps fed by one patch
-    const int slot_w = p.ks == 3 ? 16 : 8;                     // column slots per patch row
-    const uint32_t patch_bytes = (uint32_t)((TILE_H + 2 * half) * slot_w * 128);
+    constexpr int half = KS >> 1;
+    constexpr int taps_sp = KS * KS;                           // K steps fed by one patch
+    constexpr int slot_w = KS == 3 ? 16 : 8;                   // column slots per patch row
+    constexpr uint32_t patch_bytes = (uint32_t)((TILE_H + 2 * half) * slot_w * 128);
     const int n_patches = p.kt * c_chunks;                     // per tile
-    const int tpb = p.ks == 3 ? C::TPB : 1;                    // taps per weight stage (divides ks * ks)
-    const uint32_t pstages = p.ks == 3 ? C::PSTAGES : C::PSTAGES_MAX;
-    const uint32_t pslot = p.ks == 3 ? (uint32_t)PATCH_BYTES : 16384u;      // patch ring slot
+    constexpr int tpb = KS == 3 ? C::TPB : 1;                  // taps per weight stage (divides KS * KS)
+    constexpr uint32_t pstages = KS == 3 ? C::PSTAGES : C::PSTAGES_MAX;
+    constexpr uint32_t pslot = KS == 3 ? (uint32_t)PATCH_BYTES : 16384u;      // patch ring slot
 
     if (threadIdx.x == 0) {
         if (base & 1023u) __trap();
@@ -229,7 +229,7 @@ conv3d_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant
         if (leader) {
             constexpr uint32_t idesc = idesc_16(F16, 2 * BM, BN);
             constexpr uint32_t hi_b = smem_desc_hi_sw128(1024);
-            const uint32_t hi_a = smem_desc_hi_sw128((uint32_t)slot_w * 128u);      // 8-row core groups one patch row apart
+            constexpr uint32_t hi_a = smem_desc_hi_sw128((uint32_t)slot_w * 128u);      // 8-row core groups one patch row apart
             uint32_t pit = 0, bit = 0, tc = 0;
             for (int id = first; id < n_tiles_total; id += stride, ++tc) {
                 const uint32_t b = tc & 1;
@@ -240,38 +240,35 @@ conv3d_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant
                     const uint32_t ps = pit % pstages, puse = pit / pstages;
                     mbar_wait(bar(BAR_PFULL + ps), puse & 1);
                     const uint32_t patch = base + ps * pslot;
-                    int j = 0;
-                    uint32_t bstage = 0;
-                    for (int dh = 0; dh < p.ks; ++dh)
-                        for (int dw = 0; dw < p.ks; ++dw) {
-                            if (j == 0) {
-                                const uint32_t bs = bit % BSTAGES, buse = bit / BSTAGES;
-                                mbar_wait(bar(BAR_BFULL + bs), buse & 1);
-                                tc_fence_after();
-                                bstage = base + C::OFF_B + bs * BSTAGE_BYTES;
-                            }
-                            // tap (dh, dw): the patch from row slot dh * slot_w + dw on.  The start is 128-byte, not 1024-byte
-                            // aligned; the swizzle XOR is taken from the absolute shared-memory address bits (measured: run 26 —
-                            // base-offset field 0 is right, base offset = dw is wrong), which is also what the TMA write used
-                            const uint32_t alo = smem_desc_lo(patch + (uint32_t)(dh * slot_w + dw) * 128u, 16);
-                            const uint32_t blo = smem_desc_lo(bstage + j * B_BYTES, 16);
-                            if (elect_one()) {
+#pragma unroll
+                    for (int tap0 = 0; tap0 < taps_sp; tap0 += tpb, ++bit) {
+                        const uint32_t bs = bit % BSTAGES, buse = bit / BSTAGES;
+                        mbar_wait(bar(BAR_BFULL + bs), buse & 1);
+                        tc_fence_after();
+                        if (elect_one()) {
+                            const uint32_t bstage = base + C::OFF_B + bs * BSTAGE_BYTES;
+#pragma unroll
+                            for (int j = 0; j < tpb; ++j) {
+                                // tap (dh, dw): the patch from row slot dh * slot_w + dw on.  The start is 128-byte, not
+                                // 1024-byte aligned; the swizzle XOR is taken from the absolute shared-memory address bits
+                                // (measured, run 26: base-offset field 0 is right, base offset = dw is wrong), which is also
+                                // what the TMA write used
+                                const int dh = (tap0 + j) / KS, dw = (tap0 + j) % KS;
+                                const uint32_t alo = smem_desc_lo(patch + (uint32_t)(dh * slot_w + dw) * 128u, 16);
+                                const uint32_t blo = smem_desc_lo(bstage + j * B_BYTES, 16);
 #pragma unroll
                                 for (int kk = 0; kk < BK / 16; ++kk)
                                     mma2_ss(d_tmem, make_desc(alo + kk * 2, hi_a), make_desc(blo + kk * 2, hi_b), idesc,
-                                            (uint32_t)((pp | dh | dw | kk) != 0));
-                                if (j + 1 == tpb) tc_commit_pair(bar(BAR_BEMPTY + bit % BSTAGES));
-                                if (dh == p.ks - 1 && dw == p.ks - 1) {
-                                    tc_commit_pair(bar(BAR_PEMPTY + ps));
-                                    if (pp == n_patches - 1) tc_commit_pair(bar(BAR_TFULL + b));
-                                }
+                                            (uint32_t)((pp | (tap0 + j) | kk) != 0));
                             }
-                            __syncwarp();
-                            if (++j == tpb) {
-                                ++bit;
-                                j = 0;
+                            tc_commit_pair(bar(BAR_BEMPTY + bs));
+                            if (tap0 + tpb == taps_sp) {
+                                tc_commit_pair(bar(BAR_PEMPTY + ps));
+                                if (pp == n_patches - 1) tc_commit_pair(bar(BAR_TFULL + b));
                             }
                         }
+                        __syncwarp();
+                    }
                 }
             }
         }
@@ -361,13 +358,13 @@ conv3d_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant
     }
 }
 
-template <int BN, bool F16>
+template <int BN, bool F16, int KS>
 int launch(const void* x, const void* head, const void* w, void* y, Params p, cudaStream_t st) {
     const char* name = "svr2_causal_conv3d_fwd";
     p.h_tiles = (p.H + TILE_H - 1) / TILE_H;
     p.w_tiles = (p.W + 2 * TILE_W - 1) / (2 * TILE_W);
     p.n_tiles = p.Cout / BN;
-    const int slot_w = p.ks == 3 ? 16 : 8, box_h = TILE_H + 2 * (p.ks / 2);
+    constexpr int slot_w = KS == 3 ? 16 : 8, box_h = TILE_H + 2 * (KS / 2);
     CUtensorMap tx, th, tw, ty;
     int rc;
     if ((rc = make_tmap_thwc(&tx, x, p.T, p.H, p.W, p.Cin, slot_w, box_h)) != SVR2_OK) return rc;
@@ -380,11 +377,11 @@ int launch(const void* x, const void* head, const void* w, void* y, Params p, cu
     if ((rc = make_tmap_2d(&tw, w, p.Cout, ktot, ktot, BN / 2)) != SVR2_OK) return rc;
     if ((rc = make_tmap_thwc(&ty, y, p.T, p.H, p.W, p.Cout, TILE_W, 4)) != SVR2_OK) return rc;
     static PerDeviceFlag smem_ok;
-    if ((rc = ensure_dyn_smem(conv3d_tc_kernel<BN, F16>, Cfg<BN>::SMEM_BYTES, smem_ok, name)) != SVR2_OK) return rc;
+    if ((rc = ensure_dyn_smem(conv3d_tc_kernel<BN, F16, KS>, Cfg<BN>::SMEM_BYTES, smem_ok, name)) != SVR2_OK) return rc;
     const int pairs = sm_count() / 2;
     const int64_t tiles = (int64_t)p.T * p.h_tiles * p.w_tiles * p.n_tiles;
     const int grid = 2 * (int)(tiles < pairs ? tiles : pairs);
-    conv3d_tc_kernel<BN, F16><<<grid, Cfg<BN>::NTHREADS, Cfg<BN>::SMEM_BYTES, st>>>(tx, th, tw, ty, p);
+    conv3d_tc_kernel<BN, F16, KS><<<grid, Cfg<BN>::NTHREADS, Cfg<BN>::SMEM_BYTES, st>>>(tx, th, tw, ty, p);
     SVR2_CHECK_LAUNCH(name);
     return SVR2_OK;
 }
@@ -431,7 +428,15 @@ extern "C" int svr2_causal_conv3d_fwd(const void* x, const void* head, const voi
     p.bias = bias; p.resid = resid;
     const bool f16 = dtype == SVR2_DTYPE_F16;
     cudaStream_t st = (cudaStream_t)stream;
-    if (c_out % 256 == 0)
-        return f16 ? svr2::conv::launch<256, true>(x, head, weight_packed, y, p, st) : svr2::conv::launch<256, false>(x, head, weight_packed, y, p, st);
-    return f16 ? svr2::conv::launch<128, true>(x, head, weight_packed, y, p, st) : svr2::conv::launch<128, false>(x, head, weight_packed, y, p, st);
+    using namespace svr2::conv;
+#define SVR2_CONV_GO(BN, F, K) return launch<BN, F, K>(x, head, weight_packed, y, p, st)
+    if (c_out % 256 == 0) {
+        if (ks == 3) { if (f16) SVR2_CONV_GO(256, true, 3); SVR2_CONV_GO(256, false, 3); }
+        if (f16) SVR2_CONV_GO(256, true, 1);
+        SVR2_CONV_GO(256, false, 1);
+    }
+    if (ks == 3) { if (f16) SVR2_CONV_GO(128, true, 3); SVR2_CONV_GO(128, false, 3); }
+    if (f16) SVR2_CONV_GO(128, true, 1);
+    SVR2_CONV_GO(128, false, 1);
+#undef SVR2_CONV_GO
 }
