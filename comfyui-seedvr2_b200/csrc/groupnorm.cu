@@ -23,6 +23,7 @@ namespace gn {
 constexpr int kThreads = 256;
 constexpr int kChunks = SVR2_GN_CHUNKS;      // statistics partials per frame
 constexpr int kUnroll = 4;                   // independent 16-byte loads in flight per thread
+constexpr int64_t kLutMinElements = 32ll << 20;      // tensors from this size on take the table-driven activation
 
 struct Moments {
     float n, mean, m2;
@@ -64,6 +65,23 @@ __device__ __forceinline__ uint32_t pack2(float a, float b) {
     }
     const __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
     return *reinterpret_cast<const uint32_t*>(&h);
+}
+
+// SiLU whose ROUNDED result equals that of ATen's fp32 formula x / (1 + exp(-x)) (expf + IEEE division, ~25 instructions per
+// value: the apply pass was issue-bound, not HBM-bound, with it).  Fast path: ex2.approx + rcp.approx (relative error well
+// below 2^-19); its rounding to the tensor dtype can only differ from the exact value's when it lies within that error of a
+// rounding midpoint — then, and for results in the dtype's subnormal range, the exact formula is evaluated (~1 % of values).
+template <bool F16>
+__device__ __forceinline__ float silu_rounding_safe(float x) {
+    float e;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(x * -1.4426950408889634f));
+    float r = __fdividef(x, 1.0f + e);
+    constexpr int DROP = F16 ? 13 : 16;                              // fp32 mantissa bits the rounding drops
+    const uint32_t u = __float_as_uint(r);
+    const int dist = abs((int)(u & ((1u << DROP) - 1u)) - (1 << (DROP - 1)));
+    const bool subnormal = (u & 0x7FFFFFFFu) < (F16 ? 0x38800000u : 0x00800000u);
+    if (dist <= 32 || subnormal) r = x / (1.0f + expf(-x));
+    return r;
 }
 
 // Pass 1.  grid (kChunks, T): block (chunk, t) reduces positions [chunk * per, (chunk + 1) * per) of frame t.
@@ -203,7 +221,7 @@ __global__ void __launch_bounds__(kThreads) apply_kernel(const uint4* __restrict
             for (int i = 0; i < 8; ++i) {
                 // ATen: a * x + b with the fused per-channel a, b when there is an affine, (x - mean) * rstd when there is none
                 float r = round_t<F16>(affine ? fmaf(a[i], v[i], b[i]) : (v[i] - b[i]) * a[i]);
-                if (silu) r = r / (1.0f + expf(-r));                            // ATen silu: fp32 opmath, rounded by the pack below
+                if (silu) r = silu_rounding_safe<F16>(r);                       // ATen silu: fp32 opmath, rounded by the pack below
                 v[i] = r;
             }
             uint4 o;
@@ -213,11 +231,154 @@ __global__ void __launch_bounds__(kThreads) apply_kernel(const uint4* __restrict
     }
 }
 
+// ---- SiLU by table.  The activation's input is the normalisation's ROUNDED output, i.e. one of 65,536 bit patterns, so
+// silu -> round is a pure function of 16 bits: a 128-KB table (per dtype, filled once per device with ATen's exact fp32 formula)
+// held in shared memory turns ~25 issue slots per value into one conflict-prone but cheap LDS.  The arithmetic version above
+// stays for small tensors, where loading 128 KB per CTA would cost more than it saves.  Measured (run 33): apply pass at
+// 1080p x 128 channels 1.61 ms (issue-bound, 29.5 instructions per value) -> see DESIGN.md.
+static __device__ uint16_t g_silu_table[2][65536];      // [0] fp16, [1] bf16
+
+template <bool F16>
+__global__ void silu_table_kernel(uint16_t* __restrict__ table) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= 65536u) return;
+    float x;
+    if (F16) x = __half2float(__ushort_as_half((unsigned short)i));
+    else x = __bfloat162float(__ushort_as_bfloat16((unsigned short)i));
+    const float r = x / (1.0f + expf(-x));
+    table[i] = F16 ? __half_as_ushort(__float2half_rn(r)) : __bfloat16_as_ushort(__float2bfloat16_rn(r));
+}
+
+constexpr int kLutThreads = 1024;
+constexpr int kLutSmem = 65536 * 2;
+
+template <bool F16, int CPG>
+__global__ void __launch_bounds__(kLutThreads, 1) apply_lut_kernel(const uint4* __restrict__ x, const float* __restrict__ partial,
+                                                                   const void* __restrict__ gamma, const void* __restrict__ beta,
+                                                                   uint4* __restrict__ y, const uint4* __restrict__ table, int64_t HW,
+                                                                   int C, int G, float eps) {
+    extern __shared__ __align__(16) unsigned char lut_raw[];
+    uint16_t* lut = reinterpret_cast<uint16_t*>(lut_raw);
+    __shared__ float s_mean[64], s_rstd[64];
+    __shared__ Moments s_red[kLutThreads];
+    for (int i = threadIdx.x; i < kLutSmem / 16; i += kLutThreads) reinterpret_cast<uint4*>(lut_raw)[i] = __ldg(table + i);
+    const int t = blockIdx.y;
+    {
+        const int grp = threadIdx.x % G, sub = threadIdx.x / G, nsub = kLutThreads / G;
+        Moments acc = {0.f, 0.f, 0.f};
+        if (sub < nsub) {
+            const float* src = partial + ((int64_t)t * kChunks * G + grp) * 3;
+            for (int c = sub; c < kChunks; c += nsub) {
+                const Moments m = {src[(int64_t)c * G * 3], src[(int64_t)c * G * 3 + 1], src[(int64_t)c * G * 3 + 2]};
+                acc = merge(acc, m);
+            }
+            s_red[sub * G + grp] = acc;
+        }
+        __syncthreads();
+        if (threadIdx.x < G) {
+            acc = s_red[grp];
+            for (int k = 1; k < nsub; ++k) acc = merge(acc, s_red[k * G + grp]);
+            s_mean[grp] = round_t<F16>(acc.mean);                                  // see apply_kernel
+            s_rstd[grp] = round_t<F16>(rsqrtf(acc.m2 / acc.n + eps));
+        }
+    }
+    __syncthreads();
+    const int vpp = C >> 3;
+    const int lanes = kLutThreads / vpp;
+    const int vec = threadIdx.x % vpp, plane = threadIdx.x / vpp;
+    if (plane >= lanes) return;
+    const bool affine = gamma != nullptr || beta != nullptr;
+    float a[8], b[8];
+    {
+        float gm[8], bt[8];
+        if (gamma != nullptr) unpack8<F16>(__ldg(reinterpret_cast<const uint4*>(gamma) + vec), gm);
+        if (beta != nullptr) unpack8<F16>(__ldg(reinterpret_cast<const uint4*>(beta) + vec), bt);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const int grp = (vec * 8 + i) / CPG;
+            a[i] = gamma != nullptr ? s_rstd[grp] * gm[i] : s_rstd[grp];
+            b[i] = affine ? fmaf(-a[i], s_mean[grp], beta != nullptr ? bt[i] : 0.f) : s_mean[grp];
+        }
+    }
+    const int64_t base = ((int64_t)t * HW) * vpp + vec;
+    const int64_t step = (int64_t)gridDim.x * lanes;
+    for (int64_t pos = (int64_t)blockIdx.x * lanes + plane; pos < HW; pos += step * kUnroll) {
+        uint4 raw[kUnroll];
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u)
+            if (pos + u * step < HW) raw[u] = __ldg(x + base + (pos + u * step) * vpp);
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u) {
+            if (pos + u * step >= HW) break;
+            float v[8];
+            unpack8<F16>(raw[u], v);
+            uint32_t o[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const float r = affine ? fmaf(a[i], v[i], b[i]) : (v[i] - b[i]) * a[i];
+                const uint32_t bits = F16 ? (uint32_t)__half_as_ushort(__float2half_rn(r)) : (uint32_t)__bfloat16_as_ushort(__float2bfloat16_rn(r));
+                o[i] = lut[bits];
+            }
+            uint4 w;
+            w.x = o[0] | (o[1] << 16); w.y = o[2] | (o[3] << 16); w.z = o[4] | (o[5] << 16); w.w = o[6] | (o[7] << 16);
+            y[base + (pos + u * step) * vpp] = w;
+        }
+    }
+}
+
+// device address of the dtype's table, filled on first use on this device (on `st`; inside a stream capture the fill is
+// recorded with the capture every time, because a captured launch has not run yet when the next eager call looks at the flag)
+template <bool F16>
+int silu_table(const uint4** out, cudaStream_t st) {
+    static bool filled[kMaxDevices] = {};
+    static uint16_t* base[kMaxDevices] = {};
+    const int dev = cur_device();
+    if (base[dev] == nullptr) {
+        void* p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&p, g_silu_table);
+        if (e != cudaSuccess || p == nullptr) {
+            set_error("svr2_groupnorm_silu_fwd: cudaGetSymbolAddress failed on device %d: %s", dev, cudaGetErrorString(e));
+            return SVR2_E_CUDA;
+        }
+        base[dev] = (uint16_t*)p;
+    }
+    uint16_t* tab = base[dev] + (F16 ? 0 : 65536);
+    cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+    cudaStreamIsCapturing(st, &cap);
+    if (!filled[dev] || cap != cudaStreamCaptureStatusNone) {
+        silu_table_kernel<F16><<<65536 / 256, 256, 0, st>>>(tab);
+        SVR2_CHECK_LAUNCH("svr2_groupnorm_silu_fwd(table)");
+        if (cap == cudaStreamCaptureStatusNone) {
+            // other streams of this device may use the table right after this call returns
+            if (cudaStreamSynchronize(st) != cudaSuccess) {
+                set_error("svr2_groupnorm_silu_fwd: table fill failed");
+                return SVR2_E_CUDA;
+            }
+            filled[dev] = true;
+        }
+    }
+    *out = reinterpret_cast<const uint4*>(tab);
+    return SVR2_OK;
+}
+
 template <bool F16, int CPG>
 int launch(const void* x, const void* gamma, const void* beta, void* y, float* ws, int T, int64_t HW, int C, int G, float eps, int silu,
            cudaStream_t st) {
     stats_kernel<F16, CPG><<<dim3(kChunks, T), kThreads, 0, st>>>((const uint4*)x, ws, HW, C, G);
     SVR2_CHECK_LAUNCH("svr2_groupnorm_silu_fwd(stats)");
+    if (silu && (int64_t)T * HW * C >= kLutMinElements) {
+        const uint4* table = nullptr;
+        int rc = silu_table<F16>(&table, st);
+        if (rc != SVR2_OK) return rc;
+        static PerDeviceFlag smem_ok;
+        if ((rc = ensure_dyn_smem(apply_lut_kernel<F16, CPG>, kLutSmem, smem_ok, "svr2_groupnorm_silu_fwd")) != SVR2_OK) return rc;
+        int per_frame = sm_count() / T;
+        if (per_frame < 1) per_frame = 1;
+        apply_lut_kernel<F16, CPG><<<dim3((unsigned)per_frame, T), kLutThreads, kLutSmem, st>>>((const uint4*)x, ws, gamma, beta, (uint4*)y,
+                                                                                              table, HW, C, G, eps);
+        SVR2_CHECK_LAUNCH("svr2_groupnorm_silu_fwd(apply, table)");
+        return SVR2_OK;
+    }
     const int lanes = kThreads / (C >> 3);
     int64_t blocks = (HW + lanes * 8 - 1) / (lanes * 8);             // ~8 positions per thread
     const int cap = sm_count() * 16 / (T > 0 ? T : 1) + 1;

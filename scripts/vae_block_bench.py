@@ -52,6 +52,14 @@ for ci, co, T, H, W in ((128, 128, 5, 1080, 1920), (256, 128, 5, 1080, 1920), (2
             except RuntimeError:
                 res[name] = None
                 torch.cuda.empty_cache()
+        # per-kernel split of one call (CUDA events around every C-ABI launch)
+        kt = svr2.ops.KernelTimer()
+        svr2.ops.set_timer(kt)
+        mine(x, None, memory_state=MemoryState.DISABLED)
+        torch.cuda.synchronize()
+        svr2.ops.set_timer(None)
+        split = {k: [round(v, 3) for v in vs] for k, vs in kt.durations().items()}
+        gn_bytes = 3.0 * T * H * W * 2       # per channel: statistics read + apply read + write
         a = mine(x, None, memory_state=MemoryState.DISABLED).float()
         b = ref(xc, memory_state=MemoryState.DISABLED).float()
         diff = float((a - b).abs().max())
@@ -60,6 +68,8 @@ for ci, co, T, H, W in ((128, 128, 5, 1080, 1920), (256, 128, 5, 1080, 1920), (2
     print(json.dumps({"block": [ci, co, T, H, W], "ms": round(t_mine, 3), "tflops": round(flops / t_mine / 1e9, 1),
                       "reference_ms": {k: (None if v is None else round(v, 3)) for k, v in res.items()},
                       "speedup": {k: (None if v is None else round(v / t_mine, 2)) for k, v in res.items()},
-                      "max_abs_diff": diff}), flush=True)
+                      "max_abs_diff": diff, "kernels_ms": split,
+                      "groupnorm_GBps": [round(gn_bytes * c / (ms * 1e6), 0) for c, ms in zip((ci, co), split.get("svr2_groupnorm_silu_fwd", []))]}),
+          flush=True)
     del ref, mine, x, xc
     torch.cuda.empty_cache()

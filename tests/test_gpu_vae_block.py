@@ -85,6 +85,20 @@ def test_groupnorm_variants(svr2, cuda):
         svr2.vae_block.groupnorm_silu(x.float(), None, None, 32, 1e-6)
 
 
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16], ids=["fp16", "bf16"])
+def test_fused_silu_is_atens_silu_bit_for_bit(svr2, cuda, dtype):
+    """The activation takes a fast path (ex2 / rcp approximations) wherever its rounding provably equals the exact formula's and
+    the exact path elsewhere: 67 M values covering the activation's whole useful input range (|y| up to ~25), bit-equal."""
+    g = torch.Generator(device="cuda").manual_seed(4)
+    x = torch.randn(2, 512, 512, 128, generator=g, device=cuda).to(dtype)
+    w = torch.linspace(0.05, 5.0, 128, device=cuda).to(dtype)          # per-channel gain: outputs from ~0.05 sigma to 5 sigma wide
+    b = torch.linspace(-2.0, 2.0, 128, device=cuda).to(dtype)
+    y = svr2.vae_block.groupnorm_silu(x, w, b, 32, 1e-6, silu=False)
+    fused = svr2.vae_block.groupnorm_silu(x, w, b, 32, 1e-6, silu=True)
+    assert float(y.float().abs().max()) > 20
+    assert torch.equal(fused, F.silu(y))
+
+
 class ResnetBlock3D(nn.Module):
     """The reference's block from its importable parts, in the order of ResnetBlock3D.forward (attn_video_vae.py:311-361)."""
 
