@@ -49,14 +49,15 @@ SIGNATURES = {
     "svr2_rgb_to_lab_fwd": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p]),
     "svr2_lab_to_rgb_finish_fwd": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p]),
     "svr2_conv3d_pack_weight": (c_int, [c_void_p, c_void_p] + [c_int] * 5 + [c_void_p]),
-    "svr2_causal_conv3d_fwd": (c_int, [c_void_p] * 6 + [c_int] * 8 + [c_void_p]),
+    "svr2_causal_conv3d_fwd": (c_int, [c_void_p] * 7 + [c_int] * 8 + [c_void_p]),
+    "svr2_conv3d_gn_slots": (c_int, []),
     "svr2_groupnorm_workspace_bytes": (c_int64, [c_int, c_int]),
-    "svr2_groupnorm_silu_fwd": (c_int, [c_void_p] * 5 + [c_int, c_int64, c_int, c_int, c_float, c_int, c_int, c_void_p]),
+    "svr2_groupnorm_silu_fwd": (c_int, [c_void_p] * 5 + [c_int, c_int, c_int64, c_int, c_int, c_float, c_int, c_int, c_void_p]),
     "svr2_sr_input_fwd": (c_int, [c_void_p, c_void_p, c_void_p, c_float, c_float, c_int, c_void_p, c_int64, c_int, c_void_p]),
     "svr2_v_lerp_endpoint_fwd": (c_int, [c_void_p, c_void_p, c_float, c_float, c_void_p, c_int64, c_void_p]),
 }
 
-ABI_VERSION = 9      # svr2_abi_version() of the library these SIGNATURES describe
+ABI_VERSION = 10      # svr2_abi_version() of the library these SIGNATURES describe
 _lib = None
 
 

@@ -80,6 +80,8 @@ struct Params {
     int has_head;               // frames t' < 0 come from the head tensor (kt - 1 frames); otherwise frame 0 is replicated
     const void* bias;           // [Cout] or nullptr
     const void* resid;          // [T, H, W, Cout] or nullptr
+    float* gn_partials;         // [T, gn_slots, 32, 3] (count, mean, M2) of the OUTPUT per frame and group of Cout / 32 channels, or nullptr
+    int gn_slots;
 };
 
 __device__ __forceinline__ void tma_load_4d_pair(uint32_t dst, const CUtensorMap* m, uint32_t bar, int c0, int c1, int c2, int c3) {
@@ -127,6 +129,62 @@ __device__ __forceinline__ Tile decode_tile(const Params& p, int id) {
     r.h0 = (sp % p.h_tiles) * TILE_H;
     r.t = sp / p.h_tiles;
     return r;
+}
+
+// ---- GroupNorm statistics of the output, gathered by the epilogue (the next op of the VAE's residual blocks is a per-frame
+// GroupNorm over 32 groups: its statistics pass — one full read of the tensor — disappears).  Per 64-channel slab a thread holds
+// its position's rounded outputs; sums are taken against a per-group pivot (lane 0's first channel: no cancellation when
+// |mean| >> std), reduced over the warp's 32 positions by a butterfly, and the lane whose index is the group's number merges the
+// tile's (count, mean, M2) into its running triple (Chan).  One partial per (frame, epilogue warp): deterministic, no atomics.
+struct Running {
+    float n, mean, m2;
+};
+__device__ __forceinline__ void chan_merge(Running& a, float n, float mean, float m2) {
+    if (n == 0.f) return;
+    if (a.n == 0.f) { a.n = n; a.mean = mean; a.m2 = m2; return; }
+    const float tot = a.n + n, d = mean - a.mean, f = n / tot;
+    a.m2 = a.m2 + m2 + d * d * a.n * f;
+    a.mean = a.mean + d * f;
+    a.n = tot;
+}
+// QPG = channel quads per group (Cout / 32 / 4 = 1, 2, 4); o = the slab's 64 outputs of this thread's position, packed pairs
+template <bool F16, int QPG>
+__device__ __forceinline__ void slab_stats(const uint32_t* o, bool valid, int lane, int gbase, Running& run) {
+    using N = Num<F16>;
+    constexpr int GPS = 16 / QPG;                       // groups in the slab
+    float S[GPS], Q[GPS], K[GPS];
+#pragma unroll
+    for (int g = 0; g < GPS; ++g) {
+        K[g] = __shfl_sync(0xffffffffu, N::unpack(o[2 * g * QPG]).x, 0);
+        float s = 0.f, q = 0.f;
+#pragma unroll
+        for (int j = 0; j < 2 * QPG; ++j) {
+            const float2 v = N::unpack(o[2 * g * QPG + j]);
+            const float d0 = v.x - K[g], d1 = v.y - K[g];
+            s += d0 + d1;
+            q = fmaf(d0, d0, fmaf(d1, d1, q));
+        }
+        S[g] = valid ? s : 0.f;
+        Q[g] = valid ? q : 0.f;
+    }
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) {
+#pragma unroll
+        for (int g = 0; g < GPS; ++g) {
+            S[g] += __shfl_xor_sync(0xffffffffu, S[g], off);
+            Q[g] += __shfl_xor_sync(0xffffffffu, Q[g], off);
+        }
+    }
+    const float n = (float)(__popc(__ballot_sync(0xffffffffu, valid)) * 4 * QPG);
+    float s = 0.f, q = 0.f, k = 0.f;
+    bool mine = false;
+#pragma unroll
+    for (int g = 0; g < GPS; ++g)
+        if (lane == gbase + g) { s = S[g]; q = Q[g]; k = K[g]; mine = true; }
+    if (mine && n > 0.f) {
+        const float ms = s / n;
+        chan_merge(run, n, k + ms, fmaxf(q - s * ms, 0.f));
+    }
 }
 
 template <int BN, bool F16, int KS>
@@ -281,9 +339,23 @@ conv3d_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant
         const __half* bias = reinterpret_cast<const __half*>(p.bias);          // 2-byte elements either way
         const __half* resid = reinterpret_cast<const __half*>(p.resid);
         uint32_t tc = 0, n_store = 0;
+        Running run = {0.f, 0.f, 0.f};            // lane L: group L of the current frame, over this warp's positions
+        int run_t = -1;
+        const int qpg = p.Cout >> 7;              // channel quads per group (32 groups)
+        auto flush_stats = [&]() {
+            if (run_t >= 0 && run.n > 0.f) {
+                float* dst = p.gn_partials + (((int64_t)run_t * p.gn_slots + (int)blockIdx.x * 4 + q) * 32 + lane) * 3;
+                dst[0] = run.n; dst[1] = run.mean; dst[2] = run.m2;
+            }
+            run.n = run.mean = run.m2 = 0.f;
+        };
         for (int id = first; id < n_tiles_total; id += stride, ++tc) {
             const Tile tl = decode_tile(p, id);
             const uint32_t b = tc & 1;
+            if (p.gn_partials != nullptr && tl.t != run_t) {
+                flush_stats();
+                run_t = tl.t;
+            }
             const int hs = tl.h0 + q * 4, ws = tl.w0 + (int)rank * TILE_W;     // this warp's 4 rows x 8 columns of the tile
             const int h = hs + (lane >> 3), w = ws + (lane & 7);
             const bool valid = h < p.H && w < p.W;
@@ -331,6 +403,12 @@ conv3d_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant
                     __syncwarp();
                     if (lane == 0) mbar_arrive_cluster(b ? tempty_g1 : tempty_g0);
                 }
+                if (p.gn_partials != nullptr) {
+                    const int gbase = col0 / (4 * qpg);                          // the slab's first group
+                    if (qpg == 1) slab_stats<F16, 1>(o, valid, lane, gbase, run);
+                    else if (qpg == 2) slab_stats<F16, 2>(o, valid, lane, gbase, run);
+                    else slab_stats<F16, 4>(o, valid, lane, gbase, run);
+                }
                 unsigned char* slab = slab0 + (n_store & 1) * SLAB_BYTES;
                 if (lane == 0) bulk_wait_read<1>();
                 __syncwarp();
@@ -347,6 +425,7 @@ conv3d_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant
                 ++n_store;
             }
         }
+        if (p.gn_partials != nullptr) flush_stats();
         if (lane == 0) bulk_wait<0>();
     }
     tc_fence_before();
@@ -411,8 +490,11 @@ extern "C" int svr2_conv3d_pack_weight(const void* weight, void* packed, int c_o
     return SVR2_OK;
 }
 
+extern "C" int svr2_conv3d_gn_slots(void) { return svr2::sm_count() * 4; }
+
 extern "C" int svr2_causal_conv3d_fwd(const void* x, const void* head, const void* weight_packed, const void* bias, const void* resid,
-                                      void* y, int T, int H, int W, int c_in, int c_out, int kt, int ks, int dtype, void* stream) {
+                                      void* y, void* gn_partials, int T, int H, int W, int c_in, int c_out, int kt, int ks, int dtype,
+                                      void* stream) {
     const char* name = "svr2_causal_conv3d_fwd";
     SVR2_CHECK_ARG(x && weight_packed && y, "%s: null pointer", name);
     SVR2_CHECK_ARG(dtype == SVR2_DTYPE_F16 || dtype == SVR2_DTYPE_BF16, "%s: dtype %d (fp16 or bf16)", name, dtype);
@@ -426,6 +508,15 @@ extern "C" int svr2_causal_conv3d_fwd(const void* x, const void* head, const voi
     p.T = T; p.H = H; p.W = W; p.Cin = c_in; p.Cout = c_out; p.kt = kt; p.ks = ks;
     p.has_head = (head != nullptr && kt > 1) ? 1 : 0;
     p.bias = bias; p.resid = resid;
+    SVR2_CHECK_ARG(gn_partials == nullptr || c_out == 128 || c_out == 256 || c_out == 512,
+                   "%s: output statistics are gathered for 32 groups of 4, 8 or 16 channels (c_out=%d)", name, c_out);
+    p.gn_partials = (float*)gn_partials;
+    p.gn_slots = svr2::sm_count() * 4;
+    if (gn_partials != nullptr) {
+        // a warp writes its slot of a frame only if it saw positions of that frame: the rest must read as count 0
+        const cudaError_t e = cudaMemsetAsync(gn_partials, 0, (size_t)T * p.gn_slots * 32 * 3 * sizeof(float), (cudaStream_t)stream);
+        if (e != cudaSuccess) { svr2::set_error("%s: cudaMemsetAsync: %s", name, cudaGetErrorString(e)); return SVR2_E_CUDA; }
+    }
     const bool f16 = dtype == SVR2_DTYPE_F16;
     cudaStream_t st = (cudaStream_t)stream;
     using namespace svr2::conv;

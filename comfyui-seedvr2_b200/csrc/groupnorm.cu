@@ -161,7 +161,7 @@ __global__ void __launch_bounds__(kThreads) stats_kernel(const uint4* __restrict
 template <bool F16, int CPG>
 __global__ void __launch_bounds__(kThreads) apply_kernel(const uint4* __restrict__ x, const float* __restrict__ partial,
                                                          const void* __restrict__ gamma, const void* __restrict__ beta,
-                                                         uint4* __restrict__ y, int64_t HW, int C, int G, float eps, int silu) {
+                                                         uint4* __restrict__ y, int64_t HW, int C, int G, float eps, int silu, int n_partials) {
     __shared__ float s_mean[64], s_rstd[64];
     __shared__ Moments s_red[kThreads];
     const int t = blockIdx.y;
@@ -170,8 +170,8 @@ __global__ void __launch_bounds__(kThreads) apply_kernel(const uint4* __restrict
         const int grp = threadIdx.x % G, sub = threadIdx.x / G, nsub = kThreads / G;
         Moments acc = {0.f, 0.f, 0.f};
         if (sub < nsub) {
-            const float* src = partial + ((int64_t)t * kChunks * G + grp) * 3;
-            for (int c = sub; c < kChunks; c += nsub) {
+            const float* src = partial + ((int64_t)t * n_partials * G + grp) * 3;
+            for (int c = sub; c < n_partials; c += nsub) {
                 const Moments m = {src[(int64_t)c * G * 3], src[(int64_t)c * G * 3 + 1], src[(int64_t)c * G * 3 + 2]};
                 acc = merge(acc, m);
             }
@@ -256,7 +256,7 @@ template <bool F16, int CPG>
 __global__ void __launch_bounds__(kLutThreads, 1) apply_lut_kernel(const uint4* __restrict__ x, const float* __restrict__ partial,
                                                                    const void* __restrict__ gamma, const void* __restrict__ beta,
                                                                    uint4* __restrict__ y, const uint4* __restrict__ table, int64_t HW,
-                                                                   int C, int G, float eps) {
+                                                                   int C, int G, float eps, int n_partials) {
     extern __shared__ __align__(16) unsigned char lut_raw[];
     uint16_t* lut = reinterpret_cast<uint16_t*>(lut_raw);
     __shared__ float s_mean[64], s_rstd[64];
@@ -267,8 +267,8 @@ __global__ void __launch_bounds__(kLutThreads, 1) apply_lut_kernel(const uint4* 
         const int grp = threadIdx.x % G, sub = threadIdx.x / G, nsub = kLutThreads / G;
         Moments acc = {0.f, 0.f, 0.f};
         if (sub < nsub) {
-            const float* src = partial + ((int64_t)t * kChunks * G + grp) * 3;
-            for (int c = sub; c < kChunks; c += nsub) {
+            const float* src = partial + ((int64_t)t * n_partials * G + grp) * 3;
+            for (int c = sub; c < n_partials; c += nsub) {
                 const Moments m = {src[(int64_t)c * G * 3], src[(int64_t)c * G * 3 + 1], src[(int64_t)c * G * 3 + 2]};
                 acc = merge(acc, m);
             }
@@ -363,9 +363,12 @@ int silu_table(const uint4** out, cudaStream_t st) {
 
 template <bool F16, int CPG>
 int launch(const void* x, const void* gamma, const void* beta, void* y, float* ws, int T, int64_t HW, int C, int G, float eps, int silu,
-           cudaStream_t st) {
-    stats_kernel<F16, CPG><<<dim3(kChunks, T), kThreads, 0, st>>>((const uint4*)x, ws, HW, C, G);
-    SVR2_CHECK_LAUNCH("svr2_groupnorm_silu_fwd(stats)");
+           int have_partials, cudaStream_t st) {
+    const int n_partials = have_partials > 0 ? have_partials : kChunks;
+    if (have_partials <= 0) {
+        stats_kernel<F16, CPG><<<dim3(kChunks, T), kThreads, 0, st>>>((const uint4*)x, ws, HW, C, G);
+        SVR2_CHECK_LAUNCH("svr2_groupnorm_silu_fwd(stats)");
+    }
     if (silu && (int64_t)T * HW * C >= kLutMinElements) {
         const uint4* table = nullptr;
         int rc = silu_table<F16>(&table, st);
@@ -375,7 +378,7 @@ int launch(const void* x, const void* gamma, const void* beta, void* y, float* w
         int per_frame = sm_count() / T;
         if (per_frame < 1) per_frame = 1;
         apply_lut_kernel<F16, CPG><<<dim3((unsigned)per_frame, T), kLutThreads, kLutSmem, st>>>((const uint4*)x, ws, gamma, beta, (uint4*)y,
-                                                                                              table, HW, C, G, eps);
+                                                                                              table, HW, C, G, eps, n_partials);
         SVR2_CHECK_LAUNCH("svr2_groupnorm_silu_fwd(apply, table)");
         return SVR2_OK;
     }
@@ -384,19 +387,19 @@ int launch(const void* x, const void* gamma, const void* beta, void* y, float* w
     const int cap = sm_count() * 16 / (T > 0 ? T : 1) + 1;
     if (blocks > cap) blocks = cap;
     if (blocks < 1) blocks = 1;
-    apply_kernel<F16, CPG><<<dim3((unsigned)blocks, T), kThreads, 0, st>>>((const uint4*)x, ws, gamma, beta, (uint4*)y, HW, C, G, eps, silu);
+    apply_kernel<F16, CPG><<<dim3((unsigned)blocks, T), kThreads, 0, st>>>((const uint4*)x, ws, gamma, beta, (uint4*)y, HW, C, G, eps, silu, n_partials);
     SVR2_CHECK_LAUNCH("svr2_groupnorm_silu_fwd(apply)");
     return SVR2_OK;
 }
 
 template <bool F16>
 int dispatch(int cpg, const void* x, const void* gamma, const void* beta, void* y, float* ws, int T, int64_t HW, int C, int G, float eps,
-             int silu, cudaStream_t st) {
+             int silu, int have_partials, cudaStream_t st) {
     switch (cpg) {
-        case 2: return launch<F16, 2>(x, gamma, beta, y, ws, T, HW, C, G, eps, silu, st);
-        case 4: return launch<F16, 4>(x, gamma, beta, y, ws, T, HW, C, G, eps, silu, st);
-        case 8: return launch<F16, 8>(x, gamma, beta, y, ws, T, HW, C, G, eps, silu, st);
-        case 16: return launch<F16, 16>(x, gamma, beta, y, ws, T, HW, C, G, eps, silu, st);
+        case 2: return launch<F16, 2>(x, gamma, beta, y, ws, T, HW, C, G, eps, silu, have_partials, st);
+        case 4: return launch<F16, 4>(x, gamma, beta, y, ws, T, HW, C, G, eps, silu, have_partials, st);
+        case 8: return launch<F16, 8>(x, gamma, beta, y, ws, T, HW, C, G, eps, silu, have_partials, st);
+        case 16: return launch<F16, 16>(x, gamma, beta, y, ws, T, HW, C, G, eps, silu, have_partials, st);
         default: return SVR2_E_INVALID;
     }
 }
@@ -408,13 +411,14 @@ extern "C" int64_t svr2_groupnorm_workspace_bytes(int T, int groups) {
     return (int64_t)(T > 0 ? T : 0) * SVR2_GN_CHUNKS * (groups > 0 ? groups : 0) * 3 * (int64_t)sizeof(float);
 }
 
-extern "C" int svr2_groupnorm_silu_fwd(const void* x, const void* weight, const void* bias, void* y, void* workspace, int T, int64_t HW,
-                                       int C, int groups, float eps, int silu, int dtype, void* stream) {
+extern "C" int svr2_groupnorm_silu_fwd(const void* x, const void* weight, const void* bias, void* y, void* workspace, int have_partials,
+                                       int T, int64_t HW, int C, int groups, float eps, int silu, int dtype, void* stream) {
     const char* name = "svr2_groupnorm_silu_fwd";
     SVR2_CHECK_ARG(x && y && workspace, "%s: null pointer", name);
     SVR2_CHECK_ARG(dtype == SVR2_DTYPE_F16 || dtype == SVR2_DTYPE_BF16, "%s: dtype %d (fp16 or bf16)", name, dtype);
     SVR2_CHECK_ARG(T >= 0 && HW > 0, "%s: bad extent T=%d HW=%lld", name, T, (long long)HW);
     SVR2_CHECK_ARG(groups > 0 && groups <= 64 && C > 0 && C % groups == 0, "%s: C=%d groups=%d", name, C, groups);
+    SVR2_CHECK_ARG(have_partials >= 0 && (have_partials == 0 || groups == 32), "%s: statistics partials of a convolution are for 32 groups", name);
     const int cpg = C / groups;
     SVR2_CHECK_ARG(cpg == 2 || cpg == 4 || cpg == 8 || cpg == 16, "%s: %d channels per group (2, 4, 8 or 16)", name, cpg);
     SVR2_CHECK_ARG(C % 8 == 0 && C / 8 <= svr2::gn::kThreads && svr2::gn::kThreads % (C / 8) == 0,
@@ -422,6 +426,6 @@ extern "C" int svr2_groupnorm_silu_fwd(const void* x, const void* weight, const 
     if (T == 0) return SVR2_OK;
     cudaStream_t st = (cudaStream_t)stream;
     if (dtype == SVR2_DTYPE_F16)
-        return svr2::gn::dispatch<true>(cpg, x, weight, bias, y, (float*)workspace, T, HW, C, groups, eps, silu, st);
-    return svr2::gn::dispatch<false>(cpg, x, weight, bias, y, (float*)workspace, T, HW, C, groups, eps, silu, st);
+        return svr2::gn::dispatch<true>(cpg, x, weight, bias, y, (float*)workspace, T, HW, C, groups, eps, silu, have_partials, st);
+    return svr2::gn::dispatch<false>(cpg, x, weight, bias, y, (float*)workspace, T, HW, C, groups, eps, silu, have_partials, st);
 }

@@ -12,13 +12,14 @@ import torch
 from torch import nn
 
 from . import _lib, ops
-from .vae_conv import _DTYPE_CODE, CausalConv3dB200
+from .vae_conv import _DTYPE_CODE, CausalConv3dB200, GroupStats
 
 
 def groupnorm_silu(x: torch.Tensor, weight: Optional[torch.Tensor], bias: Optional[torch.Tensor], groups: int, eps: float,
-                   silu: bool = True, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+                   silu: bool = True, out: Optional[torch.Tensor] = None, stats: Optional[GroupStats] = None) -> torch.Tensor:
     """x [T, H, W, C] (or [T, HW, C]) channels-last: GroupNorm over each frame's (C / groups) x H x W values, then SiLU; rounded to
-    the tensor dtype after each of the two, like the reference's two tensor ops (causal_inflation_lib.py:366-409 + nn.SiLU)."""
+    the tensor dtype after each of the two, like the reference's two tensor ops (causal_inflation_lib.py:366-409 + nn.SiLU).
+    ``stats``: the partials the producing convolution gathered for x (32 groups) — the statistics pass is skipped."""
     code = _DTYPE_CODE.get(x.dtype)
     if code is None:
         raise NotImplementedError(f"seedvr2_b200.vae_block: fp16 or bf16 activations only (got {x.dtype})")
@@ -34,9 +35,13 @@ def groupnorm_silu(x: torch.Tensor, weight: Optional[torch.Tensor], bias: Option
     if T == 0 or hw == 0:
         return y
     lib = _lib.lib()
+    if stats is not None and groups == 32:
+        ops._call("svr2_groupnorm_silu_fwd", 1, x.device, lib.svr2_groupnorm_silu_fwd, x.data_ptr(), ops._ptr(weight), ops._ptr(bias),
+                  y.data_ptr(), stats.partials.data_ptr(), int(stats.slots), T, hw, C, 32, float(eps), int(silu), code, ops._stream(x))
+        return y
     ws = torch.empty(int(lib.svr2_groupnorm_workspace_bytes(T, groups)), dtype=torch.uint8, device=x.device)
     ops._call("svr2_groupnorm_silu_fwd", 2, x.device, lib.svr2_groupnorm_silu_fwd, x.data_ptr(), ops._ptr(weight), ops._ptr(bias),
-              y.data_ptr(), ws.data_ptr(), T, hw, C, int(groups), float(eps), int(silu), code, ops._stream(x))
+              y.data_ptr(), ws.data_ptr(), 0, T, hw, C, int(groups), float(eps), int(silu), code, ops._stream(x))
     return y
 
 
@@ -80,29 +85,56 @@ class ResnetBlock3DB200(nn.Module):
         if not x.is_contiguous():
             x = x.contiguous()
         B = x.shape[0]
+        # statistics of the input, if the block that produced it gathered them in its last convolution's epilogue
+        st_in = getattr(input_tensor, "_svr2_gn_stats", None)
+        if st_in is not None and not (B == 1 and self.groups1 == 32 and st_in.valid_for(x)):
+            st_in = None
         h = torch.empty_like(x)
         for b in range(B):
-            groupnorm_silu(x[b], self.norm1_weight, self.norm1_bias, self.groups1, self.eps1, out=h[b])
-        h = self.conv1.forward_cl(h, memory_state)
+            groupnorm_silu(x[b], self.norm1_weight, self.norm1_bias, self.groups1, self.eps1, out=h[b], stats=st_in)
+        h, st_h = self.conv1.forward_cl(h, memory_state, want_stats=self.groups2 == 32)
         for b in range(B):
-            groupnorm_silu(h[b], self.norm2_weight, self.norm2_bias, self.groups2, self.eps2, out=h[b])      # in place
+            groupnorm_silu(h[b], self.norm2_weight, self.norm2_bias, self.groups2, self.eps2, out=h[b], stats=st_h)      # in place
         skip = x if self.conv_shortcut is None else self.conv_shortcut.forward_cl(x, memory_state)
-        out = self.conv2.forward_cl(h, memory_state, resid=skip)     # (input_tensor + hidden_states), :361
+        out, st_out = self.conv2.forward_cl(h, memory_state, resid=skip, want_stats=True)     # (input_tensor + hidden_states), :361
         if self.output_scale_factor != 1.0:
-            out = out / self.output_scale_factor
-        return out.permute(0, 4, 1, 2, 3)
+            out, st_out = out / self.output_scale_factor, None
+        ret = out.permute(0, 4, 1, 2, 3)
+        if st_out is not None:
+            ret._svr2_gn_stats = st_out          # for the next block's norm1 (the VAE chains its blocks through nn.Identity)
+        return ret
 
 
-def install_vae_blocks(model: nn.Module) -> int:
-    """Replace every ``ResnetBlock3D`` of a built (CUDA, fp16 / bf16) VAE that this module mirrors; returns how many were replaced."""
-    n = 0
+def _conv_supported(conv: nn.Module) -> bool:
+    try:
+        kt, kh, kw = conv.kernel_size
+        return (tuple(conv.stride) == (1, 1, 1) and tuple(conv.dilation) == (1, 1, 1) and conv.groups == 1 and kh == kw
+                and kt in (1, 3) and kh in (1, 3) and conv.in_channels % 64 == 0 and conv.out_channels % 128 == 0
+                and conv.weight.is_cuda and conv.weight.dtype in _DTYPE_CODE)
+    except (AttributeError, TypeError, ValueError):
+        return False
+
+
+def install_vae_blocks(model: nn.Module, convs: bool = True):
+    """Replace, in a built (CUDA, fp16 / bf16) VAE, every ``ResnetBlock3D`` this module mirrors and — with ``convs`` — every other
+    stride-1 ``InflatedCausalConv3d`` the kernel covers (the up-samplers' 3 x 3 x 3 convolutions: a third of the decoder's FLOPs).
+    Returns (blocks replaced, convolutions replaced).  Anything else keeps the reference's module."""
+    n_blocks = n_convs = 0
     for parent in list(model.modules()):
         for name, child in list(parent.named_children()):
             if type(child).__name__ != "ResnetBlock3D":
                 continue
             try:
                 setattr(parent, name, ResnetBlock3DB200.from_reference(child))
-                n += 1
+                n_blocks += 1
             except NotImplementedError:
                 pass          # a configuration outside the mirror keeps the reference's block
-    return n
+    if convs:
+        for parent in list(model.modules()):
+            if isinstance(parent, (ResnetBlock3DB200, CausalConv3dB200)):
+                continue
+            for name, child in list(parent.named_children()):
+                if type(child).__name__ == "InflatedCausalConv3d" and _conv_supported(child):
+                    setattr(parent, name, CausalConv3dB200.from_reference(child))
+                    n_convs += 1
+    return n_blocks, n_convs

@@ -40,11 +40,29 @@ def pack_conv_weight(weight: torch.Tensor) -> torch.Tensor:
     return out
 
 
+class GroupStats:
+    """Statistics partials of a tensor gathered by the convolution that produced it (``svr2_causal_conv3d_fwd`` gn_partials): what
+    the per-frame GroupNorm over 32 groups that follows needs instead of its own pass over the tensor."""
+
+    def __init__(self, partials: torch.Tensor, slots: int, of: torch.Tensor):
+        self.partials, self.slots = partials, slots
+        self._ptr, self._shape, self._version = of.data_ptr(), tuple(of.shape), of._version
+
+    def valid_for(self, t: torch.Tensor) -> bool:
+        """Still describes ``t``: same storage, same shape, not written since."""
+        return t.data_ptr() == self._ptr and tuple(t.shape) == self._shape and t._version == self._version
+
+
+def gn_slots() -> int:
+    return int(_lib.lib().svr2_conv3d_gn_slots())
+
+
 def causal_conv3d(x: torch.Tensor, weight_packed: torch.Tensor, bias: Optional[torch.Tensor] = None,
                   head: Optional[torch.Tensor] = None, resid: Optional[torch.Tensor] = None,
-                  out: Optional[torch.Tensor] = None) -> torch.Tensor:
+                  out: Optional[torch.Tensor] = None, gn_partials: Optional[torch.Tensor] = None) -> torch.Tensor:
     """x [T, H, W, C_in] -> [T, H, W, C_out]; ``head`` = [kt - 1, H, W, C_in] frames in front of x (None: x[0] repeated);
-    ``resid`` [T, H, W, C_out] is added after the convolution's own rounding."""
+    ``resid`` [T, H, W, C_out] is added after the convolution's own rounding; ``gn_partials`` [T, gn_slots(), 32, 3] fp32 receives the
+    output's GroupNorm statistics."""
     code = _DTYPE_CODE.get(x.dtype)
     if code is None:
         raise NotImplementedError(f"seedvr2_b200.vae_conv: fp16 or bf16 activations only (got {x.dtype})")
@@ -65,8 +83,13 @@ def causal_conv3d(x: torch.Tensor, weight_packed: torch.Tensor, bias: Optional[t
         if tuple(resid.shape) != (T, H, W, co):
             raise RuntimeError(f"seedvr2_b200.vae_conv: resid must be {(T, H, W, co)}, got {tuple(resid.shape)}")
     y = torch.empty(T, H, W, co, dtype=x.dtype, device=x.device) if out is None else ops._need(out, "out", x.dtype)
+    if gn_partials is not None:
+        ops._need(gn_partials, "gn_partials", torch.float32)
+        if gn_partials.numel() != T * gn_slots() * 32 * 3:
+            raise RuntimeError(f"seedvr2_b200.vae_conv: gn_partials must hold {T} x {gn_slots()} x 32 x 3 floats")
     ops._call("svr2_causal_conv3d_fwd", 1, x.device, _lib.lib().svr2_causal_conv3d_fwd, x.data_ptr(), ops._ptr(head),
-              weight_packed.data_ptr(), ops._ptr(bias), ops._ptr(resid), y.data_ptr(), T, H, W, ci, co, kt, kh, code, ops._stream(x))
+              weight_packed.data_ptr(), ops._ptr(bias), ops._ptr(resid), y.data_ptr(), ops._ptr(gn_partials), T, H, W, ci, co, kt, kh,
+              code, ops._stream(x))
     return y
 
 
@@ -92,32 +115,54 @@ class CausalConv3dB200(nn.Module):
     def set_memory_limit(self, value: float) -> None:      # causal_inflation_lib.py:77-78: no workspace to bound here
         pass
 
-    def forward(self, input: torch.Tensor, memory_state="DISABLED", resid: Optional[torch.Tensor] = None) -> torch.Tensor:
-        x = input.permute(0, 2, 3, 4, 1)                                        # [B, T, H, W, C]: contiguous for channels_last_3d
-        if not x.is_contiguous():
-            x = x.contiguous()
-        r = None
-        if resid is not None:
-            r = resid.permute(0, 2, 3, 4, 1)
-            r = r if r.is_contiguous() else r.contiguous()
-        return self.forward_cl(x, memory_state, r).permute(0, 4, 1, 2, 3)       # [B, C_out, T, H, W], channels-last strides
+    def forward(self, input, memory_state="DISABLED", resid: Optional[torch.Tensor] = None):
+        """``input`` [B, C, T, H, W], or a list of such tensors = consecutive temporal pieces (the up-sampler's slicing,
+        attn_video_vae.py:126-133 -> slicing_forward :243-303): each piece's causal head is the previous piece's tail."""
+        if isinstance(input, (list, tuple)):
+            if resid is not None:
+                raise NotImplementedError("seedvr2_b200.vae_conv: a residual with a list input")
+            xs = [self._to_cl(t) for t in input]
+            return [y.permute(0, 4, 1, 2, 3) for y in self._forward_pieces(xs, memory_state)]
+        r = None if resid is None else self._to_cl(resid)
+        return self.forward_cl(self._to_cl(input), memory_state, r).permute(0, 4, 1, 2, 3)      # [B, C_out, T, H, W], channels-last strides
 
-    def forward_cl(self, x: torch.Tensor, memory_state="DISABLED", resid: Optional[torch.Tensor] = None) -> torch.Tensor:
-        """The same on channels-last tensors: x [B, T, H, W, C_in] -> [B, T, H, W, C_out]."""
+    @staticmethod
+    def _to_cl(t: torch.Tensor) -> torch.Tensor:
+        x = t.permute(0, 2, 3, 4, 1)                                            # [B, T, H, W, C]: contiguous for channels_last_3d
+        return x if x.is_contiguous() else x.contiguous()
+
+    def forward_cl(self, x: torch.Tensor, memory_state="DISABLED", resid: Optional[torch.Tensor] = None, want_stats: bool = False):
+        """The same on channels-last tensors: x [B, T, H, W, C_in] -> [B, T, H, W, C_out].  ``want_stats`` (batch 1, C_out 128 / 256 /
+        512): returns (y, GroupStats of y) — the statistics the GroupNorm after this convolution needs."""
+        if want_stats and x.shape[0] == 1 and self.out_channels in (128, 256, 512):
+            part = torch.empty(x.shape[1], gn_slots(), 32, 3, dtype=torch.float32, device=x.device)
+            y = self._forward_pieces([x], memory_state, resid, part)[0]
+            return y, GroupStats(part, gn_slots(), y)
+        y = self._forward_pieces([x], memory_state, resid)[0]
+        return (y, None) if want_stats else y
+
+    def _forward_pieces(self, xs, memory_state, resid: Optional[torch.Tensor] = None, gn_partials: Optional[torch.Tensor] = None):
         state = _state_name(memory_state)
         if state != "ACTIVE":
             self.memory = None                                                  # :216-217
         kt = self.kernel_size[0]
-        B = x.shape[0]
-        y = torch.empty(*x.shape[:4], self.out_channels, dtype=x.dtype, device=x.device)
-        for b in range(B):
-            head = self.memory[b] if (self.memory is not None and kt > 1) else None
-            causal_conv3d(x[b], self.weight_packed, self.bias, head, None if resid is None else resid[b], out=y[b])
+        head = self.memory if kt > 1 else None                                  # [B, kt - 1, H, W, C] or None (first frame repeated)
+        ys = []
+        for x in xs:
+            B = x.shape[0]
+            y = torch.empty(*x.shape[:4], self.out_channels, dtype=x.dtype, device=x.device)
+            for b in range(B):
+                causal_conv3d(x[b], self.weight_packed, self.bias, None if head is None else head[b],
+                              None if resid is None else resid[b], out=y[b], gn_partials=gn_partials)
+            ys.append(y)
+            if kt > 1:
+                # the last kt - 1 frames of (head, piece): the next piece's head (:286-296) and, at the end, the memory
+                if x.shape[1] >= kt - 1:
+                    head = x[:, -(kt - 1):]
+                else:
+                    prev = head if head is not None else x[:, :1].expand(-1, kt - 1, -1, -1, -1)
+                    head = torch.cat((prev, x), dim=1)[:, -(kt - 1):]
+                head = head if head.is_contiguous() else head.contiguous()
         if kt > 1 and state != "DISABLED":
-            # the last kt - 1 frames of (head, input): basic_forward :229-240, slicing_forward :273-283
-            if x.shape[1] >= kt - 1:
-                self.memory = x[:, -(kt - 1):].clone()
-            else:
-                prev = self.memory if self.memory is not None else x[:, :1].expand(-1, kt - 1, -1, -1, -1)
-                self.memory = torch.cat((prev, x), dim=1)[:, -(kt - 1):].contiguous()
-        return y
+            self.memory = head.clone()                                          # basic_forward :229-240, slicing_forward :273-283
+        return ys

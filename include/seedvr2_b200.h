@@ -368,20 +368,26 @@ int svr2_lab_to_rgb_finish_fwd(const float* lab, void* out, void* out_u8, int bg
  */
 int svr2_conv3d_pack_weight(const void* weight, void* packed, int c_out, int c_in, int kt, int kh, int kw, void* stream);
 int svr2_causal_conv3d_fwd(const void* x, const void* head, const void* weight_packed, const void* bias, const void* resid,
-                           void* y, int T, int H, int W, int c_in, int c_out, int kt, int ks, int dtype, void* stream);
+                           void* y, void* gn_partials, int T, int H, int W, int c_in, int c_out, int kt, int ks, int dtype, void* stream);
+/* gn_partials (or NULL): the epilogue also gathers the statistics of y that the VAE's next op, a per-frame GroupNorm over 32 groups
+ * (ResnetBlock3D.norm2 / the next block's norm1), needs — T x svr2_conv3d_gn_slots() x 32 x 3 floats (count, mean, M2), zeroed and
+ * filled by the call; hand them to svr2_groupnorm_silu_fwd (have_partials = svr2_conv3d_gn_slots()), whose statistics pass is
+ * then skipped.  c_out in {128, 256, 512}. */
+int svr2_conv3d_gn_slots(void);
 
 /*
  * The VAE's per-frame GroupNorm (+ SiLU): causal_norm_wrapper folds time into the batch before nn.GroupNorm
  * (causal_inflation_lib.py:354-409), ResnetBlock3D applies SiLU to the result (attn_video_vae.py:316-322, 348-356).
  *   x, y [T, HW, C] channels-last (y may alias x), weight / bias [C] or NULL, statistics per (frame, group) in fp32, output rounded
  *   after the affine and again after the activation like the two ATen ops; silu = 0 skips the activation.
- *   workspace: svr2_groupnorm_workspace_bytes(T, groups) bytes of device memory (the statistics partials; no allocation inside).
+ *   workspace: svr2_groupnorm_workspace_bytes(T, groups) bytes of device memory (the statistics partials; no allocation inside),
+ *   have_partials = 0; or the gn_partials a convolution gathered for this tensor, have_partials = svr2_conv3d_gn_slots().
  *   C / groups in {2, 4, 8, 16}, C = 8 x a power of two; dtype SVR2_DTYPE_F16 or SVR2_DTYPE_BF16.
  */
 #define SVR2_GN_CHUNKS 128
 int64_t svr2_groupnorm_workspace_bytes(int T, int groups);
-int svr2_groupnorm_silu_fwd(const void* x, const void* weight, const void* bias, void* y, void* workspace, int T, int64_t HW, int C,
-                            int groups, float eps, int silu, int dtype, void* stream);
+int svr2_groupnorm_silu_fwd(const void* x, const void* weight, const void* bias, void* y, void* workspace, int have_partials, int T,
+                            int64_t HW, int C, int groups, float eps, int silu, int dtype, void* stream);
 
 #ifdef __cplusplus
 }

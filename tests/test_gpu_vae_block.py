@@ -161,5 +161,77 @@ def test_resnet_block_matches_reference_parts(svr2, cuda, ci, co, full):
         whole = mine(x, None, memory_state=MemoryState.DISABLED)
         assert torch.equal(whole, torch.cat(outs_m, 2))
     # the installer finds the block by its class name and swaps it in place
-    holder = nn.Sequential(ref)
-    assert svr2.vae_block.install_vae_blocks(holder) == 1 and isinstance(holder[0], svr2.vae_block.ResnetBlock3DB200)
+    up_conv = init_causal_conv3d(co, co, 3, padding=1, inflation_mode="tail").cuda().half()          # an up-sampler's convolution
+    small = init_causal_conv3d(16, co, 3, padding=1, inflation_mode="tail").cuda().half()             # conv_in: outside the kernel's shapes
+    holder = nn.Sequential(ref, nn.Sequential(up_conv, small))
+    assert svr2.vae_block.install_vae_blocks(holder) == (1, 1)
+    assert isinstance(holder[0], svr2.vae_block.ResnetBlock3DB200) and isinstance(holder[1][0], svr2.vae_conv.CausalConv3dB200)
+    assert holder[1][1] is small
+
+
+@pytest.mark.parametrize("co", [128, 256, 512])
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16], ids=["fp16", "bf16"])
+def test_conv_epilogue_statistics_feed_the_groupnorm(svr2, cuda, co, dtype):
+    """The convolution's epilogue gathers the (count, mean, M2) partials of its output; merged, they are the per-frame group
+    statistics ATen computes, and the GroupNorm that consumes them equals the one that makes its own pass."""
+    g = torch.Generator(device="cuda").manual_seed(co)
+    T, H, W, ci = 3, 37, 50, 128                      # ragged tiles: rows / columns past the frame's edge must not be counted
+    x = (torch.randn(T, H, W, ci, generator=g, device=cuda) + 0.5).to(dtype)
+    w = (torch.randn(co, ci, 3, 3, 3, generator=g, device=cuda) * (27 * ci) ** -0.5).to(dtype)
+    b = (torch.randn(co, generator=g, device=cuda) * 2 + 3).to(dtype)               # |mean| > std: the pivot matters
+    resid = torch.randn(T, H, W, co, generator=g, device=cuda).to(dtype)
+    wp = svr2.vae_conv.pack_conv_weight(w)
+    slots = svr2.vae_conv.gn_slots()
+    part = torch.full((T, slots, 32, 3), float("nan"), device=cuda)                 # the call zeroes what it does not write
+    y = svr2.vae_conv.causal_conv3d(x, wp, b, None, resid, gn_partials=part)
+    assert torch.equal(y, svr2.vae_conv.causal_conv3d(x, wp, b, None, resid))       # gathering changes nothing in the output
+    n, mean, m2 = part[..., 0].double(), part[..., 1].double(), part[..., 2].double()
+    assert bool(torch.isfinite(part).all())
+    cnt = n.sum(1)                                                                  # [T, 32]
+    assert bool((cnt == H * W * (co // 32)).all())
+    gmean = (n * mean).sum(1) / cnt
+    gm2 = (m2 + n * (mean - gmean[:, None]) ** 2).sum(1)
+    yg = y.double().reshape(T, H * W, 32, co // 32)
+    assert float((gmean - yg.mean((1, 3))).abs().max()) < 1e-5
+    var_ref = yg.var((1, 3), unbiased=False)
+    assert float(((gm2 / cnt) / var_ref - 1).abs().max()) < 1e-5
+    gw = (1 + 0.2 * torch.randn(co, generator=g, device=cuda)).to(dtype)
+    gb = (0.2 * torch.randn(co, generator=g, device=cuda)).to(dtype)
+    own = svr2.vae_block.groupnorm_silu(y, gw, gb, 32, 1e-6)
+    stats = svr2.vae_conv.GroupStats(part, slots, y)
+    fed = svr2.vae_block.groupnorm_silu(y, gw, gb, 32, 1e-6, stats=stats)
+    d = (own.float() - fed.float()).abs()
+    ulp = 2.0 ** (-10 if dtype == torch.float16 else -7)
+    assert float((d > 0).float().mean()) < 0.05
+    assert bool((d <= ulp * 1.01 * (own.float().abs() + 1) + 1e-6).all())
+    y.add_(1)                                                                       # written since: the statistics no longer apply
+    assert not stats.valid_for(y)
+
+
+def test_block_chain_reuses_epilogue_statistics(svr2, cuda):
+    if not refstage.available():
+        pytest.skip("reference not staged")
+    refstage.activate()
+    from src.models.video_vae_v3.modules.causal_inflation_lib import causal_norm_wrapper, init_causal_conv3d
+    from src.models.video_vae_v3.modules.types import MemoryState
+    torch.manual_seed(1)
+    refs = [ResnetBlock3D(256, 128, init_causal_conv3d, causal_norm_wrapper).eval().cuda().half(),
+            ResnetBlock3D(128, 128, init_causal_conv3d, causal_norm_wrapper).eval().cuda().half()]
+    mine = [svr2.vae_block.ResnetBlock3DB200.from_reference(r) for r in refs]
+    ident = nn.Identity()
+    x = torch.randn(1, 256, 3, 40, 56, device=cuda).half().contiguous(memory_format=torch.channels_last_3d)
+    with torch.no_grad():
+        n0 = svr2.ops.launch_count()
+        h = ident(mine[0](x, None, memory_state=MemoryState.DISABLED))
+        n1 = svr2.ops.launch_count()
+        out = mine[1](h, None, memory_state=MemoryState.DISABLED)
+        n2 = svr2.ops.launch_count()
+        # block 0: norm1 makes its own statistics pass (2 kernels), norm2 is fed by conv1 (1), three convolutions -> 6;
+        # block 1: both norms are fed (1 + 1), two convolutions -> 4
+        assert (n1 - n0, n2 - n1) == (6, 4), (n1 - n0, n2 - n1)
+        r = refs[1](refs[0](x.contiguous(), memory_state=MemoryState.DISABLED), memory_state=MemoryState.DISABLED)
+        params = [{k: v.float() for k, v in rr.state_dict().items()} for rr in refs]
+        with torch.backends.cudnn.flags(enabled=True, allow_tf32=False):
+            o, _ = ovb.resnet_block3d(ovb.resnet_block3d(x.float(), params[0])[0], params[1])
+        rms_ref, rms_mine = float((r.float() - o).pow(2).mean().sqrt()), float((out.float() - o).pow(2).mean().sqrt())
+        assert rms_mine <= 1.1 * rms_ref + 1e-6, (rms_mine, rms_ref)

@@ -108,6 +108,15 @@ def test_module_streams_like_reference(svr2, cuda):
                 outs_m.append(mine(x[:, :, a:b], st))
                 if ref.kernel_size[0] > 1:
                     assert torch.equal(mine.memory.permute(0, 4, 1, 2, 3), ref.memory)
+            # the up-sampler hands the convolution a LIST of temporal pieces (attn_video_vae.py:126-133)
+            ref.memory = None
+            pieces = [x[:, :, :4].contiguous(), x[:, :, 4:].contiguous()]
+            lr = ref([p.clone() for p in pieces], memory_state=MemoryState.INITIALIZING)
+            lm = mine([x[:, :, :4], x[:, :, 4:]], MemoryState.INITIALIZING)
+            assert isinstance(lm, list) and len(lm) == 2 and torch.equal(torch.cat(lm, 2), torch.cat(outs_m, 2))
+            assert float((torch.cat(lr, 2).float() - torch.cat(lm, 2).float()).abs().max()) <= 2.0 ** -9 * float(torch.cat(lr, 2).abs().max())
+            if ref.kernel_size[0] > 1:
+                assert torch.equal(mine.memory.permute(0, 4, 1, 2, 3), ref.memory)
             r, m = torch.cat(outs_r, 2).float(), torch.cat(outs_m, 2).float()
             one_shot = mine(x, MemoryState.DISABLED)
             assert mine.memory is None
