@@ -425,6 +425,37 @@ class Job:
         return tot
 
 
+def vae_block_sample(svr2, dev):
+    """ms and TFLOP/s of one VAE residual block (ResnetBlock3D, attn_video_vae.py:253-361) through vae_block.ResnetBlock3DB200."""
+    ci = co = 128
+    T, H, W = 5, 1080, 1920
+
+    class _N:
+        def __init__(self, **kw):
+            self.__dict__.update(kw)
+    g = torch.Generator(device=dev).manual_seed(0)
+    rnd = lambda *s, k=1.0: (torch.randn(*s, generator=g, device=dev) * k).half()      # noqa: E731
+    norm = lambda c: _N(num_groups=32, eps=1e-6, weight=1 + rnd(c, k=0.1), bias=rnd(c, k=0.1))      # noqa: E731
+    conv = lambda a, b: _N(weight=rnd(b, a, 3, 3, 3, k=(27 * a) ** -0.5), bias=rnd(b, k=0.1), stride=(1, 1, 1), dilation=(1, 1, 1), groups=1)      # noqa: E731
+    blk = svr2.vae_block.ResnetBlock3DB200(norm(ci), conv(ci, co), norm(co), conv(co, co))
+    x = rnd(1, T, H, W, ci).permute(0, 4, 1, 2, 3)          # channels_last_3d
+    with torch.no_grad():
+        for _ in range(2):
+            blk(x, None, memory_state="DISABLED")
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        n = 5
+        e0.record()
+        for _ in range(n):
+            blk(x, None, memory_state="DISABLED")
+        e1.record()
+        torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / n
+    flops = 2.0 * T * H * W * 27 * (ci * co + co * co)
+    return {"ms": ms, "tflops": flops / ms / 1e9, "dtype": "f16", "shape": [ci, co, T, H, W], "frames_per_s": T / (ms * 1e-3),
+            "inputs": "5.3 GB activations per call, larger than L2"}
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -539,6 +570,14 @@ def run_ours(args):
         if world > 1:
             dist.destroy_process_group()
         return 0
+
+    # ---- SURVEY §8f N3 beside the headline: one residual block of the VAE decoder's top level (128 channels at 1080 x 1920, 5
+    # frames, fp16) — GroupNorm + SiLU, two causal 3-D convolutions, fused residual; reported, not part of `value`
+    if also is not None and world == 1:
+        try:
+            also["vae_resnet_block_1080p"] = vae_block_sample(svr2, dev)
+        except Exception as e:      # noqa: BLE001 — a side measurement must not take the headline down
+            also["vae_resnet_block_1080p"] = {"error": f"{type(e).__name__}: {e}"[:200]}
 
     pk, pk_src = peaks()
     attn_flops_step = job.attention_flops(svr2, heads)
