@@ -12,7 +12,7 @@ import torch
 from torch import nn
 
 from . import _lib, ops
-from .vae_conv import _DTYPE_CODE, CausalConv3dB200, GroupStats
+from .vae_conv import _DTYPE_CODE, CausalConv3dB200, GroupStats, to_channels_last
 
 
 def groupnorm_silu(x: torch.Tensor, weight: Optional[torch.Tensor], bias: Optional[torch.Tensor], groups: int, eps: float,
@@ -81,9 +81,7 @@ class ResnetBlock3DB200(nn.Module):
     def forward(self, input_tensor: torch.Tensor, temb=None, memory_state="DISABLED", **kwargs) -> torch.Tensor:
         if temb is not None:
             raise NotImplementedError("seedvr2_b200.vae_block: the VAE calls its residual blocks with temb=None")
-        x = input_tensor.permute(0, 2, 3, 4, 1)                      # [B, T, H, W, C]: no copy for channels_last_3d input
-        if not x.is_contiguous():
-            x = x.contiguous()
+        x = to_channels_last(input_tensor)                           # [B, T, H, W, C]: no copy for channels_last_3d input
         B = x.shape[0]
         # statistics of the input, if the block that produced it gathered them in its last convolution's epilogue
         st_in = getattr(input_tensor, "_svr2_gn_stats", None)
@@ -105,21 +103,113 @@ class ResnetBlock3DB200(nn.Module):
         return ret
 
 
+def pixel_shuffle3d(x: torch.Tensor, channels: int, spatial: int, temporal: int, drop_second_frame: bool = False) -> torch.Tensor:
+    """x [T, H, W, spatial^2 * temporal * channels] channels-last -> [T * temporal (- 1), H * spatial, W * spatial, channels]:
+    the up-sampler's rearrange "b (x y z c) f h w -> b c (f z) (h x) (w y)" (+ remove_head) as one copy kernel."""
+    ops._need(x, "x", x.dtype)
+    T, H, W, cr = x.shape
+    if x.element_size() != 2 or cr != spatial * spatial * temporal * channels:
+        raise RuntimeError("seedvr2_b200.vae_block: pixel_shuffle3d expects 2-byte elements and spatial^2 * temporal * channels inputs")
+    out = torch.empty(T * temporal - int(drop_second_frame), H * spatial, W * spatial, channels, dtype=x.dtype, device=x.device)
+    ops._call("svr2_pixel_shuffle3d_fwd", 1, x.device, _lib.lib().svr2_pixel_shuffle3d_fwd, x.data_ptr(), out.data_ptr(), T, H, W, channels,
+              spatial, temporal, int(drop_second_frame), ops._stream(x))
+    return out
+
+
+class Upsample3DB200(nn.Module):
+    """Drop-in for ``Upsample3D`` (attn_video_vae.py:58-175) as the VAE builds it (no norm, no transposed convolution, MAGViT-v2
+    expansion): 1 x 1 x 1 channel expansion, pixel / time shuffle with the duplicated first frame removed on the first temporal
+    slice, causal 3 x 3 x 3 convolution — with ``slicing`` fed as two temporal pieces, like the reference."""
+
+    def __init__(self, upscale_conv: nn.Module, conv: nn.Module, channels: int, spatial_ratio: int, temporal_ratio: int, slicing: bool):
+        super().__init__()
+        self.upscale_conv = CausalConv3dB200.from_reference(upscale_conv)
+        self.conv = CausalConv3dB200.from_reference(conv)
+        self.channels, self.spatial_ratio, self.temporal_ratio, self.slicing = channels, spatial_ratio, temporal_ratio, slicing
+        self.temporal_up = temporal_ratio == 2
+
+    @classmethod
+    def from_reference(cls, up: nn.Module) -> "Upsample3DB200":
+        if getattr(up, "norm", None) is not None or getattr(up, "use_conv_transpose", False) or getattr(up, "interpolate", False) \
+                or not getattr(up, "use_conv", True):
+            raise NotImplementedError("seedvr2_b200.vae_block: up-sampler configuration outside the mirror")
+        conv = up.conv if getattr(up, "name", "conv") == "conv" else up.Conv2d_0
+        if not (_conv_supported(conv) and _conv_supported(up.upscale_conv)) or up.channels % 8:
+            raise NotImplementedError("seedvr2_b200.vae_block: up-sampler convolutions outside the kernel's shapes")
+        return cls(up.upscale_conv, conv, up.channels, up.spatial_ratio, up.temporal_ratio, bool(getattr(up, "slicing", False)))
+
+    def forward(self, hidden_states: torch.Tensor, output_size=None, memory_state="DISABLED", **kwargs):
+        from .vae_conv import _state_name
+        x = to_channels_last(hidden_states)                          # [B, T, H, W, C]
+        if x.shape[0] != 1:
+            raise NotImplementedError("seedvr2_b200.vae_block: the up-sampler mirror takes batch 1 (the VAE decodes one clip at a time)")
+        T = x.shape[1]
+        pieces = [x[:, :T // 2], x[:, T // 2:]] if self.slicing else [x]          # :126-133
+        first = _state_name(memory_state) != "ACTIVE"
+        ups = []
+        for i, piece in enumerate(pieces):
+            if piece.shape[1] == 0:
+                continue
+            t = self.upscale_conv.forward_cl(piece.contiguous(), "DISABLED")       # [1, t, H, W, r C]
+            drop = self.temporal_up and first and i == 0                           # remove_head, :151-153
+            ups.append(pixel_shuffle3d(t[0], self.channels, self.spatial_ratio, self.temporal_ratio, drop)[None])
+        ys = self.conv._forward_pieces(ups, memory_state)
+        y = ys[0] if len(ys) == 1 else torch.cat(ys, dim=1)
+        return y.permute(0, 4, 1, 2, 3)
+
+
+def make_causal_norm_wrapper(original):
+    """A drop-in for the reference's ``causal_norm_wrapper(norm_layer, x)`` (causal_inflation_lib.py:354-409): per-frame GroupNorm of a
+    5-D CUDA fp16 / bf16 tensor runs on svr2_groupnorm_silu_fwd (no activation, channels-last result — no memory-limit chunking is
+    needed, the kernel has no workspace beyond 50 KB of partials); everything else goes to ``original``."""
+    def causal_norm_wrapper(norm_layer: nn.Module, x: torch.Tensor) -> torch.Tensor:
+        if (isinstance(norm_layer, nn.GroupNorm) and torch.is_tensor(x) and x.ndim == 5 and x.is_cuda and x.dtype in _DTYPE_CODE
+                and x.shape[1] % norm_layer.num_groups == 0 and x.shape[1] // norm_layer.num_groups in (2, 4, 8, 16)
+                and x.shape[1] % 8 == 0 and 256 % (x.shape[1] // 8) == 0 and norm_layer.weight is not None
+                and norm_layer.weight.dtype == x.dtype):
+            xc = to_channels_last(x)
+            y = torch.empty_like(xc)
+            for b in range(xc.shape[0]):
+                groupnorm_silu(xc[b], norm_layer.weight, norm_layer.bias, norm_layer.num_groups, norm_layer.eps, silu=False, out=y[b])
+            return y.permute(0, 4, 1, 2, 3)
+        return original(norm_layer, x)
+    causal_norm_wrapper._svr2_original = original
+    return causal_norm_wrapper
+
+
+def patch_causal_norm_wrapper() -> int:
+    """Replace ``causal_norm_wrapper`` in every loaded module of the reference's VAE package (the function is imported by name into
+    attn_video_vae.py, which calls it for the decoder's / encoder's output norm); returns how many module globals were rebound."""
+    import sys
+    n = 0
+    for name, mod in list(sys.modules.items()):
+        if mod is None or "video_vae_v3.modules" not in name:
+            continue
+        fn = getattr(mod, "causal_norm_wrapper", None)
+        if callable(fn) and not hasattr(fn, "_svr2_original"):
+            setattr(mod, "causal_norm_wrapper", make_causal_norm_wrapper(fn))
+            n += 1
+    return n
+
+
 def _conv_supported(conv: nn.Module) -> bool:
     try:
         kt, kh, kw = conv.kernel_size
         return (tuple(conv.stride) == (1, 1, 1) and tuple(conv.dilation) == (1, 1, 1) and conv.groups == 1 and kh == kw
-                and kt in (1, 3) and kh in (1, 3) and conv.in_channels % 64 == 0 and conv.out_channels % 128 == 0
-                and conv.weight.is_cuda and conv.weight.dtype in _DTYPE_CODE)
+                and kt in (1, 3) and kh in (1, 3) and conv.weight.is_cuda and conv.weight.dtype in _DTYPE_CODE)
     except (AttributeError, TypeError, ValueError):
         return False
 
 
-def install_vae_blocks(model: nn.Module, convs: bool = True):
+def install_vae_blocks(model: nn.Module, convs: bool = True, norms: bool = True):
     """Replace, in a built (CUDA, fp16 / bf16) VAE, every ``ResnetBlock3D`` this module mirrors and — with ``convs`` — every other
-    stride-1 ``InflatedCausalConv3d`` the kernel covers (the up-samplers' 3 x 3 x 3 convolutions: a third of the decoder's FLOPs).
-    Returns (blocks replaced, convolutions replaced).  Anything else keeps the reference's module."""
+    stride-1 ``InflatedCausalConv3d`` (the up-samplers' 3 x 3 x 3 convolutions — a third of the decoder's FLOPs — and the boundary
+    convolutions conv_in / conv_out, which run with zero-padded channels).
+    With ``norms`` the reference's ``causal_norm_wrapper`` is rebound (``patch_causal_norm_wrapper``) so that the stand-alone
+    GroupNorms (conv_norm_out) run on this library too.  Returns (blocks replaced, convolutions replaced)."""
     n_blocks = n_convs = 0
+    if norms:
+        patch_causal_norm_wrapper()
     for parent in list(model.modules()):
         for name, child in list(parent.named_children()):
             if type(child).__name__ != "ResnetBlock3D":
@@ -131,10 +221,20 @@ def install_vae_blocks(model: nn.Module, convs: bool = True):
                 pass          # a configuration outside the mirror keeps the reference's block
     if convs:
         for parent in list(model.modules()):
-            if isinstance(parent, (ResnetBlock3DB200, CausalConv3dB200)):
+            for name, child in list(parent.named_children()):
+                if type(child).__name__ == "Upsample3D":
+                    try:
+                        setattr(parent, name, Upsample3DB200.from_reference(child))
+                        n_convs += 2
+                    except (NotImplementedError, AttributeError):
+                        pass
+        for parent in list(model.modules()):
+            if isinstance(parent, (ResnetBlock3DB200, CausalConv3dB200, Upsample3DB200)):
                 continue
             for name, child in list(parent.named_children()):
-                if type(child).__name__ == "InflatedCausalConv3d" and _conv_supported(child):
+                pointwise = type(child) is nn.Conv3d and tuple(child.kernel_size) == (1, 1, 1) and tuple(child.padding) == (0, 0, 0)
+                if (type(child).__name__ == "InflatedCausalConv3d" or pointwise) and _conv_supported(child):
+                    # `pointwise`: the up-samplers' 1 x 1 x 1 channel expansion in front of the pixel shuffle (attn_video_vae.py:94-96)
                     setattr(parent, name, CausalConv3dB200.from_reference(child))
                     n_convs += 1
     return n_blocks, n_convs

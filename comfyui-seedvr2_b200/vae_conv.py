@@ -40,6 +40,40 @@ def pack_conv_weight(weight: torch.Tensor) -> torch.Tensor:
     return out
 
 
+def transpose_2b(src: torch.Tensor, dst: torch.Tensor, rows: int, cols: int, ld_src: int, ld_dst: int, batch: int, bs_src: int,
+                 bs_dst: int) -> None:
+    """dst[b][j][i] = src[b][i][j] (2-byte elements): the layout change at the boundary with the reference's NCDHW modules."""
+    ops._call("svr2_transpose_2b", 1, src.device, _lib.lib().svr2_transpose_2b, src.data_ptr(), dst.data_ptr(), rows, cols, ld_src, ld_dst,
+              batch, bs_src, bs_dst, ops._stream(src))
+
+
+def to_channels_last(t: torch.Tensor) -> torch.Tensor:
+    """[B, C, T, H, W] in any layout -> contiguous [B, T, H, W, C].  A channels_last_3d tensor is returned as a view; a contiguous
+    NCDHW tensor (what the reference's own modules produce) goes through svr2_transpose_2b; anything else through a strided copy."""
+    x = t.permute(0, 2, 3, 4, 1)
+    if x.is_contiguous():
+        return x
+    if t.is_contiguous() and t.is_cuda and t.element_size() == 2 and t.numel() > 0:
+        B, C, T, H, W = t.shape
+        out = torch.empty(B, T, H, W, C, dtype=t.dtype, device=t.device)
+        n = T * H * W
+        transpose_2b(t, out, C, n, n, C, B, C * n, C * n)
+        return out
+    return x.contiguous()
+
+
+def to_ncdhw(y: torch.Tensor, channels: Optional[int] = None) -> torch.Tensor:
+    """Contiguous [B, T, H, W, C_stored] -> contiguous NCDHW [B, channels, T, H, W] (the first `channels` of the stored ones)."""
+    B, T, H, W, cs = y.shape
+    c = cs if channels is None else channels
+    n = T * H * W
+    if not (y.is_contiguous() and y.is_cuda and y.element_size() == 2 and y.numel() > 0):
+        return y[..., :c].permute(0, 4, 1, 2, 3).contiguous()
+    out = torch.empty(B, c, T, H, W, dtype=y.dtype, device=y.device)
+    transpose_2b(y, out, n, c, cs, n, B, n * cs, c * n)
+    return out
+
+
 class GroupStats:
     """Statistics partials of a tensor gathered by the convolution that produced it (``svr2_causal_conv3d_fwd`` gn_partials): what
     the per-frame GroupNorm over 32 groups that follows needs instead of its own pass over the tensor."""
@@ -102,8 +136,18 @@ class CausalConv3dB200(nn.Module):
         if kh != kw or kt not in (1, 3) or kh not in (1, 3):
             raise NotImplementedError(f"seedvr2_b200.vae_conv: kernel {(kt, kh, kw)} (temporal 1|3, spatial 1|3 square, stride 1)")
         self.in_channels, self.out_channels, self.kernel_size = ci, co, (kt, kh, kw)
-        self.register_buffer("weight_packed", pack_conv_weight(weight.detach()), persistent=False)
-        self.register_buffer("bias", None if bias is None else bias.detach().clone(), persistent=False)
+        # the kernel's K step is 64 input channels and its N tile 128 output channels: the VAE's boundary convolutions (conv_in
+        # 16 -> 512, conv_out 128 -> 3) run with zero-padded channels — zero weights, zero inputs, the extra outputs dropped
+        self.ci_pad, self.co_pad = -(-ci // 64) * 64, -(-co // 128) * 128
+        w, b = weight.detach(), None if bias is None else bias.detach().clone()
+        if (self.ci_pad, self.co_pad) != (ci, co):
+            wp = torch.zeros(self.co_pad, self.ci_pad, kt, kh, kw, dtype=w.dtype, device=w.device)
+            wp[:co, :ci] = w
+            w = wp
+            if b is not None:
+                b = torch.cat((b, torch.zeros(self.co_pad - co, dtype=b.dtype, device=b.device)))
+        self.register_buffer("weight_packed", pack_conv_weight(w), persistent=False)
+        self.register_buffer("bias", b, persistent=False)
         self.memory: Optional[torch.Tensor] = None       # [B, kt - 1, H, W, C] — the reference keeps [B, C, kt - 1, H, W]
 
     @classmethod
@@ -122,19 +166,24 @@ class CausalConv3dB200(nn.Module):
             if resid is not None:
                 raise NotImplementedError("seedvr2_b200.vae_conv: a residual with a list input")
             xs = [self._to_cl(t) for t in input]
-            return [y.permute(0, 4, 1, 2, 3) for y in self._forward_pieces(xs, memory_state)]
+            return [self._from_cl(y) for y in self._forward_pieces(xs, memory_state)]
         r = None if resid is None else self._to_cl(resid)
-        return self.forward_cl(self._to_cl(input), memory_state, r).permute(0, 4, 1, 2, 3)      # [B, C_out, T, H, W], channels-last strides
+        return self._from_cl(self.forward_cl(self._to_cl(input), memory_state, r))
+
+    def _from_cl(self, y: torch.Tensor) -> torch.Tensor:
+        """[B, T, H, W, C_out] -> [B, C_out, T, H, W]: a channels-last view, or (padded outputs) a contiguous copy of the real ones."""
+        if self.co_pad != self.out_channels:
+            return to_ncdhw(y, self.out_channels)
+        return y.permute(0, 4, 1, 2, 3)
 
     @staticmethod
     def _to_cl(t: torch.Tensor) -> torch.Tensor:
-        x = t.permute(0, 2, 3, 4, 1)                                            # [B, T, H, W, C]: contiguous for channels_last_3d
-        return x if x.is_contiguous() else x.contiguous()
+        return to_channels_last(t)                                              # [B, T, H, W, C]: a view for channels_last_3d
 
     def forward_cl(self, x: torch.Tensor, memory_state="DISABLED", resid: Optional[torch.Tensor] = None, want_stats: bool = False):
         """The same on channels-last tensors: x [B, T, H, W, C_in] -> [B, T, H, W, C_out].  ``want_stats`` (batch 1, C_out 128 / 256 /
         512): returns (y, GroupStats of y) — the statistics the GroupNorm after this convolution needs."""
-        if want_stats and x.shape[0] == 1 and self.out_channels in (128, 256, 512):
+        if want_stats and x.shape[0] == 1 and self.out_channels in (128, 256, 512) and self.ci_pad == self.in_channels:
             part = torch.empty(x.shape[1], gn_slots(), 32, 3, dtype=torch.float32, device=x.device)
             y = self._forward_pieces([x], memory_state, resid, part)[0]
             return y, GroupStats(part, gn_slots(), y)
@@ -147,10 +196,16 @@ class CausalConv3dB200(nn.Module):
             self.memory = None                                                  # :216-217
         kt = self.kernel_size[0]
         head = self.memory if kt > 1 else None                                  # [B, kt - 1, H, W, C] or None (first frame repeated)
+        if resid is not None and self.co_pad != self.out_channels:
+            raise NotImplementedError("seedvr2_b200.vae_conv: a residual on a convolution with padded output channels")
         ys = []
         for x in xs:
             B = x.shape[0]
-            y = torch.empty(*x.shape[:4], self.out_channels, dtype=x.dtype, device=x.device)
+            if self.ci_pad != self.in_channels:
+                xp = torch.zeros(*x.shape[:4], self.ci_pad, dtype=x.dtype, device=x.device)
+                xp[..., :self.in_channels] = x
+                x = xp
+            y = torch.empty(*x.shape[:4], self.co_pad, dtype=x.dtype, device=x.device)
             for b in range(B):
                 causal_conv3d(x[b], self.weight_packed, self.bias, None if head is None else head[b],
                               None if resid is None else resid[b], out=y[b], gn_partials=gn_partials)

@@ -389,6 +389,23 @@ int64_t svr2_groupnorm_workspace_bytes(int T, int groups);
 int svr2_groupnorm_silu_fwd(const void* x, const void* weight, const void* bias, void* y, void* workspace, int have_partials, int T,
                             int64_t HW, int C, int groups, float eps, int silu, int dtype, void* stream);
 
+/*
+ * Layout change between the reference's NCDHW tensors and this library's channels-last VAE modules: dst[b][j][i] = src[b][i][j] for
+ * 2-byte elements, i < rows, j < cols, with row pitches ld_src >= cols, ld_dst >= rows (elements) and batch strides.  [C, T*H*W] ->
+ * [T*H*W, C]: rows = C, cols = T*H*W; the reverse with a channel slice (conv_out: 3 of 128): rows = T*H*W, cols = 3, ld_src = 128.
+ * No counterpart in the reference (it stays NCDHW); replaces ATen's strided `.contiguous()` at the module boundaries.
+ */
+int svr2_transpose_2b(const void* src, void* dst, int64_t rows, int64_t cols, int64_t ld_src, int64_t ld_dst, int batch,
+                      int64_t batch_stride_src, int64_t batch_stride_dst, void* stream);
+/*
+ * The up-samplers' pixel (and time) shuffle, Upsample3D.forward (attn_video_vae.py:134-153): einops
+ * "b (x y z c) f h w -> b c (f z) (h x) (w y)" after the 1 x 1 x 1 expansion, and remove_head (the duplicated second frame of the
+ * first temporal slice, causal_inflation_lib.py:412-419) — channels-last: src [T, H, W, spatial^2 * temporal * C] ->
+ * dst [T * temporal - drop_second_frame, H * spatial, W * spatial, C], 2-byte elements, C % 8 == 0.
+ */
+int svr2_pixel_shuffle3d_fwd(const void* src, void* dst, int T, int H, int W, int C, int spatial, int temporal, int drop_second_frame,
+                             void* stream);
+
 #ifdef __cplusplus
 }
 #endif

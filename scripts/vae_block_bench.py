@@ -14,7 +14,7 @@ from oracle import refstage      # noqa: E402
 refstage.activate()
 from src.models.video_vae_v3.modules.causal_inflation_lib import causal_norm_wrapper, init_causal_conv3d      # noqa: E402
 from src.models.video_vae_v3.modules.types import MemoryState      # noqa: E402
-from test_gpu_vae_block import ResnetBlock3D      # noqa: E402
+from vae_standins import ResnetBlock3D      # noqa: E402
 
 dev = torch.device("cuda:0")
 flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
@@ -39,7 +39,7 @@ def timed(fn, n=5):
 # (c_in, c_out, T, H, W): one temporal slice (4 latent frames -> up to 13 + frames at the top; 5 keeps the reference inside memory)
 for ci, co, T, H, W in ((128, 128, 5, 1080, 1920), (256, 128, 5, 1080, 1920), (256, 256, 5, 540, 960), (512, 512, 3, 270, 480)):
     torch.manual_seed(0)
-    ref = ResnetBlock3D(ci, co, init_causal_conv3d, causal_norm_wrapper, True).eval().to(dev).half()
+    ref = ResnetBlock3D(ci, co, True).eval().to(dev).half()
     mine = svr2.vae_block.ResnetBlock3DB200.from_reference(ref)
     x = torch.randn(1, ci, T, H, W, device=dev).half().contiguous(memory_format=torch.channels_last_3d)
     xc = x.contiguous()

@@ -13,6 +13,7 @@ from torch import nn
 
 from oracle import refstage
 from oracle import vae_block as ovb
+from vae_standins import DecoderTop, ResnetBlock3D, Upsample3D
 
 pytestmark = pytest.mark.gpu
 
@@ -99,35 +100,6 @@ def test_fused_silu_is_atens_silu_bit_for_bit(svr2, cuda, dtype):
     assert torch.equal(fused, F.silu(y))
 
 
-class ResnetBlock3D(nn.Module):
-    """The reference's block from its importable parts, in the order of ResnetBlock3D.forward (attn_video_vae.py:311-361)."""
-
-    def __init__(self, ci, co, init_causal_conv3d, causal_norm_wrapper, full=True):
-        super().__init__()
-        self.wrap = causal_norm_wrapper
-        self.norm1 = nn.GroupNorm(32, ci, eps=1e-6)
-        self.norm2 = nn.GroupNorm(32, co, eps=1e-6)
-        k, p = (3, 1) if full else ((1, 3, 3), (0, 1, 1))
-        self.conv1 = init_causal_conv3d(ci, co, kernel_size=k, stride=1, padding=p, inflation_mode="tail")
-        self.conv2 = init_causal_conv3d(co, co, kernel_size=3, stride=1, padding=1, inflation_mode="tail")
-        self.conv_shortcut = init_causal_conv3d(ci, co, kernel_size=1, stride=1, padding=0, inflation_mode="tail") if ci != co else None
-        self.nonlinearity = nn.SiLU()
-        self.time_emb_proj = self.upsample = self.downsample = None
-        self.output_scale_factor = 1.0
-        for n in (self.norm1, self.norm2):
-            nn.init.normal_(n.weight, 1.0, 0.2)
-            nn.init.normal_(n.bias, 0.0, 0.2)
-
-    def forward(self, x, temb=None, memory_state=None):
-        h = self.nonlinearity(self.wrap(self.norm1, x))
-        h = self.conv1(h, memory_state=memory_state)
-        h = self.nonlinearity(self.wrap(self.norm2, h))
-        h = self.conv2(h, memory_state=memory_state)
-        if self.conv_shortcut is not None:
-            x = self.conv_shortcut(x, memory_state=memory_state)
-        return (x + h) / self.output_scale_factor
-
-
 @pytest.mark.parametrize("ci,co,full", [(128, 128, True), (256, 128, True), (128, 256, False)], ids=["128", "256to128", "128to256_half"])
 def test_resnet_block_matches_reference_parts(svr2, cuda, ci, co, full):
     if not refstage.available():
@@ -136,7 +108,7 @@ def test_resnet_block_matches_reference_parts(svr2, cuda, ci, co, full):
     from src.models.video_vae_v3.modules.causal_inflation_lib import causal_norm_wrapper, init_causal_conv3d
     from src.models.video_vae_v3.modules.types import MemoryState
     torch.manual_seed(ci + co)
-    ref = ResnetBlock3D(ci, co, init_causal_conv3d, causal_norm_wrapper, full).eval().cuda().half()
+    ref = ResnetBlock3D(ci, co, full).eval().cuda().half()
     mine = svr2.vae_block.ResnetBlock3DB200.from_reference(ref)
     params = {k: v.float() for k, v in ref.state_dict().items()}
     x = (torch.randn(1, ci, 9, 40, 56, device=cuda) * 1.5).half().contiguous(memory_format=torch.channels_last_3d)
@@ -162,11 +134,11 @@ def test_resnet_block_matches_reference_parts(svr2, cuda, ci, co, full):
         assert torch.equal(whole, torch.cat(outs_m, 2))
     # the installer finds the block by its class name and swaps it in place
     up_conv = init_causal_conv3d(co, co, 3, padding=1, inflation_mode="tail").cuda().half()          # an up-sampler's convolution
-    small = init_causal_conv3d(16, co, 3, padding=1, inflation_mode="tail").cuda().half()             # conv_in: outside the kernel's shapes
-    holder = nn.Sequential(ref, nn.Sequential(up_conv, small))
+    strided = init_causal_conv3d(co, co, 3, stride=2, padding=1, inflation_mode="tail").cuda().half()  # a down-sampler's: not mirrored
+    holder = nn.Sequential(ref, nn.Sequential(up_conv, strided))
     assert svr2.vae_block.install_vae_blocks(holder) == (1, 1)
     assert isinstance(holder[0], svr2.vae_block.ResnetBlock3DB200) and isinstance(holder[1][0], svr2.vae_conv.CausalConv3dB200)
-    assert holder[1][1] is small
+    assert holder[1][1] is strided
 
 
 @pytest.mark.parametrize("co", [128, 256, 512])
@@ -215,8 +187,7 @@ def test_block_chain_reuses_epilogue_statistics(svr2, cuda):
     from src.models.video_vae_v3.modules.causal_inflation_lib import causal_norm_wrapper, init_causal_conv3d
     from src.models.video_vae_v3.modules.types import MemoryState
     torch.manual_seed(1)
-    refs = [ResnetBlock3D(256, 128, init_causal_conv3d, causal_norm_wrapper).eval().cuda().half(),
-            ResnetBlock3D(128, 128, init_causal_conv3d, causal_norm_wrapper).eval().cuda().half()]
+    refs = [ResnetBlock3D(256, 128).eval().cuda().half(), ResnetBlock3D(128, 128).eval().cuda().half()]
     mine = [svr2.vae_block.ResnetBlock3DB200.from_reference(r) for r in refs]
     ident = nn.Identity()
     x = torch.randn(1, 256, 3, 40, 56, device=cuda).half().contiguous(memory_format=torch.channels_last_3d)
@@ -235,3 +206,70 @@ def test_block_chain_reuses_epilogue_statistics(svr2, cuda):
             o, _ = ovb.resnet_block3d(ovb.resnet_block3d(x.float(), params[0])[0], params[1])
         rms_ref, rms_mine = float((r.float() - o).pow(2).mean().sqrt()), float((out.float() - o).pow(2).mean().sqrt())
         assert rms_mine <= 1.1 * rms_ref + 1e-6, (rms_mine, rms_ref)
+
+
+@pytest.mark.parametrize("slicing", [False, True], ids=["whole", "sliced_upsampler"])
+def test_decoder_top_half_with_installed_modules(svr2, cuda, slicing):
+    """The decoder's upper half (two up blocks, spatial up-sampler, output norm and convolution) built from the reference's real
+    parts, against a copy with `install_vae_blocks` applied, over two temporal slices with the memory carried: 6 residual blocks,
+    the up-sampler's expansion and (list-fed) convolution and the padded conv_out all run on this library's kernels."""
+    if not refstage.available():
+        pytest.skip("reference not staged")
+    import copy
+    from vae_standins import reference_parts
+    _, _, _, MemoryState = reference_parts()
+    torch.manual_seed(7)
+    ref = DecoderTop(128, 128, 128, slicing=slicing).eval().cuda().half()      # narrow: the test is about wiring, not width
+    mine = copy.deepcopy(ref)
+    n_blocks, n_convs = svr2.vae_block.install_vae_blocks(mine)
+    assert (n_blocks, n_convs) == (6, 3)                                      # expansion, up-sampler convolution, conv_out
+    x = torch.randn(1, 128, 6, 24, 40, device=cuda).half()
+    with torch.no_grad():
+        outs_r, outs_m = [], []
+        for i, (a, b) in enumerate(((0, 4), (4, 6))):
+            st = MemoryState.INITIALIZING if i == 0 else MemoryState.ACTIVE
+            outs_r.append(ref(x[:, :, a:b].contiguous(), memory_state=st))
+            outs_m.append(mine(x[:, :, a:b].contiguous(), memory_state=st))
+        r, m = torch.cat(outs_r, 2).float(), torch.cat(outs_m, 2).float()
+    assert m.shape == r.shape == (1, 3, 6, 48, 80)
+    # fp16 against fp16 through 14 convolutions: compare on the output's scale
+    scale = float(r.abs().max())
+    assert float((r - m).abs().max()) <= 0.02 * scale, (float((r - m).abs().max()), scale)
+    assert float((r - m).pow(2).mean().sqrt()) <= 2e-3 * scale
+
+
+@pytest.mark.parametrize("temporal_up,slicing", [(False, False), (True, False), (True, True), (False, True)],
+                         ids=["spatial", "spatial+temporal", "spatial+temporal_sliced", "spatial_sliced"])
+def test_upsampler_mirror(svr2, cuda, temporal_up, slicing):
+    """Upsample3D from the reference's parts (einops rearrange, remove_head, the real causal convolution fed a tensor or a list)
+    against the mirror (1 x 1 x 1 GEMM, shuffle kernel with the head removal folded in, implicit-GEMM convolution) over two
+    temporal slices; the shuffle itself is bit-equal to einops."""
+    if not refstage.available():
+        pytest.skip("reference not staged")
+    from einops import rearrange
+    from vae_standins import reference_parts
+    _, _, remove_head, MemoryState = reference_parts()
+    torch.manual_seed(3)
+    ref = Upsample3D(128, temporal_up=temporal_up, spatial_up=True, slicing=slicing).eval().cuda().half()
+    nn.init.normal_(ref.upscale_conv.weight, 0, 128 ** -0.5)          # not the identity initialisation: every (x, y, z) plane differs
+    mine = svr2.vae_block.Upsample3DB200.from_reference(ref)
+    z = 2 if temporal_up else 1
+    t = torch.randn(3, 10, 12, 4 * z * 128, device=cuda).half()
+    want = rearrange(t.permute(3, 0, 1, 2)[None], "b (x y z c) f h w -> b c (f z) (h x) (w y)", x=2, y=2, z=z)
+    assert torch.equal(svr2.vae_block.pixel_shuffle3d(t, 128, 2, z).permute(3, 0, 1, 2)[None], want)
+    if temporal_up:
+        assert torch.equal(svr2.vae_block.pixel_shuffle3d(t, 128, 2, z, True).permute(3, 0, 1, 2)[None], remove_head(want))
+    x = torch.randn(1, 128, 7, 20, 24, device=cuda).half()
+    with torch.no_grad():
+        outs_r, outs_m = [], []
+        for i, (a, b) in enumerate(((0, 4), (4, 7))):
+            st = MemoryState.INITIALIZING if i == 0 else MemoryState.ACTIVE
+            outs_r.append(ref(x[:, :, a:b].contiguous(), memory_state=st))
+            outs_m.append(mine(x[:, :, a:b].contiguous(), memory_state=st))
+        r, m = torch.cat(outs_r, 2).float(), torch.cat(outs_m, 2).float()
+    assert m.shape == r.shape == (1, 128, 7 * z - (1 if temporal_up else 0), 40, 48)
+    scale = float(r.abs().max())
+    assert float((r - m).abs().max()) <= 2.0 ** -8 * scale, (float((r - m).abs().max()), scale)
+    if mine.conv.kernel_size[0] > 1:
+        assert torch.equal(mine.conv.memory.permute(0, 4, 1, 2, 3).float(), ref.conv.memory.float()) or \
+            float((mine.conv.memory.permute(0, 4, 1, 2, 3).float() - ref.conv.memory.float()).abs().max()) <= 2.0 ** -9 * scale

@@ -150,6 +150,33 @@ def test_1080p_crop_against_oracle(svr2, cuda):
         assert bool((d <= 2.0 ** -11 * 1.01 * ref.abs() + 3e-6 * mag + 1e-7).all()), (h0, w0, float(d.max()))
 
 
+@pytest.mark.parametrize("ci,co", [(16, 512), (128, 3), (3, 128)], ids=["conv_in", "conv_out", "encoder_in"])
+def test_boundary_convolutions_run_with_padded_channels(svr2, cuda, ci, co):
+    """conv_in (16 -> 512) and conv_out (128 -> 3) of the decoder, conv_in (3 -> 128) of the encoder: zero-padded to the kernel's
+    channel granularity inside the module, same function, NCDHW-contiguous result; the memory bookkeeping is unchanged."""
+    if not refstage.available():
+        pytest.skip("reference not staged")
+    refstage.activate()
+    from src.models.video_vae_v3.modules.causal_inflation_lib import init_causal_conv3d
+    from src.models.video_vae_v3.modules.types import MemoryState
+    torch.manual_seed(ci)
+    ref = init_causal_conv3d(ci, co, 3, padding=1, inflation_mode="tail").eval().cuda().half()
+    mine = svr2.vae_conv.CausalConv3dB200.from_reference(ref)
+    x = torch.randn(1, ci, 6, 33, 40, device="cuda").half()
+    with torch.no_grad():
+        outs_r, outs_m = [], []
+        for i, (a, b) in enumerate(((0, 3), (3, 6))):
+            st = MemoryState.INITIALIZING if i == 0 else MemoryState.ACTIVE
+            outs_r.append(ref(x[:, :, a:b].contiguous(), memory_state=st))
+            outs_m.append(mine(x[:, :, a:b].contiguous(), st))
+        r, m = torch.cat(outs_r, 2), torch.cat(outs_m, 2)
+        exact, _ = ovc.causal_conv3d(x.float(), ref.weight.float(), ref.bias.float())
+    assert m.shape == r.shape == (1, co, 6, 33, 40)
+    assert m.is_contiguous() if co % 128 else m.is_contiguous(memory_format=torch.channels_last_3d)
+    e_ref, e_mine = float((r.float() - exact).abs().max()), float((m.float() - exact).abs().max())
+    assert e_mine <= max(1.05 * e_ref, 2.0 ** -11 * float(exact.abs().max()) * 1.01), (e_mine, e_ref)
+
+
 def test_argument_validation(svr2, cuda):
     x = torch.zeros(2, 8, 8, 48, dtype=torch.float16, device="cuda")
     w = torch.zeros(128, 3, 3, 3, 48, dtype=torch.float16, device="cuda")
@@ -163,3 +190,17 @@ def test_argument_validation(svr2, cuda):
         svr2.vae_conv.causal_conv3d(x.float(), w.float())
     with pytest.raises(RuntimeError, match="CPU"):
         svr2.vae_conv.pack_conv_weight(torch.zeros(128, 64, 3, 3, 3, dtype=torch.float16))
+
+
+@pytest.mark.parametrize("shape", [(1, 128, 3, 40, 56), (2, 16, 2, 33, 40), (1, 512, 1, 135, 240), (1, 24, 3, 7, 9)],
+                         ids=["128ch", "batch2_16ch", "512ch_135x240", "unaligned"])
+def test_layout_transposes(svr2, cuda, shape):
+    g = torch.Generator(device="cuda").manual_seed(1)
+    x = torch.randn(*shape, generator=g, device="cuda").half()
+    cl = svr2.vae_conv.to_channels_last(x)
+    assert cl.is_contiguous() and torch.equal(cl, x.permute(0, 2, 3, 4, 1).contiguous())
+    assert svr2.vae_conv.to_channels_last(cl.permute(0, 4, 1, 2, 3)).data_ptr() == cl.data_ptr()        # already channels-last: a view
+    back = svr2.vae_conv.to_ncdhw(cl)
+    assert back.is_contiguous() and torch.equal(back, x)
+    k = min(3, shape[1])
+    assert torch.equal(svr2.vae_conv.to_ncdhw(cl, k), x[:, :k].contiguous())                                # conv_out's channel slice

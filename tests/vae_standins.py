@@ -1,0 +1,104 @@
+"""Stand-ins for the VAE modules that cannot be instantiated in this image (their base classes live in `diffusers`), composed from
+the reference's real, importable parts in the order of the reference's forward methods.  Test and benchmark infrastructure."""
+import torch
+from einops import rearrange
+from torch import nn
+
+
+def reference_parts():
+    from oracle import refstage
+    refstage.activate()
+    from src.models.video_vae_v3.modules.causal_inflation_lib import causal_norm_wrapper, init_causal_conv3d, remove_head
+    from src.models.video_vae_v3.modules.types import MemoryState
+    return init_causal_conv3d, causal_norm_wrapper, remove_head, MemoryState
+
+
+class ResnetBlock3D(nn.Module):
+    """ResnetBlock3D.forward (attn_video_vae.py:311-361) as the VAE configures it."""
+
+    def __init__(self, ci, co, full=True):
+        super().__init__()
+        init_causal_conv3d, wrap, _, _ = reference_parts()
+        self.wrap = wrap
+        self.norm1 = nn.GroupNorm(32, ci, eps=1e-6)
+        self.norm2 = nn.GroupNorm(32, co, eps=1e-6)
+        k, p = (3, 1) if full else ((1, 3, 3), (0, 1, 1))
+        self.conv1 = init_causal_conv3d(ci, co, kernel_size=k, stride=1, padding=p, inflation_mode="tail")
+        self.conv2 = init_causal_conv3d(co, co, kernel_size=3, stride=1, padding=1, inflation_mode="tail")
+        self.conv_shortcut = init_causal_conv3d(ci, co, kernel_size=1, stride=1, padding=0, inflation_mode="tail") if ci != co else None
+        self.nonlinearity = nn.SiLU()
+        self.time_emb_proj = self.upsample = self.downsample = None
+        self.output_scale_factor = 1.0
+        for n in (self.norm1, self.norm2):
+            nn.init.normal_(n.weight, 1.0, 0.2)
+            nn.init.normal_(n.bias, 0.0, 0.2)
+
+    def forward(self, x, temb=None, memory_state=None):
+        h = self.nonlinearity(self.wrap(self.norm1, x))
+        h = self.conv1(h, memory_state=memory_state)
+        h = self.nonlinearity(self.wrap(self.norm2, h))
+        h = self.conv2(h, memory_state=memory_state)
+        if self.conv_shortcut is not None:
+            x = self.conv_shortcut(x, memory_state=memory_state)
+        return (x + h) / self.output_scale_factor
+
+
+class Upsample3D(nn.Module):
+    """Upsample3D.forward (attn_video_vae.py:110-175): 1 x 1 x 1 expansion, pixel (and time) shuffle, the duplicated first frame
+    removed on the first temporal slice, causal 3 x 3 x 3 convolution; with `slicing` the convolution gets two temporal pieces."""
+
+    def __init__(self, channels, temporal_up=False, spatial_up=True, slicing=False):
+        super().__init__()
+        init_causal_conv3d, _, remove_head, MemoryState = reference_parts()
+        self.remove_head, self.MemoryState = remove_head, MemoryState
+        self.temporal_ratio, self.spatial_ratio = (2 if temporal_up else 1), (2 if spatial_up else 1)
+        self.temporal_up, self.slicing = temporal_up, slicing
+        self.channels, self.name, self.norm, self.use_conv, self.use_conv_transpose, self.interpolate = channels, "conv", None, True, False, False
+        r = self.spatial_ratio ** 2 * self.temporal_ratio
+        self.upscale_conv = nn.Conv3d(channels, channels * r, kernel_size=1, padding=0)
+        self.conv = init_causal_conv3d(channels, channels, 3, padding=1, inflation_mode="tail")
+
+    def forward(self, hidden_states, memory_state=None):
+        if self.slicing:
+            split = hidden_states.size(2) // 2
+            hidden_states = list(hidden_states.split([split, hidden_states.size(2) - split], dim=2))
+        else:
+            hidden_states = [hidden_states]
+        for i in range(len(hidden_states)):
+            t = self.upscale_conv(hidden_states[i])
+            hidden_states[i] = rearrange(t, "b (x y z c) f h w -> b c (f z) (h x) (w y)", x=self.spatial_ratio, y=self.spatial_ratio,
+                                         z=self.temporal_ratio)
+        if self.temporal_up and memory_state != self.MemoryState.ACTIVE:
+            hidden_states[0] = self.remove_head(hidden_states[0])
+        if not self.slicing:
+            hidden_states = hidden_states[0]
+        hidden_states = self.conv(hidden_states, memory_state=memory_state)
+        return hidden_states if not self.slicing else torch.cat(hidden_states, dim=2)
+
+
+class DecoderTop(nn.Module):
+    """The upper half of Decoder3D.forward (attn_video_vae.py:1030-1041) for the product VAE (block_out_channels 128, 256, 512, 512;
+    three residual blocks per up block): up block 2 (512 -> 256 at 540 x 960 for a 1080p clip, spatial up-sampler), up block 3
+    (256 -> 128 at full resolution), conv_norm_out, SiLU, conv_out."""
+
+    def __init__(self, c_in=512, c_mid=256, c_top=128, slicing=False):
+        super().__init__()
+        init_causal_conv3d, _, _, _ = reference_parts()
+        self.up2 = nn.ModuleList([ResnetBlock3D(c_in, c_mid), ResnetBlock3D(c_mid, c_mid), ResnetBlock3D(c_mid, c_mid)])
+        self.up2_sampler = Upsample3D(c_mid, temporal_up=False, spatial_up=True, slicing=slicing)
+        self.up3 = nn.ModuleList([ResnetBlock3D(c_mid, c_top), ResnetBlock3D(c_top, c_top), ResnetBlock3D(c_top, c_top)])
+        self.temporal = nn.Identity()
+        self.conv_norm_out = nn.GroupNorm(32, c_top, eps=1e-6)
+        self.conv_act = nn.SiLU()
+        self.conv_out = init_causal_conv3d(c_top, 3, 3, padding=1, inflation_mode="tail")
+
+    def forward(self, sample, memory_state=None):
+        for r in self.up2:
+            sample = self.temporal(r(sample, temb=None, memory_state=memory_state))
+        sample = self.up2_sampler(sample, memory_state=memory_state)
+        for r in self.up3:
+            sample = self.temporal(r(sample, temb=None, memory_state=memory_state))
+        # attn_video_vae.py calls the name it imported from causal_inflation_lib: looked up at call time, like a module global
+        import src.models.video_vae_v3.modules.causal_inflation_lib as lib
+        sample = self.conv_act(lib.causal_norm_wrapper(self.conv_norm_out, sample))
+        return self.conv_out(sample, memory_state=memory_state)
