@@ -72,6 +72,8 @@ class ResnetBlock3DB200(nn.Module):
             raise NotImplementedError("seedvr2_b200.vae_block: SiLU blocks only")
         if not isinstance(block.norm1, nn.GroupNorm) or not isinstance(block.norm2, nn.GroupNorm):
             raise NotImplementedError("seedvr2_b200.vae_block: GroupNorm blocks only")
+        if block.conv1.in_channels % 64 or block.conv1.out_channels % 128 or block.conv2.out_channels % 128:
+            raise NotImplementedError("seedvr2_b200.vae_block: block widths outside the kernel's channel granularity (64 in, 128 out)")
         drop = getattr(block, "dropout", None)
         if drop is not None and getattr(drop, "p", 0.0) != 0.0 and block.training:
             raise NotImplementedError("seedvr2_b200.vae_block: inference only (dropout)")

@@ -273,3 +273,32 @@ def test_upsampler_mirror(svr2, cuda, temporal_up, slicing):
     if mine.conv.kernel_size[0] > 1:
         assert torch.equal(mine.conv.memory.permute(0, 4, 1, 2, 3).float(), ref.conv.memory.float()) or \
             float((mine.conv.memory.permute(0, 4, 1, 2, 3).float() - ref.conv.memory.float()).abs().max()) <= 2.0 ** -9 * scale
+
+
+def test_whole_decoder_standin_psnr(svr2, cuda):
+    """Decoder3D.forward from the reference's parts (conv_in 16 -> C, mid resnets, four up blocks with temporal + spatial up-samplers,
+    output norm, conv_out C -> 3; narrow) with everything `install_vae_blocks` covers swapped in, streamed over three temporal slices:
+    decoded pixels against the reference's modules >= 45 dB on the [-1, 1] range (SURVEY §8c's bar, here on fp16 vs fp16)."""
+    if not refstage.available():
+        pytest.skip("reference not staged")
+    import copy
+    from vae_standins import Decoder3D, reference_parts
+    _, _, _, MemoryState = reference_parts()
+    torch.manual_seed(11)
+    ref = Decoder3D(16, (128, 128, 128, 128)).eval().cuda().half()
+    mine = copy.deepcopy(ref)
+    n_blocks, n_convs = svr2.vae_block.install_vae_blocks(mine)
+    assert (n_blocks, n_convs) == (14, 8)            # 2 mid + 12 up blocks; conv_in, 3 up-samplers x 2, conv_out
+    zs = [torch.randn(1, 16, t, 9, 12, device=cuda).half() for t in (1, 2, 1)]
+    with torch.no_grad():
+        outs_r, outs_m = [], []
+        for i, z in enumerate(zs):
+            st = MemoryState.INITIALIZING if i == 0 else MemoryState.ACTIVE
+            outs_r.append(ref(z, memory_state=st))
+            outs_m.append(mine(z, memory_state=st))
+    r, m = torch.cat(outs_r, 2).float(), torch.cat(outs_m, 2).float()
+    assert m.shape == r.shape == (1, 3, 1 + 8 + 4, 72, 96)           # 4n + 1 frames, 8 x the latent's side
+    r = r / r.abs().max()                                             # random weights: bring the output to the pixel range
+    m = m / torch.cat(outs_r, 2).float().abs().max()
+    psnr = float(10 * torch.log10(4.0 / (r - m).pow(2).mean()))
+    assert psnr >= 45.0, psnr

@@ -102,3 +102,38 @@ class DecoderTop(nn.Module):
         import src.models.video_vae_v3.modules.causal_inflation_lib as lib
         sample = self.conv_act(lib.causal_norm_wrapper(self.conv_norm_out, sample))
         return self.conv_out(sample, memory_state=memory_state)
+
+
+class Decoder3D(nn.Module):
+    """Decoder3D.forward (attn_video_vae.py:1000-1041) for the product VAE (s8_c16_t4_inflation_sd3.yaml: latent 16 channels,
+    block_out_channels 128 / 256 / 512 / 512, 3 residual blocks per up block, temporal up-sampling in up blocks 0 and 1, spatial in 0-2,
+    time_receptive_field "full") WITHOUT the mid block's attention layer (diffusers' `Attention`, not in this image)."""
+
+    def __init__(self, latent=16, ch=(512, 512, 256, 128)):
+        super().__init__()
+        init_causal_conv3d, _, _, _ = reference_parts()
+        self.conv_in = init_causal_conv3d(latent, ch[0], kernel_size=3, stride=1, padding=1, inflation_mode="tail")
+        self.mid = nn.ModuleList([ResnetBlock3D(ch[0], ch[0]), ResnetBlock3D(ch[0], ch[0])])
+        self.up_resnets = nn.ModuleList()
+        self.up_samplers = nn.ModuleList()
+        prev = ch[0]
+        for i, c in enumerate(ch):
+            self.up_resnets.append(nn.ModuleList([ResnetBlock3D(prev if j == 0 else c, c) for j in range(3)]))
+            self.up_samplers.append(Upsample3D(c, temporal_up=i < 2, spatial_up=True) if i < len(ch) - 1 else nn.Identity())
+            prev = c
+        self.conv_norm_out = nn.GroupNorm(32, ch[-1], eps=1e-6)
+        self.conv_act = nn.SiLU()
+        self.conv_out = init_causal_conv3d(ch[-1], 3, 3, padding=1, inflation_mode="tail")
+
+    def forward(self, sample, memory_state=None):
+        import src.models.video_vae_v3.modules.causal_inflation_lib as lib
+        sample = self.conv_in(sample, memory_state=memory_state)
+        for r in self.mid:
+            sample = r(sample, temb=None, memory_state=memory_state)
+        for resnets, up in zip(self.up_resnets, self.up_samplers):
+            for r in resnets:
+                sample = r(sample, temb=None, memory_state=memory_state)
+            if not isinstance(up, nn.Identity):
+                sample = up(sample, memory_state=memory_state)
+        sample = self.conv_act(lib.causal_norm_wrapper(self.conv_norm_out, sample))
+        return self.conv_out(sample, memory_state=memory_state)
