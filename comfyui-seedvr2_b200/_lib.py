@@ -51,6 +51,7 @@ SIGNATURES = {
     "svr2_conv3d_pack_weight": (c_int, [c_void_p, c_void_p] + [c_int] * 5 + [c_void_p]),
     "svr2_causal_conv3d_fwd": (c_int, [c_void_p] * 7 + [c_int] * 8 + [c_void_p]),
     "svr2_conv3d_gn_slots": (c_int, []),
+    "svr2_causal_conv3d_down_fwd": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p] + [c_int] * 8 + [c_void_p]),
     "svr2_groupnorm_workspace_bytes": (c_int64, [c_int, c_int]),
     "svr2_groupnorm_silu_fwd": (c_int, [c_void_p] * 5 + [c_int, c_int, c_int64, c_int, c_int, c_float, c_int, c_int, c_void_p]),
     "svr2_transpose_2b": (c_int, [c_void_p, c_void_p, c_int64, c_int64, c_int64, c_int64, c_int, c_int64, c_int64, c_void_p]),
@@ -59,7 +60,7 @@ SIGNATURES = {
     "svr2_v_lerp_endpoint_fwd": (c_int, [c_void_p, c_void_p, c_float, c_float, c_void_p, c_int64, c_void_p]),
 }
 
-ABI_VERSION = 12      # svr2_abi_version() of the library these SIGNATURES describe
+ABI_VERSION = 13      # svr2_abi_version() of the library these SIGNATURES describe
 _lib = None
 
 

@@ -77,7 +77,11 @@ struct Params {
     int T, H, W, Cin, Cout;
     int kt, ks;                 // temporal taps (1 | 3), spatial taps per axis (1 | 3)
     int h_tiles, w_tiles, n_tiles;
-    int has_head;               // frames t' < 0 come from the head tensor (kt - 1 frames); otherwise frame 0 is replicated
+    int has_head;               // frames t' < 0 come from the head tensor (head_len frames); otherwise frame 0 is replicated
+    int head_len;               // frames in front of the slice: kt - 1 (stride 1), 2 or the memory's length (temporal stride 2)
+    int st;                     // temporal stride (1 | 2)
+    int s2;                     // spatial stride 2 (down-sampler): one strided TMA box per tap, KS = 1 instantiation, 9 x the K steps
+    int Ti, Hi, Wi;             // input extents (host: tensor maps); T, H, W above are the OUTPUT's
     const void* bias;           // [Cout] or nullptr
     const void* resid;          // [T, H, W, Cout] or nullptr
     float* gn_partials;         // [T, gn_slots, 32, 3] (count, mean, M2) of the OUTPUT per frame and group of Cout / 32 channels, or nullptr
@@ -212,7 +216,7 @@ conv3d_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant
     constexpr int taps_sp = KS * KS;                           // K steps fed by one patch
     constexpr int slot_w = KS == 3 ? 16 : 8;                   // column slots per patch row
     constexpr uint32_t patch_bytes = (uint32_t)((TILE_H + 2 * half) * slot_w * 128);
-    const int n_patches = p.kt * c_chunks;                     // per tile
+    const int n_patches = p.kt * c_chunks * ((KS == 1 && p.s2) ? 9 : 1);      // per tile
     constexpr int tpb = KS == 3 ? C::TPB : 1;                  // taps per weight stage (divides KS * KS)
     constexpr uint32_t pstages = KS == 3 ? C::PSTAGES : C::PSTAGES_MAX;
     constexpr uint32_t pslot = KS == 3 ? (uint32_t)PATCH_BYTES : 16384u;      // patch ring slot
@@ -252,22 +256,30 @@ conv3d_tc_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant
             uint32_t pit = 0, bit = 0;
             for (int id = first; id < n_tiles_total; id += stride) {
                 const Tile tl = decode_tile(p, id);
-                const int ww = tl.w0 + (int)rank * TILE_W - half;
+                const int wtile = tl.w0 + (int)rank * TILE_W;
                 const int b_row = tl.nt * BN + (int)rank * (BN / 2);
+                // strided (down-sampler) form: the 9 spatial taps are separate K-step groups, each a TMA box that samples every
+                // second row / column (element strides 2) starting at the tap's offset — the rows past the frame's bottom / right
+                // edge that the reference pads with zeros (attn_video_vae.py:239-241) are the TMA unit's zero fill
+                const int n_sp = (KS == 1 && p.s2) ? 9 : 1;
                 for (int dt = 0; dt < p.kt; ++dt) {
                     // the causal head: frames before the slice come from the previous slice's memory, or repeat frame 0
-                    int ts = tl.t + dt - (p.kt - 1);
+                    int ts = p.st * tl.t + dt - p.head_len;
                     const CUtensorMap* ta = &tm_x;
                     if (ts < 0) {
-                        if (p.has_head) { ta = &tm_head; ts += p.kt - 1; }
+                        if (p.has_head) { ta = &tm_head; ts += p.head_len; }
                         else ts = 0;
                     }
+                    for (int sp = 0; sp < n_sp; ++sp)
                     for (int cc = 0; cc < c_chunks; ++cc, ++pit) {
                         const uint32_t ps = pit % pstages, puse = pit / pstages;
                         mbar_wait(bar(BAR_PEMPTY + ps), (puse & 1) ^ 1);
                         if (leader) mbar_expect_tx(bar(BAR_PFULL + ps), 2 * patch_bytes);
-                        tma_load_4d_pair(base + ps * pslot, ta, bar(BAR_PFULL + ps), cc * BK, ww, tl.h0 - half, ts);
-                        const int kcol0 = dt * taps_sp * p.Cin + cc * BK;
+                        const int sdh = sp / 3, sdw = sp - sdh * 3;
+                        const int ww = (KS == 1 && p.s2) ? 2 * wtile + sdw : wtile - half;
+                        const int hh = (KS == 1 && p.s2) ? 2 * tl.h0 + sdh : tl.h0 - half;
+                        tma_load_4d_pair(base + ps * pslot, ta, bar(BAR_PFULL + ps), cc * BK, ww, hh, ts);
+                        const int kcol0 = (dt * n_sp + sp) * taps_sp * p.Cin + cc * BK;
                         for (int tap = 0; tap < taps_sp; tap += tpb, ++bit) {
                             const uint32_t bs = bit % BSTAGES, buse = bit / BSTAGES;
                             mbar_wait(bar(BAR_BEMPTY + bs), (buse & 1) ^ 1);
@@ -446,9 +458,10 @@ int launch(const void* x, const void* head, const void* w, void* y, Params p, cu
     constexpr int slot_w = KS == 3 ? 16 : 8, box_h = TILE_H + 2 * (KS / 2);
     CUtensorMap tx, th, tw, ty;
     int rc;
-    if ((rc = make_tmap_thwc(&tx, x, p.T, p.H, p.W, p.Cin, slot_w, box_h)) != SVR2_OK) return rc;
+    const int es = p.s2 ? 2 : 1;                 // element stride of the input boxes along W and H
+    if ((rc = make_tmap_thwc(&tx, x, p.Ti, p.Hi, p.Wi, p.Cin, slot_w, box_h, es)) != SVR2_OK) return rc;
     if (p.has_head) {
-        if ((rc = make_tmap_thwc(&th, head, p.kt - 1, p.H, p.W, p.Cin, slot_w, box_h)) != SVR2_OK) return rc;
+        if ((rc = make_tmap_thwc(&th, head, p.head_len, p.Hi, p.Wi, p.Cin, slot_w, box_h, es)) != SVR2_OK) return rc;
     } else {
         th = tx;
     }
@@ -506,6 +519,7 @@ extern "C" int svr2_causal_conv3d_fwd(const void* x, const void* head, const voi
     if (T == 0) return SVR2_OK;
     svr2::conv::Params p{};
     p.T = T; p.H = H; p.W = W; p.Cin = c_in; p.Cout = c_out; p.kt = kt; p.ks = ks;
+    p.Ti = T; p.Hi = H; p.Wi = W; p.st = 1; p.s2 = 0; p.head_len = kt - 1;
     p.has_head = (head != nullptr && kt > 1) ? 1 : 0;
     p.bias = bias; p.resid = resid;
     SVR2_CHECK_ARG(gn_partials == nullptr || c_out == 128 || c_out == 256 || c_out == 512,
@@ -530,4 +544,33 @@ extern "C" int svr2_causal_conv3d_fwd(const void* x, const void* head, const voi
     if (f16) SVR2_CONV_GO(128, true, 1);
     SVR2_CONV_GO(128, false, 1);
 #undef SVR2_CONV_GO
+}
+
+extern "C" int svr2_causal_conv3d_down_fwd(const void* x, const void* head, int head_frames, const void* weight_packed, const void* bias,
+                                           void* y, int T, int H, int W, int c_in, int c_out, int kt, int pad_hw, int dtype, void* stream) {
+    const char* name = "svr2_causal_conv3d_down_fwd";
+    SVR2_CHECK_ARG(x && weight_packed && y, "%s: null pointer", name);
+    SVR2_CHECK_ARG(dtype == SVR2_DTYPE_F16 || dtype == SVR2_DTYPE_BF16, "%s: dtype %d (fp16 or bf16)", name, dtype);
+    SVR2_CHECK_ARG(kt == 1 || kt == 3, "%s: temporal kernel %d (1: spatial down-sampling, 3: spatial + temporal)", name, kt);
+    SVR2_CHECK_ARG(pad_hw == 0 || pad_hw == 1, "%s: pad_hw is the number of zero rows / columns after the last one (0 | 1)", name);
+    SVR2_CHECK_ARG(c_in > 0 && c_in % 64 == 0 && c_out > 0 && c_out % 128 == 0, "%s: c_in %% 64, c_out %% 128 (got %d, %d)", name, c_in, c_out);
+    SVR2_CHECK_ARG(T >= 0 && H + pad_hw >= 3 && W + pad_hw >= 3, "%s: bad extent T=%d H=%d W=%d", name, T, H, W);
+    SVR2_CHECK_ARG(head == nullptr || (kt == 3 && head_frames >= 1 && head_frames <= 2), "%s: head of %d frames", name, head_frames);
+    svr2::conv::Params p{};
+    p.kt = kt; p.ks = 3; p.Cin = c_in; p.Cout = c_out;
+    p.Ti = T; p.Hi = H; p.Wi = W;
+    p.s2 = 1;
+    p.st = kt == 3 ? 2 : 1;
+    p.has_head = head != nullptr ? 1 : 0;
+    p.head_len = kt == 3 ? (head != nullptr ? head_frames : 2) : 0;      // first slice: the first frame twice (extend_head, times = 2)
+    p.T = kt == 3 ? (T + p.head_len - 3) / 2 + 1 : T;
+    p.H = (H + pad_hw - 3) / 2 + 1;
+    p.W = (W + pad_hw - 3) / 2 + 1;
+    if (T == 0 || p.T <= 0) return SVR2_OK;
+    p.bias = bias; p.resid = nullptr; p.gn_partials = nullptr; p.gn_slots = 0;
+    const bool f16 = dtype == SVR2_DTYPE_F16;
+    cudaStream_t st = (cudaStream_t)stream;
+    using namespace svr2::conv;
+    if (c_out % 256 == 0) return f16 ? launch<256, true, 1>(x, head, weight_packed, y, p, st) : launch<256, false, 1>(x, head, weight_packed, y, p, st);
+    return f16 ? launch<128, true, 1>(x, head, weight_packed, y, p, st) : launch<128, false, 1>(x, head, weight_packed, y, p, st);
 }

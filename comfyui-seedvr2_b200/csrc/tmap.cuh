@@ -15,6 +15,7 @@ int make_tmap_2d(CUtensorMap* m, const void* ptr, int64_t rows, int64_t cols, in
 // Channels-last [T, H, W, C] tensor of 2-byte elements viewed as (c, w, h, t); box = 64 c x box_w x box_h x 1 frame, 128-byte
 // swizzle: rows of the box (w fastest) land as consecutive 128-byte rows — a K-major UMMA operand of box_w * box_h positions.
 // Coordinates may be negative / past the edge: the TMA unit zero-fills on load (the convolution's zero padding), clips on store.
-int make_tmap_thwc(CUtensorMap* m, const void* ptr, int64_t T, int64_t H, int64_t W, int64_t C, int box_w, int box_h);
+// stride > 1: the box samples every stride-th row / column (TMA element strides): box_w x box_h positions are still what lands.
+int make_tmap_thwc(CUtensorMap* m, const void* ptr, int64_t T, int64_t H, int64_t W, int64_t C, int box_w, int box_h, int stride = 1);
 
 }  // namespace svr2

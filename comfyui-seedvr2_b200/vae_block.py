@@ -160,6 +160,30 @@ class Upsample3DB200(nn.Module):
         return y.permute(0, 4, 1, 2, 3)
 
 
+class Downsample3DB200(nn.Module):
+    """Drop-in for ``Downsample3D`` (attn_video_vae.py:176-246) as the encoder builds it (no norm, convolution, padding 0): the
+    zero row / column the reference appends (`pad (0, 1, 0, 1)`, :239-241) is the TMA unit's zero fill inside the strided convolution."""
+
+    def __init__(self, conv: nn.Module, channels: int):
+        super().__init__()
+        self.conv = CausalConv3dB200(conv.weight, conv.bias, tuple(conv.stride), pad_hw=1)
+        self.channels = channels
+
+    @classmethod
+    def from_reference(cls, down: nn.Module) -> "Downsample3DB200":
+        conv = down.conv
+        if getattr(down, "norm", None) is not None or not getattr(down, "use_conv", True) or getattr(down, "padding", 0) != 0 \
+                or not getattr(down, "spatial_down", False) or type(conv).__name__ != "InflatedCausalConv3d":
+            raise NotImplementedError("seedvr2_b200.vae_block: down-sampler configuration outside the mirror")
+        if conv.in_channels % 64 or conv.out_channels % 128 or tuple(conv.padding)[1:] != (0, 0) or conv.weight.dtype not in _DTYPE_CODE:
+            raise NotImplementedError("seedvr2_b200.vae_block: down-sampler convolution outside the kernel's shapes")
+        return cls(conv, down.channels)
+
+    def forward(self, hidden_states: torch.Tensor, memory_state="DISABLED", **kwargs) -> torch.Tensor:
+        x = to_channels_last(hidden_states)
+        return self.conv.forward_cl(x, memory_state).permute(0, 4, 1, 2, 3)
+
+
 def make_causal_norm_wrapper(original):
     """A drop-in for the reference's ``causal_norm_wrapper(norm_layer, x)`` (causal_inflation_lib.py:354-409): per-frame GroupNorm of a
     5-D CUDA fp16 / bf16 tensor runs on svr2_groupnorm_silu_fwd (no activation, channels-last result — no memory-limit chunking is
@@ -197,7 +221,9 @@ def patch_causal_norm_wrapper() -> int:
 def _conv_supported(conv: nn.Module) -> bool:
     try:
         kt, kh, kw = conv.kernel_size
-        return (tuple(conv.stride) == (1, 1, 1) and tuple(conv.dilation) == (1, 1, 1) and conv.groups == 1 and kh == kw
+        strided_ok = (kh == 3 and tuple(conv.stride) == ((2 if kt == 3 else 1), 2, 2) and tuple(conv.padding)[1:] == (0, 0)
+                      and conv.in_channels % 64 == 0 and conv.out_channels % 128 == 0)
+        return ((tuple(conv.stride) == (1, 1, 1) or strided_ok) and tuple(conv.dilation) == (1, 1, 1) and conv.groups == 1 and kh == kw
                 and kt in (1, 3) and kh in (1, 3) and conv.weight.is_cuda and conv.weight.dtype in _DTYPE_CODE)
     except (AttributeError, TypeError, ValueError):
         return False
@@ -230,8 +256,14 @@ def install_vae_blocks(model: nn.Module, convs: bool = True, norms: bool = True)
                         n_convs += 2
                     except (NotImplementedError, AttributeError):
                         pass
+                elif type(child).__name__ == "Downsample3D":
+                    try:
+                        setattr(parent, name, Downsample3DB200.from_reference(child))
+                        n_convs += 1
+                    except (NotImplementedError, AttributeError):
+                        pass
         for parent in list(model.modules()):
-            if isinstance(parent, (ResnetBlock3DB200, CausalConv3dB200, Upsample3DB200)):
+            if isinstance(parent, (ResnetBlock3DB200, CausalConv3dB200, Upsample3DB200, Downsample3DB200)):
                 continue
             for name, child in list(parent.named_children()):
                 pointwise = type(child) is nn.Conv3d and tuple(child.kernel_size) == (1, 1, 1) and tuple(child.padding) == (0, 0, 0)

@@ -127,14 +127,48 @@ def causal_conv3d(x: torch.Tensor, weight_packed: torch.Tensor, bias: Optional[t
     return y
 
 
+def causal_conv3d_down(x: torch.Tensor, weight_packed: torch.Tensor, bias: Optional[torch.Tensor] = None,
+                       head: Optional[torch.Tensor] = None, pad_hw: int = 1) -> torch.Tensor:
+    """The encoder's down-sampling convolution: x [T, H, W, C_in] -> [T', H', W', C_out], kernel (kt, 3, 3), stride (2 if kt == 3 else
+    1, 2, 2), ``pad_hw`` zero rows / columns after the last one (Downsample3D's pad (0, 1, 0, 1)); ``head`` [1 | 2, H, W, C_in] = the
+    previous temporal slice's memory (None: the first frame twice)."""
+    code = _DTYPE_CODE.get(x.dtype)
+    if code is None:
+        raise NotImplementedError(f"seedvr2_b200.vae_conv: fp16 or bf16 activations only (got {x.dtype})")
+    ops._need(x, "x", x.dtype)
+    ops._need(weight_packed, "weight_packed", x.dtype)
+    T, H, W, ci = x.shape
+    co, kt, kh, kw, ci_w = weight_packed.shape
+    if ci_w != ci or (kh, kw) != (3, 3) or kt not in (1, 3):
+        raise RuntimeError(f"seedvr2_b200.vae_conv: weight {tuple(weight_packed.shape)} is not a (1|3, 3, 3) kernel over {ci} channels")
+    hf = 0
+    if head is not None:
+        ops._need(head, "head", x.dtype)
+        hf = head.shape[0]
+        if kt != 3 or tuple(head.shape[1:]) != (H, W, ci):
+            raise RuntimeError(f"seedvr2_b200.vae_conv: head {tuple(head.shape)} does not fit")
+    if bias is not None:
+        ops._need(bias, "bias", x.dtype)
+    To = (T + (hf if head is not None else 2) - 3) // 2 + 1 if kt == 3 else T
+    Ho, Wo = (H + pad_hw - 3) // 2 + 1, (W + pad_hw - 3) // 2 + 1
+    y = torch.empty(max(To, 0), Ho, Wo, co, dtype=x.dtype, device=x.device)
+    ops._call("svr2_causal_conv3d_down_fwd", 1, x.device, _lib.lib().svr2_causal_conv3d_down_fwd, x.data_ptr(), ops._ptr(head), hf,
+              weight_packed.data_ptr(), ops._ptr(bias), y.data_ptr(), T, H, W, ci, co, kt, int(pad_hw), code, ops._stream(x))
+    return y
+
+
 class CausalConv3dB200(nn.Module):
     """Drop-in for a stride-1 ``InflatedCausalConv3d``; see the module docstring."""
 
-    def __init__(self, weight: torch.Tensor, bias: Optional[torch.Tensor]):
+    def __init__(self, weight: torch.Tensor, bias: Optional[torch.Tensor], stride=(1, 1, 1), pad_hw: int = 0):
         super().__init__()
         co, ci, kt, kh, kw = weight.shape
         if kh != kw or kt not in (1, 3) or kh not in (1, 3):
-            raise NotImplementedError(f"seedvr2_b200.vae_conv: kernel {(kt, kh, kw)} (temporal 1|3, spatial 1|3 square, stride 1)")
+            raise NotImplementedError(f"seedvr2_b200.vae_conv: kernel {(kt, kh, kw)} (temporal 1|3, spatial 1|3 square)")
+        stride = tuple(stride)
+        if stride != (1, 1, 1) and not (kh == 3 and stride == ((2 if kt == 3 else 1), 2, 2)):
+            raise NotImplementedError(f"seedvr2_b200.vae_conv: stride {stride} with kernel {(kt, kh, kw)} (1,1,1 or the down-samplers' (1|2, 2, 2))")
+        self.stride, self.pad_hw = stride, int(pad_hw)      # pad_hw: zero rows / columns after the last one, folded into the kernel
         self.in_channels, self.out_channels, self.kernel_size = ci, co, (kt, kh, kw)
         # the kernel's K step is 64 input channels and its N tile 128 output channels: the VAE's boundary convolutions (conv_in
         # 16 -> 512, conv_out 128 -> 3) run with zero-padded channels — zero weights, zero inputs, the extra outputs dropped
@@ -152,9 +186,11 @@ class CausalConv3dB200(nn.Module):
 
     @classmethod
     def from_reference(cls, conv: nn.Module) -> "CausalConv3dB200":
-        if tuple(conv.stride) != (1, 1, 1) or tuple(conv.dilation) != (1, 1, 1) or conv.groups != 1:
-            raise NotImplementedError("seedvr2_b200.vae_conv: stride-1, undilated, ungrouped convolutions only")
-        return cls(conv.weight, conv.bias)
+        if tuple(conv.dilation) != (1, 1, 1) or conv.groups != 1:
+            raise NotImplementedError("seedvr2_b200.vae_conv: undilated, ungrouped convolutions only")
+        if tuple(conv.stride) != (1, 1, 1) and tuple(conv.padding)[1:] != (0, 0):
+            raise NotImplementedError("seedvr2_b200.vae_conv: strided convolutions without spatial padding only (Downsample3D pads itself)")
+        return cls(conv.weight, conv.bias, tuple(conv.stride))
 
     def set_memory_limit(self, value: float) -> None:      # causal_inflation_lib.py:77-78: no workspace to bound here
         pass
@@ -195,6 +231,8 @@ class CausalConv3dB200(nn.Module):
         if state != "ACTIVE":
             self.memory = None                                                  # :216-217
         kt = self.kernel_size[0]
+        if self.stride != (1, 1, 1):
+            return self._forward_strided(xs, state, resid)
         head = self.memory if kt > 1 else None                                  # [B, kt - 1, H, W, C] or None (first frame repeated)
         if resid is not None and self.co_pad != self.out_channels:
             raise NotImplementedError("seedvr2_b200.vae_conv: a residual on a convolution with padded output channels")
@@ -220,4 +258,22 @@ class CausalConv3dB200(nn.Module):
                 head = head if head.is_contiguous() else head.contiguous()
         if kt > 1 and state != "DISABLED":
             self.memory = head.clone()                                          # basic_forward :229-240, slicing_forward :273-283
+        return ys
+
+    def _forward_strided(self, xs, state: str, resid):
+        """Down-sampler form: kernel (kt, 3, 3), stride (kt == 3 ? 2 : 1, 2, 2); the memory is the last kernel_t - stride_t = 1 input
+        frame (slicing_forward :262, :273-283)."""
+        if resid is not None or self.ci_pad != self.in_channels or self.co_pad != self.out_channels:
+            raise NotImplementedError("seedvr2_b200.vae_conv: strided convolutions take unpadded channels and no residual")
+        kt = self.kernel_size[0]
+        head = self.memory if kt > 1 else None
+        ys = []
+        for x in xs:
+            outs = [causal_conv3d_down(x[b], self.weight_packed, self.bias, None if head is None else head[b], self.pad_hw)
+                    for b in range(x.shape[0])]
+            ys.append(torch.stack(outs, 0))
+            if kt > 1 and x.shape[1] >= 1:
+                head = x[:, -1:]
+        if kt > 1 and state != "DISABLED" and head is not None:
+            self.memory = head.clone()
         return ys

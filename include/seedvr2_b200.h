@@ -374,6 +374,16 @@ int svr2_causal_conv3d_fwd(const void* x, const void* head, const void* weight_p
  * filled by the call; hand them to svr2_groupnorm_silu_fwd (have_partials = svr2_conv3d_gn_slots()), whose statistics pass is
  * then skipped.  c_out in {128, 256, 512}. */
 int svr2_conv3d_gn_slots(void);
+/*
+ * The encoder's down-sampling convolution: Downsample3D (attn_video_vae.py:176-246) = zero rows / columns after the last one
+ * (`pad (0, 1, 0, 1)`, :239-241; pad_hw = 1 — or 0 if the caller has padded already) + InflatedCausalConv3d with kernel (kt, 3, 3), stride
+ * (kt == 3 ? 2 : 1, 2, 2), no spatial padding.  x [T, H, W, c_in] -> y [T', H', W', c_out], H' = (H + pad_hw - 3) / 2 + 1 (W' alike),
+ * T' = (T + head - 3) / 2 + 1 for kt == 3, where head = 2 copies of the first frame (head == NULL, first temporal slice) or the
+ * head_frames (= kernel_t - stride_t = 1) frames the previous slice left in `memory`.  Each tap's input is one TMA box with element
+ * strides 2; the padding is the unit's zero fill.
+ */
+int svr2_causal_conv3d_down_fwd(const void* x, const void* head, int head_frames, const void* weight_packed, const void* bias, void* y,
+                                int T, int H, int W, int c_in, int c_out, int kt, int pad_hw, int dtype, void* stream);
 
 /*
  * The VAE's per-frame GroupNorm (+ SiLU): causal_norm_wrapper folds time into the batch before nn.GroupNorm

@@ -26,3 +26,20 @@ def causal_conv3d(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Te
     y = F.conv3d(xx, weight, bias, stride=1, padding=(0, kh // 2, kw // 2))
     new_memory = xx[:, :, -(kt - 1):].detach() if kt > 1 else None
     return y, new_memory
+
+
+def causal_conv3d_down(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor], memory: Optional[torch.Tensor] = None,
+                       pad_hw: int = 1) -> Tuple[torch.Tensor, Optional[torch.Tensor]]:
+    """Downsample3D.forward (attn_video_vae.py:228-246) as the encoder builds it: zero row / column after the last one
+    (`pad (0, 1, 0, 1)`, :239-241), then InflatedCausalConv3d with kernel (kt, 3, 3), stride (2 if kt == 3 else 1, 2, 2), no spatial
+    padding; the causal head is two copies of the first frame (times = temporal_padding * 2, causal_inflation_lib.py:265) or the
+    memory, which is the last kernel_t - stride_t = 1 input frame (:262, :273-283).  Returns (y, new memory)."""
+    kt = weight.shape[2]
+    st = 2 if kt == 3 else 1
+    if kt > 1:
+        head = memory.to(x) if memory is not None else x[:, :, :1].repeat(1, 1, 2, 1, 1)
+        xx = torch.cat((head, x), dim=2)
+    else:
+        xx = x
+    y = F.conv3d(F.pad(xx, (0, pad_hw, 0, pad_hw)), weight, bias, stride=(st, 2, 2))
+    return y, (xx[:, :, -1:].detach() if kt > 1 else None)

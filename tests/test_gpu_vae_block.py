@@ -302,3 +302,35 @@ def test_whole_decoder_standin_psnr(svr2, cuda):
     m = m / torch.cat(outs_r, 2).float().abs().max()
     psnr = float(10 * torch.log10(4.0 / (r - m).pow(2).mean()))
     assert psnr >= 45.0, psnr
+
+
+@pytest.mark.parametrize("temporal", [False, True], ids=["spatial", "spatial+temporal"])
+@pytest.mark.parametrize("c,hw", [(128, (37, 50)), (256, (40, 56)), (512, (17, 33))], ids=["128ch_odd", "256ch_even", "512ch_small"])
+def test_downsampler_mirror(svr2, cuda, temporal, c, hw):
+    """The encoder's Downsample3D from the reference's parts (F.pad + the real strided InflatedCausalConv3d through cuDNN) against the
+    mirror (one strided TMA box per tap, the padding as zero fill) over three temporal slices, against the fp32 oracle."""
+    if not refstage.available():
+        pytest.skip("reference not staged")
+    from oracle import vae_conv as ovc
+    from vae_standins import Downsample3D, reference_parts
+    _, _, _, MemoryState = reference_parts()
+    torch.manual_seed(c)
+    ref = Downsample3D(c, temporal_down=temporal).eval().cuda().half()
+    holder = nn.Sequential(ref)
+    assert svr2.vae_block.install_vae_blocks(holder) == (0, 1)
+    mine = holder[0]
+    assert isinstance(mine, svr2.vae_block.Downsample3DB200)
+    H, W = hw
+    x = torch.randn(1, c, 11, H, W, device=cuda).half()
+    with torch.no_grad():
+        mem, outs_r, outs_m, outs_o = None, [], [], []
+        for i, (a, b) in enumerate(((0, 5), (5, 9), (9, 11))):
+            st = MemoryState.INITIALIZING if i == 0 else MemoryState.ACTIVE
+            outs_r.append(ref(x[:, :, a:b].contiguous(), memory_state=st))
+            outs_m.append(mine(x[:, :, a:b].contiguous(), memory_state=st))
+            o, mem = ovc.causal_conv3d_down(x[:, :, a:b].float(), ref.conv.weight.float(), ref.conv.bias.float(), mem)
+            outs_o.append(o)
+        r, m, o = torch.cat(outs_r, 2).float(), torch.cat(outs_m, 2).float(), torch.cat(outs_o, 2)
+    assert m.shape == r.shape == o.shape == (1, c, 6 if temporal else 11, (H - 2) // 2 + 1, (W - 2) // 2 + 1)
+    e_ref, e_mine = float((r - o).abs().max()), float((m - o).abs().max())
+    assert e_mine <= max(1.05 * e_ref, 2.0 ** -11 * float(o.abs().max()) * 1.01), (e_mine, e_ref)

@@ -211,3 +211,34 @@ def test_vae_conv_oracle_matches_reference_module():
                 assert torch.allclose(torch.cat(outs_ref, 2), torch.cat(outs_got, 2), atol=2e-6, rtol=0)
                 # and slicing changes nothing: the streamed result is the one-shot result
                 assert torch.allclose(torch.cat(outs_got, 2), got, atol=2e-6, rtol=0)
+
+
+def test_vae_downsample_oracle_matches_reference_module():
+    """oracle/vae_conv.causal_conv3d_down against the reference's strided InflatedCausalConv3d behind Downsample3D's padding
+    (attn_video_vae.py:239-245), CPU: spatial and spatial + temporal down-sampling, streamed slices of 5, 4 and 2 frames."""
+    import torch
+    import torch.nn.functional as F
+    from oracle import refstage, vae_conv as ovc
+    if not refstage.available():
+        pytest.skip("reference not staged")
+    refstage.activate()
+    from src.models.video_vae_v3.modules.causal_inflation_lib import init_causal_conv3d
+    from src.models.video_vae_v3.modules.types import MemoryState
+    torch.manual_seed(6)
+    for temporal in (False, True):
+        tk, tr = (3, 2) if temporal else (1, 1)
+        conv = init_causal_conv3d(8, 12, kernel_size=(tk, 3, 3), stride=(tr, 2, 2), padding=(1 if temporal else 0, 0, 0),
+                                  inflation_mode="tail").eval()
+        x = torch.randn(1, 8, 11, 9, 12)
+        with torch.no_grad():
+            mem, outs_r, outs_o = None, [], []
+            for i, (a, b) in enumerate(((0, 5), (5, 9), (9, 11))):
+                st = MemoryState.INITIALIZING if i == 0 else MemoryState.ACTIVE
+                outs_r.append(conv(F.pad(x[:, :, a:b], (0, 1, 0, 1)), memory_state=st))
+                y, mem = ovc.causal_conv3d_down(x[:, :, a:b], conv.weight, conv.bias, mem)
+                outs_o.append(y)
+                if temporal:
+                    assert torch.equal(conv.memory, F.pad(mem, (0, 1, 0, 1)))
+            r, o = torch.cat(outs_r, 2), torch.cat(outs_o, 2)
+            assert r.shape == o.shape == (1, 12, 6 if temporal else 11, 4, 6)
+            assert torch.allclose(r, o, atol=2e-6, rtol=0)

@@ -137,3 +137,20 @@ class Decoder3D(nn.Module):
                 sample = up(sample, memory_state=memory_state)
         sample = self.conv_act(lib.causal_norm_wrapper(self.conv_norm_out, sample))
         return self.conv_out(sample, memory_state=memory_state)
+
+
+class Downsample3D(nn.Module):
+    """Downsample3D.forward (attn_video_vae.py:228-246) as the encoder builds it (`name="op"`, padding 0, convolution)."""
+
+    def __init__(self, channels, temporal_down=False):
+        super().__init__()
+        init_causal_conv3d, _, _, _ = reference_parts()
+        self.channels, self.out_channels, self.use_conv, self.padding, self.norm = channels, channels, True, 0, None
+        self.spatial_down, self.temporal_down = True, temporal_down
+        tk, tr = (3, 2) if temporal_down else (1, 1)
+        self.conv = init_causal_conv3d(channels, channels, kernel_size=(tk, 3, 3), stride=(tr, 2, 2),
+                                       padding=(1 if temporal_down else 0, 0, 0), inflation_mode="tail")
+
+    def forward(self, hidden_states, memory_state=None):
+        hidden_states = torch.nn.functional.pad(hidden_states, (0, 1, 0, 1), mode="constant", value=0)
+        return self.conv(hidden_states, memory_state=memory_state)
