@@ -154,3 +154,37 @@ class Downsample3D(nn.Module):
     def forward(self, hidden_states, memory_state=None):
         hidden_states = torch.nn.functional.pad(hidden_states, (0, 1, 0, 1), mode="constant", value=0)
         return self.conv(hidden_states, memory_state=memory_state)
+
+
+class Encoder3D(nn.Module):
+    """Encoder3D.forward (attn_video_vae.py:700-870) for the product VAE (3 -> 128 / 256 / 512 / 512, two residual blocks per down block,
+    spatial down-sampling after blocks 0-2, temporal as well after blocks 1-2, double-z output) WITHOUT the mid block's attention layer."""
+
+    def __init__(self, ch=(128, 256, 512, 512), latent=16):
+        super().__init__()
+        init_causal_conv3d, _, _, _ = reference_parts()
+        self.conv_in = init_causal_conv3d(3, ch[0], kernel_size=3, stride=1, padding=1, inflation_mode="tail")
+        self.down_resnets = nn.ModuleList()
+        self.down_samplers = nn.ModuleList()
+        prev = ch[0]
+        for i, c in enumerate(ch):
+            self.down_resnets.append(nn.ModuleList([ResnetBlock3D(prev if j == 0 else c, c) for j in range(2)]))
+            self.down_samplers.append(Downsample3D(c, temporal_down=i >= 1) if i < len(ch) - 1 else nn.Identity())
+            prev = c
+        self.mid = nn.ModuleList([ResnetBlock3D(ch[-1], ch[-1]), ResnetBlock3D(ch[-1], ch[-1])])
+        self.conv_norm_out = nn.GroupNorm(32, ch[-1], eps=1e-6)
+        self.conv_act = nn.SiLU()
+        self.conv_out = init_causal_conv3d(ch[-1], 2 * latent, 3, padding=1, inflation_mode="tail")
+
+    def forward(self, sample, memory_state=None):
+        import src.models.video_vae_v3.modules.causal_inflation_lib as lib
+        sample = self.conv_in(sample, memory_state=memory_state)
+        for resnets, down in zip(self.down_resnets, self.down_samplers):
+            for r in resnets:
+                sample = r(sample, temb=None, memory_state=memory_state)
+            if not isinstance(down, nn.Identity):
+                sample = down(sample, memory_state=memory_state)
+        for r in self.mid:
+            sample = r(sample, temb=None, memory_state=memory_state)
+        sample = self.conv_act(lib.causal_norm_wrapper(self.conv_norm_out, sample))
+        return self.conv_out(sample, memory_state=memory_state)
