@@ -427,6 +427,7 @@ class Job:
 
 def vae_block_sample(svr2, dev):
     """ms and TFLOP/s of one VAE residual block (ResnetBlock3D, attn_video_vae.py:253-361) through vae_block.ResnetBlock3DB200."""
+    import torch
     ci = co = 128
     T, H, W = 5, 1080, 1920
 
