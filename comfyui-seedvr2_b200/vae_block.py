@@ -143,8 +143,6 @@ class Upsample3DB200(nn.Module):
     def forward(self, hidden_states: torch.Tensor, output_size=None, memory_state="DISABLED", **kwargs):
         from .vae_conv import _state_name
         x = to_channels_last(hidden_states)                          # [B, T, H, W, C]
-        if x.shape[0] != 1:
-            raise NotImplementedError("seedvr2_b200.vae_block: the up-sampler mirror takes batch 1 (the VAE decodes one clip at a time)")
         T = x.shape[1]
         pieces = [x[:, :T // 2], x[:, T // 2:]] if self.slicing else [x]          # :126-133
         first = _state_name(memory_state) != "ACTIVE"
@@ -152,9 +150,11 @@ class Upsample3DB200(nn.Module):
         for i, piece in enumerate(pieces):
             if piece.shape[1] == 0:
                 continue
-            t = self.upscale_conv.forward_cl(piece.contiguous(), "DISABLED")       # [1, t, H, W, r C]
+            t = self.upscale_conv.forward_cl(piece.contiguous(), "DISABLED")       # [B, t, H, W, r C]
             drop = self.temporal_up and first and i == 0                           # remove_head, :151-153
-            ups.append(pixel_shuffle3d(t[0], self.channels, self.spatial_ratio, self.temporal_ratio, drop)[None])
+            ups.append(torch.stack([pixel_shuffle3d(t[b], self.channels, self.spatial_ratio, self.temporal_ratio, drop)
+                                    for b in range(t.shape[0])], 0) if t.shape[0] > 1 else
+                       pixel_shuffle3d(t[0], self.channels, self.spatial_ratio, self.temporal_ratio, drop)[None])
         ys = self.conv._forward_pieces(ups, memory_state)
         y = ys[0] if len(ys) == 1 else torch.cat(ys, dim=1)
         return y.permute(0, 4, 1, 2, 3)

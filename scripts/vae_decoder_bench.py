@@ -22,6 +22,7 @@ torch.manual_seed(0)
 ref = Decoder3D().eval().to(dev).half()
 mine = copy.deepcopy(ref)
 installed = svr2.vae_block.install_vae_blocks(mine)
+mine.use_rebound_norm = True
 z = [(torch.randn(1, 16, lat, 135, 240, device=dev)).half() for _ in range(n_slices)]
 
 

@@ -20,6 +20,7 @@ torch.manual_seed(0)
 ref = DecoderTop(512, 256, 128, slicing=False).eval().to(dev).half()
 mine = copy.deepcopy(ref)
 n_blocks, n_convs = svr2.vae_block.install_vae_blocks(mine)
+mine.use_rebound_norm = True
 x = (torch.randn(1, 512, T, 540, 960, device=dev) * 0.5).half()
 
 

@@ -21,6 +21,7 @@ torch.manual_seed(0)
 ref = Encoder3D().eval().to(dev).half()
 mine = copy.deepcopy(ref)
 installed = svr2.vae_block.install_vae_blocks(mine)
+mine.use_rebound_norm = True
 xs = [torch.randn(1, 3, 4 * n + (1 if i == 0 else 0), 1080, 1920, device=dev).half() for i in range(n_slices)]
 
 

@@ -222,6 +222,7 @@ def test_decoder_top_half_with_installed_modules(svr2, cuda, slicing):
     ref = DecoderTop(128, 128, 128, slicing=slicing).eval().cuda().half()      # narrow: the test is about wiring, not width
     mine = copy.deepcopy(ref)
     n_blocks, n_convs = svr2.vae_block.install_vae_blocks(mine)
+    mine.use_rebound_norm = True
     assert (n_blocks, n_convs) == (6, 3)                                      # expansion, up-sampler convolution, conv_out
     x = torch.randn(1, 128, 6, 24, 40, device=cuda).half()
     with torch.no_grad():
@@ -288,6 +289,7 @@ def test_whole_decoder_standin_psnr(svr2, cuda):
     ref = Decoder3D(16, (128, 128, 128, 128)).eval().cuda().half()
     mine = copy.deepcopy(ref)
     n_blocks, n_convs = svr2.vae_block.install_vae_blocks(mine)
+    mine.use_rebound_norm = True
     assert (n_blocks, n_convs) == (14, 8)            # 2 mid + 12 up blocks; conv_in, 3 up-samplers x 2, conv_out
     zs = [torch.randn(1, 16, t, 9, 12, device=cuda).half() for t in (1, 2, 1)]
     with torch.no_grad():
@@ -334,3 +336,31 @@ def test_downsampler_mirror(svr2, cuda, temporal, c, hw):
     assert m.shape == r.shape == o.shape == (1, c, 6 if temporal else 11, (H - 2) // 2 + 1, (W - 2) // 2 + 1)
     e_ref, e_mine = float((r - o).abs().max()), float((m - o).abs().max())
     assert e_mine <= max(1.05 * e_ref, 2.0 ** -11 * float(o.abs().max()) * 1.01), (e_mine, e_ref)
+
+
+def test_causal_norm_wrapper_rebinding(svr2, cuda):
+    """patch_causal_norm_wrapper rebinds the reference module's global; the replacement equals the original on a 5-D fp16 GroupNorm
+    (within ATen-vs-ours rounding flips), defers everything else to it, and is idempotent."""
+    if not refstage.available():
+        pytest.skip("reference not staged")
+    refstage.activate()
+    import src.models.video_vae_v3.modules.causal_inflation_lib as lib
+    svr2.vae_block.patch_causal_norm_wrapper()
+    assert svr2.vae_block.patch_causal_norm_wrapper() == 0                     # already rebound
+    fn, orig = lib.causal_norm_wrapper, lib.causal_norm_wrapper._svr2_original
+    assert fn is not orig
+    gn = nn.GroupNorm(32, 128, eps=1e-6).cuda().half()
+    nn.init.normal_(gn.weight, 1.0, 0.2)
+    nn.init.normal_(gn.bias, 0.0, 0.2)
+    x = torch.randn(2, 128, 3, 20, 24, device=cuda).half()
+    with torch.no_grad():
+        a, b = fn(gn, x), orig(gn, x)
+        assert a.shape == b.shape
+        d = (a.float() - b.float()).abs()
+        assert float((d > 0).float().mean()) < 0.05 and bool((d <= 2.0 ** -10 * 1.01 * b.float().abs() + 1e-6 * (1 + x.float().abs())).all())
+        # everything else goes to the original: fp32 input, LayerNorm
+        x32 = x.float()
+        gn32 = nn.GroupNorm(32, 128).cuda()
+        assert torch.equal(fn(gn32, x32), orig(gn32, x32))
+        ln = nn.LayerNorm(128).cuda().half()
+        assert torch.equal(fn(ln, x), orig(ln, x))

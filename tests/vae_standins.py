@@ -10,7 +10,20 @@ def reference_parts():
     refstage.activate()
     from src.models.video_vae_v3.modules.causal_inflation_lib import causal_norm_wrapper, init_causal_conv3d, remove_head
     from src.models.video_vae_v3.modules.types import MemoryState
-    return init_causal_conv3d, causal_norm_wrapper, remove_head, MemoryState
+    # the reference's own function, also after install_vae_blocks() has rebound the module global (the reference arm of a
+    # comparison must not run this library's GroupNorm)
+    return init_causal_conv3d, getattr(causal_norm_wrapper, "_svr2_original", causal_norm_wrapper), remove_head, MemoryState
+
+
+def output_norm(module, sample):
+    """`causal_norm_wrapper(self.conv_norm_out, sample)` as attn_video_vae.py calls it — through the module global, which
+    install_vae_blocks() rebinds.  `module.use_rebound_norm` (set on the arm that had install_vae_blocks applied) selects the
+    rebound function; the reference arm keeps the original even when both arms live in one process."""
+    import src.models.video_vae_v3.modules.causal_inflation_lib as lib
+    fn = lib.causal_norm_wrapper
+    if not getattr(module, "use_rebound_norm", False):
+        fn = getattr(fn, "_svr2_original", fn)
+    return fn(module.conv_norm_out, sample)
 
 
 class ResnetBlock3D(nn.Module):
@@ -98,9 +111,7 @@ class DecoderTop(nn.Module):
         sample = self.up2_sampler(sample, memory_state=memory_state)
         for r in self.up3:
             sample = self.temporal(r(sample, temb=None, memory_state=memory_state))
-        # attn_video_vae.py calls the name it imported from causal_inflation_lib: looked up at call time, like a module global
-        import src.models.video_vae_v3.modules.causal_inflation_lib as lib
-        sample = self.conv_act(lib.causal_norm_wrapper(self.conv_norm_out, sample))
+        sample = self.conv_act(output_norm(self, sample))
         return self.conv_out(sample, memory_state=memory_state)
 
 
@@ -126,7 +137,6 @@ class Decoder3D(nn.Module):
         self.conv_out = init_causal_conv3d(ch[-1], 3, 3, padding=1, inflation_mode="tail")
 
     def forward(self, sample, memory_state=None):
-        import src.models.video_vae_v3.modules.causal_inflation_lib as lib
         sample = self.conv_in(sample, memory_state=memory_state)
         for r in self.mid:
             sample = r(sample, temb=None, memory_state=memory_state)
@@ -135,7 +145,7 @@ class Decoder3D(nn.Module):
                 sample = r(sample, temb=None, memory_state=memory_state)
             if not isinstance(up, nn.Identity):
                 sample = up(sample, memory_state=memory_state)
-        sample = self.conv_act(lib.causal_norm_wrapper(self.conv_norm_out, sample))
+        sample = self.conv_act(output_norm(self, sample))
         return self.conv_out(sample, memory_state=memory_state)
 
 
@@ -177,7 +187,6 @@ class Encoder3D(nn.Module):
         self.conv_out = init_causal_conv3d(ch[-1], 2 * latent, 3, padding=1, inflation_mode="tail")
 
     def forward(self, sample, memory_state=None):
-        import src.models.video_vae_v3.modules.causal_inflation_lib as lib
         sample = self.conv_in(sample, memory_state=memory_state)
         for resnets, down in zip(self.down_resnets, self.down_samplers):
             for r in resnets:
@@ -186,5 +195,5 @@ class Encoder3D(nn.Module):
                 sample = down(sample, memory_state=memory_state)
         for r in self.mid:
             sample = r(sample, temb=None, memory_state=memory_state)
-        sample = self.conv_act(lib.causal_norm_wrapper(self.conv_norm_out, sample))
+        sample = self.conv_act(output_norm(self, sample))
         return self.conv_out(sample, memory_state=memory_state)
