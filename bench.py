@@ -457,6 +457,43 @@ def vae_block_sample(svr2, dev):
             "inputs": "5.3 GB activations per call, larger than L2"}
 
 
+def vae_decoder_sample(svr2, dev):
+    """The VAE decoder at 1080p through install_vae_blocks(): Decoder3D.forward composed from the reference's real modules (staged copy,
+    tests/vae_standins.py; no mid-block attention layer), product widths, latent 135 x 240, two temporal slices (1 + 4 output frames)."""
+    import torch
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from oracle import refstage
+    if not refstage.available():
+        return {"unavailable": "reference modules not staged (baseline/_ref)"}
+    import contextlib
+    with contextlib.redirect_stdout(sys.stderr):      # the reference prints a memory banner on import; stdout carries ONE JSON line
+        from vae_standins import Decoder3D, reference_parts
+        _, _, _, MemoryState = reference_parts()
+        torch.manual_seed(0)
+        dec = Decoder3D().eval().to(dev).half()
+    installed = svr2.vae_block.install_vae_blocks(dec)
+    dec.use_rebound_norm = True
+    zs = [torch.randn(1, 16, 1, 135, 240, device=dev).half() for _ in range(2)]
+
+    def run():
+        return [dec(z, memory_state=MemoryState.INITIALIZING if i == 0 else MemoryState.ACTIVE) for i, z in enumerate(zs)]
+    with torch.no_grad():
+        outs = run()
+        frames = sum(o.shape[2] for o in outs)
+        del outs
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        n = 3
+        e0.record()
+        for _ in range(n):
+            run()
+        e1.record()
+        torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / n
+    return {"ms_per_frame": ms / frames, "frames_per_s": frames / (ms * 1e-3), "output_frames": frames, "dtype": "f16",
+            "modules_replaced": list(installed), "reference_same_gpu": "profiles/r02_run37-43_vae_decoder_encoder_1080p.jsonl (153-274 ms per frame)"}
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -575,10 +612,12 @@ def run_ours(args):
     # ---- SURVEY §8f N3 beside the headline: one residual block of the VAE decoder's top level (128 channels at 1080 x 1920, 5
     # frames, fp16) — GroupNorm + SiLU, two causal 3-D convolutions, fused residual; reported, not part of `value`
     if also is not None and world == 1:
-        try:
-            also["vae_resnet_block_1080p"] = vae_block_sample(svr2, dev)
-        except Exception as e:      # noqa: BLE001 — a side measurement must not take the headline down
-            also["vae_resnet_block_1080p"] = {"error": f"{type(e).__name__}: {e}"[:200]}
+        for key, fn in (("vae_resnet_block_1080p", vae_block_sample), ("vae_decoder_1080p", vae_decoder_sample)):
+            try:
+                torch.cuda.empty_cache()
+                also[key] = fn(svr2, dev)
+            except Exception as e:      # noqa: BLE001 — a side measurement must not take the headline down
+                also[key] = {"error": f"{type(e).__name__}: {e}"[:200]}
 
     pk, pk_src = peaks()
     attn_flops_step = job.attention_flops(svr2, heads)

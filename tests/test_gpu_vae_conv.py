@@ -204,3 +204,20 @@ def test_layout_transposes(svr2, cuda, shape):
     assert back.is_contiguous() and torch.equal(back, x)
     k = min(3, shape[1])
     assert torch.equal(svr2.vae_conv.to_ncdhw(cl, k), x[:, :k].contiguous())                                # conv_out's channel slice
+
+
+def test_kernels_match_golden_vectors_of_the_real_module(svr2, cuda):
+    """tests/golden/vae_conv.pt — outputs of the real InflatedCausalConv3d (fp32 CPU) over streamed slices, stride 1 and the
+    down-samplers' strides — against the CUDA kernels in fp16 through the module mirrors, memories carried by the mirrors."""
+    import os
+    gold = torch.load(os.path.join(os.path.dirname(__file__), "golden", "vae_conv.pt"))
+    for name, c in gold.items():
+        w, b, x = c["weight"].cuda(), c["bias"].cuda(), c["x"].cuda()
+        mine = svr2.vae_conv.CausalConv3dB200(w, b, tuple(c["stride"]), pad_hw=c["pad_hw"])
+        for i, ((a, e), y_ref) in enumerate(zip(c["slices"], c["y"])):
+            y = mine(x[:, :, a:e].contiguous(), "INITIALIZING" if i == 0 else "ACTIVE")
+            y_ref = y_ref.cuda()
+            assert y.shape == y_ref.shape, name
+            d = (y.float() - y_ref).abs()
+            lim = 2.0 ** -11 * 1.01 * y_ref.abs() + 3e-6 * 40 + 1e-7          # sum |w||x| <~ 40 at these sizes
+            assert bool((d <= lim).all()), (name, i, float(d.max()))

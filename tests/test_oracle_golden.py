@@ -242,3 +242,24 @@ def test_vae_downsample_oracle_matches_reference_module():
             r, o = torch.cat(outs_r, 2), torch.cat(outs_o, 2)
             assert r.shape == o.shape == (1, 12, 6 if temporal else 11, 4, 6)
             assert torch.allclose(r, o, atol=2e-6, rtol=0)
+
+
+def test_vae_conv_oracle_matches_golden_vectors():
+    """oracle/vae_conv.py against tests/golden/vae_conv.pt (outputs and memories of the real InflatedCausalConv3d, fp32 CPU, made by
+    tests/golden/make_golden_vae.py): needs no reference checkout."""
+    import torch
+    from oracle import vae_conv as ovc
+    gold = torch.load(os.path.join(os.path.dirname(__file__), "golden", "vae_conv.pt"))
+    assert set(gold) == {"conv333", "conv133", "down_spatial", "down_temporal"}
+    for name, c in gold.items():
+        w, b, x = c["weight"].float(), c["bias"].float(), c["x"].float()
+        mem = None
+        for (a, e), y_ref, m_ref in zip(c["slices"], c["y"], c["memory"]):
+            if tuple(c["stride"]) == (1, 1, 1):
+                y, mem = ovc.causal_conv3d(x[:, :, a:e], w, b, mem)
+            else:
+                y, mem = ovc.causal_conv3d_down(x[:, :, a:e], w, b, mem, c["pad_hw"])
+            assert y.shape == y_ref.shape and torch.allclose(y, y_ref, atol=3e-6, rtol=0), name
+            if m_ref is not None:
+                # the strided module keeps its memory with Downsample3D's padding column / row attached
+                assert torch.equal(m_ref[..., :mem.shape[-2], :mem.shape[-1]], mem), name
