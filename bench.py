@@ -291,7 +291,7 @@ def run_reference(args):
         "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
     return 0
 
 
@@ -717,7 +717,7 @@ def run_ours(args):
                         "/".join(str(g.launches_per_replay) for g in job.graphs.values())) if use_graph else "kernel by kernel",
         "ms_per_step_kernel_by_kernel": ms_eager_total / steps_1b,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
     if world > 1:
         dist.destroy_process_group()
     return 0
@@ -781,9 +781,23 @@ def main():
     ap.add_argument("--no-also", action="store_true", help="skip the 121-frame side measurement of the default workload")
     ap.add_argument("--no-graph", action="store_true", help="launch the forwards kernel by kernel instead of replaying their CUDA graphs")
     args = ap.parse_args()
+    # stdout carries exactly ONE JSON line: everything else that writes to file descriptor 1 — Python prints of imported code, but
+    # also C libraries (NCCL prints its version banner there) — is sent to stderr; emit() writes the line to the real stdout
+    global _JSON_OUT
+    _JSON_OUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     if args.impl == "reference":
         return run_reference(args)
     return run_ours(args)
+
+
+_JSON_OUT = None
+
+
+def emit(line: dict) -> None:
+    out = _JSON_OUT if _JSON_OUT is not None else sys.stdout
+    out.write(json.dumps(line) + "\n")
+    out.flush()
 
 
 if __name__ == "__main__":
