@@ -1,11 +1,14 @@
-"""The video VAE's residual block on the B200: per-frame GroupNorm + SiLU as one fused pass, the two causal
-3-D convolutions as tcgen05 implicit GEMMs, the residual add in the second convolution's epilogue.
+"""The video VAE's modules on the B200.
 
-``ResnetBlock3DB200`` mirrors ``ResnetBlock3D`` (src/models/video_vae_v3/modules/attn_video_vae.py:253-361) as the VAE builds it
-(no time embedding, no sampler inside the block, SiLU, dropout 0): same ``forward(input_tensor, temb, memory_state)`` call, same
-memory bookkeeping through its convolutions.  ``install_vae_blocks(model)`` replaces every such block of a built VAE in place;
-up / down samplers, the mid-block attention and the 3- / 16-channel boundary convolutions stay the reference's.
-CUDA only — there is no other path."""
+* ``ResnetBlock3DB200`` mirrors ``ResnetBlock3D`` (src/models/video_vae_v3/modules/attn_video_vae.py:253-361) as the VAE builds it (no
+  time embedding, no sampler inside the block, SiLU, dropout 0): per-frame GroupNorm + SiLU as one fused pass, the two causal 3-D
+  convolutions as tcgen05 implicit GEMMs, the residual add and the next GroupNorm's statistics in the convolutions' epilogues.
+* ``Upsample3DB200`` / ``Downsample3DB200`` mirror the samplers (:58-175, :176-246): 1 x 1 x 1 expansion + pixel / time shuffle +
+  causal convolution; zero row / column + strided causal convolution.
+* ``make_causal_norm_wrapper`` / ``patch_causal_norm_wrapper`` put the stand-alone GroupNorms (conv_norm_out) on the same kernel.
+* ``install_vae_blocks(model)`` swaps all of it into a built VAE in place; the mid block's attention layer stays the reference's.
+Same forward signatures and memory bookkeeping (through the convolutions) as the modules they replace.  CUDA only — there is no other
+path."""
 from typing import Optional
 
 import torch

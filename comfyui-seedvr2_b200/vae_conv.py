@@ -1,11 +1,13 @@
-"""The video VAE's causal 3-D convolution on the B200 (first slice).
+"""The video VAE's causal 3-D convolutions on the B200.
 
-``CausalConv3dB200`` mirrors ``InflatedCausalConv3d`` (src/models/video_vae_v3/modules/causal_inflation_lib.py:61-272) for the
-stride-1 convolutions of the VAE's residual blocks: same constructor source (an existing module or its weight / bias), same
-``forward(input, memory_state)`` meaning — ``[B, C, T, H, W]`` in, ``[B, C_out, T, H, W]`` out, the causal head taken from the
-first frame or from the memory the previous temporal slice left behind — and the same memory bookkeeping (``self.memory`` holds the
-last ``kernel_t - 1`` input frames unless the state is DISABLED).  ``set_memory_limit`` is accepted and ignored: the reference
-splits the convolution spatially to bound cuDNN's workspace (:117-211); the implicit GEMM of csrc/conv3d.cu has no workspace.
+``CausalConv3dB200`` mirrors ``InflatedCausalConv3d`` (src/models/video_vae_v3/modules/causal_inflation_lib.py:61-303) for the
+VAE's convolutions — kernels (1|3, 1|3, 1|3) with stride 1 (residual blocks, up-samplers, conv_in / conv_out) and the
+down-samplers' (1|3, 3, 3) with stride (1|2, 2, 2): same constructor source (an existing module or its weight / bias), same
+``forward(input, memory_state)`` meaning — ``[B, C, T, H, W]`` (or a list of temporal pieces) in, ``[B, C_out, T', H', W']`` out, the
+causal head taken from the first frame or from the memory the previous temporal slice left behind — and the same memory
+bookkeeping (``self.memory`` holds the last ``kernel_t - stride_t`` input frames unless the state is DISABLED).
+``set_memory_limit`` is accepted and ignored: the reference splits the convolution spatially to bound cuDNN's workspace
+(:117-211); the implicit GEMM of csrc/conv3d.cu has no workspace.
 
 Tensors are kept channels-last (``torch.channels_last_3d``): a ``[B, C, T, H, W]`` tensor in that format is the kernel's
 ``[T, H, W, C]`` layout as it stands, and the result is returned as such a view, so a chain of these modules never transposes.
@@ -158,7 +160,7 @@ def causal_conv3d_down(x: torch.Tensor, weight_packed: torch.Tensor, bias: Optio
 
 
 class CausalConv3dB200(nn.Module):
-    """Drop-in for a stride-1 ``InflatedCausalConv3d``; see the module docstring."""
+    """Drop-in for the VAE's ``InflatedCausalConv3d``s; see the module docstring."""
 
     def __init__(self, weight: torch.Tensor, bias: Optional[torch.Tensor], stride=(1, 1, 1), pad_hw: int = 0):
         super().__init__()
@@ -271,7 +273,7 @@ class CausalConv3dB200(nn.Module):
         for x in xs:
             outs = [causal_conv3d_down(x[b], self.weight_packed, self.bias, None if head is None else head[b], self.pad_hw)
                     for b in range(x.shape[0])]
-            ys.append(torch.stack(outs, 0))
+            ys.append(outs[0][None] if len(outs) == 1 else torch.stack(outs, 0))
             if kt > 1 and x.shape[1] >= 1:
                 head = x[:, -1:]
         if kt > 1 and state != "DISABLED" and head is not None:
