@@ -221,3 +221,59 @@ def test_kernels_match_golden_vectors_of_the_real_module(svr2, cuda):
             d = (y.float() - y_ref).abs()
             lim = 2.0 ** -11 * 1.01 * y_ref.abs() + 3e-6 * 40 + 1e-7          # sum |w||x| <~ 40 at these sizes
             assert bool((d <= lim).all()), (name, i, float(d.max()))
+
+
+def test_no_writes_outside_the_outputs(svr2, cuda):
+    """Every N3 kernel writes into the middle of a guard-filled buffer (ragged shapes, so tiles hang over every edge): the guards
+    before and after the output stay untouched.  (compute-sanitizer is not available on the GPU pool.)"""
+    lib = svr2._lib.lib()
+    st = torch.cuda.current_stream().cuda_stream
+    GUARD = 4096
+
+    def guarded(n_elems, dtype):
+        buf = torch.full((n_elems + 2 * GUARD,), 7, dtype=torch.int16, device="cuda").view(dtype) if dtype != torch.float32 else \
+            torch.full((n_elems + 2 * GUARD,), 7.0, dtype=torch.float32, device="cuda")
+        return buf, buf[GUARD:GUARD + n_elems]
+
+    def check(buf, n_elems, what):
+        ref = torch.full((GUARD,), 7, dtype=torch.int16, device="cuda").view(buf.dtype) if buf.dtype != torch.float32 else \
+            torch.full((GUARD,), 7.0, device="cuda")
+        assert torch.equal(buf[:GUARD], ref) and torch.equal(buf[GUARD + n_elems:], ref), what
+
+    g = torch.Generator(device="cuda").manual_seed(2)
+    T, H, W, ci, co = 3, 21, 27, 128, 128
+    x = torch.randn(T, H, W, ci, generator=g, device="cuda").half()
+    wp = svr2.vae_conv.pack_conv_weight((torch.randn(co, ci, 3, 3, 3, generator=g, device="cuda") * 0.03).half())
+    b = torch.randn(co, generator=g, device="cuda").half()
+    # stride-1 convolution with statistics
+    ybuf, y = guarded(T * H * W * co, torch.float16)
+    pbuf, part = guarded(T * svr2.vae_conv.gn_slots() * 32 * 3, torch.float32)
+    svr2.vae_conv.causal_conv3d(x, wp, b, out=y.view(T, H, W, co), gn_partials=part.view(T, -1, 32, 3))
+    torch.cuda.synchronize()
+    check(ybuf, y.numel(), "conv output")
+    check(pbuf, part.numel(), "conv statistics")
+    # down-sampling convolution
+    To, Ho, Wo = (T + 2 - 3) // 2 + 1, (H + 1 - 3) // 2 + 1, (W + 1 - 3) // 2 + 1
+    dbuf, d = guarded(To * Ho * Wo * co, torch.float16)
+    svr2._lib.check(lib.svr2_causal_conv3d_down_fwd(x.data_ptr(), None, 0, wp.data_ptr(), b.data_ptr(), d.data_ptr(), T, H, W, ci, co, 3, 1, 2, st),
+                    "down")
+    torch.cuda.synchronize()
+    check(dbuf, d.numel(), "down-sampling convolution")
+    # GroupNorm (both activation paths write through the same indexing; the arithmetic one here)
+    gbuf, gy = guarded(T * H * W * co, torch.float16)
+    svr2.vae_block.groupnorm_silu(x, b, b, 32, 1e-6, out=gy.view(T, H, W, co))
+    torch.cuda.synchronize()
+    check(gbuf, gy.numel(), "groupnorm")
+    # transposes (aligned and scalar paths) and the pixel shuffle
+    for rows, cols in ((128, 21 * 27 * 3 - 5), (128, 1680), (24, 189)):
+        src = torch.randn(rows, cols, generator=g, device="cuda").half()
+        tbuf, t = guarded(rows * cols, torch.float16)
+        svr2._lib.check(lib.svr2_transpose_2b(src.data_ptr(), t.data_ptr(), rows, cols, cols, rows, 1, 0, 0, st), "transpose")
+        torch.cuda.synchronize()
+        check(tbuf, t.numel(), f"transpose {rows}x{cols}")
+        assert torch.equal(t.view(cols, rows), src.t().contiguous())
+    src = torch.randn(3, 5, 7, 8 * 64, generator=g, device="cuda").half()
+    sbuf, s = guarded(5 * 10 * 14 * 64, torch.float16)
+    svr2._lib.check(lib.svr2_pixel_shuffle3d_fwd(src.data_ptr(), s.data_ptr(), 3, 5, 7, 64, 2, 2, 1, st), "shuffle")
+    torch.cuda.synchronize()
+    check(sbuf, s.numel(), "pixel shuffle")
