@@ -221,6 +221,33 @@ def patch_causal_norm_wrapper() -> int:
     return n
 
 
+def clear_memory(model: nn.Module) -> int:
+    """Drop the temporal-slice memories of every swapped convolution (what VideoAutoencoderKL.slicing_encode / slicing_decode do for
+    ``InflatedCausalConv3d`` after the last slice, attn_video_vae.py:1261-1265, 1285-1289); returns how many held one."""
+    n = 0
+    for m in model.modules():
+        if isinstance(m, CausalConv3dB200) and m.memory is not None:
+            m.memory = None
+            n += 1
+    return n
+
+
+def _wrap_slicing(model: nn.Module) -> None:
+    """The reference clears its convolutions' memories by ``isinstance(m, InflatedCausalConv3d)`` at the end of slicing_encode /
+    slicing_decode; the swapped modules are not instances of that class, so the two methods are wrapped to clear theirs as well
+    (top-level feature maps of two frames per convolution would otherwise stay allocated until the next clip)."""
+    for name in ("slicing_encode", "slicing_decode"):
+        fn = getattr(model, name, None)
+        if callable(fn) and not getattr(fn, "_svr2_wrapped", False):
+            def wrapped(*args, _fn=fn, **kwargs):
+                try:
+                    return _fn(*args, **kwargs)
+                finally:
+                    clear_memory(model)
+            wrapped._svr2_wrapped = True
+            setattr(model, name, wrapped)
+
+
 def _conv_supported(conv: nn.Module) -> bool:
     try:
         kt, kh, kw = conv.kernel_size
@@ -241,6 +268,7 @@ def install_vae_blocks(model: nn.Module, convs: bool = True, norms: bool = True)
     n_blocks = n_convs = 0
     if norms:
         patch_causal_norm_wrapper()
+    _wrap_slicing(model)
     for parent in list(model.modules()):
         for name, child in list(parent.named_children()):
             if type(child).__name__ != "ResnetBlock3D":

@@ -364,3 +364,34 @@ def test_causal_norm_wrapper_rebinding(svr2, cuda):
         assert torch.equal(fn(gn32, x32), orig(gn32, x32))
         ln = nn.LayerNorm(128).cuda().half()
         assert torch.equal(fn(ln, x), orig(ln, x))
+
+
+def test_memories_are_cleared_after_the_last_slice(svr2, cuda):
+    """VideoAutoencoderKL.slicing_decode clears `InflatedCausalConv3d.memory` by isinstance after the last slice (attn_video_vae.py:
+    1285-1289); install_vae_blocks wraps the method so that the swapped convolutions drop theirs too."""
+    if not refstage.available():
+        pytest.skip("reference not staged")
+    from vae_standins import reference_parts
+    _, _, _, MemoryState = reference_parts()
+
+    class Vae(nn.Module):          # the two attributes of VideoAutoencoderKL that matter here
+        def __init__(self):
+            super().__init__()
+            self.decoder = nn.Sequential()
+            self.decoder.add_module("block", ResnetBlock3D(128, 128).eval().cuda().half())
+
+        def slicing_decode(self, z):
+            outs = [self.decoder.block(z[:, :, :3], memory_state=MemoryState.INITIALIZING),
+                    self.decoder.block(z[:, :, 3:], memory_state=MemoryState.ACTIVE)]
+            return torch.cat(outs, 2)
+
+    vae = Vae()
+    assert svr2.vae_block.install_vae_blocks(vae) == (1, 0)
+    z = torch.randn(1, 128, 5, 16, 16, device=cuda).half()
+    with torch.no_grad():
+        out = vae.slicing_decode(z)
+    assert out.shape == (1, 128, 5, 16, 16)
+    assert all(m.memory is None for m in vae.modules() if isinstance(m, svr2.vae_conv.CausalConv3dB200))
+    with torch.no_grad():          # while slicing, the memory is there
+        vae.decoder.block(z[:, :, :3], memory_state=MemoryState.INITIALIZING)
+    assert svr2.vae_block.clear_memory(vae) == 2
