@@ -239,7 +239,8 @@ class CausalConv3dB200(nn.Module):
         if resid is not None and self.co_pad != self.out_channels:
             raise NotImplementedError("seedvr2_b200.vae_conv: a residual on a convolution with padded output channels")
         ys = []
-        for x in xs:
+        fresh = False                  # `head` is a tensor of its own (not a view of a piece)
+        for i, x in enumerate(xs):
             B = x.shape[0]
             if self.ci_pad != self.in_channels:
                 xp = torch.zeros(*x.shape[:4], self.ci_pad, dtype=x.dtype, device=x.device)
@@ -250,16 +251,25 @@ class CausalConv3dB200(nn.Module):
                 causal_conv3d(x[b], self.weight_packed, self.bias, None if head is None else head[b],
                               None if resid is None else resid[b], out=y[b], gn_partials=gn_partials)
             ys.append(y)
-            if kt > 1:
+            if kt > 1 and (i + 1 < len(xs) or state != "DISABLED"):
                 # the last kt - 1 frames of (head, piece): the next piece's head (:286-296) and, at the end, the memory
-                if x.shape[1] >= kt - 1:
-                    head = x[:, -(kt - 1):]
-                else:
-                    prev = head if head is not None else x[:, :1].expand(-1, kt - 1, -1, -1, -1)
-                    head = torch.cat((prev, x), dim=1)[:, -(kt - 1):]
-                head = head if head.is_contiguous() else head.contiguous()
+                k = x.shape[1]
+                if k >= kt - 1:
+                    head, fresh = x[:, -(kt - 1):], False
+                    if not head.is_contiguous():
+                        head, fresh = head.contiguous(), True
+                elif k > 0:
+                    # a piece shorter than the head (the one-frame first slice of every clip): shift the old head, append the piece
+                    nh = torch.empty(B, kt - 1, *x.shape[2:], dtype=x.dtype, device=x.device)
+                    if head is not None:
+                        nh[:, :kt - 1 - k] = head[:, k:]
+                    else:
+                        nh[:, :kt - 1 - k] = x[:, :1]              # the replicated first frame (broadcast over the slot axis)
+                    nh[:, kt - 1 - k:] = x
+                    head, fresh = nh, True
         if kt > 1 and state != "DISABLED":
-            self.memory = head.clone()                                          # basic_forward :229-240, slicing_forward :273-283
+            # basic_forward :229-240, slicing_forward :273-283; a view of a piece is copied so the piece itself can be freed
+            self.memory = head if fresh else (None if head is None else head.clone())
         return ys
 
     def _forward_strided(self, xs, state: str, resid):
