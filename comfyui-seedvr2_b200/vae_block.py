@@ -83,10 +83,25 @@ class ResnetBlock3DB200(nn.Module):
         return cls(block.norm1, block.conv1, block.norm2, block.conv2, getattr(block, "conv_shortcut", None),
                    getattr(block, "output_scale_factor", 1.0))
 
+    def _norm_params(self, dtype: torch.dtype):
+        ps = (self.norm1_weight, self.norm1_bias, self.norm2_weight, self.norm2_bias)
+        if all(p is None or p.dtype == dtype for p in ps):
+            return ps
+        cache = self.__dict__.setdefault("_norm_cast", {})
+        hit = cache.get(dtype)
+        if hit is None or any(a is not None and a.device != b.device for a, b in zip(hit, ps)):
+            hit = tuple(None if p is None else p.to(dtype) for p in ps)
+            cache[dtype] = hit
+        return hit
+
     def forward(self, input_tensor: torch.Tensor, temb=None, memory_state="DISABLED", **kwargs) -> torch.Tensor:
         if temb is not None:
             raise NotImplementedError("seedvr2_b200.vae_block: the VAE calls its residual blocks with temb=None")
         x = to_channels_last(input_tensor)                           # [B, T, H, W, C]: no copy for channels_last_3d input
+        cd = self.conv1._compute_dtype()                             # the autocast dtype where the pipeline autocasts the VAE
+        if x.dtype != cd:
+            x = x.to(cd)
+        n1w, n1b, n2w, n2b = self._norm_params(cd)
         B = x.shape[0]
         # statistics of the input, if the block that produced it gathered them in its last convolution's epilogue
         st_in = getattr(input_tensor, "_svr2_gn_stats", None)
@@ -94,10 +109,10 @@ class ResnetBlock3DB200(nn.Module):
             st_in = None
         h = torch.empty_like(x)
         for b in range(B):
-            groupnorm_silu(x[b], self.norm1_weight, self.norm1_bias, self.groups1, self.eps1, out=h[b], stats=st_in)
+            groupnorm_silu(x[b], n1w, n1b, self.groups1, self.eps1, out=h[b], stats=st_in)
         h, st_h = self.conv1.forward_cl(h, memory_state, want_stats=self.groups2 == 32)
         for b in range(B):
-            groupnorm_silu(h[b], self.norm2_weight, self.norm2_bias, self.groups2, self.eps2, out=h[b], stats=st_h)      # in place
+            groupnorm_silu(h[b], n2w, n2b, self.groups2, self.eps2, out=h[b], stats=st_h)      # in place
         skip = x if self.conv_shortcut is None else self.conv_shortcut.forward_cl(x, memory_state)
         out, st_out = self.conv2.forward_cl(h, memory_state, resid=skip, want_stats=True)     # (input_tensor + hidden_states), :361
         if self.output_scale_factor != 1.0:
@@ -195,7 +210,7 @@ def make_causal_norm_wrapper(original):
         if (isinstance(norm_layer, nn.GroupNorm) and torch.is_tensor(x) and x.ndim == 5 and x.is_cuda and x.dtype in _DTYPE_CODE
                 and x.shape[1] % norm_layer.num_groups == 0 and x.shape[1] // norm_layer.num_groups in (2, 4, 8, 16)
                 and x.shape[1] % 8 == 0 and 256 % (x.shape[1] // 8) == 0 and norm_layer.weight is not None
-                and norm_layer.weight.dtype == x.dtype):
+                and norm_layer.weight.dtype == x.dtype and not torch.is_autocast_enabled("cuda")):
             xc = to_channels_last(x)
             y = torch.empty_like(xc)
             for b in range(xc.shape[0]):

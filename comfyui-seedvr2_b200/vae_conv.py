@@ -197,6 +197,26 @@ class CausalConv3dB200(nn.Module):
     def set_memory_limit(self, value: float) -> None:      # causal_inflation_lib.py:77-78: no workspace to bound here
         pass
 
+    def _compute_dtype(self) -> torch.dtype:
+        """The dtype the reference's convolution would compute in: the autocast dtype where the pipeline wraps the VAE in
+        ``torch.autocast`` because its inputs and the VAE's weights differ (src/core/infer.py:156-158, 232-234), else the weights'."""
+        if torch.is_autocast_enabled("cuda"):
+            dt = torch.get_autocast_dtype("cuda")
+            if dt in _DTYPE_CODE:
+                return dt
+        return self.weight_packed.dtype
+
+    def _weights_for(self, dtype: torch.dtype):
+        """(packed weight, bias) in ``dtype``; the cast of a non-native dtype is made once and kept."""
+        if dtype == self.weight_packed.dtype:
+            return self.weight_packed, self.bias
+        cache = self.__dict__.setdefault("_cast_cache", {})
+        hit = cache.get(dtype)
+        if hit is None or hit[0].device != self.weight_packed.device:
+            hit = (self.weight_packed.to(dtype), None if self.bias is None else self.bias.to(dtype))
+            cache[dtype] = hit
+        return hit
+
     def forward(self, input, memory_state="DISABLED", resid: Optional[torch.Tensor] = None):
         """``input`` [B, C, T, H, W], or a list of such tensors = consecutive temporal pieces (the up-sampler's slicing,
         attn_video_vae.py:126-133 -> slicing_forward :243-303): each piece's causal head is the previous piece's tail."""
@@ -235,7 +255,14 @@ class CausalConv3dB200(nn.Module):
         kt = self.kernel_size[0]
         if self.stride != (1, 1, 1):
             return self._forward_strided(xs, state, resid)
+        cd = self._compute_dtype()
+        wq, bq = self._weights_for(cd)
+        xs = [x if x.dtype == cd else x.to(cd) for x in xs]
+        if resid is not None and resid.dtype != cd:
+            resid = resid.to(cd)
         head = self.memory if kt > 1 else None                                  # [B, kt - 1, H, W, C] or None (first frame repeated)
+        if head is not None and head.dtype != cd:
+            head = head.to(cd)
         if resid is not None and self.co_pad != self.out_channels:
             raise NotImplementedError("seedvr2_b200.vae_conv: a residual on a convolution with padded output channels")
         ys = []
@@ -248,7 +275,7 @@ class CausalConv3dB200(nn.Module):
                 x = xp
             y = torch.empty(*x.shape[:4], self.co_pad, dtype=x.dtype, device=x.device)
             for b in range(B):
-                causal_conv3d(x[b], self.weight_packed, self.bias, None if head is None else head[b],
+                causal_conv3d(x[b], wq, bq, None if head is None else head[b],
                               None if resid is None else resid[b], out=y[b], gn_partials=gn_partials)
             ys.append(y)
             if kt > 1 and (i + 1 < len(xs) or state != "DISABLED"):
@@ -278,10 +305,15 @@ class CausalConv3dB200(nn.Module):
         if resid is not None or self.ci_pad != self.in_channels or self.co_pad != self.out_channels:
             raise NotImplementedError("seedvr2_b200.vae_conv: strided convolutions take unpadded channels and no residual")
         kt = self.kernel_size[0]
+        cd = self._compute_dtype()
+        wq, bq = self._weights_for(cd)
+        xs = [x if x.dtype == cd else x.to(cd) for x in xs]
         head = self.memory if kt > 1 else None
+        if head is not None and head.dtype != cd:
+            head = head.to(cd)
         ys = []
         for x in xs:
-            outs = [causal_conv3d_down(x[b], self.weight_packed, self.bias, None if head is None else head[b], self.pad_hw)
+            outs = [causal_conv3d_down(x[b], wq, bq, None if head is None else head[b], self.pad_hw)
                     for b in range(x.shape[0])]
             ys.append(outs[0][None] if len(outs) == 1 else torch.stack(outs, 0))
             if kt > 1 and x.shape[1] >= 1:

@@ -395,3 +395,29 @@ def test_memories_are_cleared_after_the_last_slice(svr2, cuda):
     with torch.no_grad():          # while slicing, the memory is there
         vae.decoder.block(z[:, :, :3], memory_state=MemoryState.INITIALIZING)
     assert svr2.vae_block.clear_memory(vae) == 2
+
+
+def test_block_under_autocast_like_the_pipeline(svr2, cuda):
+    """The pipeline wraps the VAE in torch.autocast when its inputs (bf16 compute dtype) and the VAE's weights (fp16) differ
+    (src/core/infer.py:156-158, 232-234): the swapped block then computes in the autocast dtype like the reference's convolutions,
+    with weights cast once."""
+    if not refstage.available():
+        pytest.skip("reference not staged")
+    from vae_standins import reference_parts
+    _, _, _, MemoryState = reference_parts()
+    torch.manual_seed(5)
+    ref = ResnetBlock3D(256, 128).eval().cuda().half()
+    mine = svr2.vae_block.ResnetBlock3DB200.from_reference(ref)
+    x = torch.randn(1, 256, 5, 24, 40, device=cuda).bfloat16()
+    params = {k: v.float() for k, v in ref.state_dict().items()}
+    with torch.no_grad():
+        with torch.autocast("cuda", torch.bfloat16):
+            r = torch.cat([ref(x[:, :, :3], memory_state=MemoryState.INITIALIZING), ref(x[:, :, 3:], memory_state=MemoryState.ACTIVE)], 2)
+            m = torch.cat([mine(x[:, :, :3], None, memory_state=MemoryState.INITIALIZING), mine(x[:, :, 3:], None, memory_state=MemoryState.ACTIVE)], 2)
+        with torch.backends.cudnn.flags(enabled=True, allow_tf32=False):
+            o, _ = ovb.resnet_block3d(x.float(), params)
+    assert m.dtype == torch.bfloat16 and m.shape == r.shape
+    rms_ref, rms_mine = float((r.float() - o).pow(2).mean().sqrt()), float((m.float() - o).pow(2).mean().sqrt())
+    # the reference keeps GroupNorm and SiLU in fp32 under autocast; the fused pass rounds twice to bf16 in between
+    assert rms_mine <= 1.5 * rms_ref + 1e-6, (rms_mine, rms_ref)
+    assert mine.conv1.memory.dtype == torch.bfloat16
