@@ -210,11 +210,16 @@ def make_causal_norm_wrapper(original):
         if (isinstance(norm_layer, nn.GroupNorm) and torch.is_tensor(x) and x.ndim == 5 and x.is_cuda and x.dtype in _DTYPE_CODE
                 and x.shape[1] % norm_layer.num_groups == 0 and x.shape[1] // norm_layer.num_groups in (2, 4, 8, 16)
                 and x.shape[1] % 8 == 0 and 256 % (x.shape[1] // 8) == 0 and norm_layer.weight is not None
-                and norm_layer.weight.dtype == x.dtype and not torch.is_autocast_enabled("cuda")):
+                and (norm_layer.weight.dtype == x.dtype or torch.is_autocast_enabled("cuda"))):
+            # under the pipeline's autocast (16-bit input, weights of the other 16-bit dtype) ATen would run this norm in fp32;
+            # here it stays in the input's dtype, with the two small parameter vectors cast on the fly
+            w, b_ = norm_layer.weight, norm_layer.bias
+            if w.dtype != x.dtype:
+                w, b_ = w.to(x.dtype), None if b_ is None else b_.to(x.dtype)
             xc = to_channels_last(x)
             y = torch.empty_like(xc)
             for b in range(xc.shape[0]):
-                groupnorm_silu(xc[b], norm_layer.weight, norm_layer.bias, norm_layer.num_groups, norm_layer.eps, silu=False, out=y[b])
+                groupnorm_silu(xc[b], w, b_, norm_layer.num_groups, norm_layer.eps, silu=False, out=y[b])
             return y.permute(0, 4, 1, 2, 3)
         return original(norm_layer, x)
     causal_norm_wrapper._svr2_original = original
