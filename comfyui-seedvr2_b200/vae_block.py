@@ -274,7 +274,7 @@ def _conv_supported(conv: nn.Module) -> bool:
         strided_ok = (kh == 3 and tuple(conv.stride) == ((2 if kt == 3 else 1), 2, 2) and tuple(conv.padding)[1:] == (0, 0)
                       and conv.in_channels % 64 == 0 and conv.out_channels % 128 == 0)
         return ((tuple(conv.stride) == (1, 1, 1) or strided_ok) and tuple(conv.dilation) == (1, 1, 1) and conv.groups == 1 and kh == kw
-                and kt in (1, 3) and kh in (1, 3) and conv.weight.is_cuda and conv.weight.dtype in _DTYPE_CODE)
+                and kt in (1, 3) and kh in (1, 3) and conv.weight.dtype in _DTYPE_CODE)
     except (AttributeError, TypeError, ValueError):
         return False
 

@@ -31,9 +31,13 @@ def _state_name(memory_state) -> str:
 
 
 def pack_conv_weight(weight: torch.Tensor) -> torch.Tensor:
-    """nn.Conv3d weight [C_out, C_in, kt, kh, kw] -> [C_out, kt, kh, kw, C_in], the K axis of the implicit GEMM."""
-    if not weight.is_cuda or weight.dtype not in _DTYPE_CODE:
-        raise RuntimeError("seedvr2_b200.vae_conv: the weight must be a CUDA fp16 / bf16 tensor; there is no CPU path")
+    """nn.Conv3d weight [C_out, C_in, kt, kh, kw] -> [C_out, kt, kh, kw, C_in], the K axis of the implicit GEMM.  A weight that is
+    still on the host (the pipeline keeps the VAE off the GPU between its phases) is re-laid out there, once, at install time —
+    the convolution itself has no CPU path."""
+    if weight.dtype not in _DTYPE_CODE:
+        raise RuntimeError("seedvr2_b200.vae_conv: the weight must be an fp16 / bf16 tensor")
+    if not weight.is_cuda:
+        return weight.permute(0, 2, 3, 4, 1).contiguous()
     w = weight.contiguous()
     co, ci, kt, kh, kw = w.shape
     out = torch.empty(co, kt, kh, kw, ci, dtype=w.dtype, device=w.device)

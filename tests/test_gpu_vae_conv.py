@@ -188,8 +188,14 @@ def test_argument_validation(svr2, cuda):
         svr2.vae_conv.causal_conv3d(x, w)
     with pytest.raises(NotImplementedError):
         svr2.vae_conv.causal_conv3d(x.float(), w.float())
-    with pytest.raises(RuntimeError, match="CPU"):
-        svr2.vae_conv.pack_conv_weight(torch.zeros(128, 64, 3, 3, 3, dtype=torch.float16))
+    # a VAE that is still on the host can be installed into (weights re-laid out there); running it needs the GPU
+    w_cpu = torch.randn(128, 64, 3, 3, 3).half()
+    assert torch.equal(svr2.vae_conv.pack_conv_weight(w_cpu).cuda(), svr2.vae_conv.pack_conv_weight(w_cpu.cuda()))
+    conv = svr2.vae_conv.CausalConv3dB200(w_cpu, None)
+    with pytest.raises(RuntimeError, match="no CPU path"):
+        conv(torch.zeros(1, 64, 2, 8, 8, dtype=torch.float16))
+    y = conv.cuda()(torch.zeros(1, 64, 2, 8, 8, dtype=torch.float16, device="cuda"))
+    assert y.shape == (1, 128, 2, 8, 8) and float(y.abs().max()) == 0.0
 
 
 @pytest.mark.parametrize("shape", [(1, 128, 3, 40, 56), (2, 16, 2, 33, 40), (1, 512, 1, 135, 240), (1, 24, 3, 7, 9)],
