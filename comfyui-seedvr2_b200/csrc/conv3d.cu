@@ -1,5 +1,6 @@
-// svr2_causal_conv3d_fwd — the video VAE's causal 3-D convolution as an implicit GEMM on tcgen05 (first
-// slice: the stride-1 convolutions of the residual blocks, which carry >95 % of the VAE's FLOPs).
+// svr2_causal_conv3d_fwd / svr2_causal_conv3d_down_fwd — the video VAE's causal 3-D convolutions as an implicit GEMM on tcgen05
+// (SURVEY §8f row N3): the stride-1 convolutions of the residual blocks, up-samplers and model boundaries (~99 % of the VAE's
+// FLOPs) and the encoder's stride-2 down-samplers.
 //
 // Reference: InflatedCausalConv3d (src/models/video_vae_v3/modules/causal_inflation_lib.py:61-262).  The temporal padding is
 // removed from the module's padding (:74) and replaced by a causal head: 2 * temporal_padding copies of the first frame
@@ -23,6 +24,12 @@
 // XOR from the absolute shared-memory address (bits 7-9 into bits 4-6), not from the row's index in the tile — verified on the
 // B200 (run 26: base-offset field left 0 gives exact results, setting it to the phase dw does not).  The nine taps therefore re-read
 // shared memory, not L2: 36 KB of input per 9 K steps instead of 9 x 16 KB.  1 x 1 kernels use a 16 x 8 box (the tile itself).
+// Stride-2 down-samplers (Downsample3D, attn_video_vae.py:176-246) run on the 1 x 1 instantiation: each of the 9 spatial taps is
+// its own K-step group fed by a 16 x 8 box with TMA element strides 2 (every second row / column from the tap's offset on), the
+// zero row / column the reference appends is the unit's zero fill, temporal stride 2 is a frame coordinate 2 t' + dt - head.
+//
+// The epilogue can also gather the (count, mean, M2) partials of the output per frame and GroupNorm group (gn_partials), so that
+// the per-frame GroupNorm that follows every convolution of a residual block needs no statistics pass of its own.
 //
 // Kernel shape: the GEMM of gemm.cu.  CTA pair, tcgen05.mma.cta_group::2 with M = 256 output positions (16 x 16 of one frame;
 // each CTA stages the patch of its 8 columns and half of the weight tile), N = 256 or 128 output channels, fp32 accumulators
