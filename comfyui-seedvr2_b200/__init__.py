@@ -8,7 +8,7 @@ The package holds only what the path needs: csrc/ (CUDA kernels + the C ABI of i
 binding, the window plan, the block modules mirroring the reference interface, a minimal NaDiT driver for benches and
 the temporal-segment partitioner.  It never imports ``oracle/`` and raises if libseedvr2_b200.so is missing.
 """
-from . import _lib, ops, plan, postprocess, sampler, vae_block, vae_conv
+from . import _lib, ops, plan, postprocess, sampler, vae_attn, vae_block, vae_conv
 from .block import NaMMSRTransformerBlockB200, NaMMSRTransformerBlockB200_7B, NaSwinAttentionB200
 from .plan import WindowPlan, get_plan
 from .stack import NaDiTStack

@@ -56,11 +56,12 @@ SIGNATURES = {
     "svr2_groupnorm_silu_fwd": (c_int, [c_void_p] * 5 + [c_int, c_int, c_int64, c_int, c_int, c_float, c_int, c_int, c_void_p]),
     "svr2_transpose_2b": (c_int, [c_void_p, c_void_p, c_int64, c_int64, c_int64, c_int64, c_int, c_int64, c_int64, c_void_p]),
     "svr2_pixel_shuffle3d_fwd": (c_int, [c_void_p, c_void_p] + [c_int] * 7 + [c_void_p]),
+    "svr2_row_softmax_fwd": (c_int, [c_void_p, c_int64, c_int, c_int, c_int, c_void_p]),
     "svr2_sr_input_fwd": (c_int, [c_void_p, c_void_p, c_void_p, c_float, c_float, c_int, c_void_p, c_int64, c_int, c_void_p]),
     "svr2_v_lerp_endpoint_fwd": (c_int, [c_void_p, c_void_p, c_float, c_float, c_void_p, c_int64, c_void_p]),
 }
 
-ABI_VERSION = 13      # svr2_abi_version() of the library these SIGNATURES describe
+ABI_VERSION = 14      # svr2_abi_version() of the library these SIGNATURES describe
 _lib = None
 
 

@@ -18,7 +18,7 @@ void set_error(const char* fmt, ...) {
 }  // namespace svr2
 
 extern "C" const char* svr2_last_error(void) { return svr2::g_err; }
-extern "C" int svr2_abi_version(void) { return 13; }   // 13: svr2_causal_conv3d_down_fwd; 12: svr2_pixel_shuffle3d_fwd; 11: svr2_transpose_2b; 10: GroupNorm statistics from the convolution's epilogue; 9: svr2_groupnorm_silu_fwd; 8: svr2_causal_conv3d_fwd; 7: LAB conversions; 6: post-processing (svr2_wavelet_level_fwd, svr2_colorfix_finish_fwd); 5: svr2_linear_qkv_pack_fwd + svr2_rope_plan; 4: svr2_linear_*_fwd; 3: svr2_window_attn_fwd_impl
+extern "C" int svr2_abi_version(void) { return 14; }   // 14: svr2_row_softmax_fwd; 13: svr2_causal_conv3d_down_fwd; 12: svr2_pixel_shuffle3d_fwd; 11: svr2_transpose_2b; 10: GroupNorm statistics from the convolution's epilogue; 9: svr2_groupnorm_silu_fwd; 8: svr2_causal_conv3d_fwd; 7: LAB conversions; 6: post-processing (svr2_wavelet_level_fwd, svr2_colorfix_finish_fwd); 5: svr2_linear_qkv_pack_fwd + svr2_rope_plan; 4: svr2_linear_*_fwd; 3: svr2_window_attn_fwd_impl
 
 namespace {
 

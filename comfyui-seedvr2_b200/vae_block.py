@@ -6,7 +6,7 @@
 * ``Upsample3DB200`` / ``Downsample3DB200`` mirror the samplers (:58-175, :176-246): 1 x 1 x 1 expansion + pixel / time shuffle +
   causal convolution; zero row / column + strided causal convolution.
 * ``make_causal_norm_wrapper`` / ``patch_causal_norm_wrapper`` put the stand-alone GroupNorms (conv_norm_out) on the same kernel.
-* ``install_vae_blocks(model)`` swaps all of it into a built VAE in place; the mid block's attention layer stays the reference's.
+* ``install_vae_blocks(model)`` swaps all of it — and the mid block's attention layer (``vae_attn.AttentionB200``) — into a built VAE in place.
 Same forward signatures and memory bookkeeping (through the convolutions) as the modules they replace.  CUDA only — there is no other
 path."""
 from typing import Optional
@@ -307,6 +307,13 @@ def install_vae_blocks(model: nn.Module, convs: bool = True, norms: bool = True)
                         n_convs += 2
                     except (NotImplementedError, AttributeError):
                         pass
+                elif type(child).__name__ == "Attention" and hasattr(child, "to_q") and hasattr(child, "group_norm"):
+                    try:
+                        from .vae_attn import AttentionB200
+                        setattr(parent, name, AttentionB200.from_reference(child))
+                        n_convs += 1
+                    except (NotImplementedError, AttributeError):
+                        pass          # multi-head / cross-attention layers keep the reference's module
                 elif type(child).__name__ == "Downsample3D":
                     try:
                         setattr(parent, name, Downsample3DB200.from_reference(child))
@@ -314,7 +321,7 @@ def install_vae_blocks(model: nn.Module, convs: bool = True, norms: bool = True)
                     except (NotImplementedError, AttributeError):
                         pass
         for parent in list(model.modules()):
-            if isinstance(parent, (ResnetBlock3DB200, CausalConv3dB200, Upsample3DB200, Downsample3DB200)):
+            if isinstance(parent, (ResnetBlock3DB200, CausalConv3dB200, Upsample3DB200, Downsample3DB200)) or type(parent).__name__ == "AttentionB200":
                 continue
             for name, child in list(parent.named_children()):
                 pointwise = type(child) is nn.Conv3d and tuple(child.kernel_size) == (1, 1, 1) and tuple(child.padding) == (0, 0, 0)

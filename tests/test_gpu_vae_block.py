@@ -421,3 +421,51 @@ def test_block_under_autocast_like_the_pipeline(svr2, cuda):
     # the reference keeps GroupNorm and SiLU in fp32 under autocast; the fused pass rounds twice to bf16 in between
     assert rms_mine <= 1.5 * rms_ref + 1e-6, (rms_mine, rms_ref)
     assert mine.conv1.memory.dtype == torch.bfloat16
+
+
+def test_row_softmax(svr2, cuda):
+    for dtype in (torch.float16, torch.bfloat16):
+        for rows, n, pitch in ((37, 1000, 1024), (5, 32400, 32512), (3, 8, 8)):
+            g = torch.Generator(device="cuda").manual_seed(n)
+            s = (torch.randn(rows, pitch, generator=g, device=cuda) * 4).to(dtype)
+            want = torch.zeros(rows, pitch, device=cuda)
+            want[:, :n] = torch.softmax(s[:, :n].float(), -1)
+            from seedvr2_b200 import vae_attn
+            got = vae_attn.row_softmax_(s.clone(), n)
+            assert float(got[:, n:].abs().max()) == 0.0 if pitch > n else True
+            ulp = 2.0 ** (-10 if dtype == torch.float16 else -7)
+            assert bool(((got.float() - want).abs() <= ulp * want + 1e-7).all())
+
+
+@pytest.mark.parametrize("hw", [(24, 40), (17, 23), (135, 240)], ids=["24x40", "17x23_unaligned", "1080p_latent"])
+def test_mid_block_attention_mirror(svr2, cuda, hw):
+    """AttentionB200 (two GEMMs on the convolution kernel around the row softmax) against the stand-in of diffusers' layer (torch
+    SDPA), fp16, called the way UNetMidBlock3D does — on the NHWC-strided "(b f) c h w" view of a channels-last clip; both against
+    the layer evaluated in fp32.  Parity unpinned (diffusers is absent): the stand-in restates AttnProcessor2_0."""
+    from vae_standins import Attention
+    from seedvr2_b200 import vae_attn
+    torch.manual_seed(2)
+    H, W = hw
+    C, F_ = 512, 2
+    ref = Attention(C).eval().cuda().half()
+    for lin in (ref.to_q, ref.to_k):
+        nn.init.normal_(lin.weight, 0, 2.0 * C ** -0.5)          # logits of a few units: a softmax that is not flat
+    holder = nn.Sequential(ref)
+    assert svr2.vae_block.install_vae_blocks(holder) == (0, 1)
+    mine = holder[0]
+    assert isinstance(mine, vae_attn.AttentionB200)
+    clip = torch.randn(1, F_, H, W, C, device=cuda).half()                                   # channels-last clip [b, f, h, w, c]
+    x = clip.permute(0, 4, 1, 2, 3).permute(0, 2, 1, 3, 4).reshape(F_, C, H, W)             # "(b f) c h w" as a strided view
+    assert x.data_ptr() == clip.data_ptr()
+    with torch.no_grad():
+        r = ref(x.contiguous())
+        m = mine(x, temb=None)
+        exact = Attention(C).eval().cuda().float()
+        exact.load_state_dict({k: v.float() for k, v in ref.state_dict().items()})
+        o = exact(x.float())
+    assert m.shape == r.shape == (F_, C, H, W) and m.dtype == torch.float16
+    e_ref, e_mine = float((r.float() - o).abs().max()), float((m.float() - o).abs().max())
+    rms_ref, rms_mine = float((r.float() - o).pow(2).mean().sqrt()), float((m.float() - o).pow(2).mean().sqrt())
+    # S is rounded to fp16 before the softmax here (SDPA keeps it in fp32): allow twice the reference's own error
+    assert rms_mine <= 2.0 * rms_ref + 1e-5, (rms_mine, rms_ref)
+    assert e_mine <= 3.0 * e_ref + 2e-3, (e_mine, e_ref)

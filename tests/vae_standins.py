@@ -197,3 +197,33 @@ class Encoder3D(nn.Module):
             sample = r(sample, temb=None, memory_state=memory_state)
         sample = self.conv_act(output_norm(self, sample))
         return self.conv_out(sample, memory_state=memory_state)
+
+
+class Attention(nn.Module):
+    """The mid block's attention layer as UNetMidBlock3D builds it (attn_video_vae.py:600-640: diffusers `Attention(in_channels,
+    heads=in_channels // attention_head_dim, dim_head=attention_head_dim, norm_num_groups=32, eps=1e-6, residual_connection=True,
+    bias=True, upcast_softmax=True, rescale_output_factor=1)`) with diffusers' attribute names and the sequence of its
+    AttnProcessor2_0.  diffusers is not in this image: this is a restatement, not the reference's code."""
+
+    def __init__(self, channels, groups=32, eps=1e-6):
+        super().__init__()
+        self.heads, self.rescale_output_factor, self.residual_connection = 1, 1.0, True
+        self.norm_cross = self.spatial_norm = self.added_kv_proj_dim = None
+        self.group_norm = nn.GroupNorm(groups, channels, eps=eps, affine=True)
+        self.to_q, self.to_k, self.to_v = (nn.Linear(channels, channels, bias=True) for _ in range(3))
+        self.to_out = nn.ModuleList([nn.Linear(channels, channels, bias=True), nn.Dropout(0.0)])
+
+    def forward(self, hidden_states, temb=None):
+        residual = hidden_states
+        b, c, h, w = hidden_states.shape
+        x = hidden_states.reshape(b, c, h * w).transpose(1, 2)
+        x = self.group_norm(x.transpose(1, 2)).transpose(1, 2)
+        q, k, v = self.to_q(x), self.to_k(x), self.to_v(x)
+        q, k, v = (t.view(b, -1, self.heads, c // self.heads).transpose(1, 2) for t in (q, k, v))
+        x = torch.nn.functional.scaled_dot_product_attention(q, k, v, attn_mask=None, dropout_p=0.0, is_causal=False)
+        x = x.transpose(1, 2).reshape(b, -1, c).to(q.dtype)
+        x = self.to_out[1](self.to_out[0](x))
+        x = x.transpose(-1, -2).reshape(b, c, h, w)
+        if self.residual_connection:
+            x = x + residual
+        return x / self.rescale_output_factor
