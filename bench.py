@@ -491,7 +491,7 @@ def vae_decoder_sample(svr2, dev):
         torch.cuda.synchronize()
     ms = e0.elapsed_time(e1) / n
     return {"ms_per_frame": ms / frames, "frames_per_s": frames / (ms * 1e-3), "output_frames": frames, "dtype": "f16",
-            "modules_replaced": list(installed), "reference_same_gpu": "profiles/r02_run37-54_vae_decoder_encoder_1080p.jsonl (153-274 ms per frame)"}
+            "modules_replaced": list(installed), "reference_same_gpu": "profiles/r02_run37-59_vae_decoder_encoder_1080p.jsonl (153-274 ms per frame)"}
 
 
 def run_ours(args):

@@ -19,7 +19,8 @@ args = [a for a in sys.argv[1:] if not a.startswith("--")]
 lat = int(args[0]) if len(args) > 0 else 1
 n_slices = int(args[1]) if len(args) > 1 else 3
 torch.manual_seed(0)
-ref = Decoder3D().eval().to(dev).half()
+ATTN = "--attention" in sys.argv
+ref = Decoder3D(attention=ATTN).eval().to(dev).half()
 mine = copy.deepcopy(ref)
 installed = svr2.vae_block.install_vae_blocks(mine)
 mine.use_rebound_norm = True
@@ -57,7 +58,7 @@ with torch.no_grad():
     torch.cuda.synchronize()
     svr2.ops.set_timer(None)
     ours_ms = {k: round(v[1], 2) for k, v in kt.summary().items()}
-    res = {"decoder_1080p": {"latent_frames_per_slice": lat, "slices": n_slices, "output_frames": frames, "installed": list(installed),
+    res = {"decoder_1080p": {"mid_attention": ATTN, "latent_frames_per_slice": lat, "slices": n_slices, "output_frames": frames, "installed": list(installed),
                              "ms": round(t_mine, 2), "ms_per_frame": round(t_mine / frames, 2), "frames_per_s": round(frames / t_mine * 1e3, 2),
                              "kernel_ms_ours": ours_ms}}
     if "--no-ref" not in sys.argv:

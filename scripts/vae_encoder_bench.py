@@ -18,7 +18,8 @@ args = [a for a in sys.argv[1:] if not a.startswith("--")]
 n = int(args[0]) if len(args) > 0 else 1
 n_slices = int(args[1]) if len(args) > 1 else 2
 torch.manual_seed(0)
-ref = Encoder3D().eval().to(dev).half()
+ATTN = "--attention" in sys.argv
+ref = Encoder3D(attention=ATTN).eval().to(dev).half()
 mine = copy.deepcopy(ref)
 installed = svr2.vae_block.install_vae_blocks(mine)
 mine.use_rebound_norm = True
@@ -52,7 +53,7 @@ with torch.no_grad():
     run(mine)
     torch.cuda.synchronize()
     svr2.ops.set_timer(None)
-    res = {"encoder_1080p": {"input_frames": frames, "slices": [x.shape[2] for x in xs], "latent_frames": sum(o.shape[2] for o in outs_m),
+    res = {"encoder_1080p": {"mid_attention": ATTN, "input_frames": frames, "slices": [x.shape[2] for x in xs], "latent_frames": sum(o.shape[2] for o in outs_m),
                              "installed": list(installed), "ms": round(t_mine, 2), "ms_per_frame": round(t_mine / frames, 2),
                              "frames_per_s": round(frames / t_mine * 1e3, 2), "kernel_ms_ours": {k: round(v[1], 2) for k, v in kt.summary().items()}}}
     if "--no-ref" not in sys.argv:

@@ -286,11 +286,12 @@ def test_whole_decoder_standin_psnr(svr2, cuda):
     from vae_standins import Decoder3D, reference_parts
     _, _, _, MemoryState = reference_parts()
     torch.manual_seed(11)
-    ref = Decoder3D(16, (128, 128, 128, 128)).eval().cuda().half()
+    ref = Decoder3D(16, (128, 128, 128, 128), attention=True).eval().cuda().half()
     mine = copy.deepcopy(ref)
     n_blocks, n_convs = svr2.vae_block.install_vae_blocks(mine)
     mine.use_rebound_norm = True
-    assert (n_blocks, n_convs) == (14, 8)            # 2 mid + 12 up blocks; conv_in, 3 up-samplers x 2, conv_out
+    assert (n_blocks, n_convs) == (14, 9)            # 2 mid + 12 up blocks; conv_in, mid attention, 3 up-samplers x 2, conv_out
+    assert not any(type(m).__name__ in ("Attention", "InflatedCausalConv3d", "ResnetBlock3D", "Upsample3D") for m in mine.modules())
     zs = [torch.randn(1, 16, t, 9, 12, device=cuda).half() for t in (1, 2, 1)]
     with torch.no_grad():
         outs_r, outs_m = [], []

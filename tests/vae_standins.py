@@ -120,11 +120,11 @@ class Decoder3D(nn.Module):
     block_out_channels 128 / 256 / 512 / 512, 3 residual blocks per up block, temporal up-sampling in up blocks 0 and 1, spatial in 0-2,
     time_receptive_field "full") WITHOUT the mid block's attention layer (diffusers' `Attention`, not in this image)."""
 
-    def __init__(self, latent=16, ch=(512, 512, 256, 128)):
+    def __init__(self, latent=16, ch=(512, 512, 256, 128), attention=False):
         super().__init__()
         init_causal_conv3d, _, _, _ = reference_parts()
         self.conv_in = init_causal_conv3d(latent, ch[0], kernel_size=3, stride=1, padding=1, inflation_mode="tail")
-        self.mid = nn.ModuleList([ResnetBlock3D(ch[0], ch[0]), ResnetBlock3D(ch[0], ch[0])])
+        self.mid_block = UNetMidBlock3D(ch[0], attention)
         self.up_resnets = nn.ModuleList()
         self.up_samplers = nn.ModuleList()
         prev = ch[0]
@@ -138,8 +138,7 @@ class Decoder3D(nn.Module):
 
     def forward(self, sample, memory_state=None):
         sample = self.conv_in(sample, memory_state=memory_state)
-        for r in self.mid:
-            sample = r(sample, temb=None, memory_state=memory_state)
+        sample = self.mid_block(sample, None, memory_state=memory_state)
         for resnets, up in zip(self.up_resnets, self.up_samplers):
             for r in resnets:
                 sample = r(sample, temb=None, memory_state=memory_state)
@@ -170,7 +169,7 @@ class Encoder3D(nn.Module):
     """Encoder3D.forward (attn_video_vae.py:700-870) for the product VAE (3 -> 128 / 256 / 512 / 512, two residual blocks per down block,
     spatial down-sampling after blocks 0-2, temporal as well after blocks 1-2, double-z output) WITHOUT the mid block's attention layer."""
 
-    def __init__(self, ch=(128, 256, 512, 512), latent=16):
+    def __init__(self, ch=(128, 256, 512, 512), latent=16, attention=False):
         super().__init__()
         init_causal_conv3d, _, _, _ = reference_parts()
         self.conv_in = init_causal_conv3d(3, ch[0], kernel_size=3, stride=1, padding=1, inflation_mode="tail")
@@ -181,7 +180,7 @@ class Encoder3D(nn.Module):
             self.down_resnets.append(nn.ModuleList([ResnetBlock3D(prev if j == 0 else c, c) for j in range(2)]))
             self.down_samplers.append(Downsample3D(c, temporal_down=i >= 1) if i < len(ch) - 1 else nn.Identity())
             prev = c
-        self.mid = nn.ModuleList([ResnetBlock3D(ch[-1], ch[-1]), ResnetBlock3D(ch[-1], ch[-1])])
+        self.mid_block = UNetMidBlock3D(ch[-1], attention)
         self.conv_norm_out = nn.GroupNorm(32, ch[-1], eps=1e-6)
         self.conv_act = nn.SiLU()
         self.conv_out = init_causal_conv3d(ch[-1], 2 * latent, 3, padding=1, inflation_mode="tail")
@@ -193,8 +192,7 @@ class Encoder3D(nn.Module):
                 sample = r(sample, temb=None, memory_state=memory_state)
             if not isinstance(down, nn.Identity):
                 sample = down(sample, memory_state=memory_state)
-        for r in self.mid:
-            sample = r(sample, temb=None, memory_state=memory_state)
+        sample = self.mid_block(sample, None, memory_state=memory_state)
         sample = self.conv_act(output_norm(self, sample))
         return self.conv_out(sample, memory_state=memory_state)
 
@@ -227,3 +225,23 @@ class Attention(nn.Module):
         if self.residual_connection:
             x = x + residual
         return x / self.rescale_output_factor
+
+
+class UNetMidBlock3D(nn.Module):
+    """UNetMidBlock3D.forward (attn_video_vae.py:656-668): residual block, attention frame by frame, residual block."""
+
+    def __init__(self, channels, attention=True):
+        super().__init__()
+        self.resnets = nn.ModuleList([ResnetBlock3D(channels, channels), ResnetBlock3D(channels, channels)])
+        self.attentions = nn.ModuleList([Attention(channels) if attention else None])
+
+    def forward(self, hidden_states, temb=None, memory_state=None):
+        video_length = hidden_states.size(2)
+        hidden_states = self.resnets[0](hidden_states, temb, memory_state=memory_state)
+        for attn, resnet in zip(self.attentions, self.resnets[1:]):
+            if attn is not None:
+                hidden_states = rearrange(hidden_states, "b c f h w -> (b f) c h w")
+                hidden_states = attn(hidden_states, temb=temb)
+                hidden_states = rearrange(hidden_states, "(b f) c h w -> b c f h w", f=video_length)
+            hidden_states = resnet(hidden_states, temb, memory_state=memory_state)
+        return hidden_states
