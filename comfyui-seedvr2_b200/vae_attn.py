@@ -21,7 +21,7 @@ from . import _lib, ops
 from .vae_block import groupnorm_silu
 from .vae_conv import _DTYPE_CODE, CausalConv3dB200, causal_conv3d, transpose_2b
 
-MAX_TOKENS = 32768      # csrc/softmax.cu: a row of S lives in the registers of one CTA
+MAX_TOKENS = 32768      # S is materialised per frame: 2 x MAX_TOKENS^2 bytes (2.1 GB at this limit)
 
 
 def row_softmax_(s: torch.Tensor, n_valid: int) -> torch.Tensor:

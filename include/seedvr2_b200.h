@@ -420,7 +420,7 @@ int svr2_pixel_shuffle3d_fwd(const void* src, void* dst, int T, int H, int W, in
  * In-place softmax over the first n_valid columns of every row of a [rows, pitch] matrix of 2-byte elements; columns n_valid .. pitch - 1
  * become zeros.  The step between the two GEMMs (svr2_causal_conv3d_fwd as 1 x 1 x 1) of the VAE mid block's attention layer —
  * UNetMidBlock3D's diffusers `Attention` (attn_video_vae.py:563-668): one 512-channel head over the H x W positions of a frame, torch
- * SDPA in the reference.  pitch % 8 == 0, pitch <= 32,768 (a 1080p latent frame has 32,400 positions).
+ * SDPA in the reference.  pitch % 8 == 0.
  */
 int svr2_row_softmax_fwd(void* x, int64_t rows, int n_valid, int pitch, int dtype, void* stream);
 
