@@ -459,7 +459,7 @@ def vae_block_sample(svr2, dev):
 
 def vae_decoder_sample(svr2, dev):
     """The VAE decoder at 1080p through install_vae_blocks(): Decoder3D.forward composed from the reference's real modules (staged copy,
-    tests/vae_standins.py; no mid-block attention layer), product widths, latent 135 x 240, two temporal slices (1 + 4 output frames)."""
+    tests/vae_standins.py, mid-block attention included), product widths, latent 135 x 240, two temporal slices (1 + 4 output frames)."""
     import torch
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     from oracle import refstage
@@ -470,7 +470,7 @@ def vae_decoder_sample(svr2, dev):
         from vae_standins import Decoder3D, reference_parts
         _, _, _, MemoryState = reference_parts()
         torch.manual_seed(0)
-        dec = Decoder3D().eval().to(dev).half()
+        dec = Decoder3D(attention=True).eval().to(dev).half()
     installed = svr2.vae_block.install_vae_blocks(dec)
     dec.use_rebound_norm = True
     zs = [torch.randn(1, 16, 1, 135, 240, device=dev).half() for _ in range(2)]
@@ -492,6 +492,41 @@ def vae_decoder_sample(svr2, dev):
     ms = e0.elapsed_time(e1) / n
     return {"ms_per_frame": ms / frames, "frames_per_s": frames / (ms * 1e-3), "output_frames": frames, "dtype": "f16",
             "modules_replaced": list(installed), "reference_same_gpu": "profiles/r02_run37-59_vae_decoder_encoder_1080p.jsonl (153-274 ms per frame)"}
+
+
+def vae_encoder_sample(svr2, dev):
+    """The VAE encoder at 1080p through install_vae_blocks(): Encoder3D.forward composed from the reference's real modules (staged copy,
+    tests/vae_standins.py, mid-block attention included), product widths, two temporal slices of 5 + 4 input frames."""
+    import contextlib
+    import torch
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from oracle import refstage
+    if not refstage.available():
+        return {"unavailable": "reference modules not staged (baseline/_ref)"}
+    with contextlib.redirect_stdout(sys.stderr):
+        from vae_standins import Encoder3D, reference_parts
+        _, _, _, MemoryState = reference_parts()
+        torch.manual_seed(0)
+        enc = Encoder3D(attention=True).eval().to(dev).half()
+    installed = svr2.vae_block.install_vae_blocks(enc)
+    enc.use_rebound_norm = True
+    xs = [torch.randn(1, 3, t, 1080, 1920, device=dev).half() for t in (5, 4)]
+
+    def run():
+        return [enc(x, memory_state=MemoryState.INITIALIZING if i == 0 else MemoryState.ACTIVE) for i, x in enumerate(xs)]
+    with torch.no_grad():
+        run()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        n = 3
+        e0.record()
+        for _ in range(n):
+            run()
+        e1.record()
+        torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / n
+    return {"ms_per_frame": ms / 9, "frames_per_s": 9 / (ms * 1e-3), "input_frames": 9, "dtype": "f16", "modules_replaced": list(installed),
+            "reference_same_gpu": "profiles/r02_run37-59_vae_decoder_encoder_1080p.jsonl (58.8-62.8 ms per frame)"}
 
 
 def run_ours(args):
@@ -612,7 +647,8 @@ def run_ours(args):
     # ---- SURVEY §8f N3 beside the headline: one residual block of the VAE decoder's top level (128 channels at 1080 x 1920, 5
     # frames, fp16) — GroupNorm + SiLU, two causal 3-D convolutions, fused residual; reported, not part of `value`
     if also is not None and world == 1:
-        for key, fn in (("vae_resnet_block_1080p", vae_block_sample), ("vae_decoder_1080p", vae_decoder_sample)):
+        for key, fn in (("vae_resnet_block_1080p", vae_block_sample), ("vae_decoder_1080p", vae_decoder_sample),
+                        ("vae_encoder_1080p", vae_encoder_sample)):
             try:
                 torch.cuda.empty_cache()
                 also[key] = fn(svr2, dev)
